@@ -1,0 +1,163 @@
+/* vamp_b200.h — C ABI of libvamp_b200.so: the B200 (sm_100a) implementation of mr-vamp's
+ * data-parallel hot path, batched forward kinematics fused with collision checking (fkcc) and
+ * discretised motion validation.
+ *
+ * This is the whole drop-in boundary.  Plain pointers and sizes only; every pointer is a HOST
+ * pointer unless its name ends in `_d`; the caller owns every buffer it passes, the library owns
+ * the handles it returns.  All functions return 0 on success or a non-zero status whose text is
+ * available from vb_last_error() (thread-local).  There is no CPU fallback: when no CUDA device is
+ * usable every query fails with VB_ERR_CUDA.
+ *
+ * What each entry point replaces in the reference (paths under src/impl/vamp/):
+ *
+ *   vb_env_add_*            collision::Environment<float> population as done by the bindings:
+ *                           bindings/environment.cc:107-163 (z-aligned classification, sort()),
+ *                           collision/shapes.hh:57-73,166-192,236-239 (min_distance),
+ *                           collision/environment.hh:26-66 (per-call float->vector conversion: gone,
+ *                           the device copy is rebuilt only by vb_env_commit)
+ *   vb_env_add_capt         collision::CAPT query buffers, collision/capt.hh:588-621
+ *   vb_env_set_attachment   Environment::attachments, collision/attachments.hh:11-73
+ *   vb_sphere_fk            Robot::sphere_fk, robots/panda_base.hh:67-71 (+ ur5/fetch/baxter/sphere .hh),
+ *                           bindings/common.hh:132-152 (Helper::fk)
+ *   vb_fkcc                 Robot::fkcc / fkcc_attach, robots/panda_base.hh:53-66 ->
+ *                           robots/<robot>/fk.hh interleaved_sphere_fk[_attachment]; one verdict per
+ *                           configuration (= the reference called on a broadcast block,
+ *                           bindings/common.hh:172-182)
+ *   vb_validate             Helper::validate_configuration, bindings/common.hh:172-182 (joint limits + fkcc)
+ *   vb_validate_motion      planning::validate_motion / validate_vector, planning/validate.hh:23-75,
+ *                           and Path::validate, planning/plan.hh:155-168 (edges of a path in one call)
+ *   vb_validate_pairs       the fork's planned MultiRobotEnvironment::check_inter_robot_collisions
+ *                           (MR_DEV_PLAN.md:176-198; no reference implementation exists)
+ */
+#ifndef VAMP_B200_H
+#define VAMP_B200_H
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef struct vb_ctx vb_ctx; /* devices, streams, scratch, optional NCCL communicator */
+typedef struct vb_env vb_env; /* host description + device-resident replicas of one environment */
+
+typedef enum
+{
+    VB_SPHERE = 0,
+    VB_UR5 = 1,
+    VB_PANDA = 2,
+    VB_FETCH = 3,
+    VB_BAXTER = 4
+} vb_robot;
+
+enum
+{
+    VB_OK = 0,
+    VB_ERR_ARG = 1,   /* bad argument */
+    VB_ERR_CUDA = 2,  /* CUDA runtime error or no device */
+    VB_ERR_NCCL = 3,  /* NCCL error */
+    VB_ERR_STATE = 4  /* e.g. environment not committed */
+};
+
+const char *vb_last_error(void);
+const char *vb_version(void);
+
+/* ---- context ------------------------------------------------------------------------------ */
+/* device_ids == NULL, n_devices == 0: device 0.  With n_devices > 1 the host-pointer queries shard
+ * their batch over the devices in contiguous index ranges; environments are replicated. */
+int vb_ctx_create(vb_ctx **out, const int *device_ids, int n_devices);
+void vb_ctx_destroy(vb_ctx *);
+int vb_ctx_device_count(const vb_ctx *);
+int vb_ctx_sm_count(const vb_ctx *, int slot);
+int vb_sync(vb_ctx *);
+
+/* ---- robots ------------------------------------------------------------------------------- */
+int vb_robot_by_name(const char *name, vb_robot *out);
+int vb_robot_info(vb_robot, int *dimension, int *n_spheres, int *resolution);
+/* joint ranges of scale_configuration: q = lo + u * range (robots/<robot>/fk.hh) */
+int vb_robot_limits(vb_robot, float *lo, float *range);
+/* configuration `index` of the synthetic stream used by the *_random entry points */
+int vb_random_config(vb_robot, uint64_t seed, uint64_t index, float *q);
+/* edge `index` of the synthetic edge stream: a = config(2*index), b = a + len * dir clipped to limits */
+int vb_random_edge(vb_robot, uint64_t seed, uint64_t index, float len_lo, float len_hi, float *a, float *b);
+/* robots::sphere global radius (robots/sphere/fk.hh:16-18); default 0.2 */
+int vb_ctx_set_sphere_radius(vb_ctx *, float r);
+
+/* ---- environment -------------------------------------------------------------------------- */
+int vb_env_create(vb_ctx *, vb_env **out);
+void vb_env_destroy(vb_env *);
+int vb_env_clear(vb_env *);
+int vb_env_add_sphere(vb_env *, float x, float y, float z, float r);
+/* c[15] = centre(3) axis1(3) axis2(3) axis3(3) half-extents(3); z-aligned iff axis_3_z == 1 */
+int vb_env_add_cuboid(vb_env *, const float *c);
+/* c[8] = x1 y1 z1 xv yv zv r rdv (rdv = 1/|v|^2); z-aligned iff xv == 0 && yv == 0 */
+int vb_env_add_capsule(vb_env *, const float *c);
+/* off_scale[6] = x y z xs ys zs (offsets, already-inverted scales as collision/factory.hh:365-386) */
+int vb_env_add_heightfield(vb_env *, const float *off_scale, size_t xd, size_t yd, const float *data);
+/* CAPT query buffers (collision/capt.hh:588-621) built by the host; aff_* hold n_aff_vec*8 floats */
+int vb_env_add_capt(vb_env *, const float *tests, size_t n_tests, const uint32_t *aff_starts, const float *aff_x,
+                    const float *aff_y, const float *aff_z, size_t n_aff_vec, const float *aabbs, size_t n_aabbs,
+                    const float *aabb_top, float r_point, int nlog2);
+/* tf[7] = tx ty tz qx qy qz qw; spheres [n][4] = x y z r (end-effector frame); n <= 16 */
+int vb_env_set_attachment(vb_env *, const float *tf, const float *spheres, size_t n);
+int vb_env_clear_attachment(vb_env *);
+/* upload / replicate to every device of the context; bumps the version */
+int vb_env_commit(vb_env *);
+/* introspection (sorted order): kind 0 spheres[5] 1 capsules[9] 2 z-capsules[9] 3 cuboids[16] 4 z-cuboids[16];
+ * rows are the shape floats followed by min_distance.  Returns the count via *n; writes when out != NULL. */
+int vb_env_export(const vb_env *, int kind, float *out, size_t *n);
+
+/* ---- queries, host buffers (sharded over the context's devices) --------------------------- */
+/* configs: row-major [n][dimension] float32; base_xyz: robot base offset in metres (Panda grid
+ * variants, robots/panda_grid.hh:10-41), NULL = origin. */
+int vb_sphere_fk(vb_ctx *, vb_robot, const float *base_xyz, const float *configs, size_t n,
+                 float *spheres_xyzr /* [n][n_spheres][4] */);
+/* valid_bits: ceil(n/32) words, bit i%32 of word i/32 = 1 iff configuration i is collision free.
+ * margin_or_null: [n] smallest |signed clearance| in metres over the tests that decided the verdict. */
+int vb_fkcc(vb_ctx *, vb_robot, const float *base_xyz, const vb_env *, const float *configs, size_t n,
+            uint32_t *valid_bits, float *margin_or_null);
+/* joint-limit test && fkcc (Helper::validate_configuration) */
+int vb_validate(vb_ctx *, vb_robot, const float *base_xyz, const vb_env *, const float *configs, size_t n,
+                uint32_t *valid_bits);
+/* resolution <= 0: the robot's own (Robot::resolution) */
+int vb_validate_motion(vb_ctx *, vb_robot, const float *base_xyz, const vb_env *, const float *starts,
+                       const float *goals, size_t n_edges, int resolution, uint32_t *valid_bits,
+                       float *margin_or_null);
+/* composite validity of two robots sharing one environment: fkcc(a) && fkcc(b) && no sphere of a
+ * overlaps a sphere of b (world frame). */
+int vb_validate_pairs(vb_ctx *, vb_robot robot_a, const float *base_a, vb_robot robot_b, const float *base_b,
+                      const vb_env *, const float *cfg_a, const float *cfg_b, size_t n, uint32_t *valid_bits);
+
+/* ---- queries, device-resident (single device slot, asynchronous on that slot's stream) ---- */
+int vb_dev_alloc(vb_ctx *, int slot, size_t bytes, void **ptr_d);
+int vb_dev_free(vb_ctx *, int slot, void *ptr_d);
+int vb_dev_upload(vb_ctx *, int slot, void *dst_d, const void *src, size_t bytes);
+int vb_dev_download(vb_ctx *, int slot, void *dst, const void *src_d, size_t bytes);
+int vb_fkcc_d(vb_ctx *, int slot, vb_robot, const float *base_xyz, const vb_env *, const float *configs_d, size_t n,
+              uint32_t *valid_bits_d, float *margin_d_or_null);
+int vb_validate_motion_d(vb_ctx *, int slot, vb_robot, const float *base_xyz, const vb_env *, const float *starts_d,
+                         const float *goals_d, size_t n_edges, int resolution, uint32_t *valid_bits_d,
+                         float *margin_d_or_null);
+/* configurations first .. first+n-1 of the synthetic stream, generated in registers (0 input bytes) */
+int vb_fkcc_random_d(vb_ctx *, int slot, vb_robot, const float *base_xyz, const vb_env *, uint64_t seed,
+                     uint64_t first, size_t n, uint32_t *valid_bits_d);
+/* CUDA-event timer on the slot's stream */
+int vb_timer_start(vb_ctx *, int slot);
+int vb_timer_stop(vb_ctx *, int slot, double *milliseconds);
+/* number of kernels this context has launched so far */
+uint64_t vb_launch_count(const vb_ctx *);
+/* counts set bits of a device bitmask with n valid bits */
+int vb_popcount_d(vb_ctx *, int slot, const uint32_t *bits_d, size_t n, uint64_t *count);
+
+/* ---- multi-process gather (one process per GPU, NCCL over NVLink) ------------------------- */
+/* id_bytes: 128-byte ncclUniqueId created by rank 0 with vb_comm_unique_id and distributed by the caller */
+int vb_comm_unique_id(void *id_bytes_128);
+int vb_comm_init(vb_ctx *, int n_ranks, int rank, const void *id_bytes_128);
+/* all ranks contribute n_words verdict words; every rank receives n_ranks*n_words in rank order */
+int vb_comm_allgather_bits_d(vb_ctx *, const uint32_t *send_d, uint32_t *recv_d, size_t n_words);
+int vb_comm_destroy(vb_ctx *);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* VAMP_B200_H */

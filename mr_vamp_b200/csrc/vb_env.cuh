@@ -1,0 +1,285 @@
+// Device-side environment: packed obstacle records + the per-sphere environment query.
+//
+// Replaces collision::Environment<FloatVector<rake>> (collision/environment.hh:11-82), the shape
+// structs (collision/shapes.hh) and sphere_environment_in_collision (collision/validity.hh:46-150).
+// Obstacles are kept in the reference's order (each list sorted by min_distance,
+// environment.hh:40-66) as float4 records so that one warp-uniform LDS.128/LDG.128 fetches a
+// quarter of a box; every lane of a warp walks the same record at the same time, so the loads
+// are broadcasts.
+#pragma once
+#include "vb_numerics.cuh"
+
+namespace vb
+{
+    // record sizes in float4 units
+    constexpr int kSphereQ = 2;   // [x y z r] [min_d 0 0 0]
+    constexpr int kCapsuleQ = 3;  // [x1 y1 z1 r] [xv yv zv rdv] [min_d 0 0 0]
+    constexpr int kZCapsQ = 2;    // [x1 y1 z1 r] [zv rdv min_d 0]
+    constexpr int kCuboidQ = 4;   // [c.xyz min_d] [ax1 r1] [ax2 r2] [ax3 r3]
+    constexpr int kZCubQ = 3;     // [c.xyz min_d] [a1x a1y a2x a2y] [r1 r2 r3 0]
+
+    struct CaptView
+    {
+        const float *tests;          // (2^nlog2 - 1) split values (capt.hh:588-590)
+        const uint32_t *aff_starts;  // 2^nlog2 + 1
+        const float4 *aff;           // per 8-point affordance vector: 6 float4 = x[0:8] y[0:8] z[0:8]
+        const float *aabbs;          // [2^nlog2][6]
+        float top[6];                // aabb_top lower(3) upper(3)
+        float r_point;
+        uint32_t n_tests;
+        int nlog2;
+    };
+
+    struct HeightFieldView
+    {
+        float x, y, z, xs, ys, zs;  // offset, scale (shapes.hh:249-262)
+        float xd2, yd2;             // half image size, already float(size_t(xd / 2))
+        float xdf, ydf;             // float(xd), float(yd)
+        int xd;
+        const float *data;
+    };
+
+    struct AttachmentView
+    {
+        float tf[7];          // tx ty tz rx ry rz rw (attachments.hh:67-73)
+        int n;                // number of attachment spheres
+        const float4 *local;  // [n] x y z r in the end-effector frame
+    };
+
+    constexpr int kMaxAttach = 16;
+
+    // Passed by value to every kernel (lives in the parameter constant bank).
+    struct EnvView
+    {
+        const float4 *prims;  // packed records: spheres | capsules | z-capsules | cuboids | z-cuboids
+        int n_quads;          // total float4 count of `prims`
+        int n_spheres, n_capsules, n_zcapsules, n_cuboids, n_zcuboids;
+        int n_heightfields, n_capts;
+        const HeightFieldView *heightfields;
+        const CaptView *capts;
+        AttachmentView attach;
+    };
+
+    // Margin bookkeeping: smallest |signed clearance| (metres) over every test that decided control
+    // flow.  Used by the parity reports to split disagreements into "within 1e-5 m of contact" and
+    // real mismatches (BASELINE north_star).
+    struct NoMargin
+    {
+        VB_D void sq(float, float) {}
+        VB_D void lin(float) {}
+    };
+    struct MinMargin
+    {
+        float m = 3.0e38f;
+        // value = d^2 - R^2  ->  |d - R|
+        VB_D void sq(float value, float R)
+        {
+            const float d = sqrtf(fmaxf(value + R * R, 0.f));
+            m = fminf(m, fabsf(d - R));
+        }
+        VB_D void lin(float value) { m = fminf(m, fabsf(value)); }
+    };
+
+    // collision/capt.hh:457-541 (collides_simd with one query per lane)
+    template <class M>
+    VB_D bool capt_hit(const CaptView &c, float x, float y, float z, float r, M &mg)
+    {
+        const float ctr[3] = {x, y, z};
+        bool inb = true;
+#pragma unroll
+        for (int k = 0; k < 3; ++k)
+        {
+            inb = inb && (ctr[k] + r >= c.top[k]) && (ctr[k] - r <= c.top[3 + k]);
+        }
+        if (!inb)
+        {
+            return false;
+        }
+        uint32_t idx = 0;
+        int k = 0;
+        for (int i = 0; i < c.nlog2; ++i)
+        {
+            idx = 2u * idx + 1u + (ctr[k] >= __ldg(c.tests + idx) ? 1u : 0u);
+            k = (k == 2) ? 0 : k + 1;
+        }
+        const uint32_t leaf = idx - c.n_tests;
+        const float R = r + c.r_point;
+        const float rsq = R * R;
+        const float *bb = c.aabbs + 6ull * leaf;
+        float dsq = 0.f;
+#pragma unroll
+        for (int a = 0; a < 3; ++a)
+        {
+            const float lo = __ldg(bb + a), hi = __ldg(bb + 3 + a);
+            const float cl = fminf(fmaxf(ctr[a], lo), hi);
+            const float d = ctr[a] - cl;
+            dsq += d * d;
+        }
+        if (!(dsq <= rsq))
+        {
+            return false;
+        }
+        const uint32_t s = __ldg(c.aff_starts + leaf), e = __ldg(c.aff_starts + leaf + 1);
+        for (uint32_t i = s; i < e; ++i)
+        {
+            const float4 *v = c.aff + 6ull * i;
+            const float4 x0 = __ldg(v), x1 = __ldg(v + 1), y0 = __ldg(v + 2), y1 = __ldg(v + 3), z0 = __ldg(v + 4),
+                         z1 = __ldg(v + 5);
+            const float px[8] = {x0.x, x0.y, x0.z, x0.w, x1.x, x1.y, x1.z, x1.w};
+            const float py[8] = {y0.x, y0.y, y0.z, y0.w, y1.x, y1.y, y1.z, y1.w};
+            const float pz[8] = {z0.x, z0.y, z0.z, z0.w, z1.x, z1.y, z1.z, z1.w};
+            bool hit = false;
+#pragma unroll
+            for (int j = 0; j < 8; ++j)
+            {
+                const float dx = px[j] - x, dy = py[j] - y, dz = pz[j] - z;
+                const float d2 = dx * dx + dy * dy + dz * dz;
+                mg.sq(d2 - rsq, R);
+                hit = hit || (d2 <= rsq);
+            }
+            if (hit)
+            {
+                return true;
+            }
+        }
+        return false;
+    }
+
+    // collision/sphere_heightfield.hh:8-30
+    VB_D float heightfield_value(const HeightFieldView &h, float x, float y, float z, float r)
+    {
+        const float xo = h.x - x, yo = h.y - y;
+        const float xi = floorf(fminf(fmaxf(h.xs * xo + h.xd2, 0.f), h.xdf));
+        const float yi = floorf(fminf(fmaxf(h.ys * yo + h.yd2, 0.f), h.ydf));
+        const int index = static_cast<int>(yi * static_cast<float>(h.xd) + xi);
+        const float zh = __ldg(h.data + index);
+        return z - r - (h.zs * zh + h.z);
+    }
+
+    // collision/validity.hh:46-150.  `P` points at the packed records (shared or global memory).
+    // Each loop stops at the first record whose min_distance is >= the sphere's largest distance
+    // from the origin, as the reference does; with an exact sqrt the cut is conservative, so the
+    // verdict equals the unpruned OR over all obstacles.
+    template <class M>
+    VB_D bool env_hit(const EnvView &e, const float4 *P, float sx, float sy, float sz, float sr, M &mg)
+    {
+        const float ext = sqrtf(sx * sx + sy * sy + sz * sz) + sr;
+        const float4 *p = P;
+        for (int i = 0; i < e.n_spheres; ++i, p += kSphereQ)
+        {
+            const float4 a = p[0];
+            if (p[1].x >= ext)
+            {
+                break;
+            }
+            const float dx = a.x - sx, dy = a.y - sy, dz = a.z - sz, rs = a.w + sr;
+            const float v = dx * dx + dy * dy + dz * dz - rs * rs;
+            mg.sq(v, rs);
+            if (v < 0.f)
+            {
+                return true;
+            }
+        }
+        p = P + kSphereQ * e.n_spheres;
+        for (int i = 0; i < e.n_capsules; ++i, p += kCapsuleQ)
+        {
+            const float4 a = p[0], b = p[1];
+            if (p[2].x >= ext)
+            {
+                break;
+            }
+            // sphere_capsule.hh:8-22
+            const float dot = (sx - a.x) * b.x + (sy - a.y) * b.y + (sz - a.z) * b.z;
+            const float cdf = fmaxf(fminf(dot * b.w, 1.f), 0.f);
+            const float dx = sx - (a.x + b.x * cdf), dy = sy - (a.y + b.y * cdf), dz = sz - (a.z + b.z * cdf);
+            const float rs = sr + a.w;
+            const float v = dx * dx + dy * dy + dz * dz - rs * rs;
+            mg.sq(v, rs);
+            if (v < 0.f)
+            {
+                return true;
+            }
+        }
+        p = P + kSphereQ * e.n_spheres + kCapsuleQ * e.n_capsules;
+        for (int i = 0; i < e.n_zcapsules; ++i, p += kZCapsQ)
+        {
+            const float4 a = p[0], b = p[1];
+            if (b.z >= ext)
+            {
+                break;
+            }
+            // sphere_capsule.hh:31-44
+            const float dot = (sz - a.z) * b.x;
+            const float cdf = fmaxf(fminf(dot * b.y, 1.f), 0.f);
+            const float dx = sx - a.x, dy = sy - a.y, dz = sz - (a.z + b.x * cdf);
+            const float rs = sr + a.w;
+            const float v = dx * dx + dy * dy + dz * dz - rs * rs;
+            mg.sq(v, rs);
+            if (v < 0.f)
+            {
+                return true;
+            }
+        }
+        const float rsq = sr * sr;
+        p = P + kSphereQ * e.n_spheres + kCapsuleQ * e.n_capsules + kZCapsQ * e.n_zcapsules;
+        for (int i = 0; i < e.n_cuboids; ++i, p += kCuboidQ)
+        {
+            const float4 c = p[0];
+            if (c.w >= ext)
+            {
+                break;
+            }
+            // sphere_cuboid.hh:8-26
+            const float4 a1 = p[1], a2 = p[2], a3 = p[3];
+            const float xs = sx - c.x, ys = sy - c.y, zs = sz - c.z;
+            const float d1 = fmaxf(fabsf(a1.x * xs + a1.y * ys + a1.z * zs) - a1.w, 0.f);
+            const float d2 = fmaxf(fabsf(a2.x * xs + a2.y * ys + a2.z * zs) - a2.w, 0.f);
+            const float d3 = fmaxf(fabsf(a3.x * xs + a3.y * ys + a3.z * zs) - a3.w, 0.f);
+            const float v = d1 * d1 + d2 * d2 + d3 * d3 - rsq;
+            mg.sq(v, sr);
+            if (v < 0.f)
+            {
+                return true;
+            }
+        }
+        p = P + kSphereQ * e.n_spheres + kCapsuleQ * e.n_capsules + kZCapsQ * e.n_zcapsules +
+            kCuboidQ * e.n_cuboids;
+        for (int i = 0; i < e.n_zcuboids; ++i, p += kZCubQ)
+        {
+            const float4 c = p[0];
+            if (c.w >= ext)
+            {
+                break;
+            }
+            // sphere_cuboid.hh:35-52
+            const float4 ax = p[1], hr = p[2];
+            const float xs = sx - c.x, ys = sy - c.y, zs = sz - c.z;
+            const float d1 = fmaxf(fabsf(ax.x * xs + ax.y * ys) - hr.x, 0.f);
+            const float d2 = fmaxf(fabsf(ax.z * xs + ax.w * ys) - hr.y, 0.f);
+            const float d3 = fmaxf(fabsf(zs) - hr.z, 0.f);
+            const float v = d1 * d1 + d2 * d2 + d3 * d3 - rsq;
+            mg.sq(v, sr);
+            if (v < 0.f)
+            {
+                return true;
+            }
+        }
+        for (int i = 0; i < e.n_heightfields; ++i)
+        {
+            const float v = heightfield_value(e.heightfields[i], sx, sy, sz, sr);
+            mg.lin(v);
+            if (v < 0.f)
+            {
+                return true;
+            }
+        }
+        for (int i = 0; i < e.n_capts; ++i)
+        {
+            if (capt_hit(e.capts[i], sx, sy, sz, sr, mg))
+            {
+                return true;
+            }
+        }
+        return false;
+    }
+}  // namespace vb
