@@ -1,18 +1,25 @@
 """Back end of the kernel compiler: robot IR (trace_parser) -> CUDA device code for sm_100a.
 
-For every robot one header ``mr_vamp_b200/_gen/<robot>_trace.cuh`` is written.  It holds a struct
-``vb::<Robot>Trace`` with three policy-templated device functions
+For every robot one header ``mr_vamp_b200/_gen/<robot>_trace.cuh`` is written.  The reference
+interleaves the FK chain with ~800 inlined collision tests in one straight-line function; that
+shape is hostile to a GPU (hundreds of KB of SASS, instruction-cache thrash, minutes of ptxas), so
+the trace is split in two:
 
-* ``fkcc(P&, const float* q)``          <- ``interleaved_sphere_fk``           (robots/<r>/fk.hh)
-* ``fkcc_attach(P&, const float* q)``   <- ``interleaved_sphere_fk_attachment``
-* ``sphere_fk(P&, const float* q)``     <- ``sphere_fk``
+* ``chain(P&, q)`` / ``chain_attach(P&, q)`` — the FK arithmetic only, straight-line, value by
+  value as in ``interleaved_sphere_fk[_attachment]`` (literals narrowed to float exactly where the
+  C++ expression narrows them: this keeps sphere centres within 1e-5 m of the reference).  Every
+  distinct sphere centre that any check uses is handed to ``p.put(slot, x, y, z)`` (robot-local
+  frame); the kernels keep those slots in shared memory, one column per thread.
+* constant-memory *check tables* (``vb_tables.cuh``): environment groups (guard sphere + fine
+  spheres), self-collision groups (guard pair + a cross product of fine spheres) and attachment
+  groups, each entry a (slot, base-offset mask, radius) reference.  The generic loops of
+  ``vb_kernels.cuh`` walk these tables, so there is ONE copy of the environment query in the
+  kernel instead of 72.
+* ``sphere_fk(P&, q)`` <- ``sphere_fk`` (all collision spheres, world frame), unchanged.
 
-The policy supplies the collision tests (``env_test``, ``self_test``, ``attach_*``), the base
-offset and the output sink, so the same straight-line trace serves the verdict kernels, the
-clearance ("margin") kernels and the work-counting kernels in ``csrc/vb_kernels.cuh``.  The emitted
-arithmetic follows the IR value by value (literals narrowed to float exactly where the C++
-expression narrows them), which is what keeps sphere centres within 1e-5 m of the reference; the
-scheduling, register allocation and FMA contraction are left to nvcc/ptxas.
+Verdicts do not depend on the order of the tests (valid = no group has guard-hit and fine-hit), so
+de-interleaving changes work, not results.  Scheduling, register allocation and FMA contraction
+are left to nvcc/ptxas.
 
 The generated headers are build products (git-ignored): the traces belong to the VAMP checkout the
 library is built against (``$VAMP_SRC``), exactly like the reference's own ``fk.hh`` files belong
@@ -45,12 +52,22 @@ def _f64(c: float) -> str:
     return repr(float(c))
 
 
+
+
 class _Emitter:
+    """Lowers one traced function to (chain lines, check tables)."""
+
     def __init__(self, fn: dict[str, Any]):
         self.values = fn["values"]
         self.program = fn["program"]
         self.lines: list[str] = []
-        self.pending_ops = 0
+        self.slots: dict[tuple, int] = {}
+        self.refs: list[tuple[int, int, float]] = []  # (slot, base mask, radius)
+        self.env: list[dict[str, Any]] = []
+        self.selfg: list[dict[str, Any]] = []
+        self.att: list[dict[str, Any]] = []
+        self.att_env = 0
+        self.has_pose = False
 
     # -- operands -----------------------------------------------------------------------------
     def opnd(self, o) -> str:
@@ -58,21 +75,39 @@ class _Emitter:
             return _f32(o["c"])
         return f"v{o}"
 
-    def arg(self, a: dict[str, Any]) -> str:
-        """Argument of a check call / output: value | literal [+ base]."""
+    def coord(self, a: dict[str, Any]) -> str:
+        return f"v{a['v']}" if a["v"] is not None else _f32(a["c"])
+
+    def out_arg(self, a: dict[str, Any]) -> str:
         base = a.get("base")
         if a.get("sym") == "radius":
             return "p.radius"
         if a["v"] is not None:
-            s = f"v{a['v']}"
-            return f"({s} + p.b{base}())" if base else s
+            return f"(v{a['v']} + p.b{base}())" if base else f"v{a['v']}"
         if base:
-            # `0.122 + base_z`: double + float -> double, narrowed when the check upcasts it
             return f"p.cb{base}({_f64(a['c'])})"
         return _f32(a["c"])
 
-    def sphere(self, s) -> str:
-        return ", ".join(self.arg(a) for a in s)
+    def ref(self, s) -> tuple[int, int, float]:
+        """Sphere argument list [x, y, z, r] -> (slot, base mask, radius); emits the put on first use."""
+        key = tuple((a["v"] if a["v"] is not None else ("c", a["c"])) for a in s[:3])
+        if key not in self.slots:
+            self.slots[key] = len(self.slots)
+            self.lines.append(
+                f"p.put({self.slots[key]}, {self.coord(s[0])}, {self.coord(s[1])}, {self.coord(s[2])});"
+            )
+        mask = sum((1 << i) for i, a in enumerate(s[:3]) if a.get("base"))
+        for i, a in enumerate(s[:3]):
+            assert a.get("base") in (None, "xyz"[i]), s
+        r = s[3]
+        radius = -1.0 if r.get("sym") == "radius" else float(r["c"])
+        assert r.get("sym") == "radius" or r["v"] is None
+        return (self.slots[key], mask, radius)
+
+    def add_refs(self, refs) -> tuple[int, int]:
+        begin = len(self.refs)
+        self.refs.extend(refs)
+        return begin, len(refs)
 
     # -- statements ---------------------------------------------------------------------------
     def value(self, vid: int):
@@ -81,54 +116,56 @@ class _Emitter:
             rhs = f"q[{a}]"
         elif op in ("mul", "add", "sub"):
             rhs = f"{self.opnd(a)} {'*' if op == 'mul' else '+' if op == 'add' else '-'} {self.opnd(b)}"
-            self.pending_ops += 1
         elif op == "neg":
             rhs = f"-{self.opnd(a)}"
-        elif op == "sin":
-            rhs = f"vamp_sin({self.opnd(a)})"
-            self.pending_ops += 11
-        elif op == "cos":
-            rhs = f"vamp_cos({self.opnd(a)})"
-            self.pending_ops += 14
+        elif op in ("sin", "cos"):
+            rhs = f"vamp_{op}({self.opnd(a)})"
         else:
             raise ValueError(op)
         self.lines.append(f"const float v{vid} = {rhs};")
 
-    def flush_ops(self):
-        if self.pending_ops:
-            self.lines.append(f"p.ops({self.pending_ops});")
-            self.pending_ops = 0
-
     def group(self, it: dict[str, Any]):
         k = it["k"]
-        self.flush_ops()
         if k == "attach_pose":
-            self.lines.append("p.attach_pose(" + ", ".join(self.arg(a) for a in it["args"]) + ");")
+            self.lines.append("p.attach_pose(" + ", ".join(self.coord(a) for a in it["args"]) + ");")
+            self.has_pose = True
             return
         if k == "attach_env":
-            self.lines.append("if (p.attach_env()) { return false; }")
+            self.att_env = 1
             return
-        if k == "env":
-            test = lambda s: f"p.env_test({self.sphere(s)})"
-        elif k == "self":
-            test = lambda s: f"p.self_test({self.sphere(s[0])}, {self.sphere(s[1])})"
-        elif k == "attach_self":
-            test = lambda s: f"p.attach_self({self.sphere(s)})"
-        else:
-            raise ValueError(k)
-        name = it.get("name", "")
         fine = it["fine"]
-        if it.get("leaf") or not fine or fine == [it["guard"]]:
-            # a bare `if (check) return false;` : the guard is the test
-            self.lines.append(f"if ({test(it['guard'])}) {{ return false; }}  // {name}")
+        leaf = bool(it.get("leaf")) or not fine or fine == [it["guard"]]
+        name = it.get("name", "")
+        if k in ("env", "attach_self"):
+            guard = self.ref(it["guard"])
+            begin, count = self.add_refs([] if leaf else [self.ref(s) for s in fine])
+            (self.env if k == "env" else self.att).append(
+                {"guard": guard, "begin": begin, "count": count, "name": name}
+            )
             return
-        self.lines.append(f"if ({test(it['guard'])})  // {name}")
-        self.lines.append("{")
-        for s in fine:
-            self.lines.append(f"    if ({test(s)}) {{ return false; }}")
-        self.lines.append("}")
+        if k == "self":
+            ga, gb = self.ref(it["guard"][0]), self.ref(it["guard"][1])
+            A: list[tuple] = []
+            B: list[tuple] = []
+            pairs = []
+            if not leaf:
+                for a, b in fine:
+                    ra, rb = self.ref(a), self.ref(b)
+                    pairs.append((ra, rb))
+                    if ra not in A:
+                        A.append(ra)
+                    if rb not in B:
+                        B.append(rb)
+                # every traced self group is the full cross product of two sphere sets
+                if sorted(pairs) != sorted((x, y) for x in A for y in B):
+                    raise ValueError("self group is not a cross product: " + name)
+            ab, ac = self.add_refs(A)
+            bb, bc = self.add_refs(B)
+            self.selfg.append({"ga": ga, "gb": gb, "a": (ab, ac), "b": (bb, bc), "name": name})
+            return
+        raise ValueError(k)
 
-    def run_checks(self) -> list[str]:
+    def run_checks(self):
         for it in self.program:
             if it["k"] == "val":
                 self.value(it["id"])
@@ -136,16 +173,14 @@ class _Emitter:
                 raise ValueError("out in check trace")
             else:
                 self.group(it)
-        self.flush_ops()
-        self.lines.append("return true;")
-        return self.lines
+        return self
 
     def run_spheres(self) -> list[str]:
         for it in self.program:
             if it["k"] == "val":
                 self.value(it["id"])
             elif it["k"] == "out":
-                self.lines.append(f"p.out_{it['field']}({it['idx']}, {self.arg(it['arg'])});")
+                self.lines.append(f"p.out_{it['field']}({it['idx']}, {self.out_arg(it['arg'])});")
             else:
                 raise ValueError(it["k"])
         return self.lines
@@ -164,10 +199,43 @@ def trace_stats(ir: dict[str, Any]) -> dict[str, Any]:
         "ops": ops,
         "env_groups": len(env_g),
         "env_fine": sum(len(g["fine"]) for g in env_g),
-        "env_leaf": sum(1 for g in env_g if g.get("leaf")),
         "self_groups": len(self_g),
         "self_fine": sum(len(g["fine"]) for g in self_g),
     }
+
+
+def _ref(r) -> str:
+    slot, mask, radius = r
+    return f"{{{slot}, {mask}, {_f32(radius) if radius >= 0 else '-1.0f'}}}"
+
+
+def _tables(name: str, em: _Emitter) -> list[str]:
+    ne, ns, na, nr = len(em.env), len(em.selfg), len(em.att), len(em.refs)
+    t = f"Tables<{max(ne, 1)}, {max(ns, 1)}, {max(na, 1)}, {max(nr, 1)}>"
+    out = [f"__constant__ {t} {name} = {{"]
+    out.append(f"    {len(em.slots)}, {ne}, {ns}, {na}, {em.att_env},")
+    out.append("    {")
+    for g in em.env or [{"guard": (0, 0, 0.0), "begin": 0, "count": 0, "name": "-"}]:
+        out.append(f"        {{{_ref(g['guard'])}, {g['begin']}, {g['count']}}},  // {g['name']}")
+    out.append("    },")
+    out.append("    {")
+    for g in em.selfg or [{"ga": (0, 0, 0.0), "gb": (0, 0, 0.0), "a": (0, 0), "b": (0, 0), "name": "-"}]:
+        out.append(
+            f"        {{{_ref(g['ga'])}, {_ref(g['gb'])}, {g['a'][0]}, {g['a'][1]}, {g['b'][0]}, {g['b'][1]}}},"
+            f"  // {g['name']}"
+        )
+    out.append("    },")
+    out.append("    {")
+    for g in em.att or [{"guard": (0, 0, 0.0), "begin": 0, "count": 0, "name": "-"}]:
+        out.append(f"        {{{_ref(g['guard'])}, {g['begin']}, {g['count']}}},  // {g['name']}")
+    out.append("    },")
+    out.append("    {")
+    refs = em.refs or [(0, 0, 0.0)]
+    for i in range(0, len(refs), 6):
+        out.append("        " + ", ".join(_ref(r) for r in refs[i : i + 6]) + ",")
+    out.append("    },")
+    out.append("};")
+    return out, t
 
 
 def emit_robot(ir: dict[str, Any]) -> str:
@@ -177,14 +245,22 @@ def emit_robot(ir: dict[str, Any]) -> str:
     fns = ir["functions"]
     has_attach = "interleaved_sphere_fk_attachment" in fns
     st = trace_stats(ir)
+    em = _Emitter(fns["interleaved_sphere_fk"]).run_checks()
+    em_att = _Emitter(fns["interleaved_sphere_fk_attachment"]).run_checks() if has_attach else None
     out: list[str] = []
     w = out.append
     w(f"// GENERATED by mr_vamp_b200/codegen/emit_cuda.py from {ir['source']} of the VAMP checkout")
     w("// this library was built against.  Build product: do not edit, do not commit.")
     w("#pragma once")
-    w('#include "../csrc/vb_numerics.cuh"')
+    w('#include "../csrc/vb_sinks.cuh"')
+    w('#include "../csrc/vb_tables.cuh"')
     w("namespace vb")
     w("{")
+    tab, ttype = _tables(f"k_{robot}_tables", em)
+    out.extend(tab)
+    if em_att:
+        tab2, ttype2 = _tables(f"k_{robot}_tables_attach", em_att)
+        out.extend(tab2)
     w(f"struct {cls}")
     w("{")
     w(f'    static constexpr const char *kName = "{robot}";')
@@ -192,9 +268,19 @@ def emit_robot(ir: dict[str, Any]) -> str:
     w(f"    static constexpr int kSpheres = {S};")
     w(f"    static constexpr int kResolution = {ir['resolution']};")
     w(f"    static constexpr bool kHasAttach = {'true' if has_attach else 'false'};")
+    n_slots = max(len(em.slots), len(em_att.slots) if em_att else 0)
+    w(f"    static constexpr int kSlots = {n_slots};  // distinct sphere centres used by the checks")
     w(f"    static constexpr int kChainFlops = {st['chain_flops']};")
     w(f"    static constexpr int kEnvGroups = {st['env_groups']}, kEnvFine = {st['env_fine']};")
     w(f"    static constexpr int kSelfGroups = {st['self_groups']}, kSelfFine = {st['self_fine']};")
+    w(f"    using TablesT = {ttype};")
+    w(f"    __device__ __forceinline__ static const TablesT &tables() {{ return k_{robot}_tables; }}")
+    if em_att:
+        w(f"    using TablesAttachT = {ttype2};")
+        w(f"    __device__ __forceinline__ static const TablesAttachT &tables_attach() {{ return k_{robot}_tables_attach; }}")
+    else:
+        w("    using TablesAttachT = TablesT;")
+        w(f"    __device__ __forceinline__ static const TablesAttachT &tables_attach() {{ return k_{robot}_tables; }}")
     lo = ", ".join(_f32(v) for v in ir["scale"]["lo"])
     rg = ", ".join(_f32(v) for v in ir["scale"]["range"])
     w("    VB_HD static float lo(int j)")
@@ -207,21 +293,25 @@ def emit_robot(ir: dict[str, Any]) -> str:
     w(f"        constexpr float t[{dim}] = {{{rg}}};")
     w("        return t[j];")
     w("    }")
+    inv = ir["scale"].get("inv")
+    w("    // descale_configuration: (q - lo) * inv, or (q - lo) / range where the reference divides")
+    w(f"    static constexpr bool kDescaleDivides = {'false' if inv else 'true'};")
+    w("    VB_HD static float inv_range(int j)")
+    w("    {")
+    w(f"        constexpr float t[{dim}] = {{{', '.join(_f32(v) for v in (inv or ir['scale']['range']))}}};")
+    w("        return t[j];")
+    w("    }")
 
-    def fn(name: str, ret: str, body: list[str]):
-        w("    template <class P>")
-        w(f"    __device__ __forceinline__ static {ret} {name}(P &p, const float *__restrict__ q)")
+    def fn(name: str, body: list[str], sink: str = "SlotSink"):
+        w(f"    __device__ __noinline__ static void {name}(const {sink} &p, const float *__restrict__ q)")
         w("    {")
         for ln in body:
             w("        " + ln)
         w("    }")
 
-    fn("fkcc", "bool", _Emitter(fns["interleaved_sphere_fk"]).run_checks())
-    if has_attach:
-        fn("fkcc_attach", "bool", _Emitter(fns["interleaved_sphere_fk_attachment"]).run_checks())
-    else:
-        fn("fkcc_attach", "bool", ["return fkcc(p, q);"])
-    fn("sphere_fk", "void", _Emitter(fns["sphere_fk"]).run_spheres())
+    fn("chain", em.lines)
+    fn("chain_attach", em_att.lines if em_att else ["chain(p, q);"])
+    fn("sphere_fk", _Emitter(fns["sphere_fk"]).run_spheres(), "SphereSink")
     w("};")
     w("}  // namespace vb")
     return "\n".join(out) + "\n"

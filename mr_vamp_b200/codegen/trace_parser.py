@@ -289,7 +289,19 @@ def _scaling(text: str, dim: int):
         rng[i] = float(m.group(3).rstrip("fF"))
     if any(v is None for v in lo):
         return None
-    return {"lo": lo, "range": rng}
+    out = {"lo": lo, "range": rng}
+    # descale_configuration: q' = inv * (q - lo) with `inv` a literal (used by the joint-limit test,
+    # bindings/common.hh:176-179)
+    try:
+        dbody = _function_body(text, "descale_configuration_block")
+        inv = [None] * dim
+        for m in re.finditer(r"q\[(\d+)\]\s*=\s*(" + _NUM + r")\s*\*\s*\(q\[\d+\]\s*-\s*(" + _NUM + r")\)", dbody):
+            inv[int(m.group(1))] = float(m.group(2).rstrip("fF"))
+        if all(v is not None for v in inv):
+            out["inv"] = inv
+    except KeyError:
+        pass
+    return out
 
 
 def parse_robot(robot: str) -> dict[str, Any]:

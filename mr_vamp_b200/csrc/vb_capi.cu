@@ -1,0 +1,1419 @@
+// libvamp_b200.so — implementation of the C ABI declared in include/vamp_b200.h.
+//
+// Host side of the fkcc path: device contexts and streams, the device-resident environment
+// (replaces collision::Environment<float> + its per-call vector conversion, collision/environment.hh),
+// batch sharding over the devices of a context, and the launches of the per-robot kernels
+// (vb_robot.cu).  No CPU implementation of any query exists here: every query either runs on a
+// CUDA device or fails.
+#include "../../include/vamp_b200.h"
+
+#include <algorithm>
+#include <atomic>
+#include <cmath>
+#include <cstdarg>
+#include <cstdio>
+#include <cstring>
+#include <memory>
+#include <string>
+#include <vector>
+
+#include <dlfcn.h>
+#include <nccl.h>  // types only: the library is dlopen()ed by vb_comm_* so the core path does not need it
+
+#include "vb_robot_ops.h"
+
+namespace
+{
+    thread_local std::string g_error;
+
+    int fail(int code, const char *fmt, ...)
+    {
+        char buf[512];
+        va_list ap;
+        va_start(ap, fmt);
+        vsnprintf(buf, sizeof(buf), fmt, ap);
+        va_end(ap);
+        g_error = buf;
+        return code;
+    }
+
+#define VB_CUDA(expr)                                                                                \
+    do                                                                                               \
+    {                                                                                                \
+        cudaError_t err__ = (expr);                                                                  \
+        if (err__ != cudaSuccess)                                                                    \
+        {                                                                                            \
+            return fail(VB_ERR_CUDA, "%s: %s (%s:%d)", #expr, cudaGetErrorString(err__), __FILE__, __LINE__); \
+        }                                                                                            \
+    } while (0)
+
+#define VB_NCCL(expr)                                                                                \
+    do                                                                                               \
+    {                                                                                                \
+        ncclResult_t err__ = (expr);                                                                 \
+        if (err__ != ncclSuccess)                                                                    \
+        {                                                                                            \
+            return fail(VB_ERR_NCCL, "%s: %s (%s:%d)", #expr, nccl().GetErrorString(err__), __FILE__, __LINE__); \
+        }                                                                                            \
+    } while (0)
+
+#define VB_TRY(expr)            \
+    do                          \
+    {                           \
+        int rc__ = (expr);      \
+        if (rc__ != VB_OK)      \
+        {                       \
+            return rc__;        \
+        }                       \
+    } while (0)
+
+    const vb::RobotOps *ops_of(vb_robot r)
+    {
+        switch (r)
+        {
+            case VB_SPHERE:
+                return vb::robot_ops_sphere();
+            case VB_UR5:
+                return vb::robot_ops_ur5();
+            case VB_PANDA:
+                return vb::robot_ops_panda();
+            case VB_FETCH:
+                return vb::robot_ops_fetch();
+            case VB_BAXTER:
+                return vb::robot_ops_baxter();
+        }
+        return nullptr;
+    }
+
+    // A grow-only device buffer.
+    struct DevBuf
+    {
+        void *p = nullptr;
+        size_t cap = 0;
+        cudaError_t reserve(size_t bytes)
+        {
+            if (bytes <= cap)
+            {
+                return cudaSuccess;
+            }
+            if (p)
+            {
+                cudaFree(p);
+                p = nullptr;
+                cap = 0;
+            }
+            const size_t want = std::max<size_t>(bytes, 256);
+            cudaError_t e = cudaMalloc(&p, want);
+            if (e == cudaSuccess)
+            {
+                cap = want;
+            }
+            return e;
+        }
+        void release()
+        {
+            if (p)
+            {
+                cudaFree(p);
+            }
+            p = nullptr;
+            cap = 0;
+        }
+        template <class T>
+        T *as() const
+        {
+            return static_cast<T *>(p);
+        }
+    };
+
+    struct Slot
+    {
+        int device = 0;
+        int sm_count = 0;
+        cudaStream_t stream = nullptr;
+        cudaEvent_t ev0 = nullptr, ev1 = nullptr;
+        DevBuf in_a, in_b, bits, margin, out, counts, prefix, scan_tmp;
+    };
+}  // namespace
+
+struct vb_ctx
+{
+    std::vector<Slot> slots;
+    float sphere_radius = 0.2f;  // robots/sphere/fk.hh:16
+    std::atomic<uint64_t> launches{0};
+    ncclComm_t comm = nullptr;
+    int comm_ranks = 0;
+};
+
+namespace
+{
+    // NCCL entry points, resolved on first use (libnccl.so.2 — torch's bundled copy when the host
+    // process already loaded it, the system one otherwise).
+    struct NcclApi
+    {
+        bool ok = false;
+        ncclResult_t (*GetUniqueId)(ncclUniqueId *) = nullptr;
+        ncclResult_t (*CommInitRank)(ncclComm_t *, int, ncclUniqueId, int) = nullptr;
+        ncclResult_t (*AllGather)(const void *, void *, size_t, ncclDataType_t, ncclComm_t, cudaStream_t) = nullptr;
+        ncclResult_t (*CommDestroy)(ncclComm_t) = nullptr;
+        const char *(*GetErrorString)(ncclResult_t) = nullptr;
+    };
+
+    NcclApi &nccl()
+    {
+        static NcclApi api = [] {
+            NcclApi a;
+            void *h = dlopen("libnccl.so.2", RTLD_NOW | RTLD_GLOBAL);
+            if (!h)
+            {
+                h = dlopen("libnccl.so", RTLD_NOW | RTLD_GLOBAL);
+            }
+            if (!h)
+            {
+                return a;
+            }
+            a.GetUniqueId = reinterpret_cast<decltype(a.GetUniqueId)>(dlsym(h, "ncclGetUniqueId"));
+            a.CommInitRank = reinterpret_cast<decltype(a.CommInitRank)>(dlsym(h, "ncclCommInitRank"));
+            a.AllGather = reinterpret_cast<decltype(a.AllGather)>(dlsym(h, "ncclAllGather"));
+            a.CommDestroy = reinterpret_cast<decltype(a.CommDestroy)>(dlsym(h, "ncclCommDestroy"));
+            a.GetErrorString = reinterpret_cast<decltype(a.GetErrorString)>(dlsym(h, "ncclGetErrorString"));
+            a.ok = a.GetUniqueId && a.CommInitRank && a.AllGather && a.CommDestroy && a.GetErrorString;
+            return a;
+        }();
+        return api;
+    }
+
+    int check_slot(const vb_ctx *ctx, int slot)
+    {
+        if (!ctx)
+        {
+            return fail(VB_ERR_ARG, "null context");
+        }
+        if (slot < 0 || slot >= static_cast<int>(ctx->slots.size()))
+        {
+            return fail(VB_ERR_ARG, "device slot %d out of range (context has %zu)", slot, ctx->slots.size());
+        }
+        return VB_OK;
+    }
+}  // namespace
+
+extern "C" {
+
+const char *vb_last_error(void)
+{
+    return g_error.c_str();
+}
+
+const char *vb_version(void)
+{
+    return "vamp_b200 0.1 (sm_100a)";
+}
+
+int vb_ctx_create(vb_ctx **out, const int *device_ids, int n_devices)
+{
+    if (!out || n_devices < 0 || (n_devices > 0 && !device_ids))
+    {
+        return fail(VB_ERR_ARG, "vb_ctx_create: bad arguments");
+    }
+    int available = 0;
+    cudaError_t e = cudaGetDeviceCount(&available);
+    if (e != cudaSuccess || available == 0)
+    {
+        return fail(VB_ERR_CUDA, "no usable CUDA device (%s); this library has no CPU path",
+                    e == cudaSuccess ? "device count is 0" : cudaGetErrorString(e));
+    }
+    std::unique_ptr<vb_ctx> ctx(new vb_ctx());
+    const int n = n_devices == 0 ? 1 : n_devices;
+    for (int i = 0; i < n; ++i)
+    {
+        Slot s;
+        s.device = n_devices == 0 ? 0 : device_ids[i];
+        if (s.device < 0 || s.device >= available)
+        {
+            return fail(VB_ERR_ARG, "device id %d not in [0, %d)", s.device, available);
+        }
+        VB_CUDA(cudaSetDevice(s.device));
+        cudaDeviceProp prop;
+        VB_CUDA(cudaGetDeviceProperties(&prop, s.device));
+        if (prop.major < 10)
+        {
+            return fail(VB_ERR_CUDA, "device %d is sm_%d%d; the kernels are built for sm_100a only", s.device,
+                        prop.major, prop.minor);
+        }
+        s.sm_count = prop.multiProcessorCount;
+        VB_CUDA(cudaStreamCreateWithFlags(&s.stream, cudaStreamNonBlocking));
+        VB_CUDA(cudaEventCreate(&s.ev0));
+        VB_CUDA(cudaEventCreate(&s.ev1));
+        ctx->slots.push_back(s);
+    }
+    *out = ctx.release();
+    return VB_OK;
+}
+
+void vb_ctx_destroy(vb_ctx *ctx)
+{
+    if (!ctx)
+    {
+        return;
+    }
+    if (ctx->comm)
+    {
+        nccl().CommDestroy(ctx->comm);
+    }
+    for (auto &s : ctx->slots)
+    {
+        cudaSetDevice(s.device);
+        cudaStreamSynchronize(s.stream);
+        for (DevBuf *b : {&s.in_a, &s.in_b, &s.bits, &s.margin, &s.out, &s.counts, &s.prefix, &s.scan_tmp})
+        {
+            b->release();
+        }
+        cudaEventDestroy(s.ev0);
+        cudaEventDestroy(s.ev1);
+        cudaStreamDestroy(s.stream);
+    }
+    delete ctx;
+}
+
+int vb_ctx_device_count(const vb_ctx *ctx)
+{
+    return ctx ? static_cast<int>(ctx->slots.size()) : 0;
+}
+
+int vb_ctx_sm_count(const vb_ctx *ctx, int slot)
+{
+    return check_slot(ctx, slot) == VB_OK ? ctx->slots[slot].sm_count : 0;
+}
+
+int vb_sync(vb_ctx *ctx)
+{
+    if (!ctx)
+    {
+        return fail(VB_ERR_ARG, "null context");
+    }
+    for (auto &s : ctx->slots)
+    {
+        VB_CUDA(cudaSetDevice(s.device));
+        VB_CUDA(cudaStreamSynchronize(s.stream));
+    }
+    return VB_OK;
+}
+
+int vb_ctx_set_sphere_radius(vb_ctx *ctx, float r)
+{
+    if (!ctx || !(r > 0.f))
+    {
+        return fail(VB_ERR_ARG, "vb_ctx_set_sphere_radius: bad arguments");
+    }
+    ctx->sphere_radius = r;
+    return VB_OK;
+}
+
+uint64_t vb_launch_count(const vb_ctx *ctx)
+{
+    return ctx ? ctx->launches.load() : 0;
+}
+
+/* ---- robots ------------------------------------------------------------------------------- */
+int vb_robot_by_name(const char *name, vb_robot *out)
+{
+    if (!name || !out)
+    {
+        return fail(VB_ERR_ARG, "vb_robot_by_name: null argument");
+    }
+    for (int r = VB_SPHERE; r <= VB_BAXTER; ++r)
+    {
+        if (std::strcmp(ops_of(static_cast<vb_robot>(r))->name, name) == 0)
+        {
+            *out = static_cast<vb_robot>(r);
+            return VB_OK;
+        }
+    }
+    return fail(VB_ERR_ARG, "unknown robot '%s'", name);
+}
+
+int vb_robot_info(vb_robot r, int *dimension, int *n_spheres, int *resolution)
+{
+    const vb::RobotOps *o = ops_of(r);
+    if (!o)
+    {
+        return fail(VB_ERR_ARG, "unknown robot id %d", static_cast<int>(r));
+    }
+    if (dimension)
+    {
+        *dimension = o->dim;
+    }
+    if (n_spheres)
+    {
+        *n_spheres = o->n_spheres;
+    }
+    if (resolution)
+    {
+        *resolution = o->resolution;
+    }
+    return VB_OK;
+}
+
+int vb_robot_limits(vb_robot r, float *lo, float *range)
+{
+    const vb::RobotOps *o = ops_of(r);
+    if (!o || !lo || !range)
+    {
+        return fail(VB_ERR_ARG, "vb_robot_limits: bad arguments");
+    }
+    std::copy_n(o->lo, o->dim, lo);
+    std::copy_n(o->range, o->dim, range);
+    return VB_OK;
+}
+
+int vb_random_config(vb_robot r, uint64_t seed, uint64_t index, float *q)
+{
+    const vb::RobotOps *o = ops_of(r);
+    if (!o || !q)
+    {
+        return fail(VB_ERR_ARG, "vb_random_config: bad arguments");
+    }
+    o->random_config(seed, index, q);
+    return VB_OK;
+}
+
+}  // extern "C"
+
+/* ================================ environment ================================================= */
+namespace
+{
+    struct HostSphere
+    {
+        float x, y, z, r, min_d;
+    };
+    struct HostCapsule
+    {
+        float c[8];  // x1 y1 z1 xv yv zv r rdv
+        float min_d;
+    };
+    struct HostCuboid
+    {
+        float c[15];  // centre, axis1, axis2, axis3, half extents
+        float min_d;
+    };
+    struct HostHeightField
+    {
+        float os[6];
+        size_t xd, yd;
+        std::vector<float> data;
+    };
+    struct HostCapt
+    {
+        std::vector<float> tests, aabbs;
+        std::vector<uint32_t> aff_starts;
+        std::vector<float> aff;  // interleaved per vector: x[8] y[8] z[8]
+        float top[6];
+        float r_point;
+        int nlog2;
+    };
+
+    float dot3(float ax, float ay, float az, float bx, float by, float bz)
+    {
+        return (ax * bx) + (ay * by) + (az * bz);
+    }
+    float clampf(float v, float lo, float hi)
+    {
+        return std::max(std::min(v, hi), lo);
+    }
+
+    // collision/shapes.hh:57-73
+    float cuboid_min_distance(const float *c)
+    {
+        const float x = c[0], y = c[1], z = c[2];
+        const float d1 = dot3(-x, -y, -z, c[3], c[4], c[5]);
+        const float d2 = dot3(-x, -y, -z, c[6], c[7], c[8]);
+        const float d3 = dot3(-x, -y, -z, c[9], c[10], c[11]);
+        const float v1 = clampf(d1, -c[12], c[12]);
+        const float v2 = clampf(d2, -c[13], c[13]);
+        const float v3 = clampf(d3, -c[14], c[14]);
+        const float xn = x + c[3] * v1 + c[6] * v2 + c[9] * v3;
+        const float yn = y + c[4] * v1 + c[7] * v2 + c[10] * v3;
+        const float zn = z + c[5] * v1 + c[8] * v2 + c[11] * v3;
+        return std::sqrt(xn * xn + yn * yn + zn * zn);
+    }
+
+    // collision/shapes.hh:166-192
+    float capsule_min_distance(const float *c)
+    {
+        const float x1 = c[0], y1 = c[1], z1 = c[2], xv = c[3], yv = c[4], zv = c[5], r = c[6], rdv = c[7];
+        const float dot = clampf(dot3(-x1, -y1, -z1, xv, yv, zv) * rdv, 0.f, 1.f);
+        const float xp = x1 + xv * dot, yp = y1 + yv * dot, zp = z1 + zv * dot;
+        float xo = -xp, yo = -yp, zo = -zp;
+        const float ol = std::sqrt(dot3(xo, yo, zo, xo, yo, zo));
+        xo = xo / ol;
+        yo = yo / ol;
+        zo = zo / ol;
+        const float ro = clampf(ol, 0.f, r);
+        const float xn = xp + ro * xo, yn = yp + ro * yo, zn = zp + ro * zo;
+        return std::sqrt(xn * xn + yn * yn + zn * zn);
+    }
+
+    struct Replica
+    {
+        DevBuf prims, hf_desc, capt_desc, att_local;
+        std::vector<DevBuf> blobs;  // heightfield data and CAPT arrays
+        vb::EnvView view{};
+    };
+}  // namespace
+
+struct vb_env
+{
+    vb_ctx *ctx = nullptr;
+    std::vector<HostSphere> spheres;
+    std::vector<HostCapsule> capsules, zcapsules;
+    std::vector<HostCuboid> cuboids, zcuboids;
+    std::vector<HostHeightField> heightfields;
+    std::vector<HostCapt> capts;
+    bool has_attachment = false;
+    float att_tf[7] = {0, 0, 0, 0, 0, 0, 1};
+    std::vector<float4> att_spheres;
+    std::vector<Replica> replicas;
+    bool committed = false;
+    uint64_t version = 0;
+};
+
+namespace
+{
+    void release_replicas(vb_env *env)
+    {
+        for (size_t i = 0; i < env->replicas.size(); ++i)
+        {
+            cudaSetDevice(env->ctx->slots[i].device);
+            Replica &r = env->replicas[i];
+            r.prims.release();
+            r.hf_desc.release();
+            r.capt_desc.release();
+            r.att_local.release();
+            for (auto &b : r.blobs)
+            {
+                b.release();
+            }
+        }
+        env->replicas.clear();
+        env->committed = false;
+    }
+
+    template <class T>
+    void sort_by_min_distance(std::vector<T> &v)
+    {
+        // environment.hh:40-66
+        std::stable_sort(v.begin(), v.end(), [](const T &a, const T &b) { return a.min_d < b.min_d; });
+    }
+
+    // float4 records in the order vb_env.cuh documents
+    std::vector<float4> pack_records(const vb_env *e)
+    {
+        std::vector<float4> q;
+        for (const auto &s : e->spheres)
+        {
+            q.push_back(make_float4(s.x, s.y, s.z, s.r));
+            q.push_back(make_float4(s.min_d, 0.f, 0.f, 0.f));
+        }
+        for (const auto &c : e->capsules)
+        {
+            q.push_back(make_float4(c.c[0], c.c[1], c.c[2], c.c[6]));
+            q.push_back(make_float4(c.c[3], c.c[4], c.c[5], c.c[7]));
+            q.push_back(make_float4(c.min_d, 0.f, 0.f, 0.f));
+        }
+        for (const auto &c : e->zcapsules)
+        {
+            q.push_back(make_float4(c.c[0], c.c[1], c.c[2], c.c[6]));
+            q.push_back(make_float4(c.c[5], c.c[7], c.min_d, 0.f));
+        }
+        for (const auto &c : e->cuboids)
+        {
+            q.push_back(make_float4(c.c[0], c.c[1], c.c[2], c.min_d));
+            q.push_back(make_float4(c.c[3], c.c[4], c.c[5], c.c[12]));
+            q.push_back(make_float4(c.c[6], c.c[7], c.c[8], c.c[13]));
+            q.push_back(make_float4(c.c[9], c.c[10], c.c[11], c.c[14]));
+        }
+        for (const auto &c : e->zcuboids)
+        {
+            q.push_back(make_float4(c.c[0], c.c[1], c.c[2], c.min_d));
+            q.push_back(make_float4(c.c[3], c.c[4], c.c[6], c.c[7]));
+            q.push_back(make_float4(c.c[12], c.c[13], c.c[14], 0.f));
+        }
+        return q;
+    }
+}  // namespace
+
+extern "C" {
+
+int vb_env_create(vb_ctx *ctx, vb_env **out)
+{
+    if (!ctx || !out)
+    {
+        return fail(VB_ERR_ARG, "vb_env_create: null argument");
+    }
+    *out = new vb_env();
+    (*out)->ctx = ctx;
+    return VB_OK;
+}
+
+void vb_env_destroy(vb_env *env)
+{
+    if (env)
+    {
+        release_replicas(env);
+        delete env;
+    }
+}
+
+int vb_env_clear(vb_env *env)
+{
+    if (!env)
+    {
+        return fail(VB_ERR_ARG, "null environment");
+    }
+    vb_ctx *ctx = env->ctx;
+    release_replicas(env);
+    *env = vb_env();
+    env->ctx = ctx;
+    return VB_OK;
+}
+
+int vb_env_add_sphere(vb_env *env, float x, float y, float z, float r)
+{
+    if (!env)
+    {
+        return fail(VB_ERR_ARG, "null environment");
+    }
+    // shapes.hh:236-239
+    env->spheres.push_back({x, y, z, r, std::sqrt(x * x + y * y + z * z) - r});
+    sort_by_min_distance(env->spheres);
+    env->committed = false;
+    return VB_OK;
+}
+
+int vb_env_add_cuboid(vb_env *env, const float *c)
+{
+    if (!env || !c)
+    {
+        return fail(VB_ERR_ARG, "vb_env_add_cuboid: null argument");
+    }
+    HostCuboid h;
+    std::copy_n(c, 15, h.c);
+    h.min_d = cuboid_min_distance(c);
+    // bindings/environment.cc:120-127
+    auto &list = (c[11] == 1.f) ? env->zcuboids : env->cuboids;
+    list.push_back(h);
+    sort_by_min_distance(list);
+    env->committed = false;
+    return VB_OK;
+}
+
+int vb_env_add_capsule(vb_env *env, const float *c)
+{
+    if (!env || !c)
+    {
+        return fail(VB_ERR_ARG, "vb_env_add_capsule: null argument");
+    }
+    HostCapsule h;
+    std::copy_n(c, 8, h.c);
+    h.min_d = capsule_min_distance(c);
+    // bindings/environment.cc:134-141
+    auto &list = (c[3] == 0.f && c[4] == 0.f) ? env->zcapsules : env->capsules;
+    list.push_back(h);
+    sort_by_min_distance(list);
+    env->committed = false;
+    return VB_OK;
+}
+
+int vb_env_add_heightfield(vb_env *env, const float *off_scale, size_t xd, size_t yd, const float *data)
+{
+    if (!env || !off_scale || !data || xd == 0 || yd == 0)
+    {
+        return fail(VB_ERR_ARG, "vb_env_add_heightfield: bad arguments");
+    }
+    HostHeightField h;
+    std::copy_n(off_scale, 6, h.os);
+    h.xd = xd;
+    h.yd = yd;
+    h.data.assign(data, data + xd * yd);
+    env->heightfields.push_back(std::move(h));
+    env->committed = false;
+    return VB_OK;
+}
+
+int vb_env_add_capt(vb_env *env, const float *tests, size_t n_tests, const uint32_t *aff_starts, const float *aff_x,
+                    const float *aff_y, const float *aff_z, size_t n_aff_vec, const float *aabbs, size_t n_aabbs,
+                    const float *aabb_top, float r_point, int nlog2)
+{
+    if (!env || !aff_starts || !aabbs || !aabb_top || nlog2 < 0 || nlog2 > 30 || (n_tests && !tests) ||
+        (n_aff_vec && (!aff_x || !aff_y || !aff_z)))
+    {
+        return fail(VB_ERR_ARG, "vb_env_add_capt: bad arguments");
+    }
+    const size_t leaves = size_t(1) << nlog2;
+    if (n_tests != leaves - 1 || n_aabbs != leaves)
+    {
+        return fail(VB_ERR_ARG, "vb_env_add_capt: nlog2=%d needs %zu tests and %zu aabbs (got %zu, %zu)", nlog2,
+                    leaves - 1, leaves, n_tests, n_aabbs);
+    }
+    if (aff_starts[leaves] > n_aff_vec)
+    {
+        return fail(VB_ERR_ARG, "vb_env_add_capt: aff_starts end %u exceeds %zu affordance vectors",
+                    aff_starts[leaves], n_aff_vec);
+    }
+    HostCapt h;
+    h.tests.assign(tests, tests + n_tests);
+    h.aabbs.assign(aabbs, aabbs + 6 * n_aabbs);
+    h.aff_starts.assign(aff_starts, aff_starts + leaves + 1);
+    h.aff.resize(24 * n_aff_vec);
+    for (size_t i = 0; i < n_aff_vec; ++i)
+    {
+        std::copy_n(aff_x + 8 * i, 8, h.aff.data() + 24 * i);
+        std::copy_n(aff_y + 8 * i, 8, h.aff.data() + 24 * i + 8);
+        std::copy_n(aff_z + 8 * i, 8, h.aff.data() + 24 * i + 16);
+    }
+    std::copy_n(aabb_top, 6, h.top);
+    h.r_point = r_point;
+    h.nlog2 = nlog2;
+    env->capts.push_back(std::move(h));
+    env->committed = false;
+    return VB_OK;
+}
+
+int vb_env_set_attachment(vb_env *env, const float *tf, const float *spheres, size_t n)
+{
+    if (!env || !tf || (n && !spheres) || n > static_cast<size_t>(vb::kMaxAttach))
+    {
+        return fail(VB_ERR_ARG, "vb_env_set_attachment: bad arguments (at most %d spheres)", vb::kMaxAttach);
+    }
+    std::copy_n(tf, 7, env->att_tf);
+    env->att_spheres.clear();
+    for (size_t i = 0; i < n; ++i)
+    {
+        env->att_spheres.push_back(make_float4(spheres[4 * i], spheres[4 * i + 1], spheres[4 * i + 2], spheres[4 * i + 3]));
+    }
+    env->has_attachment = true;
+    env->committed = false;
+    return VB_OK;
+}
+
+int vb_env_clear_attachment(vb_env *env)
+{
+    if (!env)
+    {
+        return fail(VB_ERR_ARG, "null environment");
+    }
+    env->has_attachment = false;
+    env->att_spheres.clear();
+    env->committed = false;
+    return VB_OK;
+}
+
+int vb_env_export(const vb_env *env, int kind, float *out, size_t *n)
+{
+    if (!env || !n || kind < 0 || kind > 4)
+    {
+        return fail(VB_ERR_ARG, "vb_env_export: bad arguments");
+    }
+    if (kind == 0)
+    {
+        *n = env->spheres.size();
+        for (size_t i = 0; out && i < *n; ++i)
+        {
+            const auto &s = env->spheres[i];
+            const float row[5] = {s.x, s.y, s.z, s.r, s.min_d};
+            std::copy_n(row, 5, out + 5 * i);
+        }
+    }
+    else if (kind <= 2)
+    {
+        const auto &v = kind == 1 ? env->capsules : env->zcapsules;
+        *n = v.size();
+        for (size_t i = 0; out && i < *n; ++i)
+        {
+            std::copy_n(v[i].c, 8, out + 9 * i);
+            out[9 * i + 8] = v[i].min_d;
+        }
+    }
+    else
+    {
+        const auto &v = kind == 3 ? env->cuboids : env->zcuboids;
+        *n = v.size();
+        for (size_t i = 0; out && i < *n; ++i)
+        {
+            std::copy_n(v[i].c, 15, out + 16 * i);
+            out[16 * i + 15] = v[i].min_d;
+        }
+    }
+    return VB_OK;
+}
+
+}  // extern "C"
+
+/* ================================ commit (upload) ============================================= */
+namespace
+{
+    template <class T>
+    int upload(DevBuf &buf, const std::vector<T> &host, cudaStream_t stream)
+    {
+        VB_CUDA(buf.reserve(std::max<size_t>(host.size() * sizeof(T), 16)));
+        if (!host.empty())
+        {
+            VB_CUDA(cudaMemcpyAsync(buf.p, host.data(), host.size() * sizeof(T), cudaMemcpyHostToDevice, stream));
+        }
+        return VB_OK;
+    }
+
+    int commit_replica(vb_env *env, Slot &slot, Replica &rep)
+    {
+        VB_CUDA(cudaSetDevice(slot.device));
+        const std::vector<float4> recs = pack_records(env);
+        VB_TRY(upload(rep.prims, recs, slot.stream));
+        vb::EnvView &v = rep.view;
+        v = vb::EnvView{};
+        v.prims = rep.prims.as<float4>();
+        v.n_quads = static_cast<int>(recs.size());
+        v.n_spheres = static_cast<int>(env->spheres.size());
+        v.n_capsules = static_cast<int>(env->capsules.size());
+        v.n_zcapsules = static_cast<int>(env->zcapsules.size());
+        v.n_cuboids = static_cast<int>(env->cuboids.size());
+        v.n_zcuboids = static_cast<int>(env->zcuboids.size());
+
+        rep.blobs.clear();
+        std::vector<vb::HeightFieldView> hfs;
+        for (const auto &h : env->heightfields)
+        {
+            // the reference clamps the cell index to [0, xd] x [0, yd] (sphere_heightfield.hh:18-21), one
+            // past the last row/column; pad so the same cell arithmetic stays inside the allocation
+            std::vector<float> padded(h.data);
+            padded.resize(h.data.size() + h.xd + 2, 0.f);
+            rep.blobs.emplace_back();
+            VB_TRY(upload(rep.blobs.back(), padded, slot.stream));
+            vb::HeightFieldView hv{};
+            hv.x = h.os[0];
+            hv.y = h.os[1];
+            hv.z = h.os[2];
+            hv.xs = h.os[3];
+            hv.ys = h.os[4];
+            hv.zs = h.os[5];
+            hv.xd2 = static_cast<float>(h.xd / 2);
+            hv.yd2 = static_cast<float>(h.yd / 2);
+            hv.xdf = static_cast<float>(h.xd);
+            hv.ydf = static_cast<float>(h.yd);
+            hv.xd = static_cast<int>(h.xd);
+            hv.data = rep.blobs.back().as<float>();
+            hfs.push_back(hv);
+        }
+        VB_TRY(upload(rep.hf_desc, hfs, slot.stream));
+        v.n_heightfields = static_cast<int>(hfs.size());
+        v.heightfields = rep.hf_desc.as<vb::HeightFieldView>();
+
+        std::vector<vb::CaptView> cvs;
+        for (const auto &c : env->capts)
+        {
+            vb::CaptView cv{};
+            rep.blobs.emplace_back();
+            VB_TRY(upload(rep.blobs.back(), c.tests, slot.stream));
+            cv.tests = rep.blobs.back().as<float>();
+            rep.blobs.emplace_back();
+            VB_TRY(upload(rep.blobs.back(), c.aff_starts, slot.stream));
+            cv.aff_starts = rep.blobs.back().as<uint32_t>();
+            rep.blobs.emplace_back();
+            VB_TRY(upload(rep.blobs.back(), c.aff, slot.stream));
+            cv.aff = rep.blobs.back().as<float4>();
+            rep.blobs.emplace_back();
+            VB_TRY(upload(rep.blobs.back(), c.aabbs, slot.stream));
+            cv.aabbs = rep.blobs.back().as<float>();
+            std::copy_n(c.top, 6, cv.top);
+            cv.r_point = c.r_point;
+            cv.n_tests = static_cast<uint32_t>(c.tests.size());
+            cv.nlog2 = c.nlog2;
+            cvs.push_back(cv);
+        }
+        VB_TRY(upload(rep.capt_desc, cvs, slot.stream));
+        v.n_capts = static_cast<int>(cvs.size());
+        v.capts = rep.capt_desc.as<vb::CaptView>();
+
+        VB_TRY(upload(rep.att_local, env->att_spheres, slot.stream));
+        std::copy_n(env->att_tf, 7, v.attach.tf);
+        v.attach.n = env->has_attachment ? static_cast<int>(env->att_spheres.size()) : 0;
+        v.attach.local = rep.att_local.as<float4>();
+        VB_CUDA(cudaStreamSynchronize(slot.stream));
+        return VB_OK;
+    }
+}  // namespace
+
+extern "C" int vb_env_commit(vb_env *env)
+{
+    if (!env)
+    {
+        return fail(VB_ERR_ARG, "null environment");
+    }
+    release_replicas(env);
+    env->replicas.resize(env->ctx->slots.size());
+    for (size_t i = 0; i < env->replicas.size(); ++i)
+    {
+        VB_TRY(commit_replica(env, env->ctx->slots[i], env->replicas[i]));
+    }
+    env->committed = true;
+    ++env->version;
+    return VB_OK;
+}
+
+/* ================================ queries ===================================================== */
+#include <cub/device/device_scan.cuh>
+
+namespace
+{
+    // verdict words preset to "valid" for the first n bits (edge verdicts are AND-reduced into them)
+    __global__ void fill_bits_kernel(uint32_t *bits, size_t n)
+    {
+        const size_t w = static_cast<size_t>(blockIdx.x) * blockDim.x + threadIdx.x;
+        const size_t n_words = (n + 31) / 32;
+        if (w < n_words)
+        {
+            const size_t rem = n - w * 32;
+            bits[w] = rem >= 32 ? 0xffffffffu : ((1u << rem) - 1u);
+        }
+    }
+
+    __global__ void fill_float_kernel(float *p, size_t n, float v)
+    {
+        const size_t i = static_cast<size_t>(blockIdx.x) * blockDim.x + threadIdx.x;
+        if (i < n)
+        {
+            p[i] = v;
+        }
+    }
+
+    __global__ void popcount_kernel(const uint32_t *bits, size_t n, unsigned long long *out)
+    {
+        const size_t n_words = (n + 31) / 32;
+        unsigned long long local = 0;
+        for (size_t w = static_cast<size_t>(blockIdx.x) * blockDim.x + threadIdx.x; w < n_words;
+             w += static_cast<size_t>(gridDim.x) * blockDim.x)
+        {
+            uint32_t v = bits[w];
+            const size_t rem = n - w * 32;
+            if (rem < 32)
+            {
+                v &= (1u << rem) - 1u;
+            }
+            local += __popc(v);
+        }
+        for (int o = 16; o > 0; o >>= 1)
+        {
+            local += __shfl_down_sync(0xffffffffu, local, o);
+        }
+        if ((threadIdx.x & 31) == 0 && local)
+        {
+            atomicAdd(out, local);
+        }
+    }
+
+    struct Query
+    {
+        vb_ctx *ctx;
+        Slot *slot;
+        const vb::RobotOps *ops;
+        vb::LaunchArgs args;
+    };
+
+    int begin_query(vb_ctx *ctx, int slot, vb_robot robot, const float *base, const vb_env *env, Query &q)
+    {
+        VB_TRY(check_slot(ctx, slot));
+        q.ctx = ctx;
+        q.slot = &ctx->slots[slot];
+        q.ops = ops_of(robot);
+        if (!q.ops)
+        {
+            return fail(VB_ERR_ARG, "unknown robot id %d", static_cast<int>(robot));
+        }
+        q.args = vb::LaunchArgs{};
+        if (env)
+        {
+            if (env->ctx != ctx)
+            {
+                return fail(VB_ERR_ARG, "environment belongs to another context");
+            }
+            if (!env->committed)
+            {
+                return fail(VB_ERR_STATE, "environment changed since the last vb_env_commit");
+            }
+            q.args.env = env->replicas[slot].view;
+        }
+        for (int k = 0; k < 3; ++k)
+        {
+            q.args.base[k] = base ? base[k] : 0.f;
+        }
+        q.args.sphere_radius = ctx->sphere_radius;
+        q.args.attach = (q.ops->has_attach && q.args.env.attach.n > 0) ? 1 : 0;
+        q.args.stream = q.slot->stream;
+        VB_CUDA(cudaSetDevice(q.slot->device));
+        return VB_OK;
+    }
+
+    // persistent grid: resident CTAs per SM x SM count, never more CTAs than there is work
+    int grid_for(const Query &q, size_t items, int *grid)
+    {
+        int blocks = 0, threads = 0;
+        VB_CUDA(q.ops->occupancy(q.args, &blocks, &threads));
+        if (blocks < 1)
+        {
+            return fail(VB_ERR_CUDA, "%s: environment does not fit one CTA's shared memory", q.ops->name);
+        }
+        const size_t need = (items + threads - 1) / threads;
+        *grid = static_cast<int>(std::max<size_t>(1, std::min<size_t>(need, static_cast<size_t>(blocks) * q.slot->sm_count)));
+        return VB_OK;
+    }
+
+    int run_fkcc_d(Query &q, const float *cfg_d, size_t n, uint32_t *bits_d, float *margin_d)
+    {
+        if (n == 0)
+        {
+            return VB_OK;
+        }
+        q.args.cfg = cfg_d;
+        q.args.n = n;
+        q.args.bits = bits_d;
+        q.args.margin = margin_d;
+        int grid = 1;
+        VB_TRY(grid_for(q, n, &grid));
+        VB_CUDA(q.ops->fkcc(q.args, margin_d != nullptr, grid));
+        q.ctx->launches += 1;
+        return VB_OK;
+    }
+
+    int run_motion_d(Query &q, const float *a_d, const float *b_d, size_t n, int resolution, uint32_t *bits_d,
+                     float *margin_d)
+    {
+        if (n == 0)
+        {
+            return VB_OK;
+        }
+        if (n >= (size_t(1) << 31))
+        {
+            return fail(VB_ERR_ARG, "at most 2^31 edges per call");
+        }
+        Slot &s = *q.slot;
+        q.args.cfg = a_d;
+        q.args.cfg_b = b_d;
+        q.args.n = n;
+        q.args.bits = bits_d;
+        q.args.margin = margin_d;
+        q.args.resolution = resolution > 0 ? resolution : q.ops->resolution;
+        // interpolants per edge -> exclusive prefix (prefix[n] = total, read by the kernel itself)
+        VB_CUDA(s.counts.reserve((n + 1) * sizeof(uint32_t)));
+        VB_CUDA(s.prefix.reserve((n + 1) * sizeof(uint32_t)));
+        VB_CUDA(cudaMemsetAsync(s.counts.as<uint32_t>() + n, 0, sizeof(uint32_t), s.stream));
+        VB_CUDA(q.ops->edge_count(q.args, s.counts.as<uint32_t>()));
+        size_t tmp_bytes = 0;
+        VB_CUDA(cub::DeviceScan::ExclusiveSum(nullptr, tmp_bytes, s.counts.as<uint32_t>(), s.prefix.as<uint32_t>(),
+                                              static_cast<int>(n + 1), s.stream));
+        VB_CUDA(s.scan_tmp.reserve(tmp_bytes));
+        VB_CUDA(cub::DeviceScan::ExclusiveSum(s.scan_tmp.p, tmp_bytes, s.counts.as<uint32_t>(),
+                                              s.prefix.as<uint32_t>(), static_cast<int>(n + 1), s.stream));
+        q.args.prefix = s.prefix.as<uint32_t>();
+        const unsigned fill_grid = static_cast<unsigned>(((n + 31) / 32 + 255) / 256);
+        fill_bits_kernel<<<fill_grid, 256, 0, s.stream>>>(bits_d, n);
+        if (margin_d)
+        {
+            fill_float_kernel<<<static_cast<unsigned>((n + 255) / 256), 256, 0, s.stream>>>(margin_d, n, 3.0e38f);
+        }
+        int grid = 1;
+        // at least 8 interpolants per edge; the exact total stays on the device
+        VB_TRY(grid_for(q, n * 8 * 4, &grid));
+        VB_CUDA(q.ops->motion(q.args, margin_d != nullptr, grid));
+        q.ctx->launches += 4 + (margin_d ? 1 : 0);
+        return VB_OK;
+    }
+
+    struct Shard
+    {
+        size_t lo, hi;
+    };
+
+    // contiguous index ranges, boundaries on multiples of 32 so verdict words are never shared
+    std::vector<Shard> shards_of(size_t n, size_t n_slots)
+    {
+        std::vector<Shard> out;
+        const size_t per = ((n + n_slots - 1) / n_slots + 31) / 32 * 32;
+        for (size_t i = 0; i < n_slots; ++i)
+        {
+            const size_t lo = std::min(n, i * per), hi = std::min(n, lo + per);
+            out.push_back({lo, hi});
+        }
+        return out;
+    }
+}  // namespace
+
+extern "C" {
+
+int vb_dev_alloc(vb_ctx *ctx, int slot, size_t bytes, void **ptr_d)
+{
+    VB_TRY(check_slot(ctx, slot));
+    if (!ptr_d)
+    {
+        return fail(VB_ERR_ARG, "null pointer");
+    }
+    VB_CUDA(cudaSetDevice(ctx->slots[slot].device));
+    VB_CUDA(cudaMalloc(ptr_d, std::max<size_t>(bytes, 16)));
+    return VB_OK;
+}
+
+int vb_dev_free(vb_ctx *ctx, int slot, void *ptr_d)
+{
+    VB_TRY(check_slot(ctx, slot));
+    VB_CUDA(cudaSetDevice(ctx->slots[slot].device));
+    VB_CUDA(cudaFree(ptr_d));
+    return VB_OK;
+}
+
+int vb_dev_upload(vb_ctx *ctx, int slot, void *dst_d, const void *src, size_t bytes)
+{
+    VB_TRY(check_slot(ctx, slot));
+    VB_CUDA(cudaSetDevice(ctx->slots[slot].device));
+    VB_CUDA(cudaMemcpyAsync(dst_d, src, bytes, cudaMemcpyHostToDevice, ctx->slots[slot].stream));
+    return VB_OK;
+}
+
+int vb_dev_download(vb_ctx *ctx, int slot, void *dst, const void *src_d, size_t bytes)
+{
+    VB_TRY(check_slot(ctx, slot));
+    VB_CUDA(cudaSetDevice(ctx->slots[slot].device));
+    VB_CUDA(cudaMemcpyAsync(dst, src_d, bytes, cudaMemcpyDeviceToHost, ctx->slots[slot].stream));
+    VB_CUDA(cudaStreamSynchronize(ctx->slots[slot].stream));
+    return VB_OK;
+}
+
+int vb_timer_start(vb_ctx *ctx, int slot)
+{
+    VB_TRY(check_slot(ctx, slot));
+    VB_CUDA(cudaSetDevice(ctx->slots[slot].device));
+    VB_CUDA(cudaEventRecord(ctx->slots[slot].ev0, ctx->slots[slot].stream));
+    return VB_OK;
+}
+
+int vb_timer_stop(vb_ctx *ctx, int slot, double *milliseconds)
+{
+    VB_TRY(check_slot(ctx, slot));
+    Slot &s = ctx->slots[slot];
+    VB_CUDA(cudaSetDevice(s.device));
+    VB_CUDA(cudaEventRecord(s.ev1, s.stream));
+    VB_CUDA(cudaEventSynchronize(s.ev1));
+    float ms = 0.f;
+    VB_CUDA(cudaEventElapsedTime(&ms, s.ev0, s.ev1));
+    if (milliseconds)
+    {
+        *milliseconds = ms;
+    }
+    return VB_OK;
+}
+
+int vb_popcount_d(vb_ctx *ctx, int slot, const uint32_t *bits_d, size_t n, uint64_t *count)
+{
+    VB_TRY(check_slot(ctx, slot));
+    Slot &s = ctx->slots[slot];
+    VB_CUDA(cudaSetDevice(s.device));
+    VB_CUDA(s.scan_tmp.reserve(sizeof(unsigned long long)));
+    VB_CUDA(cudaMemsetAsync(s.scan_tmp.p, 0, sizeof(unsigned long long), s.stream));
+    popcount_kernel<<<s.sm_count * 4, 256, 0, s.stream>>>(bits_d, n, s.scan_tmp.as<unsigned long long>());
+    VB_CUDA(cudaGetLastError());
+    ctx->launches += 1;
+    unsigned long long host = 0;
+    VB_CUDA(cudaMemcpyAsync(&host, s.scan_tmp.p, sizeof(host), cudaMemcpyDeviceToHost, s.stream));
+    VB_CUDA(cudaStreamSynchronize(s.stream));
+    if (count)
+    {
+        *count = host;
+    }
+    return VB_OK;
+}
+
+int vb_fkcc_d(vb_ctx *ctx, int slot, vb_robot robot, const float *base, const vb_env *env, const float *configs_d,
+              size_t n, uint32_t *valid_bits_d, float *margin_d)
+{
+    if (!env || (n && (!configs_d || !valid_bits_d)))
+    {
+        return fail(VB_ERR_ARG, "vb_fkcc_d: null argument");
+    }
+    Query q;
+    VB_TRY(begin_query(ctx, slot, robot, base, env, q));
+    return run_fkcc_d(q, configs_d, n, valid_bits_d, margin_d);
+}
+
+int vb_validate_motion_d(vb_ctx *ctx, int slot, vb_robot robot, const float *base, const vb_env *env,
+                         const float *starts_d, const float *goals_d, size_t n, int resolution,
+                         uint32_t *valid_bits_d, float *margin_d)
+{
+    if (!env || (n && (!starts_d || !goals_d || !valid_bits_d)))
+    {
+        return fail(VB_ERR_ARG, "vb_validate_motion_d: null argument");
+    }
+    Query q;
+    VB_TRY(begin_query(ctx, slot, robot, base, env, q));
+    return run_motion_d(q, starts_d, goals_d, n, resolution, valid_bits_d, margin_d);
+}
+
+int vb_fkcc_random_d(vb_ctx *ctx, int slot, vb_robot robot, const float *base, const vb_env *env, uint64_t seed,
+                     uint64_t first, size_t n, uint32_t *valid_bits_d)
+{
+    if (!env || (n && !valid_bits_d))
+    {
+        return fail(VB_ERR_ARG, "vb_fkcc_random_d: null argument");
+    }
+    Query q;
+    VB_TRY(begin_query(ctx, slot, robot, base, env, q));
+    if (n == 0)
+    {
+        return VB_OK;
+    }
+    q.args.n = n;
+    q.args.seed = seed;
+    q.args.bits = valid_bits_d;
+    int grid = 1;
+    VB_TRY(grid_for(q, n, &grid));
+    VB_CUDA(q.ops->fkcc_random(q.args, first, grid));
+    ctx->launches += 1;
+    return VB_OK;
+}
+
+/* ---- host-buffer entry points: shard -> H2D -> kernels -> D2H of the verdict words ---------- */
+int vb_sphere_fk(vb_ctx *ctx, vb_robot robot, const float *base, const float *configs, size_t n, float *spheres)
+{
+    if (!ctx || (n && (!configs || !spheres)))
+    {
+        return fail(VB_ERR_ARG, "vb_sphere_fk: null argument");
+    }
+    const vb::RobotOps *ops = ops_of(robot);
+    if (!ops)
+    {
+        return fail(VB_ERR_ARG, "unknown robot id %d", static_cast<int>(robot));
+    }
+    const auto shards = shards_of(n, ctx->slots.size());
+    for (size_t i = 0; i < shards.size(); ++i)
+    {
+        const size_t m = shards[i].hi - shards[i].lo;
+        if (m == 0)
+        {
+            continue;
+        }
+        Query q;
+        VB_TRY(begin_query(ctx, static_cast<int>(i), robot, base, nullptr, q));
+        Slot &s = *q.slot;
+        const size_t out_floats = m * ops->n_spheres * 4;
+        VB_CUDA(s.in_a.reserve(m * ops->dim * sizeof(float)));
+        VB_CUDA(s.out.reserve(out_floats * sizeof(float)));
+        VB_CUDA(cudaMemcpyAsync(s.in_a.p, configs + shards[i].lo * ops->dim, m * ops->dim * sizeof(float),
+                                cudaMemcpyHostToDevice, s.stream));
+        q.args.cfg = s.in_a.as<float>();
+        q.args.n = m;
+        q.args.spheres = s.out.as<float>();
+        VB_CUDA(ops->sphere_fk(q.args));
+        ctx->launches += 1;
+        VB_CUDA(cudaMemcpyAsync(spheres + shards[i].lo * ops->n_spheres * 4, s.out.p, out_floats * sizeof(float),
+                                cudaMemcpyDeviceToHost, s.stream));
+    }
+    return vb_sync(ctx);
+}
+
+static int fkcc_host(vb_ctx *ctx, vb_robot robot, const float *base, const vb_env *env, const float *configs, size_t n,
+                     uint32_t *valid_bits, float *margin, bool limits)
+{
+    if (!ctx || !env || (n && (!configs || !valid_bits)))
+    {
+        return fail(VB_ERR_ARG, "vb_fkcc: null argument");
+    }
+    const vb::RobotOps *ops = ops_of(robot);
+    if (!ops)
+    {
+        return fail(VB_ERR_ARG, "unknown robot id %d", static_cast<int>(robot));
+    }
+    const auto shards = shards_of(n, ctx->slots.size());
+    for (size_t i = 0; i < shards.size(); ++i)
+    {
+        const size_t m = shards[i].hi - shards[i].lo;
+        if (m == 0)
+        {
+            continue;
+        }
+        Query q;
+        VB_TRY(begin_query(ctx, static_cast<int>(i), robot, base, env, q));
+        Slot &s = *q.slot;
+        const size_t words = (m + 31) / 32;
+        VB_CUDA(s.in_a.reserve(m * ops->dim * sizeof(float)));
+        VB_CUDA(s.bits.reserve(words * sizeof(uint32_t)));
+        if (margin)
+        {
+            VB_CUDA(s.margin.reserve(m * sizeof(float)));
+        }
+        VB_CUDA(cudaMemcpyAsync(s.in_a.p, configs + shards[i].lo * ops->dim, m * ops->dim * sizeof(float),
+                                cudaMemcpyHostToDevice, s.stream));
+        VB_TRY(run_fkcc_d(q, s.in_a.as<float>(), m, s.bits.as<uint32_t>(), margin ? s.margin.as<float>() : nullptr));
+        if (limits)
+        {
+            VB_CUDA(ops->limits(q.args));
+            ctx->launches += 1;
+        }
+        VB_CUDA(cudaMemcpyAsync(valid_bits + shards[i].lo / 32, s.bits.p, words * sizeof(uint32_t),
+                                cudaMemcpyDeviceToHost, s.stream));
+        if (margin)
+        {
+            VB_CUDA(cudaMemcpyAsync(margin + shards[i].lo, s.margin.p, m * sizeof(float), cudaMemcpyDeviceToHost,
+                                    s.stream));
+        }
+    }
+    return vb_sync(ctx);
+}
+
+int vb_fkcc(vb_ctx *ctx, vb_robot robot, const float *base, const vb_env *env, const float *configs, size_t n,
+            uint32_t *valid_bits, float *margin_or_null)
+{
+    return fkcc_host(ctx, robot, base, env, configs, n, valid_bits, margin_or_null, false);
+}
+
+int vb_validate(vb_ctx *ctx, vb_robot robot, const float *base, const vb_env *env, const float *configs, size_t n,
+                uint32_t *valid_bits)
+{
+    return fkcc_host(ctx, robot, base, env, configs, n, valid_bits, nullptr, true);
+}
+
+int vb_validate_motion(vb_ctx *ctx, vb_robot robot, const float *base, const vb_env *env, const float *starts,
+                       const float *goals, size_t n, int resolution, uint32_t *valid_bits, float *margin)
+{
+    if (!ctx || !env || (n && (!starts || !goals || !valid_bits)))
+    {
+        return fail(VB_ERR_ARG, "vb_validate_motion: null argument");
+    }
+    const vb::RobotOps *ops = ops_of(robot);
+    if (!ops)
+    {
+        return fail(VB_ERR_ARG, "unknown robot id %d", static_cast<int>(robot));
+    }
+    const auto shards = shards_of(n, ctx->slots.size());
+    for (size_t i = 0; i < shards.size(); ++i)
+    {
+        const size_t m = shards[i].hi - shards[i].lo;
+        if (m == 0)
+        {
+            continue;
+        }
+        Query q;
+        VB_TRY(begin_query(ctx, static_cast<int>(i), robot, base, env, q));
+        Slot &s = *q.slot;
+        const size_t words = (m + 31) / 32, bytes = m * ops->dim * sizeof(float);
+        VB_CUDA(s.in_a.reserve(bytes));
+        VB_CUDA(s.in_b.reserve(bytes));
+        VB_CUDA(s.bits.reserve(words * sizeof(uint32_t)));
+        if (margin)
+        {
+            VB_CUDA(s.margin.reserve(m * sizeof(float)));
+        }
+        VB_CUDA(cudaMemcpyAsync(s.in_a.p, starts + shards[i].lo * ops->dim, bytes, cudaMemcpyHostToDevice, s.stream));
+        VB_CUDA(cudaMemcpyAsync(s.in_b.p, goals + shards[i].lo * ops->dim, bytes, cudaMemcpyHostToDevice, s.stream));
+        VB_TRY(run_motion_d(q, s.in_a.as<float>(), s.in_b.as<float>(), m, resolution, s.bits.as<uint32_t>(),
+                            margin ? s.margin.as<float>() : nullptr));
+        VB_CUDA(cudaMemcpyAsync(valid_bits + shards[i].lo / 32, s.bits.p, words * sizeof(uint32_t),
+                                cudaMemcpyDeviceToHost, s.stream));
+        if (margin)
+        {
+            VB_CUDA(cudaMemcpyAsync(margin + shards[i].lo, s.margin.p, m * sizeof(float), cudaMemcpyDeviceToHost,
+                                    s.stream));
+        }
+    }
+    return vb_sync(ctx);
+}
+
+int vb_validate_pairs(vb_ctx *, vb_robot, const float *, vb_robot, const float *, const vb_env *, const float *,
+                      const float *, size_t, uint32_t *)
+{
+    return fail(VB_ERR_STATE, "vb_validate_pairs: not built in this version");
+}
+
+int vb_random_edge(vb_robot r, uint64_t seed, uint64_t index, float len_lo, float len_hi, float *a, float *b)
+{
+    const vb::RobotOps *o = ops_of(r);
+    if (!o || !a || !b)
+    {
+        return fail(VB_ERR_ARG, "vb_random_edge: bad arguments");
+    }
+    // a = config(2 index); direction ~ normalised uniform cube sample; length uniform in [len_lo, len_hi];
+    // b clipped to the joint ranges ("RRTC-shaped" edges)
+    o->random_config(seed, 2 * index, a);
+    float dir[16], norm = 0.f;
+    for (int j = 0; j < o->dim; ++j)
+    {
+        dir[j] = 2.f * vb::u01(seed ^ 0xED6Eull, index, j) - 1.f;
+        norm += dir[j] * dir[j];
+    }
+    norm = std::sqrt(std::max(norm, 1e-12f));
+    const float len = len_lo + vb::u01(seed ^ 0xED6Eull, index, 63) * (len_hi - len_lo);
+    for (int j = 0; j < o->dim; ++j)
+    {
+        const float v = a[j] + len * dir[j] / norm;
+        b[j] = std::min(std::max(v, o->lo[j]), o->lo[j] + o->range[j]);
+    }
+    return VB_OK;
+}
+
+/* ---- multi-process gather -------------------------------------------------------------------- */
+int vb_comm_unique_id(void *id_bytes_128)
+{
+    if (!id_bytes_128)
+    {
+        return fail(VB_ERR_ARG, "null id buffer");
+    }
+    if (!nccl().ok)
+    {
+        return fail(VB_ERR_NCCL, "libnccl.so.2 could not be loaded");
+    }
+    static_assert(sizeof(ncclUniqueId) == 128, "ncclUniqueId is 128 bytes");
+    ncclUniqueId id;
+    VB_NCCL(nccl().GetUniqueId(&id));
+    std::memcpy(id_bytes_128, &id, sizeof(id));
+    return VB_OK;
+}
+
+int vb_comm_init(vb_ctx *ctx, int n_ranks, int rank, const void *id_bytes_128)
+{
+    if (!ctx || !id_bytes_128 || n_ranks < 1 || rank < 0 || rank >= n_ranks)
+    {
+        return fail(VB_ERR_ARG, "vb_comm_init: bad arguments");
+    }
+    if (!nccl().ok)
+    {
+        return fail(VB_ERR_NCCL, "libnccl.so.2 could not be loaded");
+    }
+    if (ctx->comm)
+    {
+        return fail(VB_ERR_STATE, "communicator already initialised");
+    }
+    ncclUniqueId id;
+    std::memcpy(&id, id_bytes_128, sizeof(id));
+    VB_CUDA(cudaSetDevice(ctx->slots[0].device));
+    VB_NCCL(nccl().CommInitRank(&ctx->comm, n_ranks, id, rank));
+    ctx->comm_ranks = n_ranks;
+    return VB_OK;
+}
+
+int vb_comm_allgather_bits_d(vb_ctx *ctx, const uint32_t *send_d, uint32_t *recv_d, size_t n_words)
+{
+    if (!ctx || !ctx->comm)
+    {
+        return fail(VB_ERR_STATE, "vb_comm_init has not been called");
+    }
+    VB_CUDA(cudaSetDevice(ctx->slots[0].device));
+    VB_NCCL(nccl().AllGather(send_d, recv_d, n_words, ncclUint32, ctx->comm, ctx->slots[0].stream));
+    return VB_OK;
+}
+
+int vb_comm_destroy(vb_ctx *ctx)
+{
+    if (ctx && ctx->comm)
+    {
+        VB_NCCL(nccl().CommDestroy(ctx->comm));
+        ctx->comm = nullptr;
+    }
+    return VB_OK;
+}
+
+}  // extern "C"

@@ -1,16 +1,17 @@
 // Kernel templates of the fkcc path, instantiated once per robot trace (see codegen/emit_cuda.py).
 //
-// One thread evaluates one configuration: the whole FK chain and every sphere centre of that
-// configuration live in that thread's registers (the trace is straight-line code), obstacles are
-// read as warp-uniform broadcasts from shared memory, and a warp ballot packs 32 verdicts into one
-// uint32 store.  Replaces Robot::fkcc / Robot::sphere_fk (robots/panda_base.hh:53-71 and the
+// One thread evaluates one configuration.  Phase A runs the robot's FK chain as straight-line
+// register code and parks every sphere centre the checks need in that thread's column of shared
+// memory; phase B walks the robot's constant-memory check tables (environment groups, self
+// collision groups, attachment groups) with ONE copy of the environment query, reading obstacles
+// as warp-uniform broadcasts from shared memory; a warp ballot packs 32 verdicts into one uint32.  Replaces Robot::fkcc / Robot::sphere_fk (robots/panda_base.hh:53-71 and the
 // per-robot equivalents) and planning::validate_motion (planning/validate.hh:23-75).
 #pragma once
-#include "vb_env.cuh"
+#include "vb_sinks.cuh"
+#include "vb_tables.cuh"
 
 namespace vb
 {
-    constexpr int kBlock = 128;           // threads per CTA
     constexpr int kMaxSharedQuads = 3072; // obstacle records staged in shared memory (48 KB)
 
     struct LaunchArgs
@@ -34,162 +35,203 @@ namespace vb
         cudaStream_t stream;
     };
 
-    // ---- policy handed to the generated traces -------------------------------------------------
-    template <class M>
-    struct CheckPolicy
+    // ---- geometry of one CTA ----------------------------------------------------------------------
+    template <class Robot>
+    constexpr int block_threads()
+    {
+        return Robot::kSlots <= 72 ? 128 : 64;
+    }
+
+    struct Scratch
+    {
+        const float4 *prims;  // obstacle records (shared or global)
+        float *col;           // this thread's slot column
+        int stride;
+    };
+
+    // dynamic shared memory: [n_quads float4 obstacle records][3 * n_slot_rows * blockDim floats]
+    VB_D Scratch stage_env(const EnvView &env)
+    {
+        extern __shared__ float4 smem[];
+        Scratch s;
+        const bool staged = env.n_quads <= kMaxSharedQuads;
+        const int nq = staged ? env.n_quads : 0;
+        if (staged)
+        {
+            for (int i = threadIdx.x; i < nq; i += blockDim.x)
+            {
+                smem[i] = env.prims[i];
+            }
+            __syncthreads();
+        }
+        s.prims = staged ? smem : env.prims;  // large scenes: L1/L2-resident broadcasts
+        s.col = reinterpret_cast<float *>(smem + nq) + threadIdx.x;
+        s.stride = blockDim.x;
+        return s;
+    }
+
+    // ---- the table walk: every collision test of one configuration -------------------------------
+    struct Center
+    {
+        float x, y, z, r;
+    };
+
+    struct TableCtx
     {
         const EnvView &env;
-        const float4 *prims;
-        float bx_, by_, bz_;
-        float radius;  // robots::sphere
-        M mg;
-        float4 posed[kMaxAttach];
-
-        VB_D CheckPolicy(const EnvView &e, const float4 *p, const float *base, float rad)
-          : env(e), prims(p), bx_(base[0]), by_(base[1]), bz_(base[2]), radius(rad)
+        Scratch sc;
+        float bx, by, bz, radius;
+        VB_D Center load(const SlotRef &ref) const
         {
-        }
-        VB_D float bx() const { return bx_; }
-        VB_D float by() const { return by_; }
-        VB_D float bz() const { return bz_; }
-        // `literal + base_*` is evaluated in double and narrowed, as the C++ expression is
-        VB_D float cbx(double c) const { return static_cast<float>(c + static_cast<double>(bx_)); }
-        VB_D float cby(double c) const { return static_cast<float>(c + static_cast<double>(by_)); }
-        VB_D float cbz(double c) const { return static_cast<float>(c + static_cast<double>(bz_)); }
-        VB_D void ops(int) {}
-
-        VB_D bool env_test(float x, float y, float z, float r) { return env_hit(env, prims, x, y, z, r, mg); }
-        // collision/validity.hh:13-44 + sphere_sphere.hh:9-23
-        VB_D bool self_test(float ax, float ay, float az, float ar, float bx, float by, float bz, float br)
-        {
-            const float dx = ax - bx, dy = ay - by, dz = az - bz, rs = ar + br;
-            const float v = dx * dx + dy * dy + dz * dz - rs * rs;
-            mg.sq(v, rs);
-            return v < 0.f;
-        }
-        // collision/attachments.hh:75-122
-        VB_D void attach_pose(float p_tx, float p_ty, float p_tz, float p_rx, float p_ry, float p_rz, float p_rw)
-        {
-            const float *t = env.attach.tf;
-            const float tf_tx = t[0], tf_ty = t[1], tf_tz = t[2], tf_rx = t[3], tf_ry = t[4], tf_rz = t[5], tf_rw = t[6];
-            const float rx = p_rw * tf_rx + p_rx * tf_rw + p_ry * tf_rz - p_rz * tf_ry;
-            const float ry = p_rw * tf_ry - p_rx * tf_rz + p_ry * tf_rw + p_rz * tf_rx;
-            const float rz = p_rw * tf_rz + p_rx * tf_ry - p_ry * tf_rx + p_rz * tf_rw;
-            const float rw = p_rw * tf_rw - p_rx * tf_rx - p_ry * tf_ry - p_rz * tf_rz;
-            const float x0 = p_ry * tf_tz - p_rz * tf_ty;
-            const float x1 = p_rx * tf_ty - p_ry * tf_tx;
-            const float x2 = p_rx * tf_tz - p_rz * tf_tx;
-            const float tx = p_tx + 2.0f * (p_rw * x0 + p_ry * x1 + p_rz * x2) + tf_tx;
-            const float ty = p_ty + 2.0f * (-p_rw * x2 - p_rx * x1 + p_rz * x0) + tf_ty;
-            const float tz = p_tz + 2.0f * (p_rw * x1 - p_rx * x2 - p_ry * x0) + tf_tz;
-            const float b0 = ry * ry, b1 = rz * rz, b2 = rw * rz, b3 = rw * ry, b4 = rx * rx, b5 = rw * rx,
-                        b6 = rx * ry, b7 = rx * rz, b8 = ry * rz;
-            const float xx = -2.0f * (b0 + b1) + 1.0f, xy = 2.0f * (b6 + b2), xz = 2.0f * (b7 - b3);
-            const float yx = 2.0f * (b6 - b2), yy = -2.0f * (b1 + b4) + 1.0f, yz = 2.0f * (b8 + b5);
-            const float zx = 2.0f * (b7 + b3), zy = 2.0f * (b8 - b5), zz = -2.0f * (b0 + b4) + 1.0f;
-#pragma unroll
-            for (int i = 0; i < kMaxAttach; ++i)
+            Center c;
+            c.x = sc.col[(3 * ref.slot + 0) * sc.stride];
+            c.y = sc.col[(3 * ref.slot + 1) * sc.stride];
+            c.z = sc.col[(3 * ref.slot + 2) * sc.stride];
+            if (ref.base & 1)
             {
-                if (i < env.attach.n)
-                {
-                    const float4 s = env.attach.local[i];
-                    posed[i] = make_float4(
-                        s.x * xx + s.y * yx + s.z * zx + tx,
-                        s.x * xy + s.y * yy + s.z * zy + ty,
-                        s.x * xz + s.y * yz + s.z * zz + tz,
-                        s.w);
-                }
+                c.x += bx;
             }
-        }
-        // validity.hh:270-293
-        VB_D bool attach_self(float x, float y, float z, float r)
-        {
-            bool hit = false;
-#pragma unroll
-            for (int i = 0; i < kMaxAttach; ++i)
+            if (ref.base & 2)
             {
-                if (i < env.attach.n)
-                {
-                    hit = hit || self_test(x, y, z, r, posed[i].x, posed[i].y, posed[i].z, posed[i].w);
-                }
+                c.y += by;
             }
-            return hit;
-        }
-        // validity.hh:251-268
-        VB_D bool attach_env()
-        {
-            bool hit = false;
-#pragma unroll
-            for (int i = 0; i < kMaxAttach; ++i)
+            if (ref.base & 4)
             {
-                if (i < env.attach.n && !hit)
-                {
-                    hit = env_test(posed[i].x, posed[i].y, posed[i].z, posed[i].w);
-                }
+                c.z += bz;
             }
-            return hit;
+            c.r = ref.r < 0.f ? radius : ref.r;
+            return c;
         }
     };
 
-    template <int S>
-    struct SpherePolicy
+    // collision/validity.hh:13-44 + sphere_sphere.hh:9-23
+    template <class M>
+    VB_D bool pair_hit(const Center &a, const Center &b, M &mg)
     {
-        float bx_, by_, bz_, radius;
-        float *out;  // this configuration's [S][4]
-        VB_D float bx() const { return bx_; }
-        VB_D float by() const { return by_; }
-        VB_D float bz() const { return bz_; }
-        VB_D float cbx(double c) const { return static_cast<float>(c + static_cast<double>(bx_)); }
-        VB_D float cby(double c) const { return static_cast<float>(c + static_cast<double>(by_)); }
-        VB_D float cbz(double c) const { return static_cast<float>(c + static_cast<double>(bz_)); }
-        VB_D void ops(int) {}
-        VB_D void out_x(int i, float v) { out[4 * i + 0] = v; }
-        VB_D void out_y(int i, float v) { out[4 * i + 1] = v; }
-        VB_D void out_z(int i, float v) { out[4 * i + 2] = v; }
-        VB_D void out_r(int i, float v) { out[4 * i + 3] = v; }
-    };
+        const float dx = a.x - b.x, dy = a.y - b.y, dz = a.z - b.z, rs = a.r + b.r;
+        const float v = dx * dx + dy * dy + dz * dz - rs * rs;
+        mg.sq(v, rs);
+        return v < 0.f;
+    }
 
-    // ---- shared-memory staging of the obstacle records -----------------------------------------
-    VB_D const float4 *stage_env(const EnvView &env, float4 *smem)
+    template <class T, class M>
+    VB_D bool walk_tables(const T &t, const TableCtx &c, int att_slot0, M &mg)
     {
-        if (env.n_quads > kMaxSharedQuads)
+        // environment groups (robots/<robot>/fk.hh: `if (sphere_environment_in_collision(bounding)) {...}`)
+        for (int g = 0; g < t.n_env; ++g)
         {
-            return env.prims;  // large scenes: L1/L2-resident broadcasts
+            const RefGroup grp = t.env[g];
+            const Center b = c.load(grp.guard);
+            if (env_hit(c.env, c.sc.prims, b.x, b.y, b.z, b.r, mg))
+            {
+                if (grp.count == 0)
+                {
+                    return false;
+                }
+                for (int k = 0; k < grp.count; ++k)
+                {
+                    const Center s = c.load(t.refs[grp.begin + k]);
+                    if (env_hit(c.env, c.sc.prims, s.x, s.y, s.z, s.r, mg))
+                    {
+                        return false;
+                    }
+                }
+            }
         }
-        for (int i = threadIdx.x; i < env.n_quads; i += blockDim.x)
+        // self-collision groups
+        for (int g = 0; g < t.n_self; ++g)
         {
-            smem[i] = env.prims[i];
+            const SelfGroup grp = t.self[g];
+            if (pair_hit(c.load(grp.ga), c.load(grp.gb), mg))
+            {
+                if (grp.a_count == 0)
+                {
+                    return false;
+                }
+                for (int i = 0; i < grp.a_count; ++i)
+                {
+                    const Center a = c.load(t.refs[grp.a_begin + i]);
+                    bool hit = false;
+                    for (int j = 0; j < grp.b_count; ++j)
+                    {
+                        hit = pair_hit(a, c.load(t.refs[grp.b_begin + j]), mg) || hit;
+                    }
+                    if (hit)
+                    {
+                        return false;
+                    }
+                }
+            }
         }
-        __syncthreads();
-        return smem;
+        // attachment vs robot (validity.hh:270-293) and attachment vs environment (validity.hh:251-268)
+        const AttachmentView &att = c.env.attach;
+        for (int g = 0; g < t.n_att; ++g)
+        {
+            const RefGroup grp = t.att[g];
+            const Center b = c.load(grp.guard);
+            bool hit = false;
+            for (int i = 0; i < att.n; ++i)
+            {
+                SlotRef ar{static_cast<uint16_t>(att_slot0 + i), 0, att.local[i].w};
+                hit = pair_hit(b, c.load(ar), mg) || hit;
+            }
+            if (hit)
+            {
+                if (grp.count == 0)
+                {
+                    return false;
+                }
+                for (int k = 0; k < grp.count; ++k)
+                {
+                    const Center s = c.load(t.refs[grp.begin + k]);
+                    for (int i = 0; i < att.n; ++i)
+                    {
+                        SlotRef ar{static_cast<uint16_t>(att_slot0 + i), 0, att.local[i].w};
+                        if (pair_hit(s, c.load(ar), mg))
+                        {
+                            return false;
+                        }
+                    }
+                }
+            }
+        }
+        if (t.att_env)
+        {
+            for (int i = 0; i < att.n; ++i)
+            {
+                SlotRef ar{static_cast<uint16_t>(att_slot0 + i), 0, att.local[i].w};
+                const Center s = c.load(ar);
+                if (env_hit(c.env, c.sc.prims, s.x, s.y, s.z, s.r, mg))
+                {
+                    return false;
+                }
+            }
+        }
+        return true;
     }
 
     template <class Robot, class M>
-    VB_D bool check_config(const LaunchArgs &a, const float4 *prims, const float *q, bool attach, M &mg_out)
+    VB_D bool check_config(const LaunchArgs &a, const Scratch &sc, const float *q, bool attach, M &mg)
     {
-        CheckPolicy<M> pol(a.env, prims, a.base, a.sphere_radius);
-        bool ok;
+        SlotSink sink{sc.col, sc.stride, &a.env.attach, Robot::kSlots};
+        const TableCtx ctx{a.env, sc, a.base[0], a.base[1], a.base[2], a.sphere_radius};
         if (Robot::kHasAttach && attach)
         {
-            ok = Robot::fkcc_attach(pol, q);
+            Robot::chain_attach(sink, q);
+            return walk_tables(Robot::tables_attach(), ctx, Robot::kSlots, mg);
         }
-        else
-        {
-            ok = Robot::fkcc(pol, q);
-        }
-        mg_out = pol.mg;
-        return ok;
+        Robot::chain(sink, q);
+        return walk_tables(Robot::tables(), ctx, Robot::kSlots, mg);
     }
 
     // ---- K1: batched fkcc over explicit configurations -----------------------------------------
     template <class Robot, bool kMargin>
-    __global__ void __launch_bounds__(kBlock) fkcc_kernel(const LaunchArgs a)
+    __global__ void __launch_bounds__(block_threads<Robot>()) fkcc_kernel(const LaunchArgs a)
     {
-        extern __shared__ float4 smem[];
-        const float4 *prims = stage_env(a.env, smem);
-        const size_t stride = static_cast<size_t>(gridDim.x) * kBlock;
+        const Scratch prims = stage_env(a.env);
+        const size_t stride = static_cast<size_t>(gridDim.x) * blockDim.x;
         const size_t n_round = (a.n + 31) / 32 * 32;
-        for (size_t i = static_cast<size_t>(blockIdx.x) * kBlock + threadIdx.x; i < n_round; i += stride)
+        for (size_t i = static_cast<size_t>(blockIdx.x) * blockDim.x + threadIdx.x; i < n_round; i += stride)
         {
             bool ok = false;
             if (i < a.n)
@@ -233,13 +275,12 @@ namespace vb
 
     // ---- K1r: fkcc over device-synthesised configurations (0 input bytes) -----------------------
     template <class Robot>
-    __global__ void __launch_bounds__(kBlock) fkcc_random_kernel(const LaunchArgs a, size_t first)
+    __global__ void __launch_bounds__(block_threads<Robot>()) fkcc_random_kernel(const LaunchArgs a, size_t first)
     {
-        extern __shared__ float4 smem[];
-        const float4 *prims = stage_env(a.env, smem);
-        const size_t stride = static_cast<size_t>(gridDim.x) * kBlock;
+        const Scratch prims = stage_env(a.env);
+        const size_t stride = static_cast<size_t>(gridDim.x) * blockDim.x;
         const size_t n_round = (a.n + 31) / 32 * 32;
-        for (size_t i = static_cast<size_t>(blockIdx.x) * kBlock + threadIdx.x; i < n_round; i += stride)
+        for (size_t i = static_cast<size_t>(blockIdx.x) * blockDim.x + threadIdx.x; i < n_round; i += stride)
         {
             bool ok = false;
             if (i < a.n)
@@ -259,9 +300,9 @@ namespace vb
 
     // ---- K2: sphere_fk ---------------------------------------------------------------------------
     template <class Robot>
-    __global__ void __launch_bounds__(kBlock) sphere_fk_kernel(const LaunchArgs a)
+    __global__ void __launch_bounds__(block_threads<Robot>()) sphere_fk_kernel(const LaunchArgs a)
     {
-        const size_t i = static_cast<size_t>(blockIdx.x) * kBlock + threadIdx.x;
+        const size_t i = static_cast<size_t>(blockIdx.x) * blockDim.x + threadIdx.x;
         if (i >= a.n)
         {
             return;
@@ -272,9 +313,39 @@ namespace vb
         {
             q[j] = __ldg(a.cfg + i * Robot::kDim + j);
         }
-        SpherePolicy<Robot::kSpheres> pol{a.base[0], a.base[1], a.base[2], a.sphere_radius,
+        SphereSink pol{a.base[0], a.base[1], a.base[2], a.sphere_radius,
                                           a.spheres + i * Robot::kSpheres * 4};
         Robot::sphere_fk(pol, q);
+    }
+
+    // ---- joint-limit test of Helper::validate_configuration (bindings/common.hh:172-179) ----------
+    // descale_configuration then all(0 <= q' <= 1); ANDed into the verdict words.
+    template <class Robot>
+    __global__ void limits_kernel(const LaunchArgs a)
+    {
+        const size_t n_round = (a.n + 31) / 32 * 32;
+        const size_t i = static_cast<size_t>(blockIdx.x) * blockDim.x + threadIdx.x;
+        if (i >= n_round)
+        {
+            return;
+        }
+        bool ok = false;
+        if (i < a.n)
+        {
+            ok = true;
+#pragma unroll
+            for (int j = 0; j < Robot::kDim; ++j)
+            {
+                const float d = VB_ADD(__ldg(a.cfg + i * Robot::kDim + j), -Robot::lo(j));
+                const float u = Robot::kDescaleDivides ? d / Robot::inv_range(j) : VB_MUL(d, Robot::inv_range(j));
+                ok = ok && (u <= 1.f) && (u >= 0.f);
+            }
+        }
+        const uint32_t word = __ballot_sync(0xffffffffu, ok);
+        if ((threadIdx.x & 31) == 0)
+        {
+            a.bits[i >> 5] &= word;
+        }
     }
 
     // ---- K3: discretised motion validation --------------------------------------------------------
@@ -340,12 +411,12 @@ namespace vb
     }
 
     template <class Robot, bool kMargin>
-    __global__ void __launch_bounds__(kBlock) motion_kernel(const LaunchArgs a)
+    __global__ void __launch_bounds__(block_threads<Robot>()) motion_kernel(const LaunchArgs a)
     {
-        extern __shared__ float4 smem[];
-        const float4 *prims = stage_env(a.env, smem);
-        const size_t stride = static_cast<size_t>(gridDim.x) * kBlock;
-        for (size_t t = static_cast<size_t>(blockIdx.x) * kBlock + threadIdx.x; t < a.n_points; t += stride)
+        const Scratch prims = stage_env(a.env);
+        const size_t stride = static_cast<size_t>(gridDim.x) * blockDim.x;
+        const size_t n_points = __ldg(a.prefix + a.n);  // total interpolants, left on the device by the scan
+        for (size_t t = static_cast<size_t>(blockIdx.x) * blockDim.x + threadIdx.x; t < n_points; t += stride)
         {
             // binary search: last edge with prefix[e] <= t
             size_t lo = 0, hi = a.n;

@@ -7,13 +7,41 @@ namespace vb
 {
     using R = VB_TRACE;
 
+    constexpr int kBlock = block_threads<R>();
+
+    // obstacle records (when staged) + one slot column per thread
     static size_t smem_bytes(const LaunchArgs &a)
     {
-        return a.env.n_quads > kMaxSharedQuads ? 0 : sizeof(float4) * static_cast<size_t>(a.env.n_quads);
+        const size_t quads = a.env.n_quads > kMaxSharedQuads ? 0 : static_cast<size_t>(a.env.n_quads);
+        const size_t slots = R::kSlots + (a.attach ? a.env.attach.n : 0);
+        return sizeof(float4) * quads + sizeof(float) * 3 * slots * kBlock;
+    }
+
+    template <class K>
+    static cudaError_t allow_smem(K kernel)
+    {
+        return cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024);
+    }
+
+    static cudaError_t prepare()
+    {
+        static cudaError_t once = [] {
+            cudaError_t e = allow_smem(fkcc_kernel<R, true>);
+            if (e == cudaSuccess) e = allow_smem(fkcc_kernel<R, false>);
+            if (e == cudaSuccess) e = allow_smem(fkcc_random_kernel<R>);
+            if (e == cudaSuccess) e = allow_smem(motion_kernel<R, true>);
+            if (e == cudaSuccess) e = allow_smem(motion_kernel<R, false>);
+            return e;
+        }();
+        return once;
     }
 
     static cudaError_t launch_fkcc(const LaunchArgs &a, bool margin, int grid)
     {
+        if (cudaError_t e = prepare(); e != cudaSuccess)
+        {
+            return e;
+        }
         if (margin)
         {
             fkcc_kernel<R, true><<<grid, kBlock, smem_bytes(a), a.stream>>>(a);
@@ -27,6 +55,10 @@ namespace vb
 
     static cudaError_t launch_fkcc_random(const LaunchArgs &a, size_t first, int grid)
     {
+        if (cudaError_t e = prepare(); e != cudaSuccess)
+        {
+            return e;
+        }
         fkcc_random_kernel<R><<<grid, kBlock, smem_bytes(a), a.stream>>>(a, first);
         return cudaGetLastError();
     }
@@ -45,8 +77,19 @@ namespace vb
         return cudaGetLastError();
     }
 
+    static cudaError_t launch_limits(const LaunchArgs &a)
+    {
+        const size_t grid = ((a.n + 31) / 32 * 32 + 255) / 256;
+        limits_kernel<R><<<static_cast<unsigned>(grid), 256, 0, a.stream>>>(a);
+        return cudaGetLastError();
+    }
+
     static cudaError_t launch_motion(const LaunchArgs &a, bool margin, int grid)
     {
+        if (cudaError_t e = prepare(); e != cudaSuccess)
+        {
+            return e;
+        }
         if (margin)
         {
             motion_kernel<R, true><<<grid, kBlock, smem_bytes(a), a.stream>>>(a);
@@ -58,9 +101,14 @@ namespace vb
         return cudaGetLastError();
     }
 
-    static cudaError_t occupancy(int *blocks)
+    static cudaError_t occupancy(const LaunchArgs &a, int *blocks, int *threads)
     {
-        return cudaOccupancyMaxActiveBlocksPerMultiprocessor(blocks, fkcc_kernel<R, false>, kBlock, 0);
+        if (cudaError_t e = prepare(); e != cudaSuccess)
+        {
+            return e;
+        }
+        *threads = kBlock;
+        return cudaOccupancyMaxActiveBlocksPerMultiprocessor(blocks, fkcc_kernel<R, false>, kBlock, smem_bytes(a));
     }
 
     static void host_random_config(uint64_t seed, uint64_t index, float *q)
@@ -77,6 +125,7 @@ namespace vb
             o.n_spheres = R::kSpheres;
             o.resolution = R::kResolution;
             o.has_attach = R::kHasAttach;
+            o.n_slots = R::kSlots;
             o.chain_flops = R::kChainFlops;
             o.env_groups = R::kEnvGroups;
             o.env_fine = R::kEnvFine;
@@ -92,6 +141,7 @@ namespace vb
             o.sphere_fk = &launch_sphere_fk;
             o.edge_count = &launch_edge_count;
             o.motion = &launch_motion;
+            o.limits = &launch_limits;
             o.occupancy = &occupancy;
             o.random_config = &host_random_config;
             return o;

@@ -8,7 +8,7 @@ namespace vb
     struct RobotOps
     {
         const char *name;
-        int dim, n_spheres, resolution, has_attach;
+        int dim, n_spheres, resolution, has_attach, n_slots;
         int chain_flops, env_groups, env_fine, self_groups, self_fine;
         float lo[16], range[16];
         cudaError_t (*fkcc)(const LaunchArgs &, bool margin, int grid);
@@ -16,7 +16,8 @@ namespace vb
         cudaError_t (*sphere_fk)(const LaunchArgs &);
         cudaError_t (*edge_count)(const LaunchArgs &, uint32_t *counts_d);
         cudaError_t (*motion)(const LaunchArgs &, bool margin, int grid);
-        cudaError_t (*occupancy)(int *blocks_per_sm);  // of the fkcc kernel
+        cudaError_t (*limits)(const LaunchArgs &);
+        cudaError_t (*occupancy)(const LaunchArgs &, int *blocks_per_sm, int *threads);  // of the fkcc kernel
         void (*random_config)(uint64_t seed, uint64_t index, float *q);
     };
 

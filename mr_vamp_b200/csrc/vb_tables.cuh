@@ -1,0 +1,41 @@
+// Check tables emitted by codegen/emit_cuda.py: which sphere slots form which collision groups.
+// They restate the control structure of interleaved_sphere_fk (robots/<robot>/fk.hh): a group is
+// "if (guard test) { fine tests }" and the configuration is valid iff no group has both a guard
+// hit and a fine hit.
+#pragma once
+#include <stdint.h>
+
+namespace vb
+{
+    struct SlotRef
+    {
+        uint16_t slot;  // sphere-centre slot written by the chain
+        uint16_t base;  // bit k set: add the robot base offset to coordinate k (Panda, robots/panda/fk.hh)
+        float r;        // radius; < 0: the run-time radius of robots::sphere
+    };
+
+    // sphere_environment_in_collision(guard) { sphere_environment_in_collision(fine_i)... };
+    // count == 0: the guard itself is the test
+    struct RefGroup
+    {
+        SlotRef guard;
+        uint16_t begin, count;
+    };
+
+    // sphere_sphere_self_collision(ga, gb) { all pairs a_i x b_j }; a_count == 0: the guard is the test
+    struct SelfGroup
+    {
+        SlotRef ga, gb;
+        uint16_t a_begin, a_count, b_begin, b_count;
+    };
+
+    template <int NE, int NS, int NA, int NR>
+    struct Tables
+    {
+        int n_slots, n_env, n_self, n_att, att_env;
+        RefGroup env[NE];
+        SelfGroup self[NS];
+        RefGroup att[NA];  // attachment_sphere_collision groups (robot sphere vs every attachment sphere)
+        SlotRef refs[NR];
+    };
+}  // namespace vb
