@@ -1,0 +1,484 @@
+"""Python face of ``libvamp_b200.so`` (ctypes over the C ABI of ``include/vamp_b200.h``).
+
+Mirrors the part of the reference's nanobind module ``vamp._core_ext`` that sits on the fkcc path:
+shape constructors and ``Environment.add_*`` (``bindings/environment.cc:18-250``), and per robot
+``validate`` / ``fk`` (``bindings/common.hh:132-189,685-710``) — plus the batch entry points the
+reference lists as a TODO (``README.md:308``): ``validate_batch``, ``validate_motion_batch``,
+``fk_batch``.  Nothing here computes a verdict: every query goes to the CUDA library, and the
+import fails loudly when the library is missing.
+"""
+from __future__ import annotations
+
+import ctypes as C
+import math
+import os
+from typing import Iterable, Optional, Sequence
+
+import numpy as np
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(_HERE, "lib", "libvamp_b200.so")
+
+_f32p = C.POINTER(C.c_float)
+_u32p = C.POINTER(C.c_uint32)
+_vp = C.c_void_p
+
+ROBOT_IDS = {"sphere": 0, "ur5": 1, "panda": 2, "fetch": 3, "baxter": 4}
+
+# every symbol include/vamp_b200.h declares: (name, restype, argtypes)
+_SIGNATURES = [
+    ("vb_last_error", C.c_char_p, []),
+    ("vb_version", C.c_char_p, []),
+    ("vb_ctx_create", C.c_int, [C.POINTER(_vp), C.POINTER(C.c_int), C.c_int]),
+    ("vb_ctx_destroy", None, [_vp]),
+    ("vb_ctx_device_count", C.c_int, [_vp]),
+    ("vb_ctx_sm_count", C.c_int, [_vp, C.c_int]),
+    ("vb_sync", C.c_int, [_vp]),
+    ("vb_robot_by_name", C.c_int, [C.c_char_p, C.POINTER(C.c_int)]),
+    ("vb_robot_info", C.c_int, [C.c_int, C.POINTER(C.c_int), C.POINTER(C.c_int), C.POINTER(C.c_int)]),
+    ("vb_robot_limits", C.c_int, [C.c_int, _f32p, _f32p]),
+    ("vb_random_config", C.c_int, [C.c_int, C.c_uint64, C.c_uint64, _f32p]),
+    ("vb_random_edge", C.c_int, [C.c_int, C.c_uint64, C.c_uint64, C.c_float, C.c_float, _f32p, _f32p]),
+    ("vb_ctx_set_sphere_radius", C.c_int, [_vp, C.c_float]),
+    ("vb_env_create", C.c_int, [_vp, C.POINTER(_vp)]),
+    ("vb_env_destroy", None, [_vp]),
+    ("vb_env_clear", C.c_int, [_vp]),
+    ("vb_env_add_sphere", C.c_int, [_vp, C.c_float, C.c_float, C.c_float, C.c_float]),
+    ("vb_env_add_cuboid", C.c_int, [_vp, _f32p]),
+    ("vb_env_add_capsule", C.c_int, [_vp, _f32p]),
+    ("vb_env_add_heightfield", C.c_int, [_vp, _f32p, C.c_size_t, C.c_size_t, _f32p]),
+    ("vb_env_add_capt", C.c_int, [_vp, _f32p, C.c_size_t, _u32p, _f32p, _f32p, _f32p, C.c_size_t, _f32p,
+                                  C.c_size_t, _f32p, C.c_float, C.c_int]),
+    ("vb_env_set_attachment", C.c_int, [_vp, _f32p, _f32p, C.c_size_t]),
+    ("vb_env_clear_attachment", C.c_int, [_vp]),
+    ("vb_env_commit", C.c_int, [_vp]),
+    ("vb_env_export", C.c_int, [_vp, C.c_int, _f32p, C.POINTER(C.c_size_t)]),
+    ("vb_sphere_fk", C.c_int, [_vp, C.c_int, _f32p, _f32p, C.c_size_t, _f32p]),
+    ("vb_fkcc", C.c_int, [_vp, C.c_int, _f32p, _vp, _f32p, C.c_size_t, _u32p, _f32p]),
+    ("vb_validate", C.c_int, [_vp, C.c_int, _f32p, _vp, _f32p, C.c_size_t, _u32p]),
+    ("vb_validate_motion", C.c_int, [_vp, C.c_int, _f32p, _vp, _f32p, _f32p, C.c_size_t, C.c_int, _u32p, _f32p]),
+    ("vb_validate_pairs", C.c_int, [_vp, C.c_int, _f32p, C.c_int, _f32p, _vp, _f32p, _f32p, C.c_size_t, _u32p]),
+    ("vb_dev_alloc", C.c_int, [_vp, C.c_int, C.c_size_t, C.POINTER(_vp)]),
+    ("vb_dev_free", C.c_int, [_vp, C.c_int, _vp]),
+    ("vb_dev_upload", C.c_int, [_vp, C.c_int, _vp, _vp, C.c_size_t]),
+    ("vb_dev_download", C.c_int, [_vp, C.c_int, _vp, _vp, C.c_size_t]),
+    ("vb_fkcc_d", C.c_int, [_vp, C.c_int, C.c_int, _f32p, _vp, _vp, C.c_size_t, _vp, _vp]),
+    ("vb_validate_motion_d", C.c_int, [_vp, C.c_int, C.c_int, _f32p, _vp, _vp, _vp, C.c_size_t, C.c_int, _vp, _vp]),
+    ("vb_fkcc_random_d", C.c_int, [_vp, C.c_int, C.c_int, _f32p, _vp, C.c_uint64, C.c_uint64, C.c_size_t, _vp]),
+    ("vb_timer_start", C.c_int, [_vp, C.c_int]),
+    ("vb_timer_stop", C.c_int, [_vp, C.c_int, C.POINTER(C.c_double)]),
+    ("vb_launch_count", C.c_uint64, [_vp]),
+    ("vb_popcount_d", C.c_int, [_vp, C.c_int, _vp, C.c_size_t, C.POINTER(C.c_uint64)]),
+    ("vb_comm_unique_id", C.c_int, [_vp]),
+    ("vb_comm_init", C.c_int, [_vp, C.c_int, C.c_int, _vp]),
+    ("vb_comm_allgather_bits_d", C.c_int, [_vp, _vp, _vp, C.c_size_t]),
+    ("vb_comm_destroy", C.c_int, [_vp]),
+]
+
+_lib = None
+
+
+class VampB200Error(RuntimeError):
+    pass
+
+
+def lib():
+    """Load the CUDA library.  There is no fallback: a missing library is an error."""
+    global _lib
+    if _lib is None:
+        if not os.path.exists(LIB_PATH):
+            raise VampB200Error(f"{LIB_PATH} is missing: build it with `make` (nvcc, sm_100a); there is no CPU path")
+        L = C.CDLL(LIB_PATH)
+        for name, res, args in _SIGNATURES:
+            fn = getattr(L, name)
+            fn.restype = res
+            fn.argtypes = args
+        _lib = L
+    return _lib
+
+
+def exported_symbols() -> list[str]:
+    return [s[0] for s in _SIGNATURES]
+
+
+def _check(rc: int):
+    if rc != 0:
+        raise VampB200Error(f"[{rc}] {lib().vb_last_error().decode()}")
+
+
+def _f32(a) -> np.ndarray:
+    return np.ascontiguousarray(a, dtype=np.float32)
+
+
+def _ptr(a: Optional[np.ndarray], typ=_f32p):
+    return None if a is None else a.ctypes.data_as(typ)
+
+
+def unpack_bits(words: np.ndarray, n: int) -> np.ndarray:
+    """uint32 verdict words -> bool[n] (bit i%32 of word i//32)."""
+    return np.unpackbits(words.view(np.uint8), bitorder="little")[:n].astype(bool)
+
+
+# ---- shapes (collision/factory.hh; arithmetic in float32 like the reference's Eigen::*f types) ----
+def _rotation_xyz(euler_xyz: Sequence[float]) -> np.ndarray:
+    """Rz(phi) * Ry(theta) * Rx(rho) (collision/factory.hh:37-39)."""
+    rho, theta, phi = (np.float32(v) for v in euler_xyz)
+    cx, sx = np.float32(math.cos(rho)), np.float32(math.sin(rho))
+    cy, sy = np.float32(math.cos(theta)), np.float32(math.sin(theta))
+    cz, sz = np.float32(math.cos(phi)), np.float32(math.sin(phi))
+    rx = np.array([[1, 0, 0], [0, cx, -sx], [0, sx, cx]], dtype=np.float32)
+    ry = np.array([[cy, 0, sy], [0, 1, 0], [-sy, 0, cy]], dtype=np.float32)
+    rz = np.array([[cz, -sz, 0], [sz, cz, 0], [0, 0, 1]], dtype=np.float32)
+    return (rz @ ry @ rx).astype(np.float32)
+
+
+class Sphere:
+    """bindings/environment.cc:20-36."""
+
+    def __init__(self, center: Sequence[float], radius: float):
+        self.x, self.y, self.z = (float(np.float32(v)) for v in center)
+        self.r = float(np.float32(radius))
+        self.name = ""
+
+    @property
+    def position(self):
+        return [self.x, self.y, self.z]
+
+
+class Cuboid:
+    """bindings/environment.cc:70-98; raw() = the 15 floats of collision/shapes.hh:34-50."""
+
+    def __init__(self, center: Sequence[float], euler_xyz: Sequence[float], half_extents: Sequence[float]):
+        rot = _rotation_xyz(euler_xyz)
+        self._raw = np.concatenate(
+            [_f32(center), rot[:, 0], rot[:, 1], rot[:, 2], _f32(half_extents)]
+        ).astype(np.float32)
+        self.name = ""
+
+    @classmethod
+    def from_raw(cls, raw15: Sequence[float]) -> "Cuboid":
+        c = cls.__new__(cls)
+        c._raw = _f32(raw15).copy()
+        assert c._raw.shape == (15,)
+        c.name = ""
+        return c
+
+    def raw(self) -> np.ndarray:
+        return self._raw
+
+
+class Cylinder:
+    """bindings/environment.cc:38-68: (center, euler_xyz, radius, length) or (endpoint1, endpoint2, radius)."""
+
+    def __init__(self, a: Sequence[float], b: Sequence[float], radius: float, length: Optional[float] = None):
+        if length is not None:
+            rot = _rotation_xyz(b)
+            half = np.float32(length) / np.float32(2)
+            ctr = _f32(a)
+            p1 = rot @ np.array([0, 0, half], dtype=np.float32) + ctr
+            p2 = rot @ np.array([0, 0, -half], dtype=np.float32) + ctr
+        else:
+            p1, p2 = _f32(a), _f32(b)
+        v = (p2 - p1).astype(np.float32)
+        dot = np.float32(v[0] * v[0]) + np.float32(v[1] * v[1]) + np.float32(v[2] * v[2])
+        rdv = np.float32(1.0 / float(dot))  # collision/factory.hh:233-244
+        self._raw = np.array([p1[0], p1[1], p1[2], v[0], v[1], v[2], np.float32(radius), rdv], dtype=np.float32)
+        self.name = ""
+
+    @classmethod
+    def from_raw(cls, raw8: Sequence[float]) -> "Cylinder":
+        c = cls.__new__(cls)
+        c._raw = _f32(raw8).copy()
+        assert c._raw.shape == (8,)
+        c.name = ""
+        return c
+
+    def raw(self) -> np.ndarray:
+        return self._raw
+
+
+Capsule = Cylinder
+
+
+class HeightField:
+    """collision/factory.hh:365-386 (make_heightfield): scales are stored inverted."""
+
+    def __init__(self, center: Sequence[float], scaling: Sequence[float], data: np.ndarray):
+        data = _f32(data)
+        assert data.ndim == 2
+        self.yd, self.xd = data.shape
+        inv = [np.float32(1.0) / np.float32(v) for v in scaling]
+        self.off_scale = np.array([center[0], center[1], center[2], inv[0], inv[1], inv[2]], dtype=np.float32)
+        self.data = data.reshape(-1)
+
+    @classmethod
+    def from_raw(cls, off_scale6, xd: int, yd: int, data) -> "HeightField":
+        h = cls.__new__(cls)
+        h.off_scale = _f32(off_scale6).copy()
+        h.xd, h.yd = int(xd), int(yd)
+        h.data = _f32(data).reshape(-1)
+        return h
+
+
+class Attachment:
+    """collision/attachments.hh:11-73: transform (translation + xyzw quaternion) and local spheres."""
+
+    def __init__(self, position: Sequence[float], quaternion_xyzw: Sequence[float]):
+        self.tf = np.concatenate([_f32(position), _f32(quaternion_xyzw)]).astype(np.float32)
+        self.spheres: list[Sphere] = []
+
+    def add_spheres(self, spheres: Iterable[Sphere]):
+        self.spheres.extend(spheres)
+
+
+# ---- context ---------------------------------------------------------------------------------
+class Context:
+    def __init__(self, devices: Optional[Sequence[int]] = None):
+        self._h = _vp()
+        if devices is None:
+            _check(lib().vb_ctx_create(C.byref(self._h), None, 0))
+        else:
+            ids = (C.c_int * len(devices))(*devices)
+            _check(lib().vb_ctx_create(C.byref(self._h), ids, len(devices)))
+
+    def close(self):
+        if self._h:
+            lib().vb_ctx_destroy(self._h)
+            self._h = _vp()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    @property
+    def handle(self):
+        return self._h
+
+    @property
+    def n_devices(self) -> int:
+        return lib().vb_ctx_device_count(self._h)
+
+    def sm_count(self, slot: int = 0) -> int:
+        return lib().vb_ctx_sm_count(self._h, slot)
+
+    def sync(self):
+        _check(lib().vb_sync(self._h))
+
+    def launch_count(self) -> int:
+        return int(lib().vb_launch_count(self._h))
+
+    def set_sphere_radius(self, r: float):
+        _check(lib().vb_ctx_set_sphere_radius(self._h, r))
+
+
+_default_ctx: Optional[Context] = None
+
+
+def default_context() -> Context:
+    global _default_ctx
+    if _default_ctx is None:
+        _default_ctx = Context()
+    return _default_ctx
+
+
+# ---- environment -----------------------------------------------------------------------------
+class Environment:
+    """Mirror of ``vamp.Environment`` (bindings/environment.cc:107-163).  Mutations are recorded on
+    the host; the device copy is rebuilt lazily (one upload per change set instead of the reference's
+    float->vector deep copy on every query, bindings/common.hh:181)."""
+
+    def __init__(self, ctx: Optional[Context] = None):
+        self.ctx = ctx or default_context()
+        self._h = _vp()
+        _check(lib().vb_env_create(self.ctx.handle, C.byref(self._h)))
+        self._dirty = True
+
+    def __del__(self):
+        try:
+            if self._h and self.ctx._h:
+                lib().vb_env_destroy(self._h)
+        except Exception:
+            pass
+
+    def add_sphere(self, s: Sphere):
+        _check(lib().vb_env_add_sphere(self._h, s.x, s.y, s.z, s.r))
+        self._dirty = True
+
+    def add_cuboid(self, c: Cuboid):
+        _check(lib().vb_env_add_cuboid(self._h, _ptr(c.raw())))
+        self._dirty = True
+
+    def add_capsule(self, c: Cylinder):
+        _check(lib().vb_env_add_capsule(self._h, _ptr(c.raw())))
+        self._dirty = True
+
+    def add_heightfield(self, h: HeightField):
+        _check(lib().vb_env_add_heightfield(self._h, _ptr(h.off_scale), h.xd, h.yd, _ptr(h.data)))
+        self._dirty = True
+
+    def add_capt_buffers(self, tests, aff_starts, aff_x, aff_y, aff_z, aabbs, aabb_top, r_point: float, nlog2: int):
+        """CAPT query buffers built on the host (collision/capt.hh:588-621)."""
+        tests, aff_x, aff_y, aff_z, aabbs = (_f32(a).reshape(-1) for a in (tests, aff_x, aff_y, aff_z, aabbs))
+        aff_starts = np.ascontiguousarray(aff_starts, dtype=np.uint32)
+        top = _f32(aabb_top)
+        _check(
+            lib().vb_env_add_capt(
+                self._h, _ptr(tests), tests.size, _ptr(aff_starts, _u32p), _ptr(aff_x), _ptr(aff_y), _ptr(aff_z),
+                aff_x.size // 8, _ptr(aabbs), aabbs.size // 6, _ptr(top), r_point, nlog2,
+            )
+        )
+        self._dirty = True
+
+    def attach(self, a: Attachment):
+        sph = _f32([[s.x, s.y, s.z, s.r] for s in a.spheres]).reshape(-1, 4)
+        _check(lib().vb_env_set_attachment(self._h, _ptr(a.tf), _ptr(sph), len(a.spheres)))
+        self._dirty = True
+
+    def detach(self):
+        _check(lib().vb_env_clear_attachment(self._h))
+        self._dirty = True
+
+    def export(self, kind: int) -> np.ndarray:
+        width = {0: 5, 1: 9, 2: 9, 3: 16, 4: 16}[kind]
+        n = C.c_size_t()
+        _check(lib().vb_env_export(self._h, kind, None, C.byref(n)))
+        out = np.zeros((n.value, width), dtype=np.float32)
+        if n.value:
+            _check(lib().vb_env_export(self._h, kind, _ptr(out), C.byref(n)))
+        return out
+
+    @property
+    def handle(self):
+        if self._dirty:
+            _check(lib().vb_env_commit(self._h))
+            self._dirty = False
+        return self._h
+
+
+# ---- robots ----------------------------------------------------------------------------------
+class Robot:
+    """One robot submodule of the reference's Python module (``vamp.panda`` etc., bindings/common.hh:355-728),
+    restricted to the fkcc path, plus the batch calls."""
+
+    def __init__(self, name: str, base: Sequence[float] = (0.0, 0.0, 0.0), ctx: Optional[Context] = None):
+        self.name = name
+        self.robot_id = ROBOT_IDS[name]
+        self._ctx = ctx
+        self.base = _f32(base)
+        d, s, r = C.c_int(), C.c_int(), C.c_int()
+        _check(lib().vb_robot_info(self.robot_id, C.byref(d), C.byref(s), C.byref(r)))
+        self.dimension, self.n_spheres, self.resolution = d.value, s.value, r.value
+        lo = np.zeros(self.dimension, dtype=np.float32)
+        rg = np.zeros(self.dimension, dtype=np.float32)
+        _check(lib().vb_robot_limits(self.robot_id, _ptr(lo), _ptr(rg)))
+        self.lower_bounds, self.ranges = lo, rg
+
+    @property
+    def ctx(self) -> Context:
+        return self._ctx or default_context()
+
+    def _env(self, env: Optional[Environment]) -> Environment:
+        if env is None:
+            if not hasattr(self, "_empty_env") or self._empty_env.ctx is not self.ctx:
+                self._empty_env = Environment(self.ctx)
+            return self._empty_env
+        return env
+
+    def _configs(self, q) -> np.ndarray:
+        q = _f32(q)
+        if q.ndim == 1:
+            q = q[None, :]
+        if q.ndim != 2 or q.shape[1] != self.dimension:
+            raise ValueError(f"{self.name}: expected [n, {self.dimension}] configurations, got {q.shape}")
+        return q
+
+    # -- batch API (README.md:308 "Batch configuration validation") ------------------------------
+    def fkcc_batch(self, configs, env: Optional[Environment] = None, margin: bool = False):
+        """Robot::fkcc per configuration -> bool[n] (True = collision free) [, float32[n] margins]."""
+        q = self._configs(configs)
+        n = q.shape[0]
+        bits = np.zeros((n + 31) // 32, dtype=np.uint32)
+        mg = np.zeros(n, dtype=np.float32) if margin else None
+        _check(lib().vb_fkcc(self.ctx.handle, self.robot_id, _ptr(self.base), self._env(env).handle, _ptr(q), n,
+                             _ptr(bits, _u32p), _ptr(mg)))
+        ok = unpack_bits(bits, n)
+        return (ok, mg) if margin else ok
+
+    def validate_batch(self, configs, env: Optional[Environment] = None) -> np.ndarray:
+        """Helper::validate_configuration per configuration: joint limits && fkcc."""
+        q = self._configs(configs)
+        n = q.shape[0]
+        bits = np.zeros((n + 31) // 32, dtype=np.uint32)
+        _check(lib().vb_validate(self.ctx.handle, self.robot_id, _ptr(self.base), self._env(env).handle, _ptr(q), n,
+                                 _ptr(bits, _u32p)))
+        return unpack_bits(bits, n)
+
+    def validate_motion_batch(self, starts, goals, env: Optional[Environment] = None, resolution: int = 0,
+                              margin: bool = False):
+        """planning::validate_motion per edge -> bool[n]."""
+        a, b = self._configs(starts), self._configs(goals)
+        if a.shape != b.shape:
+            raise ValueError("starts and goals differ in shape")
+        n = a.shape[0]
+        bits = np.zeros((n + 31) // 32, dtype=np.uint32)
+        mg = np.zeros(n, dtype=np.float32) if margin else None
+        _check(lib().vb_validate_motion(self.ctx.handle, self.robot_id, _ptr(self.base), self._env(env).handle,
+                                        _ptr(a), _ptr(b), n, resolution, _ptr(bits, _u32p), _ptr(mg)))
+        ok = unpack_bits(bits, n)
+        return (ok, mg) if margin else ok
+
+    def fk_batch(self, configs) -> np.ndarray:
+        """Robot::sphere_fk -> float32[n, n_spheres, 4] (x, y, z, r), world frame."""
+        q = self._configs(configs)
+        out = np.zeros((q.shape[0], self.n_spheres, 4), dtype=np.float32)
+        _check(lib().vb_sphere_fk(self.ctx.handle, self.robot_id, _ptr(self.base), _ptr(q), q.shape[0], _ptr(out)))
+        return out
+
+    # -- the reference's single-query signatures -------------------------------------------------
+    def validate(self, configuration, environment: Optional[Environment] = None) -> bool:
+        """vamp.<robot>.validate(configuration, environment) (bindings/common.hh:685-697)."""
+        return bool(self.validate_batch(configuration, environment)[0])
+
+    def fk(self, configuration) -> list[Sphere]:
+        """vamp.<robot>.fk(configuration) -> list[Sphere] (bindings/common.hh:706-710)."""
+        return [Sphere(s[:3], s[3]) for s in self.fk_batch(configuration)[0]]
+
+    def validate_path(self, waypoints, environment: Optional[Environment] = None) -> bool:
+        """Path.validate(env) (planning/plan.hh:155-168): every consecutive edge in ONE batch call."""
+        w = self._configs(waypoints)
+        if w.shape[0] < 2:
+            return True
+        return bool(self.validate_motion_batch(w[:-1], w[1:], environment).all())
+
+    # -- synthetic streams shared with the device-side generators ---------------------------------
+    def random_configs(self, seed: int, first: int, n: int) -> np.ndarray:
+        out = np.zeros((n, self.dimension), dtype=np.float32)
+        for i in range(n):
+            _check(lib().vb_random_config(self.robot_id, seed, first + i, _ptr(out[i])))
+        return out
+
+    def random_edges(self, seed: int, first: int, n: int, len_lo: float, len_hi: float):
+        a = np.zeros((n, self.dimension), dtype=np.float32)
+        b = np.zeros((n, self.dimension), dtype=np.float32)
+        for i in range(n):
+            _check(lib().vb_random_edge(self.robot_id, seed, first + i, len_lo, len_hi, _ptr(a[i]), _ptr(b[i])))
+        return a, b
+
+
+def panda_grid(x100: int, y100: int, z100: int = 0, ctx: Optional[Context] = None) -> Robot:
+    """PandaBase<X100, Y100, Z100> (robots/panda_base.hh:15-51): base offset in centimetres."""
+    base = [np.float32(x100) / np.float32(100.0), np.float32(y100) / np.float32(100.0), np.float32(z100) / np.float32(100.0)]
+    return Robot("panda", base, ctx)
+
+
+def robot(name: str, ctx: Optional[Context] = None) -> Robot:
+    """Robots by the reference's names: sphere, ur5, fetch, baxter, panda (= the fork's default
+    PandaBase<200,200,0>, robots/panda_grid.hh:39-41), panda_X_Y (grid variants, metres)."""
+    if name == "panda":
+        return panda_grid(200, 200, 0, ctx)
+    if name.startswith("panda_"):
+        x, y = name.split("_")[1:3]
+        return panda_grid(int(x) * 100, int(y) * 100, 0, ctx)
+    return Robot(name, ctx=ctx)

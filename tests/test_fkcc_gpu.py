@@ -1,0 +1,121 @@
+"""GPU parity of the fkcc path against the reference compiled as an oracle (oracle/_ref).
+
+Bars (BASELINE.json north_star): sphere centres within 1e-5 m; verdicts identical except where the
+decisive clearance is within 1e-5 m of contact (those are counted and reported, not hidden).
+"""
+import numpy as np
+import pytest
+
+from mr_vamp_b200 import scenes
+from conftest import apply_ref
+
+pytestmark = pytest.mark.gpu
+
+BAND = 1e-5
+ROBOTS = ["sphere", "ur5", "panda", "fetch", "baxter"]
+REF_NAME = {"panda": "panda_0_0"}
+
+
+def _cfgs(robot, seed, n):
+    rng = np.random.default_rng(seed)
+    return (robot.lower_bounds + rng.random((n, robot.dimension), dtype=np.float32) * robot.ranges).astype(np.float32)
+
+
+def _compare(ok_gpu, margin, ok_ref, what):
+    diff = ok_gpu != ok_ref
+    hard = diff & (margin > BAND)
+    print(f"{what}: n={ok_ref.size} valid_ref={ok_ref.mean():.3f} differ={int(diff.sum())} "
+          f"in-band={int((diff & ~hard).sum())} hard={int(hard.sum())}")
+    assert hard.sum() == 0, f"{what}: {int(hard.sum())} verdict mismatches outside the {BAND} m band"
+
+
+@pytest.mark.parametrize("name", ROBOTS)
+def test_sphere_fk_centres(vb, ref, name):
+    robot = vb.Robot(name)
+    q = _cfgs(robot, 1, 4096)
+    got = robot.fk_batch(q)
+    want = ref.sphere_fk(REF_NAME.get(name, name), q)
+    err = np.abs(got[..., :3] - want[..., :3]).max()
+    print(f"{name}: max centre error {err:.3e} m")
+    assert err <= BAND
+    assert np.array_equal(got[..., 3], want[..., 3])
+
+
+@pytest.mark.parametrize("base", ["panda_0_0", "panda_1_0", "panda_2_2"])
+def test_panda_base_variants(vb, ref, base):
+    robot = vb.robot(base)
+    q = _cfgs(robot, 2, 1024)
+    err = np.abs(robot.fk_batch(q) - ref.sphere_fk(base, q)).max()
+    assert err <= BAND
+    off = robot.base
+    spec = scenes.cage(offset=off)
+    env = scenes.apply(spec, vb.Environment())
+    renv = apply_ref(spec, ref.Env())
+    ok, mg = robot.fkcc_batch(q, env, margin=True)
+    _compare(ok, mg, ref.fkcc(base, renv, q), f"{base} cage")
+
+
+@pytest.mark.parametrize("name", ROBOTS)
+@pytest.mark.parametrize("scene", ["empty", "cage", "clutter"])
+def test_fkcc_verdicts(vb, ref, name, scene):
+    robot = vb.Robot(name)
+    spec = {"empty": [], "cage": scenes.cage(), "clutter": scenes.random_scene(7)}[scene]
+    env = scenes.apply(spec, vb.Environment())
+    renv = apply_ref(spec, ref.Env())
+    q = _cfgs(robot, 3, 20000)
+    ok, mg = robot.fkcc_batch(q, env, margin=True)
+    ok2 = robot.fkcc_batch(q, env)
+    assert np.array_equal(ok, ok2), "margin and plain kernels disagree"
+    _compare(ok, mg, ref.fkcc(REF_NAME.get(name, name), renv, q, threads=8), f"{name}/{scene}")
+
+
+def test_cage_known_answers(vb):
+    # scripts/sphere_cage_example.py:10-13,67: start and goal are valid in the nominal cage
+    robot = vb.Robot("panda")
+    env = scenes.apply(scenes.cage(), vb.Environment())
+    assert robot.validate(scenes.CAGE_START, env) and robot.validate(scenes.CAGE_GOAL, env)
+    # scripts/cpp/test_panda_fk.cc:81-83,121-126: a sphere at the base of the origin robot collides with it
+    # and not with the robot at (2, 2, 0), and vice versa (evaluated at the cage start configuration;
+    # the all-zero configuration of that script is in self collision for every base)
+    q = np.asarray(scenes.CAGE_START, dtype=np.float32)
+    origin, offset = robot, vb.robot("panda_2_2")
+    e2 = vb.Environment()
+    e2.add_sphere(vb.Sphere([0.05, 0.05, 0.05], 0.1))
+    assert not origin.fkcc_batch(q, e2)[0] and offset.fkcc_batch(q, e2)[0]
+    e3 = vb.Environment()
+    e3.add_sphere(vb.Sphere([2.05, 2.05, 0.05], 0.1))
+    assert origin.fkcc_batch(q, e3)[0] and not offset.fkcc_batch(q, e3)[0]
+    e4 = vb.Environment()
+    e4.add_sphere(vb.Sphere([5.0, 5.0, 0.5], 0.3))
+    assert origin.fkcc_batch(q, e4)[0] and offset.fkcc_batch(q, e4)[0]
+    assert not origin.fkcc_batch(np.zeros(7, dtype=np.float32), e4)[0]  # self collision at q = 0
+
+
+@pytest.mark.parametrize("name", ROBOTS)
+@pytest.mark.parametrize("scene", ["empty", "cage", "clutter"])
+def test_validate_motion(vb, ref, name, scene):
+    robot = vb.Robot(name)
+    spec = {"empty": [], "cage": scenes.cage(), "clutter": scenes.random_scene(11)}[scene]
+    env = scenes.apply(spec, vb.Environment())
+    renv = apply_ref(spec, ref.Env())
+    n = 3000
+    a = _cfgs(robot, 5, n)
+    rng = np.random.default_rng(6)
+    step = rng.normal(size=(n, robot.dimension)).astype(np.float32)
+    step *= (rng.uniform(0.02, 1.5, (n, 1)) / np.linalg.norm(step, axis=1, keepdims=True)).astype(np.float32)
+    b = np.clip(a + step, robot.lower_bounds, robot.lower_bounds + robot.ranges).astype(np.float32)
+    b[: n // 10] = _cfgs(robot, 8, n // 10)  # some long (PRM-shaped) edges
+    ok, mg = robot.validate_motion_batch(a, b, env, margin=True)
+    ok2 = robot.validate_motion_batch(a, b, env)
+    assert np.array_equal(ok, ok2)
+    _compare(ok, mg, ref.validate_motion(REF_NAME.get(name, name), renv, a, b, threads=8), f"{name}/{scene} edges")
+
+
+def test_validate_joint_limits(vb, ref):
+    robot = vb.Robot("panda")
+    q = _cfgs(robot, 9, 2000)
+    q[::3] += np.float32(0.5)  # push a third of them around/over the limits
+    env = vb.Environment()
+    got = robot.validate_batch(q, env)
+    want = ref.validate("panda_0_0", ref.Env(), q)
+    assert np.array_equal(got, want)
