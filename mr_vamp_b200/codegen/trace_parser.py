@@ -272,7 +272,7 @@ _ROBOT_META = {
     "ur5": (6, 32),
     "fetch": (8, 32),
     "baxter": (14, 64),
-    "sphere": (3, 1),
+    "sphere": (3, 32),
 }
 
 

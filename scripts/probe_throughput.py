@@ -9,8 +9,11 @@ from mr_vamp_b200 import api, scenes
 
 ctx = api.default_context()
 L = api.lib()
-for name, spec_name in [("panda", "empty"), ("panda", "cage"), ("panda", "clutter"), ("ur5", "clutter"),
-                        ("fetch", "clutter"), ("baxter", "clutter"), ("sphere", "clutter")]:
+cases = [("panda", "empty"), ("panda", "cage"), ("panda", "clutter"), ("ur5", "clutter"),
+         ("fetch", "clutter"), ("baxter", "clutter"), ("sphere", "clutter")]
+if len(sys.argv) > 2:
+    cases = [(sys.argv[1], sys.argv[2])]
+for name, spec_name in cases:
     robot = api.Robot(name)
     spec = {"empty": [], "cage": scenes.cage(), "clutter": scenes.random_scene(7)}[spec_name]
     env = scenes.apply(spec, api.Environment())
@@ -24,5 +27,5 @@ for name, spec_name in [("panda", "empty"), ("panda", "cage"), ("panda", "clutte
         api._check(L.vb_timer_stop(ctx.handle, 0, C.byref(ms)))
     cnt = C.c_uint64()
     api._check(L.vb_popcount_d(ctx.handle, 0, bits, n, C.byref(cnt)))
-    print(f"{name:7s} {spec_name:8s} n={n} {ms.value:8.2f} ms  {n / ms.value / 1e6:8.2f} Mcfg/s  valid={cnt.value / n:.3f}", flush=True)
+    print(f"{name:7s} {spec_name:8s} n={n} {ms.value:8.2f} ms  {n / ms.value / 1e3:8.2f} Mcfg/s  valid={cnt.value / n:.3f}", flush=True)
     api._check(L.vb_dev_free(ctx.handle, 0, bits))
