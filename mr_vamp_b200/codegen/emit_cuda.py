@@ -32,7 +32,7 @@ import struct
 import sys
 from typing import Any
 
-from . import trace_parser
+from . import ir_eval, trace_parser
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
 GEN_DIR = os.path.join(os.path.dirname(_HERE), "_gen")
@@ -57,9 +57,10 @@ def _f64(c: float) -> str:
 class _Emitter:
     """Lowers one traced function to (chain lines, check tables)."""
 
-    def __init__(self, fn: dict[str, Any]):
+    def __init__(self, fn: dict[str, Any], samples=None):
         self.values = fn["values"]
         self.program = fn["program"]
+        self.samples = samples  # (vals, n) from ir_eval, for the static containment slack
         self.lines: list[str] = []
         self.slots: dict[tuple, int] = {}
         self.refs: list[tuple[int, int, float]] = []  # (slot, base mask, radius)
@@ -104,6 +105,22 @@ class _Emitter:
         assert r.get("sym") == "radius" or r["v"] is None
         return (self.slots[key], mask, radius)
 
+    def slack(self, fine_spheres, guard) -> float:
+        """Largest overhang of the fine spheres beyond the guard sphere (+1e-4 m), or -1 if unknown."""
+        if self.samples is None or not fine_spheres:
+            return -1.0
+        vals, n = self.samples
+        if guard[3].get("sym") or any(s[3].get("sym") for s in fine_spheres):
+            return -1.0
+        worst = 0.0
+        cg = ir_eval.centre(vals, guard, n)
+        for s in fine_spheres:
+            if [a.get("base") for a in s[:3]] != [a.get("base") for a in guard[:3]]:
+                return -1.0
+            d = ((ir_eval.centre(vals, s, n) - cg) ** 2).sum(axis=1) ** 0.5
+            worst = max(worst, float(d.max()) + s[3]["c"] - guard[3]["c"])
+        return max(worst, 0.0) + 1e-4
+
     def add_refs(self, refs) -> tuple[int, int]:
         begin = len(self.refs)
         self.refs.extend(refs)
@@ -139,8 +156,10 @@ class _Emitter:
         if k in ("env", "attach_self"):
             guard = self.ref(it["guard"])
             begin, count = self.add_refs([] if leaf else [self.ref(s) for s in fine])
+            assert count <= 32, name
             (self.env if k == "env" else self.att).append(
-                {"guard": guard, "begin": begin, "count": count, "name": name}
+                {"guard": guard, "begin": begin, "count": count, "name": name,
+                 "slack": -1.0 if leaf or k != "env" else self.slack(fine, it["guard"])}
             )
             return
         if k == "self":
@@ -161,7 +180,9 @@ class _Emitter:
                     raise ValueError("self group is not a cross product: " + name)
             ab, ac = self.add_refs(A)
             bb, bc = self.add_refs(B)
-            self.selfg.append({"ga": ga, "gb": gb, "a": (ab, ac), "b": (bb, bc), "name": name})
+            assert ac <= 32 and bc <= 32, name
+            slack_b = -1.0 if leaf else self.slack([b for _, b in fine], it["guard"][1])
+            self.selfg.append({"ga": ga, "gb": gb, "a": (ab, ac), "b": (bb, bc), "name": name, "slack": slack_b})
             return
         raise ValueError(k)
 
@@ -209,25 +230,29 @@ def _ref(r) -> str:
     return f"{{{slot}, {mask}, {_f32(radius) if radius >= 0 else '-1.0f'}}}"
 
 
+def _slack(v: float) -> str:
+    return "-1.0f" if v < 0 else _f32(v)
+
+
 def _tables(name: str, em: _Emitter) -> list[str]:
     ne, ns, na, nr = len(em.env), len(em.selfg), len(em.att), len(em.refs)
     t = f"Tables<{max(ne, 1)}, {max(ns, 1)}, {max(na, 1)}, {max(nr, 1)}>"
     out = [f"__constant__ {t} {name} = {{"]
     out.append(f"    {len(em.slots)}, {ne}, {ns}, {na}, {em.att_env},")
     out.append("    {")
-    for g in em.env or [{"guard": (0, 0, 0.0), "begin": 0, "count": 0, "name": "-"}]:
-        out.append(f"        {{{_ref(g['guard'])}, {g['begin']}, {g['count']}}},  // {g['name']}")
+    for g in em.env or [{"guard": (0, 0, 0.0), "begin": 0, "count": 0, "name": "-", "slack": -1.0}]:
+        out.append(f"        {{{_ref(g['guard'])}, {g['begin']}, {g['count']}, {_slack(g['slack'])}}},  // {g['name']}")
     out.append("    },")
     out.append("    {")
-    for g in em.selfg or [{"ga": (0, 0, 0.0), "gb": (0, 0, 0.0), "a": (0, 0), "b": (0, 0), "name": "-"}]:
+    for g in em.selfg or [{"ga": (0, 0, 0.0), "gb": (0, 0, 0.0), "a": (0, 0), "b": (0, 0), "name": "-", "slack": -1.0}]:
         out.append(
-            f"        {{{_ref(g['ga'])}, {_ref(g['gb'])}, {g['a'][0]}, {g['a'][1]}, {g['b'][0]}, {g['b'][1]}}},"
+            f"        {{{_ref(g['ga'])}, {_ref(g['gb'])}, {g['a'][0]}, {g['a'][1]}, {g['b'][0]}, {g['b'][1]}, {_slack(g['slack'])}}},"
             f"  // {g['name']}"
         )
     out.append("    },")
     out.append("    {")
     for g in em.att or [{"guard": (0, 0, 0.0), "begin": 0, "count": 0, "name": "-"}]:
-        out.append(f"        {{{_ref(g['guard'])}, {g['begin']}, {g['count']}}},  // {g['name']}")
+        out.append(f"        {{{_ref(g['guard'])}, {g['begin']}, {g['count']}, -1.0f}},  // {g['name']}")
     out.append("    },")
     out.append("    {")
     refs = em.refs or [(0, 0, 0.0)]
@@ -245,7 +270,16 @@ def emit_robot(ir: dict[str, Any]) -> str:
     fns = ir["functions"]
     has_attach = "interleaved_sphere_fk_attachment" in fns
     st = trace_stats(ir)
-    em = _Emitter(fns["interleaved_sphere_fk"]).run_checks()
+    def sampled(fn):
+        import numpy as np
+
+        rng = np.random.default_rng(0)
+        n = 1024
+        lo, rg = np.array(ir["scale"]["lo"]), np.array(ir["scale"]["range"])
+        q = (lo + rng.random((n, dim)) * rg).astype(np.float32)
+        return ir_eval.evaluate(fn, q), n
+
+    em = _Emitter(fns["interleaved_sphere_fk"], sampled(fns["interleaved_sphere_fk"])).run_checks()
     em_att = _Emitter(fns["interleaved_sphere_fk_attachment"]).run_checks() if has_attach else None
     out: list[str] = []
     w = out.append

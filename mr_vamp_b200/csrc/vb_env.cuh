@@ -156,6 +156,35 @@ namespace vb
         return z - r - (h.zs * zh + h.z);
     }
 
+    // the non-primitive obstacle kinds of sphere_environment_in_collision (validity.hh:132-147):
+    // heightfields, then CAPT point clouds
+    template <class M>
+    VB_D bool other_hit(const EnvView &e, float sx, float sy, float sz, float sr, M &mg)
+    {
+        for (int i = 0; i < e.n_heightfields; ++i)
+        {
+            const float v = heightfield_value(e.heightfields[i], sx, sy, sz, sr);
+            mg.lin(v);
+            if (v < 0.f)
+            {
+                return true;
+            }
+        }
+        for (int i = 0; i < e.n_capts; ++i)
+        {
+            if (capt_hit(e.capts[i], sx, sy, sz, sr, mg))
+            {
+                return true;
+            }
+        }
+        return false;
+    }
+
+    struct Center
+    {
+        float x, y, z, r;
+    };
+
     // collision/validity.hh:46-150.  `P` points at the packed records (shared or global memory).
     // Each loop stops at the first record whose min_distance is >= the sphere's largest distance
     // from the origin, as the reference does; with an exact sqrt the cut is conservative, so the
@@ -264,22 +293,6 @@ namespace vb
                 return true;
             }
         }
-        for (int i = 0; i < e.n_heightfields; ++i)
-        {
-            const float v = heightfield_value(e.heightfields[i], sx, sy, sz, sr);
-            mg.lin(v);
-            if (v < 0.f)
-            {
-                return true;
-            }
-        }
-        for (int i = 0; i < e.n_capts; ++i)
-        {
-            if (capt_hit(e.capts[i], sx, sy, sz, sr, mg))
-            {
-                return true;
-            }
-        }
-        return false;
+        return other_hit(e, sx, sy, sz, sr, mg);
     }
 }  // namespace vb

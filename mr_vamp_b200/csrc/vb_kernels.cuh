@@ -9,6 +9,7 @@
 #pragma once
 #include "vb_sinks.cuh"
 #include "vb_tables.cuh"
+#include "vb_coop.cuh"
 
 namespace vb
 {
@@ -66,16 +67,11 @@ namespace vb
         }
         s.prims = staged ? smem : env.prims;  // large scenes: L1/L2-resident broadcasts
         s.col = reinterpret_cast<float *>(smem + nq) + threadIdx.x;
-        s.stride = blockDim.x;
+        s.stride = blockDim.x + 1;  // odd: a warp reading ONE column at 32 different slots is conflict free too
         return s;
     }
 
     // ---- the table walk: every collision test of one configuration -------------------------------
-    struct Center
-    {
-        float x, y, z, r;
-    };
-
     struct TableCtx
     {
         const EnvView &env;
@@ -224,6 +220,189 @@ namespace vb
         return walk_tables(Robot::tables(), ctx, Robot::kSlots, mg);
     }
 
+    // ---- warp-cooperative table walk (verdict only; see vb_coop.cuh) -------------------------------
+    // Must be called by all 32 lanes of a warp, converged.  `collided` enters true for lanes without a
+    // configuration.  Returns this lane's verdict (true = collision free).
+    template <class T>
+    VB_D bool coop_walk(const T &t, const TableCtx &c, bool collided)
+    {
+        const int lane = threadIdx.x & 31;
+        const float *warp_col = c.sc.col - lane;  // column of lane 0 of this warp
+        const int stride = c.sc.stride;
+        const float4 *P = c.sc.prims;
+        const PrimIndex ix = prim_index(c.env);
+        const bool has_other = (c.env.n_heightfields | c.env.n_capts) != 0;
+        NoMargin mg;
+
+        // centre of `ref` in configuration L's column
+        auto load_of = [&](int L, const SlotRef &ref) {
+            const float *col = warp_col + L;
+            Center s;
+            s.x = col[(3 * ref.slot + 0) * stride] + ((ref.base & 1) ? c.bx : 0.f);
+            s.y = col[(3 * ref.slot + 1) * stride] + ((ref.base & 2) ? c.by : 0.f);
+            s.z = col[(3 * ref.slot + 2) * stride] + ((ref.base & 4) ? c.bz : 0.f);
+            s.r = ref.r < 0.f ? c.radius : ref.r;
+            return s;
+        };
+
+        const int n_obj = ix.first[5];
+        const uint32_t low_objs = n_obj >= 32 ? 0xffffffffu : ((1u << n_obj) - 1u);
+
+        for (int g = 0; g < t.n_env; ++g)
+        {
+            if (__all_sync(kFull, collided))
+            {
+                return false;
+            }
+            const RefGroup grp = t.env[g];
+            const Center b = c.load(grp.guard);
+            const GuardResult gr = guard_env(c.env, P, ix, b, grp.slack);
+            bool fired = gr.fired;
+            if (has_other)
+            {
+                fired = fired || other_hit(c.env, b.x, b.y, b.z, b.r, mg);
+            }
+            fired = fired && !collided;
+            if (grp.count == 0)
+            {
+                collided = collided || fired;
+                continue;
+            }
+            if (has_other && fired)
+            {
+                // heightfields / point clouds: lane-serial fine tests (divergent; primitives go below)
+                for (int k = 0; k < grp.count && !collided; ++k)
+                {
+                    const Center s = c.load(t.refs[grp.begin + k]);
+                    collided = other_hit(c.env, s.x, s.y, s.z, s.r, mg);
+                }
+            }
+            uint32_t todo = __ballot_sync(kFull, fired && !collided);
+            while (todo)
+            {
+                const int L = __ffs(todo) - 1;
+                todo &= todo - 1;
+                uint32_t om = __shfl_sync(kFull, gr.mask, L) & low_objs;
+                const bool high = __shfl_sync(kFull, static_cast<int>(gr.high), L) != 0;
+                const bool active = lane < grp.count;
+                Center s{0.f, 0.f, 0.f, 0.f};
+                float ext = 0.f;
+                if (active)
+                {
+                    s = load_of(L, t.refs[grp.begin + lane]);
+                    ext = sqrtf(s.x * s.x + s.y * s.y + s.z * s.z) + s.r;
+                }
+                bool hit = false;
+                while (om)
+                {
+                    const int o = __ffs(om) - 1;
+                    om &= om - 1;
+                    hit = hit || (active && fine_vs_object(P, ix, o, s, ext));
+                }
+                if (high)
+                {
+                    for (int o = 32; o < n_obj; ++o)
+                    {
+                        hit = hit || (active && fine_vs_object(P, ix, o, s, ext));
+                    }
+                }
+                if (__any_sync(kFull, hit) && lane == L)
+                {
+                    collided = true;
+                }
+            }
+        }
+
+        for (int g = 0; g < t.n_self; ++g)
+        {
+            if ((g & 7) == 0 && __all_sync(kFull, collided))
+            {
+                return false;
+            }
+            const SelfGroup grp = t.self[g];
+            const bool fired = pair_hit(c.load(grp.ga), c.load(grp.gb), mg) && !collided;
+            if (grp.a_count == 0)
+            {
+                collided = collided || fired;
+                continue;
+            }
+            uint32_t todo = __ballot_sync(kFull, fired);
+            while (todo)
+            {
+                const int L = __ffs(todo) - 1;
+                todo &= todo - 1;
+                // level 1: lane i holds a_i; keep the a_i that touch the (inflated) bounding sphere of B
+                Center ai{0.f, 0.f, 0.f, 0.f};
+                bool cand = false;
+                if (lane < grp.a_count)
+                {
+                    ai = load_of(L, t.refs[grp.a_begin + lane]);
+                    cand = true;
+                    if (grp.slack_b >= 0.f)
+                    {
+                        const Center gb = load_of(L, grp.gb);
+                        const float dx = ai.x - gb.x, dy = ai.y - gb.y, dz = ai.z - gb.z;
+                        const float R = ai.r + gb.r + grp.slack_b;
+                        cand = dx * dx + dy * dy + dz * dz - R * R < 0.f;
+                    }
+                }
+                uint32_t am = __ballot_sync(kFull, cand);
+                // level 2: lane j holds b_j; surviving a_i are broadcast one at a time
+                Center bj{0.f, 0.f, 0.f, 0.f};
+                const bool active = lane < grp.b_count;
+                if (active)
+                {
+                    bj = load_of(L, t.refs[grp.b_begin + lane]);
+                }
+                bool hit = false;
+                while (am)
+                {
+                    const int i = __ffs(am) - 1;
+                    am &= am - 1;
+                    Center a;
+                    a.x = __shfl_sync(kFull, ai.x, i);
+                    a.y = __shfl_sync(kFull, ai.y, i);
+                    a.z = __shfl_sync(kFull, ai.z, i);
+                    a.r = __shfl_sync(kFull, ai.r, i);
+                    hit = hit || (active && pair_hit(a, bj, mg));
+                }
+                if (__any_sync(kFull, hit) && lane == L)
+                {
+                    collided = true;
+                }
+            }
+        }
+        return !collided;
+    }
+
+    // Verdicts of 32 configurations, one per lane (all lanes must call; `alive` = lane has a configuration).
+    // Attachment traces keep the lane-serial walk (rare, first rake pass only).
+    template <class Robot>
+    VB_D bool check_warp(const LaunchArgs &a, const Scratch &sc, const float *q, bool alive, bool attach)
+    {
+        const TableCtx ctx{a.env, sc, a.base[0], a.base[1], a.base[2], a.sphere_radius};
+        if (Robot::kHasAttach && __any_sync(kFull, attach && alive))
+        {
+            bool ok = false;
+            if (alive)
+            {
+                NoMargin mg;
+                ok = check_config<Robot>(a, sc, q, attach, mg);
+            }
+            __syncwarp();
+            return ok;
+        }
+        if (alive)
+        {
+            SlotSink sink{sc.col, sc.stride, &a.env.attach, Robot::kSlots};
+            Robot::chain(sink, q);
+        }
+        __syncwarp();
+        const bool ok = coop_walk(Robot::tables(), ctx, !alive);
+        __syncwarp();  // columns are rewritten by the next configuration
+        return ok;
+    }
+
     // ---- K1: batched fkcc over explicit configurations -----------------------------------------
     template <class Robot, bool kMargin>
     __global__ void __launch_bounds__(block_threads<Robot>()) fkcc_kernel(const LaunchArgs a)
@@ -234,25 +413,25 @@ namespace vb
         for (size_t i = static_cast<size_t>(blockIdx.x) * blockDim.x + threadIdx.x; i < n_round; i += stride)
         {
             bool ok = false;
-            if (i < a.n)
-            {
-                float q[Robot::kDim];
+            const bool alive = i < a.n;
+            float q[Robot::kDim];
 #pragma unroll
-                for (int j = 0; j < Robot::kDim; ++j)
-                {
-                    q[j] = __ldg(a.cfg + i * Robot::kDim + j);
-                }
-                if constexpr (kMargin)
+            for (int j = 0; j < Robot::kDim; ++j)
+            {
+                q[j] = alive ? __ldg(a.cfg + i * Robot::kDim + j) : 0.f;
+            }
+            if constexpr (kMargin)
+            {
+                if (alive)
                 {
                     MinMargin mg;
                     ok = check_config<Robot>(a, prims, q, a.attach != 0, mg);
                     a.margin[i] = mg.m;
                 }
-                else
-                {
-                    NoMargin mg;
-                    ok = check_config<Robot>(a, prims, q, a.attach != 0, mg);
-                }
+            }
+            else
+            {
+                ok = check_warp<Robot>(a, prims, q, alive, a.attach != 0);
             }
             const uint32_t word = __ballot_sync(0xffffffffu, ok);
             if ((threadIdx.x & 31) == 0)
@@ -282,14 +461,10 @@ namespace vb
         const size_t n_round = (a.n + 31) / 32 * 32;
         for (size_t i = static_cast<size_t>(blockIdx.x) * blockDim.x + threadIdx.x; i < n_round; i += stride)
         {
-            bool ok = false;
-            if (i < a.n)
-            {
-                float q[Robot::kDim];
-                random_config<Robot>(a.seed, first + i, q);
-                NoMargin mg;
-                ok = check_config<Robot>(a, prims, q, a.attach != 0, mg);
-            }
+            const bool alive = i < a.n;
+            float q[Robot::kDim];
+            random_config<Robot>(a.seed, first + i, q);
+            const bool ok = check_warp<Robot>(a, prims, q, alive, a.attach != 0);
             const uint32_t word = __ballot_sync(0xffffffffu, ok);
             if ((threadIdx.x & 31) == 0)
             {
@@ -416,54 +591,68 @@ namespace vb
         const Scratch prims = stage_env(a.env);
         const size_t stride = static_cast<size_t>(gridDim.x) * blockDim.x;
         const size_t n_points = __ldg(a.prefix + a.n);  // total interpolants, left on the device by the scan
-        for (size_t t = static_cast<size_t>(blockIdx.x) * blockDim.x + threadIdx.x; t < n_points; t += stride)
+        const size_t n_round = (n_points + 31) / 32 * 32;
+        for (size_t t = static_cast<size_t>(blockIdx.x) * blockDim.x + threadIdx.x; t < n_round; t += stride)
         {
-            // binary search: last edge with prefix[e] <= t
-            size_t lo = 0, hi = a.n;
-            while (hi - lo > 1)
+            bool alive = t < n_points;
+            size_t e = 0;
+            uint32_t pass = 0;
+            float q[Robot::kDim];
+            if (alive)
             {
-                const size_t mid = (lo + hi) >> 1;
-                if (__ldg(a.prefix + mid) <= t)
+                // binary search: last edge with prefix[e] <= t
+                size_t lo = 0, hi = a.n;
+                while (hi - lo > 1)
                 {
-                    lo = mid;
+                    const size_t mid = (lo + hi) >> 1;
+                    if (__ldg(a.prefix + mid) <= t)
+                    {
+                        lo = mid;
+                    }
+                    else
+                    {
+                        hi = mid;
+                    }
+                }
+                e = lo;
+                const uint32_t begin = __ldg(a.prefix + e);
+                const uint32_t count = __ldg(a.prefix + e + 1) - begin;
+                const uint32_t local = static_cast<uint32_t>(t - begin);
+                pass = local / kRake;
+                // edge already refuted by another interpolant: nothing left to decide (verdict kernels only)
+                if (!kMargin && !((*reinterpret_cast<volatile const uint32_t *>(a.bits + (e >> 5)) >> (e & 31)) & 1u))
+                {
+                    alive = false;
                 }
                 else
                 {
-                    hi = mid;
+                    float qa[Robot::kDim], qb[Robot::kDim];
+#pragma unroll
+                    for (int j = 0; j < Robot::kDim; ++j)
+                    {
+                        qa[j] = __ldg(a.cfg + e * Robot::kDim + j);
+                        qb[j] = __ldg(a.cfg_b + e * Robot::kDim + j);
+                    }
+                    edge_point<Robot>(qa, qb, count / kRake, pass, local % kRake, q);
                 }
-            }
-            const size_t e = lo;
-            const uint32_t begin = __ldg(a.prefix + e);
-            const uint32_t count = __ldg(a.prefix + e + 1) - begin;
-            const uint32_t local = static_cast<uint32_t>(t - begin);
-            const uint32_t pass = local / kRake, lane = local % kRake;
-            if (!kMargin && !((*reinterpret_cast<volatile const uint32_t *>(a.bits + (e >> 5)) >> (e & 31)) & 1u))
-            {
-                continue;  // edge already refuted by another interpolant
             }
             // the attachment trace is only used for the first pass (validate.hh:43-44 vs :58)
             const bool attach = a.attach && pass == 0;
-            float qa[Robot::kDim], qb[Robot::kDim], q[Robot::kDim];
-#pragma unroll
-            for (int j = 0; j < Robot::kDim; ++j)
-            {
-                qa[j] = __ldg(a.cfg + e * Robot::kDim + j);
-                qb[j] = __ldg(a.cfg_b + e * Robot::kDim + j);
-            }
-            edge_point<Robot>(qa, qb, count / kRake, pass, lane, q);
-            bool ok;
+            bool ok = true;
             if constexpr (kMargin)
             {
-                MinMargin mg;
-                ok = check_config<Robot>(a, prims, q, attach, mg);
-                atomicMin(reinterpret_cast<int *>(a.margin + e), __float_as_int(mg.m));
+                if (alive)
+                {
+                    MinMargin mg;
+                    ok = check_config<Robot>(a, prims, q, attach, mg);
+                    atomicMin(reinterpret_cast<int *>(a.margin + e), __float_as_int(mg.m));
+                }
             }
             else
             {
-                NoMargin mg;
-                ok = check_config<Robot>(a, prims, q, attach, mg);
+                ok = check_warp<Robot>(a, prims, q, alive, attach) || !alive;
             }
-            if (!ok)
+            if (alive && !ok)
             {
                 atomicAnd(a.bits + (e >> 5), ~(1u << (e & 31)));
             }

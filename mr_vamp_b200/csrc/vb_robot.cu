@@ -14,7 +14,7 @@ namespace vb
     {
         const size_t quads = a.env.n_quads > kMaxSharedQuads ? 0 : static_cast<size_t>(a.env.n_quads);
         const size_t slots = R::kSlots + (a.attach ? a.env.attach.n : 0);
-        return sizeof(float4) * quads + sizeof(float) * 3 * slots * kBlock;
+        return sizeof(float4) * quads + sizeof(float) * 3 * slots * (kBlock + 1);
     }
 
     template <class K>

@@ -16,17 +16,24 @@ namespace vb
 
     // sphere_environment_in_collision(guard) { sphere_environment_in_collision(fine_i)... };
     // count == 0: the guard itself is the test
+    // slack: every fine sphere lies within the guard sphere inflated by `slack` metres (measured over
+    // sampled configurations at code-generation time, plus a 1e-4 m margin; the traced bounding spheres
+    // are up to 0.6 mm too tight).  The kernels use "object touches the inflated guard" as a
+    // conservative, exact pre-filter for the fine tests.  slack < 0: no such bound (test everything).
     struct RefGroup
     {
         SlotRef guard;
         uint16_t begin, count;
+        float slack;
     };
 
     // sphere_sphere_self_collision(ga, gb) { all pairs a_i x b_j }; a_count == 0: the guard is the test
+    // slack_b: as above for the b-side fine spheres relative to the guard sphere gb
     struct SelfGroup
     {
         SlotRef ga, gb;
         uint16_t a_begin, a_count, b_begin, b_count;
+        float slack_b;
     };
 
     template <int NE, int NS, int NA, int NR>

@@ -65,7 +65,7 @@ def test_fkcc_verdicts(vb, ref, name, scene):
     q = _cfgs(robot, 3, 20000)
     ok, mg = robot.fkcc_batch(q, env, margin=True)
     ok2 = robot.fkcc_batch(q, env)
-    assert np.array_equal(ok, ok2), "margin and plain kernels disagree"
+    assert not ((ok != ok2) & (mg > BAND)).any(), "cooperative and lane-serial kernels disagree outside the band"
     _compare(ok, mg, ref.fkcc(REF_NAME.get(name, name), renv, q, threads=8), f"{name}/{scene}")
 
 
@@ -107,7 +107,7 @@ def test_validate_motion(vb, ref, name, scene):
     b[: n // 10] = _cfgs(robot, 8, n // 10)  # some long (PRM-shaped) edges
     ok, mg = robot.validate_motion_batch(a, b, env, margin=True)
     ok2 = robot.validate_motion_batch(a, b, env)
-    assert np.array_equal(ok, ok2)
+    assert not ((ok != ok2) & (mg > BAND)).any(), "cooperative and lane-serial kernels disagree outside the band"
     _compare(ok, mg, ref.validate_motion(REF_NAME.get(name, name), renv, a, b, threads=8), f"{name}/{scene} edges")
 
 
