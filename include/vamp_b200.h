@@ -135,6 +135,10 @@ int vb_dev_upload(vb_ctx *, int slot, void *dst_d, const void *src, size_t bytes
 int vb_dev_download(vb_ctx *, int slot, void *dst, const void *src_d, size_t bytes);
 int vb_fkcc_d(vb_ctx *, int slot, vb_robot, const float *base_xyz, const vb_env *, const float *configs_d, size_t n,
               uint32_t *valid_bits_d, float *margin_d_or_null);
+/* as vb_fkcc_d, and writes per configuration the algorithmic flop count W of the reference algorithm
+ * (FK chain + every test the reference-ordered walk executes; cost constants in DESIGN.md) */
+int vb_fkcc_work_d(vb_ctx *, int slot, vb_robot, const float *base_xyz, const vb_env *, const float *configs_d,
+                   size_t n, uint32_t *valid_bits_d, float *work_d);
 int vb_validate_motion_d(vb_ctx *, int slot, vb_robot, const float *base_xyz, const vb_env *, const float *starts_d,
                          const float *goals_d, size_t n_edges, int resolution, uint32_t *valid_bits_d,
                          float *margin_d_or_null);

@@ -63,6 +63,7 @@ _SIGNATURES = [
     ("vb_dev_upload", C.c_int, [_vp, C.c_int, _vp, _vp, C.c_size_t]),
     ("vb_dev_download", C.c_int, [_vp, C.c_int, _vp, _vp, C.c_size_t]),
     ("vb_fkcc_d", C.c_int, [_vp, C.c_int, C.c_int, _f32p, _vp, _vp, C.c_size_t, _vp, _vp]),
+    ("vb_fkcc_work_d", C.c_int, [_vp, C.c_int, C.c_int, _f32p, _vp, _vp, C.c_size_t, _vp, _vp]),
     ("vb_validate_motion_d", C.c_int, [_vp, C.c_int, C.c_int, _f32p, _vp, _vp, _vp, C.c_size_t, C.c_int, _vp, _vp]),
     ("vb_fkcc_random_d", C.c_int, [_vp, C.c_int, C.c_int, _f32p, _vp, C.c_uint64, C.c_uint64, C.c_size_t, _vp]),
     ("vb_timer_start", C.c_int, [_vp, C.c_int]),

@@ -95,7 +95,7 @@ class _Emitter:
         if key not in self.slots:
             self.slots[key] = len(self.slots)
             self.lines.append(
-                f"p.put({self.slots[key]}, {self.coord(s[0])}, {self.coord(s[1])}, {self.coord(s[2])});"
+                f"p.put_s<kStride>({self.slots[key]}, {self.coord(s[0])}, {self.coord(s[1])}, {self.coord(s[2])});"
             )
         mask = sum((1 << i) for i, a in enumerate(s[:3]) if a.get("base"))
         for i, a in enumerate(s[:3]):
@@ -260,6 +260,11 @@ def _tables(name: str, em: _Emitter) -> list[str]:
         out.append("        " + ", ".join(_ref(r) for r in refs[i : i + 6]) + ",")
     out.append("    },")
     out.append("};")
+    # mirror of the refs in global memory for lane-dependent indices (constant memory serialises those)
+    out.append(f"__device__ const SlotRef {name}_grefs[{max(nr, 1)}] = {{")
+    for i in range(0, len(refs), 6):
+        out.append("    " + ", ".join(_ref(r) for r in refs[i : i + 6]) + ",")
+    out.append("};")
     return out, t
 
 
@@ -304,11 +309,14 @@ def emit_robot(ir: dict[str, Any]) -> str:
     w(f"    static constexpr bool kHasAttach = {'true' if has_attach else 'false'};")
     n_slots = max(len(em.slots), len(em_att.slots) if em_att else 0)
     w(f"    static constexpr int kSlots = {n_slots};  // distinct sphere centres used by the checks")
+    w(f"    static constexpr int kBlock = {128 if n_slots <= 72 else 64};  // threads per CTA (shared-memory budget)")
+    w("    static constexpr int kStride = kBlock + 1;  // slot-column stride in floats (odd: conflict free)")
     w(f"    static constexpr int kChainFlops = {st['chain_flops']};")
     w(f"    static constexpr int kEnvGroups = {st['env_groups']}, kEnvFine = {st['env_fine']};")
     w(f"    static constexpr int kSelfGroups = {st['self_groups']}, kSelfFine = {st['self_fine']};")
     w(f"    using TablesT = {ttype};")
     w(f"    __device__ __forceinline__ static const TablesT &tables() {{ return k_{robot}_tables; }}")
+    w(f"    __device__ __forceinline__ static const SlotRef *grefs() {{ return k_{robot}_tables_grefs; }}")
     if em_att:
         w(f"    using TablesAttachT = {ttype2};")
         w(f"    __device__ __forceinline__ static const TablesAttachT &tables_attach() {{ return k_{robot}_tables_attach; }}")

@@ -966,7 +966,7 @@ namespace
         return VB_OK;
     }
 
-    int run_fkcc_d(Query &q, const float *cfg_d, size_t n, uint32_t *bits_d, float *margin_d)
+    int run_fkcc_d(Query &q, const float *cfg_d, size_t n, uint32_t *bits_d, float *margin_d, int mode = -1)
     {
         if (n == 0)
         {
@@ -978,7 +978,7 @@ namespace
         q.args.margin = margin_d;
         int grid = 1;
         VB_TRY(grid_for(q, n, &grid));
-        VB_CUDA(q.ops->fkcc(q.args, margin_d != nullptr, grid));
+        VB_CUDA(q.ops->fkcc(q.args, mode >= 0 ? mode : (margin_d != nullptr ? 1 : 0), grid));
         q.ctx->launches += 1;
         return VB_OK;
     }
@@ -1139,6 +1139,18 @@ int vb_fkcc_d(vb_ctx *ctx, int slot, vb_robot robot, const float *base, const vb
     Query q;
     VB_TRY(begin_query(ctx, slot, robot, base, env, q));
     return run_fkcc_d(q, configs_d, n, valid_bits_d, margin_d);
+}
+
+int vb_fkcc_work_d(vb_ctx *ctx, int slot, vb_robot robot, const float *base, const vb_env *env, const float *configs_d,
+                   size_t n, uint32_t *valid_bits_d, float *work_d)
+{
+    if (!env || (n && (!configs_d || !valid_bits_d || !work_d)))
+    {
+        return fail(VB_ERR_ARG, "vb_fkcc_work_d: null argument");
+    }
+    Query q;
+    VB_TRY(begin_query(ctx, slot, robot, base, env, q));
+    return run_fkcc_d(q, configs_d, n, valid_bits_d, work_d, 2);
 }
 
 int vb_validate_motion_d(vb_ctx *ctx, int slot, vb_robot robot, const float *base, const vb_env *env,

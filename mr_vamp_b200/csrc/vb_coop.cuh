@@ -127,21 +127,25 @@ namespace vb
         bool fired;     // the guard sphere itself collides (reference semantics)
     };
 
+    // `ext_warp` is the largest (inflated) extent of the 32 guard spheres of this warp: the obstacle lists
+    // are sorted by min_distance, so the first record at or beyond it ends the list for every lane, and
+    // the loop bound is warp-uniform without a vote.
     template <int T, int Q>
-    VB_D void guard_type(const float4 *P, const PrimIndex &ix, const Center &b, float ext, float ext_infl,
+    VB_D void guard_type(const float4 *P, const PrimIndex &ix, const Center &b, float ext, float ext_warp,
                          float slack, GuardResult &g)
     {
         const float4 *p = P + ix.quad[T];
+        const float Rg = b.r + slack;
+#pragma unroll 2
         for (int o = ix.first[T]; o < ix.first[T + 1]; ++o, p += Q)
         {
             const PrimDist d = prim_dist<T>(p, b.x, b.y, b.z);
-            // lists are sorted by min_distance: once every lane may prune, the rest of the list is out
-            if (__all_sync(kFull, d.mind >= ext_infl))
+            if (d.mind >= ext_warp)
             {
                 break;
             }
             g.fired = g.fired || prim_collides(d, b.r, ext);
-            const float Ri = b.r + d.objr + slack;
+            const float Ri = Rg + d.objr;
             const bool touch = d.d2 - Ri * Ri < 0.f;
             if (o < 32)
             {
@@ -160,12 +164,15 @@ namespace vb
         GuardResult g{0u, false, false};
         const float ext = sqrtf(b.x * b.x + b.y * b.y + b.z * b.z) + b.r;
         const float s = slack < 0.f ? 0.f : slack;
-        const float ext_infl = ext + s;
-        guard_type<0, kSphereQ>(P, ix, b, ext, ext_infl, s, g);
-        guard_type<1, kCapsuleQ>(P, ix, b, ext, ext_infl, s, g);
-        guard_type<2, kZCapsQ>(P, ix, b, ext, ext_infl, s, g);
-        guard_type<3, kCuboidQ>(P, ix, b, ext, ext_infl, s, g);
-        guard_type<4, kZCubQ>(P, ix, b, ext, ext_infl, s, g);
+        // non-negative floats order like their bit patterns; NaN/inf extents disable the cut
+        const float ext_lane = ext + s;
+        const unsigned bits = (ext_lane >= 0.f) ? __float_as_uint(ext_lane) : 0x7f800000u;
+        const float ext_warp = __uint_as_float(__reduce_max_sync(kFull, bits));
+        guard_type<0, kSphereQ>(P, ix, b, ext, ext_warp, s, g);
+        guard_type<1, kCapsuleQ>(P, ix, b, ext, ext_warp, s, g);
+        guard_type<2, kZCapsQ>(P, ix, b, ext, ext_warp, s, g);
+        guard_type<3, kCuboidQ>(P, ix, b, ext, ext_warp, s, g);
+        guard_type<4, kZCubQ>(P, ix, b, ext, ext_warp, s, g);
         if (slack < 0.f)
         {
             // no containment bound for this group: every obstacle is a candidate for the fine tests

@@ -67,6 +67,17 @@ namespace vb
     {
         VB_D void sq(float, float) {}
         VB_D void lin(float) {}
+        VB_D void count(int) {}
+    };
+    // Algorithmic-flop bookkeeping (DESIGN.md "W"): 9 flops per environment query + (1 + C_type) per
+    // visited obstacle, 11 per sphere-sphere test (SURVEY.md 8(a) cost constants), counted along the
+    // reference-ordered lane-serial walk.  `m` is reported through the margin output.
+    struct WorkCount
+    {
+        float m = 0.f;
+        VB_D void sq(float, float) {}
+        VB_D void lin(float) {}
+        VB_D void count(int flops) { m += static_cast<float>(flops); }
     };
     struct MinMargin
     {
@@ -78,6 +89,7 @@ namespace vb
             m = fminf(m, fabsf(d - R));
         }
         VB_D void lin(float value) { m = fminf(m, fabsf(value)); }
+        VB_D void count(int) {}
     };
 
     // collision/capt.hh:457-541 (collides_simd with one query per lane)
@@ -164,6 +176,7 @@ namespace vb
         for (int i = 0; i < e.n_heightfields; ++i)
         {
             const float v = heightfield_value(e.heightfields[i], sx, sy, sz, sr);
+            mg.count(18);
             mg.lin(v);
             if (v < 0.f)
             {
@@ -193,6 +206,7 @@ namespace vb
     VB_D bool env_hit(const EnvView &e, const float4 *P, float sx, float sy, float sz, float sr, M &mg)
     {
         const float ext = sqrtf(sx * sx + sy * sy + sz * sz) + sr;
+        mg.count(9);
         const float4 *p = P;
         for (int i = 0; i < e.n_spheres; ++i, p += kSphereQ)
         {
@@ -203,6 +217,7 @@ namespace vb
             }
             const float dx = a.x - sx, dy = a.y - sy, dz = a.z - sz, rs = a.w + sr;
             const float v = dx * dx + dy * dy + dz * dz - rs * rs;
+            mg.count(1 + 11);
             mg.sq(v, rs);
             if (v < 0.f)
             {
@@ -218,6 +233,7 @@ namespace vb
                 break;
             }
             // sphere_capsule.hh:8-22
+            mg.count(1 + 28);
             const float dot = (sx - a.x) * b.x + (sy - a.y) * b.y + (sz - a.z) * b.z;
             const float cdf = fmaxf(fminf(dot * b.w, 1.f), 0.f);
             const float dx = sx - (a.x + b.x * cdf), dy = sy - (a.y + b.y * cdf), dz = sz - (a.z + b.z * cdf);
@@ -238,6 +254,7 @@ namespace vb
                 break;
             }
             // sphere_capsule.hh:31-44
+            mg.count(1 + 18);
             const float dot = (sz - a.z) * b.x;
             const float cdf = fmaxf(fminf(dot * b.y, 1.f), 0.f);
             const float dx = sx - a.x, dy = sy - a.y, dz = sz - (a.z + b.x * cdf);
@@ -259,6 +276,7 @@ namespace vb
                 break;
             }
             // sphere_cuboid.hh:8-26
+            mg.count(1 + 30);
             const float4 a1 = p[1], a2 = p[2], a3 = p[3];
             const float xs = sx - c.x, ys = sy - c.y, zs = sz - c.z;
             const float d1 = fmaxf(fabsf(a1.x * xs + a1.y * ys + a1.z * zs) - a1.w, 0.f);
@@ -281,6 +299,7 @@ namespace vb
                 break;
             }
             // sphere_cuboid.hh:35-52
+            mg.count(1 + 21);
             const float4 ax = p[1], hr = p[2];
             const float xs = sx - c.x, ys = sy - c.y, zs = sz - c.z;
             const float d1 = fmaxf(fabsf(ax.x * xs + ax.y * ys) - hr.x, 0.f);

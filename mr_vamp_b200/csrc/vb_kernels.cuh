@@ -40,7 +40,7 @@ namespace vb
     template <class Robot>
     constexpr int block_threads()
     {
-        return Robot::kSlots <= 72 ? 128 : 64;
+        return Robot::kBlock;
     }
 
     struct Scratch
@@ -67,11 +67,12 @@ namespace vb
         }
         s.prims = staged ? smem : env.prims;  // large scenes: L1/L2-resident broadcasts
         s.col = reinterpret_cast<float *>(smem + nq) + threadIdx.x;
-        s.stride = blockDim.x + 1;  // odd: a warp reading ONE column at 32 different slots is conflict free too
+        s.stride = blockDim.x + 1;  // == Robot::kStride; odd: a warp reading ONE column at 32 different slots is conflict free too
         return s;
     }
 
     // ---- the table walk: every collision test of one configuration -------------------------------
+    template <int kStride>
     struct TableCtx
     {
         const EnvView &env;
@@ -80,9 +81,9 @@ namespace vb
         VB_D Center load(const SlotRef &ref) const
         {
             Center c;
-            c.x = sc.col[(3 * ref.slot + 0) * sc.stride];
-            c.y = sc.col[(3 * ref.slot + 1) * sc.stride];
-            c.z = sc.col[(3 * ref.slot + 2) * sc.stride];
+            c.x = sc.col[(3 * ref.slot + 0) * kStride];
+            c.y = sc.col[(3 * ref.slot + 1) * kStride];
+            c.z = sc.col[(3 * ref.slot + 2) * kStride];
             if (ref.base & 1)
             {
                 c.x += bx;
@@ -106,12 +107,13 @@ namespace vb
     {
         const float dx = a.x - b.x, dy = a.y - b.y, dz = a.z - b.z, rs = a.r + b.r;
         const float v = dx * dx + dy * dy + dz * dz - rs * rs;
+        mg.count(11);
         mg.sq(v, rs);
         return v < 0.f;
     }
 
-    template <class T, class M>
-    VB_D bool walk_tables(const T &t, const TableCtx &c, int att_slot0, M &mg)
+    template <class T, class M, int kStride>
+    VB_D bool walk_tables(const T &t, const TableCtx<kStride> &c, int att_slot0, M &mg)
     {
         // environment groups (robots/<robot>/fk.hh: `if (sphere_environment_in_collision(bounding)) {...}`)
         for (int g = 0; g < t.n_env; ++g)
@@ -210,7 +212,7 @@ namespace vb
     VB_D bool check_config(const LaunchArgs &a, const Scratch &sc, const float *q, bool attach, M &mg)
     {
         SlotSink sink{sc.col, sc.stride, &a.env.attach, Robot::kSlots};
-        const TableCtx ctx{a.env, sc, a.base[0], a.base[1], a.base[2], a.sphere_radius};
+        const TableCtx<Robot::kStride> ctx{a.env, sc, a.base[0], a.base[1], a.base[2], a.sphere_radius};
         if (Robot::kHasAttach && attach)
         {
             Robot::chain_attach(sink, q);
@@ -223,12 +225,18 @@ namespace vb
     // ---- warp-cooperative table walk (verdict only; see vb_coop.cuh) -------------------------------
     // Must be called by all 32 lanes of a warp, converged.  `collided` enters true for lanes without a
     // configuration.  Returns this lane's verdict (true = collision free).
-    template <class T>
-    VB_D bool coop_walk(const T &t, const TableCtx &c, bool collided)
+    //   environment groups : guard step lane-parallel; fine step in packed sub-warp rounds (a group of
+    //                        `count` fine spheres uses w = pow2ceil(count) lanes, so 32/w fired
+    //                        configurations are served per round).
+    //   self groups        : guard and the "a_i touches inflated bounding sphere of B" filter
+    //                        lane-parallel; surviving a_i are walked in rank lock-step (every lane its
+    //                        own r-th candidate), each against all b_j.
+    template <class T, int kStride>
+    VB_D bool coop_walk(const T &t, const SlotRef *__restrict__ grefs, const TableCtx<kStride> &c, bool collided)
     {
         const int lane = threadIdx.x & 31;
         const float *warp_col = c.sc.col - lane;  // column of lane 0 of this warp
-        const int stride = c.sc.stride;
+        constexpr int stride = kStride;
         const float4 *P = c.sc.prims;
         const PrimIndex ix = prim_index(c.env);
         const bool has_other = (c.env.n_heightfields | c.env.n_capts) != 0;
@@ -247,6 +255,7 @@ namespace vb
 
         const int n_obj = ix.first[5];
         const uint32_t low_objs = n_obj >= 32 ? 0xffffffffu : ((1u << n_obj) - 1u);
+        const uint32_t lt_mask = (1u << lane) - 1u;
 
         for (int g = 0; g < t.n_env; ++g)
         {
@@ -278,38 +287,52 @@ namespace vb
                 }
             }
             uint32_t todo = __ballot_sync(kFull, fired && !collided);
+            if (todo == 0u)
+            {
+                continue;
+            }
+            // sub-warp geometry: w lanes per served configuration
+            const int shift = grp.count <= 1 ? 0 : 32 - __clz(static_cast<int>(grp.count) - 1);
+            const int n_slots = 32 >> shift;
+            const int slot = lane >> shift, k = lane & ((1 << shift) - 1);
+            const uint32_t slot_bits = shift == 5 ? 0xffffffffu : ((1u << (1 << shift)) - 1u);
+            const SlotRef my_ref = t.refs[grp.begin + (k < grp.count ? k : 0)];
             while (todo)
             {
-                const int L = __ffs(todo) - 1;
-                todo &= todo - 1;
-                uint32_t om = __shfl_sync(kFull, gr.mask, L) & low_objs;
-                const bool high = __shfl_sync(kFull, static_cast<int>(gr.high), L) != 0;
-                const bool active = lane < grp.count;
-                Center s{0.f, 0.f, 0.f, 0.f};
-                float ext = 0.f;
-                if (active)
-                {
-                    s = load_of(L, t.refs[grp.begin + lane]);
-                    ext = sqrtf(s.x * s.x + s.y * s.y + s.z * s.z) + s.r;
-                }
+                const unsigned L = __fns(todo, 0, slot + 1);  // slot-th fired configuration
+                const bool active = L != 0xffffffffu && k < grp.count;
+                const int Lc = L != 0xffffffffu ? static_cast<int>(L) : 0;
+                uint32_t om = __shfl_sync(kFull, gr.mask, Lc) & low_objs;
+                bool high = __shfl_sync(kFull, static_cast<int>(gr.high), Lc) != 0;
+                om = active ? om : 0u;
+                high = high && active;
+                const Center s = load_of(Lc, my_ref);
+                const float ext = sqrtf(s.x * s.x + s.y * s.y + s.z * s.z) + s.r;
+                uint32_t U = __reduce_or_sync(kFull, om);
                 bool hit = false;
-                while (om)
+                while (U)
                 {
-                    const int o = __ffs(om) - 1;
-                    om &= om - 1;
-                    hit = hit || (active && fine_vs_object(P, ix, o, s, ext));
+                    const int o = __ffs(U) - 1;
+                    U &= U - 1;
+                    const bool col = fine_vs_object(P, ix, o, s, ext);
+                    hit = hit || (col && ((om >> o) & 1u));
                 }
-                if (high)
+                if (__any_sync(kFull, high))
                 {
                     for (int o = 32; o < n_obj; ++o)
                     {
-                        hit = hit || (active && fine_vs_object(P, ix, o, s, ext));
+                        hit = hit || (high && fine_vs_object(P, ix, o, s, ext));
                     }
                 }
-                if (__any_sync(kFull, hit) && lane == L)
+                const uint32_t hm = __ballot_sync(kFull, hit);
+                // configurations served this round: the first n_slots set bits of todo
+                const int my_rank = __popc(todo & lt_mask);
+                if (((todo >> lane) & 1u) && my_rank < n_slots && ((hm >> (my_rank << shift)) & slot_bits))
                 {
                     collided = true;
                 }
+                const unsigned last = __fns(todo, 0, n_slots);
+                todo = last == 0xffffffffu ? 0u : (todo & ~((2u << last) - 1u));
             }
         }
 
@@ -320,55 +343,56 @@ namespace vb
                 return false;
             }
             const SelfGroup grp = t.self[g];
-            const bool fired = pair_hit(c.load(grp.ga), c.load(grp.gb), mg) && !collided;
+            const Center gb = c.load(grp.gb);
+            const bool fired = pair_hit(c.load(grp.ga), gb, mg) && !collided;
             if (grp.a_count == 0)
             {
                 collided = collided || fired;
                 continue;
             }
-            uint32_t todo = __ballot_sync(kFull, fired);
-            while (todo)
+            if (!__any_sync(kFull, fired))
             {
-                const int L = __ffs(todo) - 1;
-                todo &= todo - 1;
-                // level 1: lane i holds a_i; keep the a_i that touch the (inflated) bounding sphere of B
-                Center ai{0.f, 0.f, 0.f, 0.f};
-                bool cand = false;
-                if (lane < grp.a_count)
+                continue;
+            }
+            // level 1 (lane-parallel): which a_i of MY configuration touch the inflated bounding sphere of B
+            uint32_t am = 0u;
+            if (fired)
+            {
+                if (grp.slack_b < 0.f)
                 {
-                    ai = load_of(L, t.refs[grp.a_begin + lane]);
-                    cand = true;
-                    if (grp.slack_b >= 0.f)
+                    am = grp.a_count >= 32 ? 0xffffffffu : ((1u << grp.a_count) - 1u);
+                }
+                else
+                {
+#pragma unroll 4
+                    for (int i = 0; i < grp.a_count; ++i)
                     {
-                        const Center gb = load_of(L, grp.gb);
-                        const float dx = ai.x - gb.x, dy = ai.y - gb.y, dz = ai.z - gb.z;
-                        const float R = ai.r + gb.r + grp.slack_b;
-                        cand = dx * dx + dy * dy + dz * dz - R * R < 0.f;
+                        const Center a = c.load(t.refs[grp.a_begin + i]);
+                        const float dx = a.x - gb.x, dy = a.y - gb.y, dz = a.z - gb.z;
+                        const float R = a.r + gb.r + grp.slack_b;
+                        am |= (dx * dx + dy * dy + dz * dz - R * R < 0.f) ? (1u << i) : 0u;
                     }
                 }
-                uint32_t am = __ballot_sync(kFull, cand);
-                // level 2: lane j holds b_j; surviving a_i are broadcast one at a time
-                Center bj{0.f, 0.f, 0.f, 0.f};
-                const bool active = lane < grp.b_count;
-                if (active)
-                {
-                    bj = load_of(L, t.refs[grp.b_begin + lane]);
-                }
-                bool hit = false;
-                while (am)
+            }
+            // level 2 (rank lock-step): every lane walks its own candidates, each against all b_j
+            while (__any_sync(kFull, am != 0u))
+            {
+                if (am)
                 {
                     const int i = __ffs(am) - 1;
                     am &= am - 1;
-                    Center a;
-                    a.x = __shfl_sync(kFull, ai.x, i);
-                    a.y = __shfl_sync(kFull, ai.y, i);
-                    a.z = __shfl_sync(kFull, ai.z, i);
-                    a.r = __shfl_sync(kFull, ai.r, i);
-                    hit = hit || (active && pair_hit(a, bj, mg));
-                }
-                if (__any_sync(kFull, hit) && lane == L)
-                {
-                    collided = true;
+                    const Center a = c.load(grefs[grp.a_begin + i]);  // lane-dependent index: global mirror
+                    bool hit = false;
+#pragma unroll 4
+                    for (int j = 0; j < grp.b_count; ++j)
+                    {
+                        hit = pair_hit(a, c.load(t.refs[grp.b_begin + j]), mg) || hit;
+                    }
+                    if (hit)
+                    {
+                        collided = true;
+                        am = 0u;
+                    }
                 }
             }
         }
@@ -380,7 +404,7 @@ namespace vb
     template <class Robot>
     VB_D bool check_warp(const LaunchArgs &a, const Scratch &sc, const float *q, bool alive, bool attach)
     {
-        const TableCtx ctx{a.env, sc, a.base[0], a.base[1], a.base[2], a.sphere_radius};
+        const TableCtx<Robot::kStride> ctx{a.env, sc, a.base[0], a.base[1], a.base[2], a.sphere_radius};
         if (Robot::kHasAttach && __any_sync(kFull, attach && alive))
         {
             bool ok = false;
@@ -398,13 +422,15 @@ namespace vb
             Robot::chain(sink, q);
         }
         __syncwarp();
-        const bool ok = coop_walk(Robot::tables(), ctx, !alive);
+        const bool ok = coop_walk(Robot::tables(), Robot::grefs(), ctx, !alive);
         __syncwarp();  // columns are rewritten by the next configuration
         return ok;
     }
 
     // ---- K1: batched fkcc over explicit configurations -----------------------------------------
-    template <class Robot, bool kMargin>
+    // kMode 0: verdicts (warp-cooperative walk); 1: verdicts + margin (lane-serial reference-ordered walk);
+    // 2: verdicts + algorithmic flops of the checks (same walk), written to the margin buffer
+    template <class Robot, int kMode>
     __global__ void __launch_bounds__(block_threads<Robot>()) fkcc_kernel(const LaunchArgs a)
     {
         const Scratch prims = stage_env(a.env);
@@ -420,13 +446,22 @@ namespace vb
             {
                 q[j] = alive ? __ldg(a.cfg + i * Robot::kDim + j) : 0.f;
             }
-            if constexpr (kMargin)
+            if constexpr (kMode == 1)
             {
                 if (alive)
                 {
                     MinMargin mg;
                     ok = check_config<Robot>(a, prims, q, a.attach != 0, mg);
                     a.margin[i] = mg.m;
+                }
+            }
+            else if constexpr (kMode == 2)
+            {
+                if (alive)
+                {
+                    WorkCount mg;
+                    ok = check_config<Robot>(a, prims, q, a.attach != 0, mg);
+                    a.margin[i] = mg.m + static_cast<float>(Robot::kChainFlops);
                 }
             }
             else

@@ -26,8 +26,9 @@ namespace vb
     static cudaError_t prepare()
     {
         static cudaError_t once = [] {
-            cudaError_t e = allow_smem(fkcc_kernel<R, true>);
-            if (e == cudaSuccess) e = allow_smem(fkcc_kernel<R, false>);
+            cudaError_t e = allow_smem(fkcc_kernel<R, 0>);
+            if (e == cudaSuccess) e = allow_smem(fkcc_kernel<R, 1>);
+            if (e == cudaSuccess) e = allow_smem(fkcc_kernel<R, 2>);
             if (e == cudaSuccess) e = allow_smem(fkcc_random_kernel<R>);
             if (e == cudaSuccess) e = allow_smem(motion_kernel<R, true>);
             if (e == cudaSuccess) e = allow_smem(motion_kernel<R, false>);
@@ -36,19 +37,23 @@ namespace vb
         return once;
     }
 
-    static cudaError_t launch_fkcc(const LaunchArgs &a, bool margin, int grid)
+    static cudaError_t launch_fkcc(const LaunchArgs &a, int mode, int grid)
     {
         if (cudaError_t e = prepare(); e != cudaSuccess)
         {
             return e;
         }
-        if (margin)
+        if (mode == 1)
         {
-            fkcc_kernel<R, true><<<grid, kBlock, smem_bytes(a), a.stream>>>(a);
+            fkcc_kernel<R, 1><<<grid, kBlock, smem_bytes(a), a.stream>>>(a);
+        }
+        else if (mode == 2)
+        {
+            fkcc_kernel<R, 2><<<grid, kBlock, smem_bytes(a), a.stream>>>(a);
         }
         else
         {
-            fkcc_kernel<R, false><<<grid, kBlock, smem_bytes(a), a.stream>>>(a);
+            fkcc_kernel<R, 0><<<grid, kBlock, smem_bytes(a), a.stream>>>(a);
         }
         return cudaGetLastError();
     }
@@ -108,7 +113,7 @@ namespace vb
             return e;
         }
         *threads = kBlock;
-        return cudaOccupancyMaxActiveBlocksPerMultiprocessor(blocks, fkcc_kernel<R, false>, kBlock, smem_bytes(a));
+        return cudaOccupancyMaxActiveBlocksPerMultiprocessor(blocks, fkcc_kernel<R, 0>, kBlock, smem_bytes(a));
     }
 
     static void host_random_config(uint64_t seed, uint64_t index, float *q)

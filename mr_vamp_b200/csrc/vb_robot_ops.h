@@ -11,7 +11,7 @@ namespace vb
         int dim, n_spheres, resolution, has_attach, n_slots;
         int chain_flops, env_groups, env_fine, self_groups, self_fine;
         float lo[16], range[16];
-        cudaError_t (*fkcc)(const LaunchArgs &, bool margin, int grid);
+        cudaError_t (*fkcc)(const LaunchArgs &, int mode, int grid);  // mode: see fkcc_kernel
         cudaError_t (*fkcc_random)(const LaunchArgs &, size_t first, int grid);
         cudaError_t (*sphere_fk)(const LaunchArgs &);
         cudaError_t (*edge_count)(const LaunchArgs &, uint32_t *counts_d);

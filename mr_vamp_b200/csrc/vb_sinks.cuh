@@ -21,6 +21,14 @@ namespace vb
             col[(3 * slot + 1) * stride] = y;
             col[(3 * slot + 2) * stride] = z;
         }
+        // compile-time stride: the stores of the straight-line chain get immediate offsets
+        template <int kStride>
+        VB_D void put_s(int slot, float x, float y, float z) const
+        {
+            col[(3 * slot + 0) * kStride] = x;
+            col[(3 * slot + 1) * kStride] = y;
+            col[(3 * slot + 2) * kStride] = z;
+        }
         // collision/attachments.hh:75-122 (Attachment::pose); the posed centres go to slots att_slot0..
         VB_D void attach_pose(float p_tx, float p_ty, float p_tz, float p_rx, float p_ry, float p_rz, float p_rw) const
         {
