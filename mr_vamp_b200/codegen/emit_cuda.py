@@ -63,6 +63,7 @@ class _Emitter:
         self.samples = samples  # (vals, n) from ir_eval, for the static containment slack
         self.lines: list[str] = []
         self.slots: dict[tuple, int] = {}
+        self.const_slots: set[int] = set()
         self.refs: list[tuple[int, int, float]] = []  # (slot, base mask, radius)
         self.env: list[dict[str, Any]] = []
         self.selfg: list[dict[str, Any]] = []
@@ -94,6 +95,8 @@ class _Emitter:
         key = tuple((a["v"] if a["v"] is not None else ("c", a["c"])) for a in s[:3])
         if key not in self.slots:
             self.slots[key] = len(self.slots)
+            if all(a["v"] is None for a in s[:3]):
+                self.const_slots.add(self.slots[key])
             self.lines.append(
                 f"p.put_s<kStride>({self.slots[key]}, {self.coord(s[0])}, {self.coord(s[1])}, {self.coord(s[2])});"
             )
@@ -120,6 +123,14 @@ class _Emitter:
             d = ((ir_eval.centre(vals, s, n) - cg) ** 2).sum(axis=1) ** 0.5
             worst = max(worst, float(d.max()) + s[3]["c"] - guard[3]["c"])
         return max(worst, 0.0) + 1e-4
+
+    def fire_rate(self, ga, gb) -> float:
+        """Fraction of the sampled configurations whose guard pair (ga, gb) overlaps."""
+        if self.samples is None:
+            return 0.0
+        vals, n = self.samples
+        d = ((ir_eval.centre(vals, ga, n) - ir_eval.centre(vals, gb, n)) ** 2).sum(axis=1) ** 0.5
+        return float((d < ga[3]["c"] + gb[3]["c"]).mean())
 
     def add_refs(self, refs) -> tuple[int, int]:
         begin = len(self.refs)
@@ -182,7 +193,9 @@ class _Emitter:
             bb, bc = self.add_refs(B)
             assert ac <= 32 and bc <= 32, name
             slack_b = -1.0 if leaf else self.slack([b for _, b in fine], it["guard"][1])
-            self.selfg.append({"ga": ga, "gb": gb, "a": (ab, ac), "b": (bb, bc), "name": name, "slack": slack_b})
+            dense = (not leaf) and self.fire_rate(it["guard"][0], it["guard"][1]) > 0.4
+            self.selfg.append({"ga": ga, "gb": gb, "a": (ab, ac), "b": (bb, bc), "name": name, "slack": slack_b,
+                               "dense": dense})
             return
         raise ValueError(k)
 
@@ -234,38 +247,235 @@ def _slack(v: float) -> str:
     return "-1.0f" if v < 0 else _f32(v)
 
 
-def _tables(name: str, em: _Emitter) -> list[str]:
-    ne, ns, na, nr = len(em.env), len(em.selfg), len(em.att), len(em.refs)
+def _tables(name: str, em: _Emitter, walk: bool = False) -> list[str]:
+    """Constant-memory check tables; with `walk` also the global-memory mirrors and work-unit tables of
+    the warp walk (vb_walk.cuh).  Returns (lines, table type, geometry dict)."""
+    refs = list(em.refs)
+    # work units: environment groups -> their fine refs; a leaf group -> a copy of its guard behind the refs
+    ref_group = [0xFFFF] * len(refs)
+    for gi, g in enumerate(em.env):
+        if g["count"] == 0:
+            g["ubegin"], g["ucount"] = len(refs), 1
+            refs.append(g["guard"])
+            ref_group.append(gi | 0x8000)
+        else:
+            g["ubegin"], g["ucount"] = g["begin"], g["count"]
+            for k in range(g["count"]):
+                ref_group[g["begin"] + k] = gi
+    units = []
+    for gi, g in enumerate(em.selfg):
+        g["unit0"] = len(units)
+        for i in range(g["a"][1]):
+            units.append((g["a"][0] + i, gi))
+    assert len(refs) < 2048 and len(units) < 2048, (name, len(refs), len(units))
+    ne, ns, na, nr = len(em.env), len(em.selfg), len(em.att), len(refs)
     t = f"Tables<{max(ne, 1)}, {max(ns, 1)}, {max(na, 1)}, {max(nr, 1)}>"
+
+    def env_rows():
+        rows = []
+        for g in em.env or [{"guard": (0, 0, 0.0), "begin": 0, "count": 0, "name": "-", "slack": -1.0, "ubegin": 0, "ucount": 0}]:
+            rows.append(f"    {{{_ref(g['guard'])}, {g['begin']}, {g['count']}, {_slack(g['slack'])}, {g['ubegin']}, {g['ucount']}}},  // {g['name']}")
+        return rows
+
+    def self_rows():
+        rows = []
+        for g in em.selfg or [{"ga": (0, 0, 0.0), "gb": (0, 0, 0.0), "a": (0, 0), "b": (0, 0), "name": "-", "slack": -1.0, "unit0": 0, "dense": False}]:
+            rows.append(
+                f"    {{{_ref(g['ga'])}, {_ref(g['gb'])}, {g['a'][0]}, {g['a'][1]}, {g['b'][0]}, {g['b'][1]}, {_slack(g['slack'])}, "
+                f"{g['unit0']}, {1 if g.get('dense') else 0}}},  // {g['name']}"
+            )
+        return rows
+
+    def ref_rows(rr):
+        return ["    " + ", ".join(_ref(r) for r in rr[i : i + 6]) + "," for i in range(0, len(rr), 6)]
+
+    rr = refs or [(0, 0, 0.0)]
     out = [f"__constant__ {t} {name} = {{"]
     out.append(f"    {len(em.slots)}, {ne}, {ns}, {na}, {em.att_env},")
     out.append("    {")
-    for g in em.env or [{"guard": (0, 0, 0.0), "begin": 0, "count": 0, "name": "-", "slack": -1.0}]:
-        out.append(f"        {{{_ref(g['guard'])}, {g['begin']}, {g['count']}, {_slack(g['slack'])}}},  // {g['name']}")
+    out.extend("    " + r for r in env_rows())
     out.append("    },")
     out.append("    {")
-    for g in em.selfg or [{"ga": (0, 0, 0.0), "gb": (0, 0, 0.0), "a": (0, 0), "b": (0, 0), "name": "-", "slack": -1.0}]:
-        out.append(
-            f"        {{{_ref(g['ga'])}, {_ref(g['gb'])}, {g['a'][0]}, {g['a'][1]}, {g['b'][0]}, {g['b'][1]}, {_slack(g['slack'])}}},"
-            f"  // {g['name']}"
-        )
+    out.extend("    " + r for r in self_rows())
     out.append("    },")
     out.append("    {")
     for g in em.att or [{"guard": (0, 0, 0.0), "begin": 0, "count": 0, "name": "-"}]:
-        out.append(f"        {{{_ref(g['guard'])}, {g['begin']}, {g['count']}, -1.0f}},  // {g['name']}")
+        out.append(f"        {{{_ref(g['guard'])}, {g['begin']}, {g['count']}, -1.0f, 0, 0}},  // {g['name']}")
     out.append("    },")
     out.append("    {")
-    refs = em.refs or [(0, 0, 0.0)]
-    for i in range(0, len(refs), 6):
-        out.append("        " + ", ".join(_ref(r) for r in refs[i : i + 6]) + ",")
+    out.extend("    " + r for r in ref_rows(rr))
     out.append("    },")
     out.append("};")
-    # mirror of the refs in global memory for lane-dependent indices (constant memory serialises those)
-    out.append(f"__device__ const SlotRef {name}_grefs[{max(nr, 1)}] = {{")
-    for i in range(0, len(refs), 6):
-        out.append("    " + ", ".join(_ref(r) for r in refs[i : i + 6]) + ",")
-    out.append("};")
-    return out, t
+    geom = {}
+    if walk:
+        # global-memory mirrors for lane-dependent indices (constant memory serialises those)
+        out.append(f"__device__ const SlotRef {name}_grefs[{len(rr)}] = {{")
+        out.extend(ref_rows(rr))
+        out.append("};")
+        rg = ref_group or [0xFFFF]
+        out.append(f"__device__ const uint16_t {name}_ref_group[{len(rg)}] = {{")
+        for i in range(0, len(rg), 16):
+            out.append("    " + ", ".join(str(v) for v in rg[i : i + 16]) + ",")
+        out.append("};")
+        out.append(f"__device__ const RefGroup {name}_genv[{max(ne, 1)}] = {{")
+        out.extend(env_rows())
+        out.append("};")
+        out.append(f"__device__ const SelfGroup {name}_gself[{max(ns, 1)}] = {{")
+        out.extend(self_rows())
+        out.append("};")
+        uu = units or [(0, 0)]
+        out.append(f"__device__ const SelfUnit {name}_units[{len(uu)}] = {{")
+        for i in range(0, len(uu), 8):
+            out.append("    " + ", ".join(f"{{{a}, {g}}}" for a, g in uu[i : i + 8]) + ",")
+        out.append("};")
+        max_u = max([g["ucount"] for g in em.env] or [1])
+        max_a = max([g["a"][1] for g in em.selfg if not g.get("dense")] or [1])
+        geom = {"env_q": 256, "self_q": 256, "pair_q": 256, "env_groups": max(ne, 1)}
+    return out, t, geom
+
+
+def _uniform(em: _Emitter) -> list[str]:
+    """Straight-line guard phase of the warp walk (vb_walk.cuh): every self-collision guard pair, the
+    a-side filters of the dense self groups and every environment guard lookup, with immediate
+    shared-memory offsets and radii.  No lane-dependent branch, all loads independent: this is the
+    part of the walk that every configuration executes."""
+    import numpy as np
+
+    F = np.float32
+    ns, ne = len(em.selfg), len(em.env)
+    sw, ew = max((ns + 31) // 32, 1), max((ne + 31) // 32, 1)
+    dense = [gi for gi, g in enumerate(em.selfg) if g.get("dense")]
+    leaf_mask, dense_mask = [0] * sw, [0] * sw
+    for gi, g in enumerate(em.selfg):
+        if g["a"][1] == 0:
+            leaf_mask[gi // 32] |= 1 << (gi % 32)
+        if g.get("dense"):
+            dense_mask[gi // 32] |= 1 << (gi % 32)
+    out: list[str] = []
+    w = out.append
+    w(f"    static constexpr int kSelfWords = {sw}, kEnvWords = {ew}, kDenseN = {max(len(dense), 1)}, kDenseUsed = {len(dense)};")
+
+    def table(name, typ, vals):
+        w(f"    VB_D static {typ} {name}(int i)")
+        w("    {")
+        w(f"        constexpr {typ} t[{len(vals)}] = {{{', '.join(str(v) + ('u' if typ == 'uint32_t' else '') for v in vals)}}};")
+        w("        return t[i];")
+        w("    }")
+
+    # environment groups whose guard and fine spheres do not depend on the configuration (e.g. the base link):
+    # their verdict is a property of (environment, base) and is evaluated once per warp, not per configuration
+    const_slots = set(getattr(em, "const_slots", ()))
+    const_mask = [0] * ew
+    for gi, g in enumerate(em.env):
+        slots = [g["guard"][0]] + [em.refs[g["begin"] + k][0] for k in range(g["count"])]
+        if all(sl in const_slots for sl in slots) and g["guard"][2] >= 0:
+            const_mask[gi // 32] |= 1 << (gi % 32)
+    table("env_const_mask", "uint32_t", const_mask)
+    w(f"    static constexpr bool kEnvConstAny = {'true' if any(const_mask) else 'false'};")
+    table("self_leaf_mask", "uint32_t", leaf_mask)
+    table("self_dense_mask", "uint32_t", dense_mask)
+    table("dense_group", "int", dense or [0])
+
+    loaded: set[int] = set()
+    body: list[str] = []
+
+    def need(slot: int):
+        if slot not in loaded:
+            loaded.add(slot)
+            body.append(
+                f"const float s{slot}x = col[{3 * slot} * kStride], s{slot}y = col[{3 * slot + 1} * kStride], s{slot}z = col[{3 * slot + 2} * kStride];"
+            )
+
+    def d2(a: int, b: int) -> str:
+        need(a)
+        need(b)
+        return (f"sqd(s{a}x - s{b}x, s{a}y - s{b}y, s{a}z - s{b}z)")
+
+    for wi in range(sw):
+        body.append(f"uint32_t f{wi} = 0u;")
+    for gi, g in enumerate(em.selfg):
+        (sa, _, ra), (sb, _, rb) = g["ga"], g["gb"]
+        rs = F(ra) + F(rb)
+        rs2 = F(rs * rs)
+        body.append(f"f{gi // 32} |= ({d2(sa, sb)} < {_f32(float(rs2))}) ? {1 << (gi % 32)}u : 0u;  // {g['name']}")
+    for wi in range(sw):
+        body.append(f"fired[{wi}] = f{wi};")
+    for di, gi in enumerate(dense):
+        g = em.selfg[gi]
+        sb, rb = g["gb"][0], g["gb"][2]
+        terms = []
+        for i in range(g["a"][1]):
+            sa, _, ra = em.refs[g["a"][0] + i]
+            if g["slack"] < 0:
+                terms.append(f"{1 << i}u")
+                continue
+            R = F(F(ra) + F(rb)) + F(g["slack"])
+            terms.append(f"(({d2(sa, sb)} < {_f32(float(F(R * R)))}) ? {1 << i}u : 0u)")
+        body.append(f"dpass[{di}] = " + " | ".join(terms) + f";  // {g['name']}")
+    w("    // self-collision guard pairs (bit g of fired[]) and a-side filters of the dense groups (bit i of dpass[d])")
+    w("    __device__ __forceinline__ static void self_guards(const float *__restrict__ col, uint32_t *__restrict__ fired, uint32_t *__restrict__ dpass)")
+    w("    {")
+    w("        auto sqd = [](float dx, float dy, float dz) { return dx * dx + dy * dy + dz * dz; };")
+    for ln in body:
+        w("        " + ln)
+    w("    }")
+    # environment guards: one branch-free grid fetch each, classified after the self-collision phase
+    w("    // issues the grid-cell load of every environment guard sphere (bit g of inside[]: centre inside the grid)")
+    w("    __device__ __forceinline__ static void env_fetch(const float *__restrict__ col, float bx, float by, float bz,")
+    w("                                                     const SdfView &grid, uint2 *__restrict__ cells, uint32_t *__restrict__ inside)")
+    w("    {")
+    w("        bool in;")
+    for wi in range(ew):
+        w(f"        uint32_t i{wi} = 0u;")
+    for gi, g in enumerate(em.env):
+        slot, mask, r = g["guard"]
+        xyz = []
+        for c in range(3):
+            e = f"col[{3 * slot + c} * kStride]"
+            if mask & (1 << c):
+                e += f" + b{'xyz'[c]}"
+            xyz.append(e)
+        w(f"        cells[{gi}] = grid_fetch(grid, {xyz[0]}, {xyz[1]}, {xyz[2]}, in); i{gi // 32} |= in ? {1 << (gi % 32)}u : 0u;  // {g['name']}")
+    for wi in range(ew):
+        w(f"        inside[{wi}] = i{wi};")
+    w("    }")
+    w("    // bit g of maybe[] (guard not certainly free) and cert[] (guard certainly hit); gm[32 * g] = candidate obstacles of group g")
+    w("    __device__ __forceinline__ static void env_classify(const uint2 *__restrict__ cells, const uint32_t *__restrict__ inside, float radius,")
+    w("                                                        const SdfView &grid, uint32_t *__restrict__ maybe, uint32_t *__restrict__ cert, uint32_t *gm)")
+    w("    {")
+    w("        bool mb, ct;")
+    w("        uint32_t mk;")
+    for wi in range(ew):
+        w(f"        uint32_t m{wi} = 0u, c{wi} = 0u;")
+    for gi, g in enumerate(em.env):
+        slot, mask, r = g["guard"]
+        rr = "radius" if r < 0 else _f32(r)
+        if g["count"] == 0:
+            reach = rr
+        elif g["slack"] < 0 or r < 0:
+            reach = "-1.0f"
+        else:
+            reach = _f32(r + g["slack"])
+        bit = f"{1 << (gi % 32)}u"
+        w(f"        grid_class(grid, cells[{gi}], (inside[{gi // 32}] & {bit}) != 0u, {rr}, {reach}, mb, ct, mk); "
+          f"m{gi // 32} |= mb ? {bit} : 0u; c{gi // 32} |= ct ? {bit} : 0u; gm[{32 * gi}] = mk;  // {g['name']}")
+    for wi in range(ew):
+        w(f"        maybe[{wi}] = m{wi}; cert[{wi}] = c{wi};")
+    w("    }")
+    return out
+
+
+def _geometry(n_slots: int, geom: dict) -> tuple[int, int]:
+    """(warps per CTA, CTAs per SM) maximising resident warps within 227 KB of shared memory per SM."""
+    queue = 2 * (geom["env_q"] + geom["self_q"] + geom["pair_q"]) + 128 * geom["env_groups"] + 16
+    per_warp = 3 * n_slots * 4 * 32 + queue
+    fixed = 128 * 16 + 3 * n_slots * 4 + 16 + 1024  # staged records, stride padding, per-CTA reserve
+    best = (1, 1)
+    for ctas in (1, 2, 3, 4, 6, 8):
+        w = min((227 * 1024 // ctas - fixed) // per_warp, 16, 32 // ctas)
+        if w >= 1 and w * ctas > best[0] * best[1]:
+            best = (int(w), ctas)
+    return best
 
 
 def emit_robot(ir: dict[str, Any]) -> str:
@@ -293,12 +503,13 @@ def emit_robot(ir: dict[str, Any]) -> str:
     w("#pragma once")
     w('#include "../csrc/vb_sinks.cuh"')
     w('#include "../csrc/vb_tables.cuh"')
+    w('#include "../csrc/vb_sdf.cuh"')
     w("namespace vb")
     w("{")
-    tab, ttype = _tables(f"k_{robot}_tables", em)
+    tab, ttype, geom = _tables(f"k_{robot}_tables", em, walk=True)
     out.extend(tab)
     if em_att:
-        tab2, ttype2 = _tables(f"k_{robot}_tables_attach", em_att)
+        tab2, ttype2, _ = _tables(f"k_{robot}_tables_attach", em_att)
         out.extend(tab2)
     w(f"struct {cls}")
     w("{")
@@ -308,15 +519,20 @@ def emit_robot(ir: dict[str, Any]) -> str:
     w(f"    static constexpr int kResolution = {ir['resolution']};")
     w(f"    static constexpr bool kHasAttach = {'true' if has_attach else 'false'};")
     n_slots = max(len(em.slots), len(em_att.slots) if em_att else 0)
+    warps, ctas = _geometry(n_slots, geom)
     w(f"    static constexpr int kSlots = {n_slots};  // distinct sphere centres used by the checks")
-    w(f"    static constexpr int kBlock = {128 if n_slots <= 72 else 64};  // threads per CTA (shared-memory budget)")
+    w(f"    static constexpr int kBlock = {32 * warps};  // threads per CTA: {warps} warps x {ctas} CTA(s) per SM fill the shared memory")
     w("    static constexpr int kStride = kBlock + 1;  // slot-column stride in floats (odd: conflict free)")
+    w(f"    static constexpr int kEnvQ = {geom['env_q']}, kSelfQ = {geom['self_q']}, kPairQ = {geom['pair_q']};  // work-queue capacities (units)")
     w(f"    static constexpr int kChainFlops = {st['chain_flops']};")
     w(f"    static constexpr int kEnvGroups = {st['env_groups']}, kEnvFine = {st['env_fine']};")
     w(f"    static constexpr int kSelfGroups = {st['self_groups']}, kSelfFine = {st['self_fine']};")
     w(f"    using TablesT = {ttype};")
     w(f"    __device__ __forceinline__ static const TablesT &tables() {{ return k_{robot}_tables; }}")
-    w(f"    __device__ __forceinline__ static const SlotRef *grefs() {{ return k_{robot}_tables_grefs; }}")
+    w("    __device__ __forceinline__ static WalkTables walk_tables()")
+    w("    {")
+    w(f"        return WalkTables{{k_{robot}_tables_grefs, k_{robot}_tables_ref_group, k_{robot}_tables_genv, k_{robot}_tables_gself, k_{robot}_tables_units}};")
+    w("    }")
     if em_att:
         w(f"    using TablesAttachT = {ttype2};")
         w(f"    __device__ __forceinline__ static const TablesAttachT &tables_attach() {{ return k_{robot}_tables_attach; }}")
@@ -351,6 +567,7 @@ def emit_robot(ir: dict[str, Any]) -> str:
             w("        " + ln)
         w("    }")
 
+    out.extend(_uniform(em))
     fn("chain", em.lines)
     fn("chain_attach", em_att.lines if em_att else ["chain(p, q);"])
     fn("sphere_fk", _Emitter(fns["sphere_fk"]).run_spheres(), "SphereSink")

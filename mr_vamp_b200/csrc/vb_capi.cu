@@ -132,7 +132,7 @@ namespace
         int sm_count = 0;
         cudaStream_t stream = nullptr;
         cudaEvent_t ev0 = nullptr, ev1 = nullptr;
-        DevBuf in_a, in_b, bits, margin, out, counts, prefix, scan_tmp;
+        DevBuf in_a, in_b, bits, margin, out, counts, prefix, scan_tmp, att;
     };
 }  // namespace
 
@@ -264,7 +264,7 @@ void vb_ctx_destroy(vb_ctx *ctx)
     {
         cudaSetDevice(s.device);
         cudaStreamSynchronize(s.stream);
-        for (DevBuf *b : {&s.in_a, &s.in_b, &s.bits, &s.margin, &s.out, &s.counts, &s.prefix, &s.scan_tmp})
+        for (DevBuf *b : {&s.in_a, &s.in_b, &s.bits, &s.margin, &s.out, &s.counts, &s.prefix, &s.scan_tmp, &s.att})
         {
             b->release();
         }
@@ -455,7 +455,7 @@ namespace
 
     struct Replica
     {
-        DevBuf prims, hf_desc, capt_desc, att_local;
+        DevBuf prims, hf_desc, capt_desc, att_local, sdf;
         std::vector<DevBuf> blobs;  // heightfield data and CAPT arrays
         vb::EnvView view{};
     };
@@ -489,6 +489,7 @@ namespace
             r.hf_desc.release();
             r.capt_desc.release();
             r.att_local.release();
+            r.sdf.release();
             for (auto &b : r.blobs)
             {
                 b.release();
@@ -763,6 +764,118 @@ namespace
         return VB_OK;
     }
 
+    // one thread per voxel of the distance / candidate grid (vb_sdf.cuh)
+    __global__ void sdf_build_kernel(const vb::EnvView e, uint2 *cell)
+    {
+        const vb::SdfView &g = e.sdf;
+        const size_t n = static_cast<size_t>(g.nx) * g.ny * g.nz;
+        const float h = 1.f / g.inv_h;
+        const float reach = vb::kMaskReach + g.pad;
+        for (size_t v = static_cast<size_t>(blockIdx.x) * blockDim.x + threadIdx.x; v < n;
+             v += static_cast<size_t>(gridDim.x) * blockDim.x)
+        {
+            const int ix = static_cast<int>(v % g.nx), iy = static_cast<int>((v / g.nx) % g.ny),
+                      iz = static_cast<int>(v / (static_cast<size_t>(g.nx) * g.ny));
+            float best = 3.0e38f;
+            uint32_t mask = 0u;
+            vb::sdf_objects(e, g.ox + (ix + 0.5f) * h, g.oy + (iy + 0.5f) * h, g.oz + (iz + 0.5f) * h,
+                            [&](int o, float d) {
+                                best = fminf(best, d);
+                                if (d < reach)
+                                {
+                                    mask |= 1u << (o < 31 ? o : 31);
+                                }
+                            });
+            cell[v] = make_uint2(__float_as_uint(best), mask);
+        }
+    }
+
+    // Bounding box of the primitive obstacles -> grid geometry.  The box is inflated by kSdfCover so that
+    // "outside the grid" means "at least kSdfCover away from every obstacle"; scenes larger than the
+    // +-kSdfReach cube around the origin are clipped to it and lose that guarantee (cover = 0).
+    constexpr float kSdfReach = 4.0f;
+    constexpr size_t kSdfMaxVoxels = size_t(4) << 20;
+    constexpr float kSdfMinVoxel = 0.015f;
+
+    bool sdf_geometry(const vb_env *env, vb::SdfView &g)
+    {
+        float lo[3] = {3e38f, 3e38f, 3e38f}, hi[3] = {-3e38f, -3e38f, -3e38f};
+        auto grow = [&](const float *c, const float *e) {
+            for (int k = 0; k < 3; ++k)
+            {
+                lo[k] = std::min(lo[k], c[k] - e[k]);
+                hi[k] = std::max(hi[k], c[k] + e[k]);
+            }
+        };
+        for (const auto &s : env->spheres)
+        {
+            const float c[3] = {s.x, s.y, s.z}, e[3] = {s.r, s.r, s.r};
+            grow(c, e);
+        }
+        auto capsule = [&](const HostCapsule &c) {
+            const float e[3] = {c.c[6], c.c[6], c.c[6]};
+            const float p2[3] = {c.c[0] + c.c[3], c.c[1] + c.c[4], c.c[2] + c.c[5]};
+            grow(c.c, e);
+            grow(p2, e);
+        };
+        for (const auto &c : env->capsules) capsule(c);
+        for (const auto &c : env->zcapsules) capsule(c);
+        auto cuboid = [&](const HostCuboid &c) {
+            float e[3];
+            for (int k = 0; k < 3; ++k)
+            {
+                e[k] = std::fabs(c.c[3 + k]) * c.c[12] + std::fabs(c.c[6 + k]) * c.c[13] + std::fabs(c.c[9 + k]) * c.c[14];
+            }
+            grow(c.c, e);
+        };
+        for (const auto &c : env->cuboids) cuboid(c);
+        for (const auto &c : env->zcuboids) cuboid(c);
+        if (!(lo[0] <= hi[0]))
+        {
+            return false;  // no primitives (or NaNs): no grid
+        }
+        bool clipped = false;
+        float ext[3];
+        for (int k = 0; k < 3; ++k)
+        {
+            lo[k] -= vb::kSdfCover + 0.01f;
+            hi[k] += vb::kSdfCover + 0.01f;
+            if (!(lo[k] >= -kSdfReach) || !(hi[k] <= kSdfReach) || !std::isfinite(lo[k]) || !std::isfinite(hi[k]))
+            {
+                clipped = true;
+                lo[k] = std::isfinite(lo[k]) ? std::max(lo[k], -kSdfReach) : -kSdfReach;
+                hi[k] = std::isfinite(hi[k]) ? std::min(hi[k], kSdfReach) : kSdfReach;
+                if (!(lo[k] < hi[k]))
+                {
+                    return false;
+                }
+            }
+            ext[k] = hi[k] - lo[k];
+        }
+        float h = std::max(kSdfMinVoxel, std::cbrt(ext[0] * ext[1] * ext[2] / static_cast<float>(kSdfMaxVoxels)));
+        for (;;)
+        {
+            g.nx = static_cast<int>(std::ceil(ext[0] / h));
+            g.ny = static_cast<int>(std::ceil(ext[1] / h));
+            g.nz = static_cast<int>(std::ceil(ext[2] / h));
+            if (static_cast<size_t>(g.nx) * g.ny * g.nz <= kSdfMaxVoxels)
+            {
+                break;
+            }
+            h *= 1.05f;
+        }
+        g.ox = lo[0];
+        g.oy = lo[1];
+        g.oz = lo[2];
+        g.inv_h = 1.f / h;
+        g.fnx = static_cast<float>(g.nx);
+        g.fny = static_cast<float>(g.ny);
+        g.fnz = static_cast<float>(g.nz);
+        g.pad = 0.5f * std::sqrt(3.f) * h * 1.001f + vb::kSdfMargin;
+        g.cover = clipped ? 0.f : vb::kSdfCover;
+        return true;
+    }
+
     int commit_replica(vb_env *env, Slot &slot, Replica &rep)
     {
         VB_CUDA(cudaSetDevice(slot.device));
@@ -837,6 +950,15 @@ namespace
         std::copy_n(env->att_tf, 7, v.attach.tf);
         v.attach.n = env->has_attachment ? static_cast<int>(env->att_spheres.size()) : 0;
         v.attach.local = rep.att_local.as<float4>();
+        // distance grid over the primitives (an acceleration structure: never changes a verdict)
+        if (v.n_quads > 0 && sdf_geometry(env, v.sdf))
+        {
+            const size_t voxels = static_cast<size_t>(v.sdf.nx) * v.sdf.ny * v.sdf.nz;
+            VB_CUDA(rep.sdf.reserve(voxels * sizeof(uint2)));
+            v.sdf.cell = rep.sdf.as<uint2>();
+            sdf_build_kernel<<<slot.sm_count * 8, 256, 0, slot.stream>>>(v, rep.sdf.as<uint2>());
+            VB_CUDA(cudaGetLastError());
+        }
         VB_CUDA(cudaStreamSynchronize(slot.stream));
         return VB_OK;
     }
@@ -963,6 +1085,13 @@ namespace
         }
         const size_t need = (items + threads - 1) / threads;
         *grid = static_cast<int>(std::max<size_t>(1, std::min<size_t>(need, static_cast<size_t>(blocks) * q.slot->sm_count)));
+        if (q.args.attach)
+        {
+            // posed attachment spheres live in a global scratch column per thread
+            Slot &s = *q.slot;
+            VB_CUDA(s.att.reserve(sizeof(float) * 3 * vb::kMaxAttach * static_cast<size_t>(*grid) * threads));
+            const_cast<Query &>(q).args.att_scratch = s.att.as<float>();
+        }
         return VB_OK;
     }
 

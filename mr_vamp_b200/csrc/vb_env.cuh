@@ -48,6 +48,18 @@ namespace vb
 
     constexpr int kMaxAttach = 16;
 
+    // Distance / candidate grid over the primitive obstacles (vb_sdf.cuh); cell == nullptr: no grid.
+    struct SdfView
+    {
+        const uint2 *cell;     // [nz][ny][nx]: x = float bits of the signed distance at the voxel centre, y = candidate mask
+        float ox, oy, oz;      // lower corner
+        float inv_h;           // 1 / voxel edge
+        float fnx, fny, fnz;   // float(nx), float(ny), float(nz)
+        int nx, ny, nz;
+        float pad;             // half voxel diagonal + safety margin
+        float cover;           // outside the grid every obstacle is at least this far away (0: unknown)
+    };
+
     // Passed by value to every kernel (lives in the parameter constant bank).
     struct EnvView
     {
@@ -58,6 +70,7 @@ namespace vb
         const HeightFieldView *heightfields;
         const CaptView *capts;
         AttachmentView attach;
+        SdfView sdf;
     };
 
     // Margin bookkeeping: smallest |signed clearance| (metres) over every test that decided control

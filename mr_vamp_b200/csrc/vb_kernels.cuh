@@ -2,18 +2,19 @@
 //
 // One thread evaluates one configuration.  Phase A runs the robot's FK chain as straight-line
 // register code and parks every sphere centre the checks need in that thread's column of shared
-// memory; phase B walks the robot's constant-memory check tables (environment groups, self
-// collision groups, attachment groups) with ONE copy of the environment query, reading obstacles
-// as warp-uniform broadcasts from shared memory; a warp ballot packs 32 verdicts into one uint32.  Replaces Robot::fkcc / Robot::sphere_fk (robots/panda_base.hh:53-71 and the
+// memory; phase B decides the collision tests of the 32 configurations of a warp together
+// (vb_walk.cuh: uniform guard phase, then compacted work units); a warp ballot packs 32 verdicts
+// into one uint32.  The lane-serial walk below (reference test order, one copy of the environment
+// query) serves the margin / work-count outputs and attachments.  Replaces Robot::fkcc / Robot::sphere_fk (robots/panda_base.hh:53-71 and the
 // per-robot equivalents) and planning::validate_motion (planning/validate.hh:23-75).
 #pragma once
 #include "vb_sinks.cuh"
 #include "vb_tables.cuh"
-#include "vb_coop.cuh"
+#include "vb_walk.cuh"
 
 namespace vb
 {
-    constexpr int kMaxSharedQuads = 3072; // obstacle records staged in shared memory (48 KB)
+    constexpr int kStageQuads = 128;  // obstacle records staged in shared memory when they fit (2 KB)
 
     struct LaunchArgs
     {
@@ -29,6 +30,7 @@ namespace vb
         unsigned long long *counters;  // optional work counters
         const uint32_t *prefix; // edges: exclusive prefix of interpolant counts [n+1]
         size_t n_points;        // edges: total interpolants
+        float *att_scratch;    // posed attachment spheres [3 * kMaxAttach][gridDim * blockDim] (attachment runs)
         int resolution;
         int attach;            // use the attachment trace
         float sphere_radius;   // robots::sphere global radius (robots/sphere/fk.hh:16)
@@ -43,19 +45,31 @@ namespace vb
         return Robot::kBlock;
     }
 
+    // bytes of the per-warp work queues of the warp walk (vb_walk.cuh)
+    template <class Robot>
+    __host__ __device__ constexpr int queue_bytes()
+    {
+        return 2 * (Robot::kEnvQ + Robot::kSelfQ + Robot::kPairQ) + 128 * (Robot::kEnvGroups > 0 ? Robot::kEnvGroups : 1) + 16;
+    }
+
     struct Scratch
     {
         const float4 *prims;  // obstacle records (shared or global)
         float *col;           // this thread's slot column
         int stride;
+        float *att_col;       // this thread's column of posed attachment spheres (global memory)
+        int att_stride;
+        unsigned char *queues;  // this warp's work queues
     };
 
-    // dynamic shared memory: [n_quads float4 obstacle records][3 * n_slot_rows * blockDim floats]
-    VB_D Scratch stage_env(const EnvView &env)
+    // dynamic shared memory: [staged obstacle records][3 * kSlots * (blockDim + 1) floats][per-warp queues]
+    template <class Robot>
+    VB_D Scratch stage_env(const LaunchArgs &a, bool with_queues)
     {
         extern __shared__ float4 smem[];
+        const EnvView &env = a.env;
         Scratch s;
-        const bool staged = env.n_quads <= kMaxSharedQuads;
+        const bool staged = env.n_quads <= kStageQuads;
         const int nq = staged ? env.n_quads : 0;
         if (staged)
         {
@@ -65,9 +79,16 @@ namespace vb
             }
             __syncthreads();
         }
-        s.prims = staged ? smem : env.prims;  // large scenes: L1/L2-resident broadcasts
-        s.col = reinterpret_cast<float *>(smem + nq) + threadIdx.x;
-        s.stride = blockDim.x + 1;  // == Robot::kStride; odd: a warp reading ONE column at 32 different slots is conflict free too
+        s.prims = staged ? smem : env.prims;  // large scenes: L1/L2-resident
+        float *slots = reinterpret_cast<float *>(smem + nq);
+        s.col = slots + threadIdx.x;
+        s.stride = Robot::kStride;  // odd: a warp reading ONE column at 32 different slots is conflict free too
+        s.att_stride = static_cast<int>(gridDim.x * blockDim.x);
+        s.att_col = a.att_scratch ? a.att_scratch + static_cast<size_t>(blockIdx.x) * blockDim.x + threadIdx.x : nullptr;
+        // 16-byte aligned start of the queues
+        const size_t slot_floats = (static_cast<size_t>(3 * Robot::kSlots * Robot::kStride) + 3) & ~static_cast<size_t>(3);
+        s.queues = with_queues ? reinterpret_cast<unsigned char *>(slots + slot_floats) + (threadIdx.x >> 5) * queue_bytes<Robot>()
+                               : nullptr;
         return s;
     }
 
@@ -99,6 +120,16 @@ namespace vb
             c.r = ref.r < 0.f ? radius : ref.r;
             return c;
         }
+        // posed attachment sphere i (world frame, written by SlotSink::attach_pose)
+        VB_D Center load_att(int i) const
+        {
+            Center c;
+            c.x = sc.att_col[(3 * i + 0) * static_cast<size_t>(sc.att_stride)];
+            c.y = sc.att_col[(3 * i + 1) * static_cast<size_t>(sc.att_stride)];
+            c.z = sc.att_col[(3 * i + 2) * static_cast<size_t>(sc.att_stride)];
+            c.r = env.attach.local[i].w;
+            return c;
+        }
     };
 
     // collision/validity.hh:13-44 + sphere_sphere.hh:9-23
@@ -113,7 +144,7 @@ namespace vb
     }
 
     template <class T, class M, int kStride>
-    VB_D bool walk_tables(const T &t, const TableCtx<kStride> &c, int att_slot0, M &mg)
+    VB_D bool walk_tables(const T &t, const TableCtx<kStride> &c, M &mg)
     {
         // environment groups (robots/<robot>/fk.hh: `if (sphere_environment_in_collision(bounding)) {...}`)
         for (int g = 0; g < t.n_env; ++g)
@@ -170,8 +201,7 @@ namespace vb
             bool hit = false;
             for (int i = 0; i < att.n; ++i)
             {
-                SlotRef ar{static_cast<uint16_t>(att_slot0 + i), 0, att.local[i].w};
-                hit = pair_hit(b, c.load(ar), mg) || hit;
+                hit = pair_hit(b, c.load_att(i), mg) || hit;
             }
             if (hit)
             {
@@ -184,8 +214,7 @@ namespace vb
                     const Center s = c.load(t.refs[grp.begin + k]);
                     for (int i = 0; i < att.n; ++i)
                     {
-                        SlotRef ar{static_cast<uint16_t>(att_slot0 + i), 0, att.local[i].w};
-                        if (pair_hit(s, c.load(ar), mg))
+                        if (pair_hit(s, c.load_att(i), mg))
                         {
                             return false;
                         }
@@ -197,8 +226,7 @@ namespace vb
         {
             for (int i = 0; i < att.n; ++i)
             {
-                SlotRef ar{static_cast<uint16_t>(att_slot0 + i), 0, att.local[i].w};
-                const Center s = c.load(ar);
+                const Center s = c.load_att(i);
                 if (env_hit(c.env, c.sc.prims, s.x, s.y, s.z, s.r, mg))
                 {
                     return false;
@@ -211,200 +239,22 @@ namespace vb
     template <class Robot, class M>
     VB_D bool check_config(const LaunchArgs &a, const Scratch &sc, const float *q, bool attach, M &mg)
     {
-        SlotSink sink{sc.col, sc.stride, &a.env.attach, Robot::kSlots};
+        SlotSink sink{sc.col, sc.stride, &a.env.attach, sc.att_col, sc.att_stride};
         const TableCtx<Robot::kStride> ctx{a.env, sc, a.base[0], a.base[1], a.base[2], a.sphere_radius};
         if (Robot::kHasAttach && attach)
         {
             Robot::chain_attach(sink, q);
-            return walk_tables(Robot::tables_attach(), ctx, Robot::kSlots, mg);
+            return walk_tables(Robot::tables_attach(), ctx, mg);
         }
         Robot::chain(sink, q);
-        return walk_tables(Robot::tables(), ctx, Robot::kSlots, mg);
-    }
-
-    // ---- warp-cooperative table walk (verdict only; see vb_coop.cuh) -------------------------------
-    // Must be called by all 32 lanes of a warp, converged.  `collided` enters true for lanes without a
-    // configuration.  Returns this lane's verdict (true = collision free).
-    //   environment groups : guard step lane-parallel; fine step in packed sub-warp rounds (a group of
-    //                        `count` fine spheres uses w = pow2ceil(count) lanes, so 32/w fired
-    //                        configurations are served per round).
-    //   self groups        : guard and the "a_i touches inflated bounding sphere of B" filter
-    //                        lane-parallel; surviving a_i are walked in rank lock-step (every lane its
-    //                        own r-th candidate), each against all b_j.
-    template <class T, int kStride>
-    VB_D bool coop_walk(const T &t, const SlotRef *__restrict__ grefs, const TableCtx<kStride> &c, bool collided)
-    {
-        const int lane = threadIdx.x & 31;
-        const float *warp_col = c.sc.col - lane;  // column of lane 0 of this warp
-        constexpr int stride = kStride;
-        const float4 *P = c.sc.prims;
-        const PrimIndex ix = prim_index(c.env);
-        const bool has_other = (c.env.n_heightfields | c.env.n_capts) != 0;
-        NoMargin mg;
-
-        // centre of `ref` in configuration L's column
-        auto load_of = [&](int L, const SlotRef &ref) {
-            const float *col = warp_col + L;
-            Center s;
-            s.x = col[(3 * ref.slot + 0) * stride] + ((ref.base & 1) ? c.bx : 0.f);
-            s.y = col[(3 * ref.slot + 1) * stride] + ((ref.base & 2) ? c.by : 0.f);
-            s.z = col[(3 * ref.slot + 2) * stride] + ((ref.base & 4) ? c.bz : 0.f);
-            s.r = ref.r < 0.f ? c.radius : ref.r;
-            return s;
-        };
-
-        const int n_obj = ix.first[5];
-        const uint32_t low_objs = n_obj >= 32 ? 0xffffffffu : ((1u << n_obj) - 1u);
-        const uint32_t lt_mask = (1u << lane) - 1u;
-
-        for (int g = 0; g < t.n_env; ++g)
-        {
-            if (__all_sync(kFull, collided))
-            {
-                return false;
-            }
-            const RefGroup grp = t.env[g];
-            const Center b = c.load(grp.guard);
-            const GuardResult gr = guard_env(c.env, P, ix, b, grp.slack);
-            bool fired = gr.fired;
-            if (has_other)
-            {
-                fired = fired || other_hit(c.env, b.x, b.y, b.z, b.r, mg);
-            }
-            fired = fired && !collided;
-            if (grp.count == 0)
-            {
-                collided = collided || fired;
-                continue;
-            }
-            if (has_other && fired)
-            {
-                // heightfields / point clouds: lane-serial fine tests (divergent; primitives go below)
-                for (int k = 0; k < grp.count && !collided; ++k)
-                {
-                    const Center s = c.load(t.refs[grp.begin + k]);
-                    collided = other_hit(c.env, s.x, s.y, s.z, s.r, mg);
-                }
-            }
-            uint32_t todo = __ballot_sync(kFull, fired && !collided);
-            if (todo == 0u)
-            {
-                continue;
-            }
-            // sub-warp geometry: w lanes per served configuration
-            const int shift = grp.count <= 1 ? 0 : 32 - __clz(static_cast<int>(grp.count) - 1);
-            const int n_slots = 32 >> shift;
-            const int slot = lane >> shift, k = lane & ((1 << shift) - 1);
-            const uint32_t slot_bits = shift == 5 ? 0xffffffffu : ((1u << (1 << shift)) - 1u);
-            const SlotRef my_ref = t.refs[grp.begin + (k < grp.count ? k : 0)];
-            while (todo)
-            {
-                const unsigned L = __fns(todo, 0, slot + 1);  // slot-th fired configuration
-                const bool active = L != 0xffffffffu && k < grp.count;
-                const int Lc = L != 0xffffffffu ? static_cast<int>(L) : 0;
-                uint32_t om = __shfl_sync(kFull, gr.mask, Lc) & low_objs;
-                bool high = __shfl_sync(kFull, static_cast<int>(gr.high), Lc) != 0;
-                om = active ? om : 0u;
-                high = high && active;
-                const Center s = load_of(Lc, my_ref);
-                const float ext = sqrtf(s.x * s.x + s.y * s.y + s.z * s.z) + s.r;
-                uint32_t U = __reduce_or_sync(kFull, om);
-                bool hit = false;
-                while (U)
-                {
-                    const int o = __ffs(U) - 1;
-                    U &= U - 1;
-                    const bool col = fine_vs_object(P, ix, o, s, ext);
-                    hit = hit || (col && ((om >> o) & 1u));
-                }
-                if (__any_sync(kFull, high))
-                {
-                    for (int o = 32; o < n_obj; ++o)
-                    {
-                        hit = hit || (high && fine_vs_object(P, ix, o, s, ext));
-                    }
-                }
-                const uint32_t hm = __ballot_sync(kFull, hit);
-                // configurations served this round: the first n_slots set bits of todo
-                const int my_rank = __popc(todo & lt_mask);
-                if (((todo >> lane) & 1u) && my_rank < n_slots && ((hm >> (my_rank << shift)) & slot_bits))
-                {
-                    collided = true;
-                }
-                const unsigned last = __fns(todo, 0, n_slots);
-                todo = last == 0xffffffffu ? 0u : (todo & ~((2u << last) - 1u));
-            }
-        }
-
-        for (int g = 0; g < t.n_self; ++g)
-        {
-            if ((g & 7) == 0 && __all_sync(kFull, collided))
-            {
-                return false;
-            }
-            const SelfGroup grp = t.self[g];
-            const Center gb = c.load(grp.gb);
-            const bool fired = pair_hit(c.load(grp.ga), gb, mg) && !collided;
-            if (grp.a_count == 0)
-            {
-                collided = collided || fired;
-                continue;
-            }
-            if (!__any_sync(kFull, fired))
-            {
-                continue;
-            }
-            // level 1 (lane-parallel): which a_i of MY configuration touch the inflated bounding sphere of B
-            uint32_t am = 0u;
-            if (fired)
-            {
-                if (grp.slack_b < 0.f)
-                {
-                    am = grp.a_count >= 32 ? 0xffffffffu : ((1u << grp.a_count) - 1u);
-                }
-                else
-                {
-#pragma unroll 4
-                    for (int i = 0; i < grp.a_count; ++i)
-                    {
-                        const Center a = c.load(t.refs[grp.a_begin + i]);
-                        const float dx = a.x - gb.x, dy = a.y - gb.y, dz = a.z - gb.z;
-                        const float R = a.r + gb.r + grp.slack_b;
-                        am |= (dx * dx + dy * dy + dz * dz - R * R < 0.f) ? (1u << i) : 0u;
-                    }
-                }
-            }
-            // level 2 (rank lock-step): every lane walks its own candidates, each against all b_j
-            while (__any_sync(kFull, am != 0u))
-            {
-                if (am)
-                {
-                    const int i = __ffs(am) - 1;
-                    am &= am - 1;
-                    const Center a = c.load(grefs[grp.a_begin + i]);  // lane-dependent index: global mirror
-                    bool hit = false;
-#pragma unroll 4
-                    for (int j = 0; j < grp.b_count; ++j)
-                    {
-                        hit = pair_hit(a, c.load(t.refs[grp.b_begin + j]), mg) || hit;
-                    }
-                    if (hit)
-                    {
-                        collided = true;
-                        am = 0u;
-                    }
-                }
-            }
-        }
-        return !collided;
+        return walk_tables(Robot::tables(), ctx, mg);
     }
 
     // Verdicts of 32 configurations, one per lane (all lanes must call; `alive` = lane has a configuration).
     // Attachment traces keep the lane-serial walk (rare, first rake pass only).
     template <class Robot>
-    VB_D bool check_warp(const LaunchArgs &a, const Scratch &sc, const float *q, bool alive, bool attach)
+    VB_D bool check_warp(const LaunchArgs &a, const Scratch &sc, const float *q, bool alive, bool attach, int &cstate)
     {
-        const TableCtx<Robot::kStride> ctx{a.env, sc, a.base[0], a.base[1], a.base[2], a.sphere_radius};
         if (Robot::kHasAttach && __any_sync(kFull, attach && alive))
         {
             bool ok = false;
@@ -418,11 +268,23 @@ namespace vb
         }
         if (alive)
         {
-            SlotSink sink{sc.col, sc.stride, &a.env.attach, Robot::kSlots};
+            SlotSink sink{sc.col, sc.stride, &a.env.attach, sc.att_col, sc.att_stride};
             Robot::chain(sink, q);
         }
         __syncwarp();
-        const bool ok = coop_walk(Robot::tables(), Robot::grefs(), ctx, !alive);
+        WalkCtx wc;
+        wc.wcol = sc.col - (threadIdx.x & 31);
+        wc.prims = sc.prims;
+        wc.envq = reinterpret_cast<uint16_t *>(sc.queues);
+        wc.selfq = wc.envq + Robot::kEnvQ;
+        wc.pairq = wc.selfq + Robot::kSelfQ;
+        wc.gmask = reinterpret_cast<uint32_t *>(wc.pairq + Robot::kPairQ);
+        wc.cmask = wc.gmask + 32 * (Robot::kEnvGroups > 0 ? Robot::kEnvGroups : 1);
+        wc.bx = a.base[0];
+        wc.by = a.base[1];
+        wc.bz = a.base[2];
+        wc.radius = a.sphere_radius;
+        const bool ok = Walk<Robot>::run(a.env, wc, !alive, cstate);
         __syncwarp();  // columns are rewritten by the next configuration
         return ok;
     }
@@ -433,7 +295,8 @@ namespace vb
     template <class Robot, int kMode>
     __global__ void __launch_bounds__(block_threads<Robot>()) fkcc_kernel(const LaunchArgs a)
     {
-        const Scratch prims = stage_env(a.env);
+        const Scratch prims = stage_env<Robot>(a, kMode == 0);
+        int cstate = -1;
         const size_t stride = static_cast<size_t>(gridDim.x) * blockDim.x;
         const size_t n_round = (a.n + 31) / 32 * 32;
         for (size_t i = static_cast<size_t>(blockIdx.x) * blockDim.x + threadIdx.x; i < n_round; i += stride)
@@ -466,7 +329,7 @@ namespace vb
             }
             else
             {
-                ok = check_warp<Robot>(a, prims, q, alive, a.attach != 0);
+                ok = check_warp<Robot>(a, prims, q, alive, a.attach != 0, cstate);
             }
             const uint32_t word = __ballot_sync(0xffffffffu, ok);
             if ((threadIdx.x & 31) == 0)
@@ -491,7 +354,8 @@ namespace vb
     template <class Robot>
     __global__ void __launch_bounds__(block_threads<Robot>()) fkcc_random_kernel(const LaunchArgs a, size_t first)
     {
-        const Scratch prims = stage_env(a.env);
+        const Scratch prims = stage_env<Robot>(a, true);
+        int cstate = -1;
         const size_t stride = static_cast<size_t>(gridDim.x) * blockDim.x;
         const size_t n_round = (a.n + 31) / 32 * 32;
         for (size_t i = static_cast<size_t>(blockIdx.x) * blockDim.x + threadIdx.x; i < n_round; i += stride)
@@ -499,7 +363,7 @@ namespace vb
             const bool alive = i < a.n;
             float q[Robot::kDim];
             random_config<Robot>(a.seed, first + i, q);
-            const bool ok = check_warp<Robot>(a, prims, q, alive, a.attach != 0);
+            const bool ok = check_warp<Robot>(a, prims, q, alive, a.attach != 0, cstate);
             const uint32_t word = __ballot_sync(0xffffffffu, ok);
             if ((threadIdx.x & 31) == 0)
             {
@@ -623,7 +487,8 @@ namespace vb
     template <class Robot, bool kMargin>
     __global__ void __launch_bounds__(block_threads<Robot>()) motion_kernel(const LaunchArgs a)
     {
-        const Scratch prims = stage_env(a.env);
+        const Scratch prims = stage_env<Robot>(a, !kMargin);
+        int cstate = -1;
         const size_t stride = static_cast<size_t>(gridDim.x) * blockDim.x;
         const size_t n_points = __ldg(a.prefix + a.n);  // total interpolants, left on the device by the scan
         const size_t n_round = (n_points + 31) / 32 * 32;
@@ -685,7 +550,7 @@ namespace vb
             }
             else
             {
-                ok = check_warp<Robot>(a, prims, q, alive, attach) || !alive;
+                ok = check_warp<Robot>(a, prims, q, alive, attach, cstate) || !alive;
             }
             if (alive && !ok)
             {

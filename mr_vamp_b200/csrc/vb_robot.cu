@@ -9,12 +9,13 @@ namespace vb
 
     constexpr int kBlock = block_threads<R>();
 
-    // obstacle records (when staged) + one slot column per thread
-    static size_t smem_bytes(const LaunchArgs &a)
+    // staged obstacle records + one slot column per thread (+ the per-warp work queues of the warp walk)
+    static size_t smem_bytes(const LaunchArgs &a, bool queues)
     {
-        const size_t quads = a.env.n_quads > kMaxSharedQuads ? 0 : static_cast<size_t>(a.env.n_quads);
-        const size_t slots = R::kSlots + (a.attach ? a.env.attach.n : 0);
-        return sizeof(float4) * quads + sizeof(float) * 3 * slots * (kBlock + 1);
+        const size_t quads = a.env.n_quads > kStageQuads ? 0 : static_cast<size_t>(a.env.n_quads);
+        const size_t slot_floats = (static_cast<size_t>(3 * R::kSlots * R::kStride) + 3) & ~static_cast<size_t>(3);
+        return sizeof(float4) * quads + sizeof(float) * slot_floats +
+               (queues ? static_cast<size_t>(kBlock / 32) * queue_bytes<R>() : 0);
     }
 
     template <class K>
@@ -45,15 +46,15 @@ namespace vb
         }
         if (mode == 1)
         {
-            fkcc_kernel<R, 1><<<grid, kBlock, smem_bytes(a), a.stream>>>(a);
+            fkcc_kernel<R, 1><<<grid, kBlock, smem_bytes(a, false), a.stream>>>(a);
         }
         else if (mode == 2)
         {
-            fkcc_kernel<R, 2><<<grid, kBlock, smem_bytes(a), a.stream>>>(a);
+            fkcc_kernel<R, 2><<<grid, kBlock, smem_bytes(a, false), a.stream>>>(a);
         }
         else
         {
-            fkcc_kernel<R, 0><<<grid, kBlock, smem_bytes(a), a.stream>>>(a);
+            fkcc_kernel<R, 0><<<grid, kBlock, smem_bytes(a, true), a.stream>>>(a);
         }
         return cudaGetLastError();
     }
@@ -64,7 +65,7 @@ namespace vb
         {
             return e;
         }
-        fkcc_random_kernel<R><<<grid, kBlock, smem_bytes(a), a.stream>>>(a, first);
+        fkcc_random_kernel<R><<<grid, kBlock, smem_bytes(a, true), a.stream>>>(a, first);
         return cudaGetLastError();
     }
 
@@ -97,11 +98,11 @@ namespace vb
         }
         if (margin)
         {
-            motion_kernel<R, true><<<grid, kBlock, smem_bytes(a), a.stream>>>(a);
+            motion_kernel<R, true><<<grid, kBlock, smem_bytes(a, false), a.stream>>>(a);
         }
         else
         {
-            motion_kernel<R, false><<<grid, kBlock, smem_bytes(a), a.stream>>>(a);
+            motion_kernel<R, false><<<grid, kBlock, smem_bytes(a, true), a.stream>>>(a);
         }
         return cudaGetLastError();
     }
@@ -113,7 +114,7 @@ namespace vb
             return e;
         }
         *threads = kBlock;
-        return cudaOccupancyMaxActiveBlocksPerMultiprocessor(blocks, fkcc_kernel<R, 0>, kBlock, smem_bytes(a));
+        return cudaOccupancyMaxActiveBlocksPerMultiprocessor(blocks, fkcc_kernel<R, 0>, kBlock, smem_bytes(a, true));
     }
 
     static void host_random_config(uint64_t seed, uint64_t index, float *q)

@@ -13,7 +13,8 @@ namespace vb
         float *col;
         int stride;
         const AttachmentView *att;
-        int att_slot0;  // first slot of the posed attachment spheres
+        float *att_col;  // this thread's column of posed attachment spheres (global scratch)
+        int att_stride;
 
         VB_D void put(int slot, float x, float y, float z) const
         {
@@ -29,7 +30,7 @@ namespace vb
             col[(3 * slot + 1) * kStride] = y;
             col[(3 * slot + 2) * kStride] = z;
         }
-        // collision/attachments.hh:75-122 (Attachment::pose); the posed centres go to slots att_slot0..
+        // collision/attachments.hh:75-122 (Attachment::pose); the posed centres go to the global scratch column
         VB_D void attach_pose(float p_tx, float p_ty, float p_tz, float p_rx, float p_ry, float p_rz, float p_rw) const
         {
             const float *t = att->tf;
@@ -52,10 +53,9 @@ namespace vb
             for (int i = 0; i < att->n; ++i)
             {
                 const float4 s = att->local[i];
-                put(att_slot0 + i,
-                    s.x * xx + s.y * yx + s.z * zx + tx,
-                    s.x * xy + s.y * yy + s.z * zy + ty,
-                    s.x * xz + s.y * yz + s.z * zz + tz);
+                att_col[(3 * i + 0) * static_cast<size_t>(att_stride)] = s.x * xx + s.y * yx + s.z * zx + tx;
+                att_col[(3 * i + 1) * static_cast<size_t>(att_stride)] = s.x * xy + s.y * yy + s.z * zy + ty;
+                att_col[(3 * i + 2) * static_cast<size_t>(att_stride)] = s.x * xz + s.y * yz + s.z * zz + tz;
             }
         }
     };

@@ -15,25 +15,38 @@ namespace vb
     };
 
     // sphere_environment_in_collision(guard) { sphere_environment_in_collision(fine_i)... };
-    // count == 0: the guard itself is the test
+    // count == 0: the guard itself is the test ("leaf" group)
     // slack: every fine sphere lies within the guard sphere inflated by `slack` metres (measured over
     // sampled configurations at code-generation time, plus a 1e-4 m margin; the traced bounding spheres
-    // are up to 0.6 mm too tight).  The kernels use "object touches the inflated guard" as a
-    // conservative, exact pre-filter for the fine tests.  slack < 0: no such bound (test everything).
+    // are up to 0.6 mm too tight).  slack < 0: no such bound.
+    // ubegin/ucount: the work units of the warp walk (vb_walk.cuh): refs[ubegin .. ubegin+ucount) are the
+    // spheres to test once the guard may have fired (= the fine spheres; for a leaf group a copy of the
+    // guard, appended behind the regular refs).
     struct RefGroup
     {
         SlotRef guard;
         uint16_t begin, count;
         float slack;
+        uint16_t ubegin, ucount;
     };
 
     // sphere_sphere_self_collision(ga, gb) { all pairs a_i x b_j }; a_count == 0: the guard is the test
     // slack_b: as above for the b-side fine spheres relative to the guard sphere gb
+    // unit0: index of this group's first (group, a_i) work unit; dense: the guard fires for most
+    // configurations (sampled at code-generation time), so the a-side filter runs lane-parallel
     struct SelfGroup
     {
         SlotRef ga, gb;
         uint16_t a_begin, a_count, b_begin, b_count;
         float slack_b;
+        uint16_t unit0, dense;
+    };
+
+    // one (self group, a_i) work unit of the warp walk
+    struct SelfUnit
+    {
+        uint16_t a_ref;  // index into refs
+        uint16_t group;  // index into self
     };
 
     template <int NE, int NS, int NA, int NR>
@@ -44,5 +57,15 @@ namespace vb
         SelfGroup self[NS];
         RefGroup att[NA];  // attachment_sphere_collision groups (robot sphere vs every attachment sphere)
         SlotRef refs[NR];
+    };
+
+    // Global-memory mirrors for lane-dependent indices (constant memory serialises those).
+    struct WalkTables
+    {
+        const SlotRef *refs;        // refs + leaf-guard copies
+        const uint16_t *ref_group;  // environment group of refs[i] (0xffff: not an environment unit)
+        const RefGroup *env;
+        const SelfGroup *self;
+        const SelfUnit *units;
     };
 }  // namespace vb

@@ -1,0 +1,541 @@
+// Warp-level collision walk of 32 configurations (one per lane): verdicts only.
+//
+// The reference returns at the first colliding sphere of an 8-lane block (robots/<robot>/fk.hh); a
+// literal SIMT port of that control flow leaves most lanes idle, because the lanes of a warp
+// disagree on which groups fire.  Here the walk is split into a uniform phase and compacted work:
+//
+//   guard phase   straight-line code generated per robot (codegen/emit_cuda.py: self_guards,
+//                 env_guards): every lane tests ITS configuration's guard pairs (self collision) and
+//                 looks its guard spheres up in the distance grid (environment, vb_sdf.cuh).  No
+//                 lane-dependent branch, every load independent of every other.
+//   work items    every (configuration, group) whose guard fired becomes a 16-bit item in a per-warp
+//                 shared-memory queue: lane | group << 5, appended group by group with a ballot.  The
+//                 32 lanes of the warp then take one item each, whatever configuration it belongs
+//                 to, and read that configuration's sphere centres from its shared-memory column.
+//   stages        self collision: filter (every a_i of the item against the inflated bounding sphere of
+//                 the other link) -> pair units (a_i against every b_j); environment: every fine
+//                 sphere of the item against the distance grid -> exact primitive arithmetic for the
+//                 few spheres the grid cannot decide, including the exact guard test the reference's
+//                 `if (guard) {...}` nesting asks for.
+//
+// The verdict is the same boolean function as the reference's (valid iff no group has a guard hit
+// and a fine hit, collision/validity.hh:13-150 + robots/<robot>/fk.hh); only the order of evaluation
+// differs.  Collided lanes are recorded in a per-warp bit mask.
+#pragma once
+#include "vb_sdf.cuh"
+#include "vb_tables.cuh"
+
+namespace vb
+{
+    constexpr unsigned kFull = 0xffffffffu;
+
+    // warp-uniform state of one walk
+    struct WalkCtx
+    {
+        const float *wcol;  // slot column of lane 0 of this warp
+        const float4 *prims;
+        uint16_t *envq, *selfq, *pairq;
+        uint32_t *gmask;  // [group][lane]: candidate obstacles of the lane's guard sphere (vb_sdf.cuh)
+        unsigned *cmask;  // [0] bit L set: configuration of lane L collides; [1] pair-queue fill
+        float bx, by, bz, radius;
+    };
+
+    template <class Robot>
+    struct Walk
+    {
+        static constexpr int S = Robot::kStride;
+
+        VB_D static unsigned vol(const unsigned *p)
+        {
+            return *reinterpret_cast<volatile const unsigned *>(p);
+        }
+
+        VB_D static bool done(const WalkCtx &c, int L)
+        {
+            return (vol(c.cmask) >> L) & 1u;
+        }
+
+        VB_D static Center centre(const WalkCtx &c, int L, const SlotRef &ref)
+        {
+            const float *col = c.wcol + L + 3 * static_cast<int>(ref.slot) * S;
+            Center s;
+            s.x = col[0] + ((ref.base & 1) ? c.bx : 0.f);
+            s.y = col[S] + ((ref.base & 2) ? c.by : 0.f);
+            s.z = col[2 * S] + ((ref.base & 4) ? c.bz : 0.f);
+            s.r = ref.r < 0.f ? c.radius : ref.r;
+            return s;
+        }
+
+        // local frame (self collision: no base offset, fixed radii)
+        VB_D static void local(const WalkCtx &c, int L, int slot, float &x, float &y, float &z)
+        {
+            const float *col = c.wcol + L + 3 * slot * S;
+            x = col[0];
+            y = col[S];
+            z = col[2 * S];
+        }
+
+        // a_i of configuration L against every b_j of its group
+        VB_D static bool pair_unit(const WalkCtx &c, const WalkTables &w, int L, const SlotRef &ar, int bb, int bc)
+        {
+            float ax, ay, az;
+            local(c, L, ar.slot, ax, ay, az);
+            bool hit = false;
+#pragma unroll 4
+            for (int j = 0; j < bc; ++j)
+            {
+                const SlotRef br = w.refs[bb + j];
+                float bx, by, bz;
+                local(c, L, br.slot, bx, by, bz);
+                const float dx = ax - bx, dy = ay - by, dz = az - bz, rs = ar.r + br.r;
+                hit = hit || (dx * dx + dy * dy + dz * dz - rs * rs < 0.f);
+            }
+            return hit;
+        }
+
+        // ---- self collision, stage 2: queued (configuration, a_i) units ----------------------------
+        __device__ __noinline__ static void pair_stage(const WalkCtx &c)
+        {
+            const WalkTables w = Robot::walk_tables();
+            const int lane = threadIdx.x & 31;
+            __syncwarp();
+            const int np = min(static_cast<int>(vol(c.cmask + 1)), Robot::kPairQ);
+            for (int base = 0; base < np; base += 32)
+            {
+                const int i = base + lane;
+                if (i < np)
+                {
+                    const unsigned code = c.pairq[i];
+                    const int L = code & 31;
+                    if (!done(c, L))
+                    {
+                        const SelfUnit su = w.units[code >> 5];
+                        const SelfGroup *G = w.self + su.group;
+                        if (pair_unit(c, w, L, w.refs[su.a_ref], G->b_begin, G->b_count))
+                        {
+                            atomicOr(c.cmask, 1u << L);
+                        }
+                    }
+                }
+            }
+            __syncwarp();
+            if (lane == 0)
+            {
+                c.cmask[1] = 0u;
+            }
+            __syncwarp();
+        }
+
+        // queue one (configuration, a_i) unit; when the queue is full the lane runs the unit itself
+        VB_D static void push_pair(const WalkCtx &c, const WalkTables &w, int L, int unit, const SlotRef &ar, const SelfGroup *G)
+        {
+            const unsigned at = atomicAdd(c.cmask + 1, 1u);
+            if (at < static_cast<unsigned>(Robot::kPairQ))
+            {
+                c.pairq[at] = static_cast<uint16_t>(L | (unit << 5));
+            }
+            else if (pair_unit(c, w, L, ar, G->b_begin, G->b_count))
+            {
+                atomicOr(c.cmask, 1u << L);
+            }
+        }
+
+        // ---- self collision, stage 1: one (configuration, group) item per lane ------------------------
+        // every a_i of the item against the inflated bounding sphere of the other link
+        __device__ __noinline__ static void filter_stage(const WalkCtx &c, int nq)
+        {
+            const WalkTables w = Robot::walk_tables();
+            const int lane = threadIdx.x & 31;
+            for (int base = 0; base < nq; base += 32)
+            {
+                const int i = base + lane;
+                if (i < nq)
+                {
+                    const unsigned code = c.selfq[i];
+                    const int L = code & 31;
+                    if (!done(c, L))
+                    {
+                        const SelfGroup *G = w.self + (code >> 5);
+                        const float slack = G->slack_b, rb = G->gb.r;
+                        const int a0 = G->a_begin, ac = G->a_count, u0 = G->unit0;
+                        float gx, gy, gz;
+                        local(c, L, G->gb.slot, gx, gy, gz);
+#pragma unroll 2
+                        for (int k = 0; k < ac; ++k)
+                        {
+                            const SlotRef ar = w.refs[a0 + k];
+                            float ax, ay, az;
+                            local(c, L, ar.slot, ax, ay, az);
+                            const float dx = ax - gx, dy = ay - gy, dz = az - gz, R = ar.r + rb + slack;
+                            if (slack < 0.f || dx * dx + dy * dy + dz * dz - R * R < 0.f)
+                            {
+                                push_pair(c, w, L, u0 + k, ar, G);
+                            }
+                        }
+                    }
+                }
+                __syncwarp();
+                if (vol(c.cmask + 1) >= static_cast<unsigned>(Robot::kPairQ) / 2)
+                {
+                    pair_stage(c);
+                }
+            }
+            __syncwarp();
+        }
+
+        // convergent variant of push_pair: all 32 lanes call, lanes with `on` queue one unit each
+        VB_D static void push_pairs(const WalkCtx &c, bool on, unsigned code)
+        {
+            const int lane = threadIdx.x & 31;
+            const unsigned m = __ballot_sync(kFull, on);
+            unsigned base = vol(c.cmask + 1);
+            if (base + 32u > static_cast<unsigned>(Robot::kPairQ))
+            {
+                pair_stage(c);
+                base = 0u;
+            }
+            if (on)
+            {
+                c.pairq[base + __popc(m & ((1u << lane) - 1u))] = static_cast<uint16_t>(code);
+            }
+            __syncwarp();
+            if (lane == 0)
+            {
+                c.cmask[1] = base + __popc(m);
+            }
+            __syncwarp();
+        }
+
+        // one fine sphere refs[idx] of configuration L against the tight candidates of its group
+        VB_D static bool fine_unit(const WalkCtx &c, const WalkTables &w, const PrimIndex &ix, int L, int idx)
+        {
+            const int g = w.ref_group[idx] & 0x7fff;
+            uint32_t tight = c.gmask[32 * g + L];
+            const bool thigh = (tight >> 31) != 0u;
+            tight &= 0x7fffffffu;
+            const Center s = centre(c, L, w.refs[idx]);
+            bool hit = false;
+            int cur = 0;
+            for (int o = next_candidate(tight, thigh, ix.first[5], cur); o >= 0 && !hit;
+                 o = next_candidate(tight, thigh, ix.first[5], cur))
+            {
+                hit = object_hit(object_dist(c.prims, ix, o, s.x, s.y, s.z), s.r);
+            }
+            return hit;
+        }
+
+        // ---- environment, stage 2: queued (configuration, fine sphere) units ---------------------------
+        __device__ __noinline__ static void fine_stage(const EnvView &env, const WalkCtx &c)
+        {
+            const WalkTables w = Robot::walk_tables();
+            const int lane = threadIdx.x & 31;
+            const PrimIndex ix = prim_index(env);
+            __syncwarp();
+            const int nu = min(static_cast<int>(vol(c.cmask + 1)), Robot::kPairQ);
+            for (int base = 0; base < nu; base += 32)
+            {
+                const int i = base + lane;
+                if (i < nu)
+                {
+                    const unsigned code = c.pairq[i];
+                    const int L = code & 31;
+                    if (!done(c, L) && fine_unit(c, w, ix, L, code >> 5))
+                    {
+                        atomicOr(c.cmask, 1u << L);
+                    }
+                }
+            }
+            __syncwarp();
+            if (lane == 0)
+            {
+                c.cmask[1] = 0u;
+            }
+            __syncwarp();
+        }
+
+        // ---- environment, stage 1: one (configuration, group) item per lane ---------------------------
+        // The item's guard sphere is tested exactly against the candidate obstacles of its grid cell (this
+        // is the reference's `if (guard collides)`), which also narrows the candidates to the obstacles
+        // that touch the guard sphere inflated by the group's static slack.  The fine spheres of a fired
+        // guard become units of stage 2 (the pair queue is free at this point and is reused), where they
+        // are tested, with the exact primitive arithmetic of the reference, against those few obstacles.
+        __device__ __noinline__ static void env_stage(const EnvView &env, const WalkCtx &c, int ne)
+        {
+            const WalkTables w = Robot::walk_tables();
+            const int lane = threadIdx.x & 31;
+            const bool has_other = (env.n_heightfields | env.n_capts) != 0;
+            const PrimIndex ix = prim_index(env);
+            const int n_obj = ix.first[5];
+            for (int base = 0; base < ne; base += 32)
+            {
+                const int i = base + lane;
+                if (i < ne)
+                {
+                    const unsigned code = c.envq[i];
+                    const int L = code & 31, g = code >> 5;
+                    if (!done(c, L))
+                    {
+                        const RefGroup *G = w.env + g;
+                        const int u0 = G->ubegin, uc = G->ucount;
+                        bool hit = false;
+                        if (!has_other)
+                        {
+                            const uint32_t mask = c.gmask[32 * g + L];
+                            const Center b = centre(c, L, G->guard);
+                            const float slack = G->slack;
+                            uint32_t low = mask & 0x7fffffffu, tight = 0u;
+                            if (n_obj < 31)
+                            {
+                                low &= (1u << n_obj) - 1u;
+                            }
+                            const bool high = (mask >> 31) != 0u;
+                            bool ghit = false;
+                            int cursor = 0;
+                            for (int o = next_candidate(low, high, n_obj, cursor); o >= 0;
+                                 o = next_candidate(low, high, n_obj, cursor))
+                            {
+                                const ObjDist d = object_dist(c.prims, ix, o, b.x, b.y, b.z);
+                                ghit = ghit || object_hit(d, b.r);
+                                if (slack < 0.f || object_hit(d, b.r + slack))
+                                {
+                                    tight |= 1u << (o < 31 ? o : 31);
+                                }
+                            }
+                            if (G->count == 0)
+                            {
+                                hit = ghit;  // leaf group: the guard is the test
+                            }
+                            else if (ghit)
+                            {
+                                c.gmask[32 * g + L] = tight;
+                                const unsigned at = atomicAdd(c.cmask + 1, static_cast<unsigned>(uc));
+                                for (int k = 0; k < uc; ++k)
+                                {
+                                    if (at + k < static_cast<unsigned>(Robot::kPairQ))
+                                    {
+                                        c.pairq[at + k] = static_cast<uint16_t>(L | ((u0 + k) << 5));
+                                    }
+                                    else
+                                    {
+                                        hit = hit || fine_unit(c, w, ix, L, u0 + k);  // queue full: run the unit here
+                                    }
+                                }
+                            }
+                        }
+                        else
+                        {
+                            // height fields / point clouds: the full query of the reference (guards were tested exactly)
+                            NoMargin mg;
+                            for (int k = 0; k < uc && !hit; ++k)
+                            {
+                                const Center s = centre(c, L, w.refs[u0 + k]);
+                                hit = env_hit(env, c.prims, s.x, s.y, s.z, s.r, mg);
+                            }
+                        }
+                        if (hit)
+                        {
+                            atomicOr(c.cmask, 1u << L);
+                        }
+                    }
+                }
+                __syncwarp();
+                if (vol(c.cmask + 1) >= static_cast<unsigned>(Robot::kPairQ) / 2)
+                {
+                    fine_stage(env, c);
+                }
+            }
+            fine_stage(env, c);
+        }
+
+        // Must be called by all 32 lanes of a warp, converged, after the chain of every live lane has
+        // written its slot column (and a __syncwarp).  `collided` enters true for lanes without a
+        // configuration.  Returns this lane's verdict (true = collision free).
+        // `cstate` is the warp's cached verdict of the configuration-independent environment groups
+        // (-1 unknown, 0 free, 1 colliding): a property of (environment, base), evaluated once.
+        VB_D static bool run(const EnvView &env, const WalkCtx &c, bool collided, int &cstate)
+        {
+            const auto &t = Robot::tables();
+            const int lane = threadIdx.x & 31;
+            const unsigned lt = (1u << lane) - 1u;
+            const float *col = c.wcol + lane;
+            if (lane < 2)
+            {
+                c.cmask[lane] = 0u;
+            }
+            __syncwarp();
+            if (Robot::kEnvConstAny && (env.n_quads > 0 || ((env.n_heightfields | env.n_capts) != 0)))
+            {
+                const unsigned alive = __ballot_sync(kFull, !collided);
+                if (cstate < 0 && alive != 0u)
+                {
+                    // reference semantics, evaluated on the column of the first live lane (the spheres are constants)
+                    const int L0 = __ffs(alive) - 1;
+                    NoMargin mg;
+                    bool hit = false;
+                    for (int g = 0; g < t.n_env && !hit; ++g)
+                    {
+                        if (!((Robot::env_const_mask(g >> 5) >> (g & 31)) & 1u))
+                        {
+                            continue;
+                        }
+                        const RefGroup grp = t.env[g];
+                        const Center b = centre(c, L0, grp.guard);
+                        if (env_hit(env, c.prims, b.x, b.y, b.z, b.r, mg))
+                        {
+                            hit = grp.count == 0;
+                            for (int k = 0; k < grp.count && !hit; ++k)
+                            {
+                                const Center s = centre(c, L0, t.refs[grp.begin + k]);
+                                hit = env_hit(env, c.prims, s.x, s.y, s.z, s.r, mg);
+                            }
+                        }
+                    }
+                    cstate = hit ? 1 : 0;
+                }
+                if (cstate > 0)
+                {
+                    return false;
+                }
+            }
+            // the grid cells of the environment guard spheres are fetched now and consumed after the
+            // self-collision phase, which hides their L2 latency
+            const bool has_other = (env.n_heightfields | env.n_capts) != 0;
+            const bool grid = env.sdf.cell != nullptr && !has_other;
+            uint2 cells[Robot::kEnvGroups > 0 ? Robot::kEnvGroups : 1];
+            uint32_t inside[Robot::kEnvWords];
+            if (grid)
+            {
+                Robot::env_fetch(col, c.bx, c.by, c.bz, env.sdf, cells, inside);
+            }
+
+            // ---------------- self collision ----------------
+            if (t.n_self > 0)
+            {
+                uint32_t fired[Robot::kSelfWords], dpass[Robot::kDenseN];
+                Robot::self_guards(col, fired, dpass);
+                const uint32_t live = collided ? 0u : 0xffffffffu;
+#pragma unroll
+                for (int wi = 0; wi < Robot::kSelfWords; ++wi)
+                {
+                    fired[wi] &= live;
+                    collided = collided || (fired[wi] & Robot::self_leaf_mask(wi)) != 0u;
+                }
+                const WalkTables w = Robot::walk_tables();
+                // dense groups: the a-side filter ran lane-parallel in the guard phase; queue the survivors
+#pragma unroll
+                for (int d = 0; d < Robot::kDenseUsed; ++d)
+                {
+                    const int g = Robot::dense_group(d);
+                    uint32_t todo = ((fired[g >> 5] >> (g & 31)) & 1u) && !collided ? dpass[d] : 0u;
+                    const int unit0 = t.self[g].unit0;
+                    while (__any_sync(kFull, todo != 0u))
+                    {
+                        const bool on = todo != 0u;
+                        const int k = on ? __ffs(todo) - 1 : 0;
+                        todo &= todo - 1u;
+                        push_pairs(c, on, lane | ((unit0 + k) << 5));
+                    }
+                }
+                // rare groups: one item per (lane, fired group), appended group by group
+                int nq = 0;
+#pragma unroll
+                for (int wi = 0; wi < Robot::kSelfWords; ++wi)
+                {
+                    const uint32_t mine = collided ? 0u : (fired[wi] & ~Robot::self_leaf_mask(wi) & ~Robot::self_dense_mask(wi));
+                    uint32_t any = __reduce_or_sync(kFull, mine);
+                    while (any)
+                    {
+                        const int b = __ffs(any) - 1;
+                        any &= any - 1u;
+                        const bool on = (mine >> b) & 1u;
+                        const unsigned m = __ballot_sync(kFull, on);
+                        if (nq + 32 > Robot::kSelfQ)
+                        {
+                            filter_stage(c, nq);
+                            pair_stage(c);
+                            nq = 0;
+                        }
+                        if (on)
+                        {
+                            c.selfq[nq + __popc(m & lt)] = static_cast<uint16_t>(lane | ((wi * 32 + b) << 5));
+                        }
+                        nq += __popc(m);
+                    }
+                }
+                __syncwarp();
+                filter_stage(c, nq);
+                pair_stage(c);
+                collided = collided || done(c, lane);
+            }
+            if (__all_sync(kFull, collided))
+            {
+                return false;
+            }
+
+            // ---------------- environment ----------------
+            if (env.n_quads == 0 && !has_other)
+            {
+                return !collided;
+            }
+            uint32_t maybe[Robot::kEnvWords], cert[Robot::kEnvWords];
+            if (grid)
+            {
+                Robot::env_classify(cells, inside, c.radius, env.sdf, maybe, cert, c.gmask + lane);
+            }
+            else
+            {
+                // height fields / point clouds (or no grid): exact guard tests, lane-parallel
+#pragma unroll
+                for (int wi = 0; wi < Robot::kEnvWords; ++wi)
+                {
+                    maybe[wi] = cert[wi] = 0u;
+                }
+                for (int g = 0; g < t.n_env; ++g)
+                {
+                    const RefGroup grp = t.env[g];
+                    const Center b = centre(c, lane, grp.guard);
+                    NoMargin mg;
+                    const bool hit = !collided && env_hit(env, c.prims, b.x, b.y, b.z, b.r, mg);
+                    c.gmask[32 * g + lane] = 0xffffffffu;
+#pragma unroll
+                    for (int wi = 0; wi < Robot::kEnvWords; ++wi)
+                    {
+                        if (wi == (g >> 5) && hit)
+                        {
+                            maybe[wi] |= 1u << (g & 31);
+                            cert[wi] |= 1u << (g & 31);
+                        }
+                    }
+                }
+            }
+            int ne = 0;
+#pragma unroll
+            for (int wi = 0; wi < Robot::kEnvWords; ++wi)
+            {
+                const uint32_t mine = collided ? 0u : (maybe[wi] & ~Robot::env_const_mask(wi));
+                uint32_t any = __reduce_or_sync(kFull, mine);
+                while (any)
+                {
+                    const int b = __ffs(any) - 1;
+                    any &= any - 1u;
+                    const bool on = (mine >> b) & 1u;
+                    const unsigned m = __ballot_sync(kFull, on);
+                    if (ne + 32 > Robot::kEnvQ)
+                    {
+                        __syncwarp();
+                        env_stage(env, c, ne);
+                        ne = 0;
+                    }
+                    if (on)
+                    {
+                        c.envq[ne + __popc(m & lt)] = static_cast<uint16_t>(lane | ((wi * 32 + b) << 5));
+                    }
+                    ne += __popc(m);
+                }
+            }
+            __syncwarp();
+            env_stage(env, c, ne);
+            return !(collided || done(c, lane));
+        }
+    };
+}  // namespace vb

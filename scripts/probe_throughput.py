@@ -9,13 +9,18 @@ from mr_vamp_b200 import api, scenes
 
 ctx = api.default_context()
 L = api.lib()
-cases = [("panda", "empty"), ("panda", "cage"), ("panda", "clutter"), ("ur5", "clutter"),
+cases = [("panda", "mbm"), ("panda", "empty"), ("panda", "cage"), ("panda", "clutter"), ("ur5", "clutter"),
          ("fetch", "clutter"), ("baxter", "clutter"), ("sphere", "clutter")]
 if len(sys.argv) > 2:
     cases = [(sys.argv[1], sys.argv[2])]
 for name, spec_name in cases:
     robot = api.Robot(name)
-    spec = {"empty": [], "cage": scenes.cage(), "clutter": scenes.random_scene(7)}[spec_name]
+    if spec_name == "mbm":
+        import os
+        mbm = scenes.load_mbm(os.path.join(scenes.GOLDEN_DIR, f"mbm_{name}.json.gz"))
+        spec = scenes.problem_to_spec(next(iter(mbm["problems"].values()))[0] if name != "panda" else mbm["problems"]["table_pick"][0])
+    else:
+        spec = {"empty": [], "cage": scenes.cage(), "clutter": scenes.random_scene(7)}[spec_name]
     env = scenes.apply(spec, api.Environment())
     n = 1 << 24
     bits = C.c_void_p()
