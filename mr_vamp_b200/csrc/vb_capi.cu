@@ -131,8 +131,9 @@ namespace
         int device = 0;
         int sm_count = 0;
         cudaStream_t stream = nullptr;
-        cudaEvent_t ev0 = nullptr, ev1 = nullptr;
-        DevBuf in_a, in_b, bits, margin, out, counts, prefix, scan_tmp, att;
+        cudaStream_t stream2 = nullptr;  // second lane of the host-buffer pipeline (copy of chunk k+1 under the kernel of chunk k)
+        cudaEvent_t ev0 = nullptr, ev1 = nullptr, evj = nullptr;
+        DevBuf in_a, in_a2, in_b, bits, margin, out, counts, prefix, scan_tmp, att;
     };
 }  // namespace
 
@@ -242,6 +243,8 @@ int vb_ctx_create(vb_ctx **out, const int *device_ids, int n_devices)
         }
         s.sm_count = prop.multiProcessorCount;
         VB_CUDA(cudaStreamCreateWithFlags(&s.stream, cudaStreamNonBlocking));
+        VB_CUDA(cudaStreamCreateWithFlags(&s.stream2, cudaStreamNonBlocking));
+        VB_CUDA(cudaEventCreateWithFlags(&s.evj, cudaEventDisableTiming));
         VB_CUDA(cudaEventCreate(&s.ev0));
         VB_CUDA(cudaEventCreate(&s.ev1));
         ctx->slots.push_back(s);
@@ -264,7 +267,10 @@ void vb_ctx_destroy(vb_ctx *ctx)
     {
         cudaSetDevice(s.device);
         cudaStreamSynchronize(s.stream);
-        for (DevBuf *b : {&s.in_a, &s.in_b, &s.bits, &s.margin, &s.out, &s.counts, &s.prefix, &s.scan_tmp, &s.att})
+        cudaStreamSynchronize(s.stream2);
+        cudaStreamDestroy(s.stream2);
+        cudaEventDestroy(s.evj);
+        for (DevBuf *b : {&s.in_a, &s.in_a2, &s.in_b, &s.bits, &s.margin, &s.out, &s.counts, &s.prefix, &s.scan_tmp, &s.att})
         {
             b->release();
         }
@@ -295,6 +301,7 @@ int vb_sync(vb_ctx *ctx)
     {
         VB_CUDA(cudaSetDevice(s.device));
         VB_CUDA(cudaStreamSynchronize(s.stream));
+        VB_CUDA(cudaStreamSynchronize(s.stream2));
     }
     return VB_OK;
 }
@@ -547,7 +554,7 @@ extern "C" {
 
 int vb_env_create(vb_ctx *ctx, vb_env **out)
 {
-    if (!ctx || !out)
+    if (!out)
     {
         return fail(VB_ERR_ARG, "vb_env_create: null argument");
     }
@@ -970,6 +977,10 @@ extern "C" int vb_env_commit(vb_env *env)
     {
         return fail(VB_ERR_ARG, "null environment");
     }
+    if (!env->ctx)
+    {
+        return fail(VB_ERR_STATE, "vb_env_commit: environment was created without a context (host-side description only)");
+    }
     release_replicas(env);
     env->replicas.resize(env->ctx->slots.size());
     for (size_t i = 0; i < env->replicas.size(); ++i)
@@ -1357,6 +1368,10 @@ int vb_sphere_fk(vb_ctx *ctx, vb_robot robot, const float *base, const float *co
     return vb_sync(ctx);
 }
 
+// Host buffers are processed in chunks on two streams per device, so that the host->device copy of
+// chunk k+1 and the device->host copy of chunk k-1 run under the kernel of chunk k.
+static constexpr size_t kHostChunk = size_t(1) << 22;  // configurations per chunk (multiple of 32)
+
 static int fkcc_host(vb_ctx *ctx, vb_robot robot, const float *base, const vb_env *env, const float *configs, size_t n,
                      uint32_t *valid_bits, float *margin, bool limits)
 {
@@ -1380,27 +1395,44 @@ static int fkcc_host(vb_ctx *ctx, vb_robot robot, const float *base, const vb_en
         Query q;
         VB_TRY(begin_query(ctx, static_cast<int>(i), robot, base, env, q));
         Slot &s = *q.slot;
-        const size_t words = (m + 31) / 32;
-        VB_CUDA(s.in_a.reserve(m * ops->dim * sizeof(float)));
-        VB_CUDA(s.bits.reserve(words * sizeof(uint32_t)));
+        const size_t chunk = std::min(m, kHostChunk);
+        VB_CUDA(s.in_a.reserve(chunk * ops->dim * sizeof(float)));
+        if (m > chunk)
+        {
+            VB_CUDA(s.in_a2.reserve(chunk * ops->dim * sizeof(float)));
+        }
+        VB_CUDA(s.bits.reserve((m + 31) / 32 * sizeof(uint32_t)));
         if (margin)
         {
             VB_CUDA(s.margin.reserve(m * sizeof(float)));
         }
-        VB_CUDA(cudaMemcpyAsync(s.in_a.p, configs + shards[i].lo * ops->dim, m * ops->dim * sizeof(float),
-                                cudaMemcpyHostToDevice, s.stream));
-        VB_TRY(run_fkcc_d(q, s.in_a.as<float>(), m, s.bits.as<uint32_t>(), margin ? s.margin.as<float>() : nullptr));
-        if (limits)
+        // the second stream starts after whatever the caller queued on the first
+        VB_CUDA(cudaEventRecord(s.evj, s.stream));
+        VB_CUDA(cudaStreamWaitEvent(s.stream2, s.evj, 0));
+        size_t k = 0;
+        for (size_t lo = 0; lo < m; lo += chunk, ++k)
         {
-            VB_CUDA(ops->limits(q.args));
-            ctx->launches += 1;
-        }
-        VB_CUDA(cudaMemcpyAsync(valid_bits + shards[i].lo / 32, s.bits.p, words * sizeof(uint32_t),
-                                cudaMemcpyDeviceToHost, s.stream));
-        if (margin)
-        {
-            VB_CUDA(cudaMemcpyAsync(margin + shards[i].lo, s.margin.p, m * sizeof(float), cudaMemcpyDeviceToHost,
-                                    s.stream));
+            const size_t c = std::min(chunk, m - lo);
+            const bool second = (k & 1) && !q.args.attach;  // attachment runs share one scratch buffer: one stream
+            cudaStream_t st = second ? s.stream2 : s.stream;
+            float *in = (second ? s.in_a2 : s.in_a).as<float>();
+            uint32_t *bits_d = s.bits.as<uint32_t>() + lo / 32;
+            float *margin_d = margin ? s.margin.as<float>() + lo : nullptr;
+            q.args.stream = st;
+            VB_CUDA(cudaMemcpyAsync(in, configs + (shards[i].lo + lo) * ops->dim, c * ops->dim * sizeof(float),
+                                    cudaMemcpyHostToDevice, st));
+            VB_TRY(run_fkcc_d(q, in, c, bits_d, margin_d));
+            if (limits)
+            {
+                VB_CUDA(ops->limits(q.args));
+                ctx->launches += 1;
+            }
+            VB_CUDA(cudaMemcpyAsync(valid_bits + (shards[i].lo + lo) / 32, bits_d, (c + 31) / 32 * sizeof(uint32_t),
+                                    cudaMemcpyDeviceToHost, st));
+            if (margin)
+            {
+                VB_CUDA(cudaMemcpyAsync(margin + shards[i].lo + lo, margin_d, c * sizeof(float), cudaMemcpyDeviceToHost, st));
+            }
         }
     }
     return vb_sync(ctx);
