@@ -290,15 +290,17 @@ class Environment:
     the host; the device copy is rebuilt lazily (one upload per change set instead of the reference's
     float->vector deep copy on every query, bindings/common.hh:181)."""
 
-    def __init__(self, ctx: Optional[Context] = None):
-        self.ctx = ctx or default_context()
+    def __init__(self, ctx: Optional[Context] = None, host_only: bool = False):
+        """host_only: a host-side description without a device context (population, classification,
+        sorting and export work; queries against it fail) -- used by tools and the CPU tests."""
+        self.ctx = None if host_only else (ctx or default_context())
         self._h = _vp()
-        _check(lib().vb_env_create(self.ctx.handle, C.byref(self._h)))
+        _check(lib().vb_env_create(self.ctx.handle if self.ctx else None, C.byref(self._h)))
         self._dirty = True
 
     def __del__(self):
         try:
-            if self._h and self.ctx._h:
+            if self._h and (self.ctx is None or self.ctx._h):
                 lib().vb_env_destroy(self._h)
         except Exception:
             pass

@@ -1,0 +1,129 @@
+"""CPU tests of the checkers themselves (no GPU): the compiled reference (oracle/_ref) against the
+reference's own known answers and the MotionBenchMaker fixtures, and the numpy restatement
+(oracle/port.py) against the compiled reference."""
+import os
+
+import numpy as np
+import pytest
+
+from mr_vamp_b200 import scenes
+from mr_vamp_b200.codegen import ir_eval
+from conftest import apply_ref
+
+REF_NAME = {"panda": "panda_0_0"}
+ROBOTS = ["ur5", "panda", "fetch", "baxter"]
+
+
+def _cfgs(ref, name, seed, n):
+    dim = ref.robot_info(REF_NAME.get(name, name))[0]
+    return ref.scale(REF_NAME.get(name, name), np.random.default_rng(seed).random((n, dim), dtype=np.float32))
+
+
+def test_reference_trig_matches_restated_polynomial(ref):
+    # vector/interface.hh:438-469: max abs error vs libm ~1.14e-5 on [-pi, pi]
+    x = np.linspace(-np.pi, np.pi, 200001, dtype=np.float32)
+    s, c = ref.trig(x)
+    # the compiled reference contracts the polynomial into FMAs (-ffp-contract=fast): ulp-level spread only
+    assert np.abs(s - ir_eval.vamp_sin(x)).max() < 1e-6
+    assert np.abs(c - ir_eval.vamp_cos(x)).max() < 1e-6
+    assert 0.9e-5 < np.abs(s - np.sin(x.astype(np.float64))).max() < 1.3e-5
+
+
+def test_reference_known_answers(ref):
+    # scripts/sphere_cage_example.py:10-13,67: start and goal valid in the nominal cage
+    renv = apply_ref(scenes.cage(), ref.Env())
+    q = np.asarray([scenes.CAGE_START, scenes.CAGE_GOAL], dtype=np.float32)
+    assert ref.validate("panda_0_0", renv, q).all()
+    assert ref.validate_motion("panda_0_0", renv, q[:1], q[:1])[0]
+    # scripts/cpp/test_panda_fk.cc:81-83,121-126: a sphere at the origin robot's base collides with it only
+    e = ref.Env()
+    e.add_sphere(0.05, 0.05, 0.05, 0.1)
+    assert not ref.fkcc("panda_0_0", e, q[:1])[0] and ref.fkcc("panda_2_2", e, q[:1])[0]
+    # test_hybrid_approach.py:20-22: first sphere of the (2, 2) variant is ~(2, 2, 0.05)
+    s0 = ref.sphere_fk("panda_2_2", q[:1])[0, 0]
+    assert abs(s0[0] - 2) < 0.1 and abs(s0[1] - 2) < 0.1 and abs(s0[2] - 0.05) < 0.1
+    # last sphere of PandaBase<0,0,0> at the cage start
+    s_last = ref.sphere_fk("panda_0_0", q[:1])[0, -1, :3]
+    assert np.allclose(s_last, [0.306985, 0.073001, 0.487866], atol=2e-6)
+
+
+@pytest.mark.parametrize("robot,expect", [("panda", 699), ("ur5", 608), ("fetch", None)])
+def test_mbm_validity_counts(ref, robot, expect):
+    """resources/README.md:146,81,210: valid problems of the 700 MotionBenchMaker problems per robot
+    (valid = start valid and some goal valid, resources/problem_tar_to_pkl_json.py:79-85)."""
+    path = os.path.join(scenes.GOLDEN_DIR, f"mbm_{robot}.json.gz")
+    mbm = scenes.load_mbm(path)
+    name = REF_NAME.get(robot, robot)
+    valid = total = 0
+    for problems in mbm["problems"].values():
+        for p in problems:
+            renv = apply_ref(scenes.problem_to_spec(p), ref.Env())
+            q = np.asarray([p["start"]] + p["goals"], dtype=np.float32)
+            ok = ref.validate(name, renv, q)
+            valid += bool(ok[0] and ok[1:].any())
+            total += 1
+    print(f"{robot}: {valid} of {total} MotionBenchMaker problems valid (reference README: {expect})")
+    assert total == 700
+    if expect is not None:
+        assert abs(valid - expect) <= 2  # the README numbers come from upstream VAMP's Eigen-built shapes
+    else:
+        # Fetch: the README's 679 is not reproduced by the fork's own fetch trace compiled here (539);
+        # recorded in DESIGN.md as an unexplained difference of the reference, not used as a pin
+        assert valid == 539
+
+
+@pytest.mark.parametrize("name", ROBOTS)
+def test_port_sphere_fk_matches_reference(ref, name):
+    from oracle import port
+
+    q = _cfgs(ref, name, 1, 2000)
+    err = np.abs(port.sphere_fk(name, q) - ref.sphere_fk(REF_NAME.get(name, name), q)).max()
+    assert err <= 1e-5
+
+
+def test_port_base_offsets(ref):
+    from oracle import port
+
+    q = _cfgs(ref, "panda", 2, 500)
+    assert np.abs(port.sphere_fk("panda", q, base=(2, 2, 0)) - ref.sphere_fk("panda_2_2", q)).max() <= 1e-5
+    assert np.abs(port.sphere_fk("panda", q, base=(1, 0, 0)) - ref.sphere_fk("panda_1_0", q)).max() <= 1e-5
+
+
+@pytest.mark.parametrize("name", ROBOTS)
+@pytest.mark.parametrize("scene", ["empty", "cage", "clutter"])
+def test_port_verdicts_match_reference(ref, name, scene):
+    from oracle import port
+
+    spec = {"empty": [], "cage": scenes.cage(), "clutter": scenes.random_scene(7)}[scene]
+    q = _cfgs(ref, name, 3, 4000)
+    want = ref.fkcc(REF_NAME.get(name, name), apply_ref(spec, ref.Env()), q, threads=4)
+    got = port.fkcc(name, port.Env(spec), q)
+    # ulp-level differences (FMA contraction in the compiled reference) may flip grazing contacts
+    assert (got != want).sum() <= 2, f"{(got != want).sum()} verdicts differ"
+
+
+def test_port_validate_motion_matches_reference(ref):
+    from oracle import port
+
+    spec = scenes.cage()
+    a = _cfgs(ref, "panda", 5, 120)
+    rng = np.random.default_rng(6)
+    step = rng.normal(size=a.shape).astype(np.float32)
+    step *= (rng.uniform(0.02, 1.2, (a.shape[0], 1)) / np.linalg.norm(step, axis=1, keepdims=True)).astype(np.float32)
+    b = (a + step).astype(np.float32)
+    want = ref.validate_motion("panda_0_0", apply_ref(spec, ref.Env()), a, b)
+    got = port.validate_motion("panda", port.Env(spec), a, b)
+    assert (got != want).sum() <= 1
+
+
+def test_port_interpolants_follow_the_rake(ref):
+    # planning/validate.hh:23-65: 8n points, the last block row reaches the goal exactly for k = 7, i = 0
+    from oracle import port
+
+    a = np.zeros(7, np.float32)
+    b = np.full(7, 0.3, np.float32)
+    pts = port.motion_points(a, b, 32)
+    n = int(np.ceil(np.sqrt(7 * 0.09) / 8 * 32))
+    assert pts.shape == (8 * n, 7)
+    assert np.allclose(pts[7], b)
+    assert np.allclose(sorted(pts[:, 0]), np.arange(1, 8 * n + 1) * 0.3 / (8 * n), atol=1e-6)
