@@ -253,7 +253,8 @@ namespace vb
     // Verdicts of 32 configurations, one per lane (all lanes must call; `alive` = lane has a configuration).
     // Attachment traces keep the lane-serial walk (rare, first rake pass only).
     template <class Robot>
-    VB_D bool check_warp(const LaunchArgs &a, const Scratch &sc, const float *q, bool alive, bool attach, int &cstate)
+    VB_D bool check_warp(const LaunchArgs &a, const Scratch &sc, const float *q, bool alive, bool attach, int &cstate,
+                         bool octet = false)
     {
         if (Robot::kHasAttach && __any_sync(kFull, attach && alive))
         {
@@ -284,6 +285,7 @@ namespace vb
         wc.by = a.base[1];
         wc.bz = a.base[2];
         wc.radius = a.sphere_radius;
+        wc.octet = octet;
         const bool ok = Walk<Robot>::run(a.env, wc, !alive, cstate);
         __syncwarp();  // columns are rewritten by the next configuration
         return ok;
@@ -550,7 +552,7 @@ namespace vb
             }
             else
             {
-                ok = check_warp<Robot>(a, prims, q, alive, attach, cstate) || !alive;
+                ok = check_warp<Robot>(a, prims, q, alive, attach, cstate, true) || !alive;
             }
             if (alive && !ok)
             {

@@ -38,6 +38,11 @@ namespace vb
         uint32_t *gmask;  // [group][lane]: candidate obstacles of the lane's guard sphere (vb_sdf.cuh)
         unsigned *cmask;  // [0] bit L set: configuration of lane L collides; [1] pair-queue fill
         float bx, by, bz, radius;
+        // Motion validation: the 8 lanes of an octet are the 8 interpolants of one rake block of the
+        // reference (planning/validate.hh:36-60), whose `if (guard collides in ANY lane)` opens the fine
+        // tests of ALL lanes.  That coupling changes verdicts where a guard query is unreliable: CAPT point
+        // clouds queried with a bounding-sphere radius beyond the tree's r_max.
+        bool octet;
     };
 
     template <class Robot>
@@ -505,6 +510,19 @@ namespace vb
                             maybe[wi] |= 1u << (g & 31);
                             cert[wi] |= 1u << (g & 31);
                         }
+                    }
+                }
+                if (c.octet)
+                {
+                    // the guard of a rake block fires when it fires in any of its 8 lanes
+#pragma unroll
+                    for (int wi = 0; wi < Robot::kEnvWords; ++wi)
+                    {
+                        uint32_t v = maybe[wi];
+                        v |= __shfl_xor_sync(kFull, v, 1);
+                        v |= __shfl_xor_sync(kFull, v, 2);
+                        v |= __shfl_xor_sync(kFull, v, 4);
+                        maybe[wi] = v;
                     }
                 }
             }

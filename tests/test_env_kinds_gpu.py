@@ -1,0 +1,146 @@
+"""GPU parity of the remaining obstacle kinds of sphere_environment_in_collision (collision/validity.hh:
+132-147) and of the attachment trace: CAPT point clouds (collision/capt.hh:457-541, buffers built by the
+reference and uploaded verbatim), height fields (collision/sphere_heightfield.hh:8-30) and fkcc_attach
+(robots/<robot>/fk.hh interleaved_sphere_fk_attachment + collision/attachments.hh:75-122)."""
+import numpy as np
+import pytest
+
+from mr_vamp_b200 import scenes
+
+pytestmark = pytest.mark.gpu
+BAND = 1e-5
+
+
+def _cfgs(robot, seed, n):
+    rng = np.random.default_rng(seed)
+    return (robot.lower_bounds + rng.random((n, robot.dimension), dtype=np.float32) * robot.ranges).astype(np.float32)
+
+
+def _surface_cloud(seed, n):
+    """Points on a table top, a wall and a post around the robot (a small stand-in for SURVEY M3)."""
+    rng = np.random.default_rng(seed)
+    k = n // 3
+    table = np.stack([rng.uniform(0.25, 0.9, k), rng.uniform(-0.5, 0.5, k), np.full(k, 0.3)], axis=1)
+    wall = np.stack([np.full(k, -0.45), rng.uniform(-0.6, 0.6, k), rng.uniform(0.0, 1.0, k)], axis=1)
+    post = np.stack([0.1 * np.cos(rng.uniform(0, 6.28, n - 2 * k)) + 0.3, 0.1 * np.sin(rng.uniform(0, 6.28, n - 2 * k)) - 0.55,
+                     rng.uniform(0.0, 0.9, n - 2 * k)], axis=1)
+    return np.concatenate([table, wall, post]).astype(np.float32)
+
+
+def _upload_capt(vb, ref, points, extra_spec=()):
+    renv = ref.Env()
+    renv.add_pointcloud(points, 0.012, 0.06, 0.0025)  # src/vamp/constants.py:57-63,77 (panda radii, point radius)
+    c = renv.capt(0)
+    env = vb.Environment()
+    env.add_capt_buffers(c["tests"], c["aff_starts"], c["aff_x"], c["aff_y"], c["aff_z"], c["aabbs"], c["aabb_top"],
+                         c["r_point"], c["nlog2"])
+    for item in extra_spec:
+        renv.add_sphere(*[float(np.float32(v)) for v in item[1:5]])
+    scenes.apply(list(extra_spec), env)
+    return env, renv
+
+
+@pytest.mark.parametrize("n_points", [3000, 40000])
+def test_capt_pointcloud_fkcc_and_edges(vb, ref, n_points):
+    robot = vb.Robot("panda")
+    env, renv = _upload_capt(vb, ref, _surface_cloud(0, n_points))
+    q = _cfgs(robot, 21, 20000)
+    ok, mg = robot.fkcc_batch(q, env, margin=True)
+    ok2 = robot.fkcc_batch(q, env)
+    want = ref.fkcc("panda_0_0", renv, q, threads=8)
+    hard = (ok != want) & (mg > BAND)
+    print(f"capt {n_points} pts: valid_ref={want.mean():.3f} differ={int((ok != want).sum())} hard={int(hard.sum())}")
+    assert hard.sum() == 0
+    assert not ((ok2 != ok) & (mg > BAND)).any()
+    a, b = q[:2000], np.clip(q[:2000] + np.float32(0.15), robot.lower_bounds, robot.lower_bounds + robot.ranges)
+    # The reference checks 8 interpolants per block and opens a group's fine tests for ALL lanes when the
+    # guard fires in ANY lane; with a point cloud the guard query is unreliable (bounding-sphere radius >
+    # the tree's r_max), so block verdicts are not the AND of per-configuration verdicts.  The verdict
+    # kernel reproduces the block coupling; the margin kernel keeps per-configuration semantics and only
+    # classifies disagreements.
+    _, e_mg = robot.validate_motion_batch(a, b, env, margin=True)
+    e_ok = robot.validate_motion_batch(a, b, env)
+    e_want = ref.validate_motion("panda_0_0", renv, a, b, threads=8)
+    print(f"capt {n_points} pts edges: valid_ref={e_want.mean():.3f} differ={int((e_ok != e_want).sum())}")
+    assert not ((e_ok != e_want) & (e_mg > BAND)).any()
+
+
+def test_capt_with_primitives(vb, ref):
+    robot = vb.Robot("ur5")
+    env, renv = _upload_capt(vb, ref, _surface_cloud(3, 5000), extra_spec=scenes.cage()[:6])
+    q = _cfgs(robot, 22, 10000)
+    ok, mg = robot.fkcc_batch(q, env, margin=True)
+    want = ref.fkcc("ur5", renv, q, threads=8)
+    assert not ((ok != want) & (mg > BAND)).any()
+    assert not ((robot.fkcc_batch(q, env) != ok) & (mg > BAND)).any()
+
+
+def test_capt_sphere_queries_match_collides_simd(vb, ref):
+    """robots::sphere turns fkcc into a bare sphere query: CAPT::collides_simd parity (the
+    SIMD and scalar queries of the reference differ; the kernels follow the SIMD one)."""
+    pts = _surface_cloud(5, 20000)
+    env, renv = _upload_capt(vb, ref, pts)
+    robot = vb.Robot("sphere")
+    rng = np.random.default_rng(9)
+    centres = (pts[rng.integers(0, len(pts), 20000)] + rng.normal(0, 0.05, (20000, 3))).astype(np.float32)
+    for radius in (0.012, 0.06, 0.15):
+        robot.ctx.set_sphere_radius(radius)
+        got = robot.fkcc_batch(centres, env)
+        hit_simd, _ = renv.capt_query(np.concatenate([centres, np.full((len(centres), 1), radius, np.float32)], axis=1))
+        assert np.array_equal(got, ~hit_simd.astype(bool)), radius
+    robot.ctx.set_sphere_radius(0.2)
+
+
+def test_heightfield(vb, ref):
+    rng = np.random.default_rng(4)
+    data = (0.15 + 0.25 * rng.random((48, 64))).astype(np.float32)
+    # terrain 5..30 cm below the base plane; 3.2 m x 2.4 m so that every robot sphere stays over the field: past
+    # the last row/column the reference clamps the cell index to xd / yd and reads beyond its buffer
+    # (sphere_heightfield.hh:18-21), which is undefined there and zero-padded here
+    hf = vb.HeightField([0.0, 0.0, -0.45], [0.05, 0.05, 1.0], data)
+    spec = [("heightfield", hf.off_scale, data), ("sphere", 0.9, 0.0, 0.9, 0.15), ("sphere", 0.5, 0.6, 1.0, 0.15)]
+    env = scenes.apply(spec, vb.Environment())
+    from conftest import apply_ref
+
+    renv = apply_ref(spec, ref.Env())
+    for name in ("panda", "fetch"):
+        robot = vb.Robot(name)
+        q = _cfgs(robot, 31, 10000)
+        ok, mg = robot.fkcc_batch(q, env, margin=True)
+        want = ref.fkcc("panda_0_0" if name == "panda" else name, renv, q, threads=8)
+        print(f"heightfield {name}: valid_ref={want.mean():.3f} differ={int((ok != want).sum())}")
+        assert name != "panda" or 0.02 < want.mean() < 0.98
+        assert not ((ok != want) & (mg > BAND)).any()
+        assert not ((robot.fkcc_batch(q, env) != ok) & (mg > BAND)).any()
+
+
+@pytest.mark.parametrize("name", ["panda", "ur5", "fetch"])
+def test_attachment(vb, ref, name):
+    robot = vb.Robot(name)
+    # the cage surrounds a table-top arm; the Fetch base stands at the origin, so its obstacles sit in front of it
+    spec = scenes.cage() if name != "fetch" else [("sphere", 0.95, 0.0, 0.9, 0.15), ("sphere", 0.7, 0.55, 1.2, 0.15),
+                                                  ("sphere", 0.7, -0.5, 0.6, 0.2), ("sphere", 1.0, 0.3, 0.5, 0.2)]
+    env = scenes.apply(spec, vb.Environment())
+    from conftest import apply_ref
+
+    renv = apply_ref(spec, ref.Env())
+    att = vb.Attachment([0.0, 0.0, 0.08], [0.0, 0.0, 0.0, 1.0])
+    att.add_spheres([vb.Sphere([0.0, 0.0, 0.0], 0.04), vb.Sphere([0.0, 0.0, 0.07], 0.03), vb.Sphere([0.03, 0.0, 0.12], 0.025)])
+    env.attach(att)
+    renv.attach(att.tf, [[s.x, s.y, s.z, s.r] for s in att.spheres])
+    rn = "panda_0_0" if name == "panda" else name
+    q = _cfgs(robot, 41, 10000)
+    ok, mg = robot.fkcc_batch(q, env, margin=True)
+    want = ref.fkcc_attach(rn, renv, q, threads=8)
+    plain = ref.fkcc(rn, apply_ref(spec, ref.Env()), q, threads=8)
+    print(f"attach {name}: valid_ref={want.mean():.3f} (without attachment {plain.mean():.3f}) differ={int((ok != want).sum())}")
+    assert (want != plain).any(), "the attachment must matter for this test to mean anything"
+    assert not ((ok != want) & (mg > BAND)).any()
+    assert not ((robot.fkcc_batch(q, env) != ok) & (mg > BAND)).any()
+    # edges: the attachment trace is used for the first rake pass only (planning/validate.hh:43-44 vs :58)
+    a, b = q[:1500], np.clip(q[:1500] + np.float32(0.1), robot.lower_bounds, robot.lower_bounds + robot.ranges)
+    e_ok, e_mg = robot.validate_motion_batch(a, b, env, margin=True)
+    e_want = ref.validate_motion(rn, renv, a, b, threads=8)
+    assert not ((e_ok != e_want) & (e_mg > BAND)).any()
+    env.detach()
+    assert not ((robot.fkcc_batch(q, env) != plain) & (mg > BAND)).any()
