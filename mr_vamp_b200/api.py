@@ -470,6 +470,20 @@ class Robot:
         return a, b
 
 
+def validate_pairs_batch(robot_a: Robot, cfg_a, robot_b: Robot, cfg_b, env: Optional[Environment] = None) -> np.ndarray:
+    """Composite validity of two robots sharing one environment (the fork's planned
+    MultiRobotEnvironment::check_inter_robot_collisions, MR_DEV_PLAN.md:176-198): fkcc(a) and fkcc(b) and
+    no world-frame sphere of a overlaps a sphere of b.  -> bool[n]."""
+    qa, qb = robot_a._configs(cfg_a), robot_b._configs(cfg_b)
+    if qa.shape[0] != qb.shape[0]:
+        raise ValueError("both robots need the same number of configurations")
+    n = qa.shape[0]
+    bits = np.zeros((n + 31) // 32, dtype=np.uint32)
+    _check(lib().vb_validate_pairs(robot_a.ctx.handle, robot_a.robot_id, _ptr(robot_a.base), robot_b.robot_id, _ptr(robot_b.base),
+                                   robot_a._env(env).handle, _ptr(qa), _ptr(qb), n, _ptr(bits, _u32p)))
+    return unpack_bits(bits, n)
+
+
 def panda_grid(x100: int, y100: int, z100: int = 0, ctx: Optional[Context] = None) -> Robot:
     """PandaBase<X100, Y100, Z100> (robots/panda_base.hh:15-51): base offset in centimetres."""
     base = [np.float32(x100) / np.float32(100.0), np.float32(y100) / np.float32(100.0), np.float32(z100) / np.float32(100.0)]

@@ -1496,10 +1496,162 @@ int vb_validate_motion(vb_ctx *ctx, vb_robot robot, const float *base, const vb_
     return vb_sync(ctx);
 }
 
-int vb_validate_pairs(vb_ctx *, vb_robot, const float *, vb_robot, const float *, const vb_env *, const float *,
-                      const float *, size_t, uint32_t *)
+}  // extern "C"
+
+namespace
 {
-    return fail(VB_ERR_STATE, "vb_validate_pairs: not built in this version");
+    // Robot-robot sphere pairs of composite configurations (the fork's planned
+    // MultiRobotEnvironment::check_inter_robot_collisions, MR_DEV_PLAN.md:176-198; primitive:
+    // collision/sphere_sphere.hh:9-23 on world-frame spheres of Robot::sphere_fk).  One warp per composite
+    // configuration: robot A's spheres are parked in shared memory, every lane owns spheres of robot B and
+    // sweeps all of A against them; an axis-aligned box test on the two sphere sets skips configurations
+    // whose robots are nowhere near each other.  ANDs "no pair overlaps" into the verdict words.
+    constexpr int kPairWarps = 8;
+    constexpr int kPairMaxSpheres = 128;
+
+    __global__ void __launch_bounds__(kPairWarps * 32)
+        pairs_kernel(const float4 *__restrict__ sa, int n_a, const float4 *__restrict__ sb, int n_b, size_t n, uint32_t *bits)
+    {
+        __shared__ float4 park[kPairWarps][kPairMaxSpheres];
+        const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+        const size_t n_warps = static_cast<size_t>(gridDim.x) * kPairWarps;
+        for (size_t i = static_cast<size_t>(blockIdx.x) * kPairWarps + warp; i < n; i += n_warps)
+        {
+            const float4 *A = sa + i * n_a, *B = sb + i * n_b;
+            float lo_a[3] = {3e38f, 3e38f, 3e38f}, hi_a[3] = {-3e38f, -3e38f, -3e38f};
+            float lo_b[3] = {3e38f, 3e38f, 3e38f}, hi_b[3] = {-3e38f, -3e38f, -3e38f};
+            for (int k = lane; k < n_a; k += 32)
+            {
+                const float4 s = A[k];
+                park[warp][k] = s;
+                const float c[3] = {s.x, s.y, s.z};
+#pragma unroll
+                for (int d = 0; d < 3; ++d)
+                {
+                    lo_a[d] = fminf(lo_a[d], c[d] - s.w);
+                    hi_a[d] = fmaxf(hi_a[d], c[d] + s.w);
+                }
+            }
+            for (int k = lane; k < n_b; k += 32)
+            {
+                const float4 s = B[k];
+                const float c[3] = {s.x, s.y, s.z};
+#pragma unroll
+                for (int d = 0; d < 3; ++d)
+                {
+                    lo_b[d] = fminf(lo_b[d], c[d] - s.w);
+                    hi_b[d] = fmaxf(hi_b[d], c[d] + s.w);
+                }
+            }
+            bool apart = false;
+#pragma unroll
+            for (int d = 0; d < 3; ++d)
+            {
+                for (int o = 16; o > 0; o >>= 1)
+                {
+                    lo_a[d] = fminf(lo_a[d], __shfl_xor_sync(0xffffffffu, lo_a[d], o));
+                    hi_a[d] = fmaxf(hi_a[d], __shfl_xor_sync(0xffffffffu, hi_a[d], o));
+                    lo_b[d] = fminf(lo_b[d], __shfl_xor_sync(0xffffffffu, lo_b[d], o));
+                    hi_b[d] = fmaxf(hi_b[d], __shfl_xor_sync(0xffffffffu, hi_b[d], o));
+                }
+                apart = apart || lo_a[d] > hi_b[d] || lo_b[d] > hi_a[d];
+            }
+            __syncwarp();
+            bool hit = false;
+            if (!apart)
+            {
+                for (int k = lane; k < n_b; k += 32)
+                {
+                    const float4 b = B[k];
+#pragma unroll 4
+                    for (int j = 0; j < n_a; ++j)
+                    {
+                        const float4 a = park[warp][j];
+                        const float dx = a.x - b.x, dy = a.y - b.y, dz = a.z - b.z, rs = a.w + b.w;
+                        hit = hit || (dx * dx + dy * dy + dz * dz - rs * rs < 0.f);
+                    }
+                }
+            }
+            const bool any = __any_sync(0xffffffffu, hit);
+            if (any && lane == 0)
+            {
+                atomicAnd(bits + (i >> 5), ~(1u << (i & 31)));
+            }
+            __syncwarp();
+        }
+    }
+}  // namespace
+
+extern "C" {
+
+int vb_validate_pairs(vb_ctx *ctx, vb_robot robot_a, const float *base_a, vb_robot robot_b, const float *base_b,
+                      const vb_env *env, const float *cfg_a, const float *cfg_b, size_t n, uint32_t *valid_bits)
+{
+    if (!ctx || !env || (n && (!cfg_a || !cfg_b || !valid_bits)))
+    {
+        return fail(VB_ERR_ARG, "vb_validate_pairs: null argument");
+    }
+    const vb::RobotOps *oa = ops_of(robot_a), *ob = ops_of(robot_b);
+    if (!oa || !ob)
+    {
+        return fail(VB_ERR_ARG, "vb_validate_pairs: unknown robot id");
+    }
+    if (oa->n_spheres > kPairMaxSpheres)
+    {
+        return fail(VB_ERR_ARG, "vb_validate_pairs: robot A has more than %d spheres", kPairMaxSpheres);
+    }
+    // each robot's own validity (environment + self collision), all devices
+    std::vector<uint32_t> bits_b((n + 31) / 32);
+    VB_TRY(vb_fkcc(ctx, robot_a, base_a, env, cfg_a, n, valid_bits, nullptr));
+    VB_TRY(vb_fkcc(ctx, robot_b, base_b, env, cfg_b, n, bits_b.data(), nullptr));
+    for (size_t w = 0; w < bits_b.size(); ++w)
+    {
+        valid_bits[w] &= bits_b[w];
+    }
+    // robot-robot pairs, chunked so that the two sphere buffers stay below ~1 GB per device
+    const size_t per_cfg = static_cast<size_t>(oa->n_spheres + ob->n_spheres) * sizeof(float4);
+    const size_t chunk = std::max<size_t>(32, (size_t(1) << 30) / per_cfg / 32 * 32);
+    const auto shards = shards_of(n, ctx->slots.size());
+    for (size_t i = 0; i < shards.size(); ++i)
+    {
+        const size_t m = shards[i].hi - shards[i].lo;
+        if (m == 0)
+        {
+            continue;
+        }
+        Query qa, qb;
+        VB_TRY(begin_query(ctx, static_cast<int>(i), robot_a, base_a, nullptr, qa));
+        VB_TRY(begin_query(ctx, static_cast<int>(i), robot_b, base_b, nullptr, qb));
+        Slot &s = *qa.slot;
+        const size_t c_max = std::min(m, chunk);
+        VB_CUDA(s.in_a.reserve(c_max * oa->dim * sizeof(float)));
+        VB_CUDA(s.in_b.reserve(c_max * ob->dim * sizeof(float)));
+        VB_CUDA(s.out.reserve(c_max * per_cfg));
+        VB_CUDA(s.bits.reserve((c_max + 31) / 32 * sizeof(uint32_t)));
+        for (size_t lo = 0; lo < m; lo += chunk)
+        {
+            const size_t c = std::min(chunk, m - lo), g0 = shards[i].lo + lo, words = (c + 31) / 32;
+            float4 *sph_a = s.out.as<float4>(), *sph_b = sph_a + c * oa->n_spheres;
+            VB_CUDA(cudaMemcpyAsync(s.in_a.p, cfg_a + g0 * oa->dim, c * oa->dim * sizeof(float), cudaMemcpyHostToDevice, s.stream));
+            VB_CUDA(cudaMemcpyAsync(s.in_b.p, cfg_b + g0 * ob->dim, c * ob->dim * sizeof(float), cudaMemcpyHostToDevice, s.stream));
+            VB_CUDA(cudaMemcpyAsync(s.bits.p, valid_bits + g0 / 32, words * sizeof(uint32_t), cudaMemcpyHostToDevice, s.stream));
+            qa.args.cfg = s.in_a.as<float>();
+            qa.args.n = c;
+            qa.args.spheres = reinterpret_cast<float *>(sph_a);
+            VB_CUDA(oa->sphere_fk(qa.args));
+            qb.args.cfg = s.in_b.as<float>();
+            qb.args.n = c;
+            qb.args.spheres = reinterpret_cast<float *>(sph_b);
+            VB_CUDA(ob->sphere_fk(qb.args));
+            const unsigned grid = static_cast<unsigned>(std::min<size_t>((c + kPairWarps - 1) / kPairWarps, size_t(s.sm_count) * 8));
+            pairs_kernel<<<grid, kPairWarps * 32, 0, s.stream>>>(sph_a, oa->n_spheres, sph_b, ob->n_spheres, c, s.bits.as<uint32_t>());
+            VB_CUDA(cudaGetLastError());
+            ctx->launches += 3;
+            VB_CUDA(cudaMemcpyAsync(valid_bits + g0 / 32, s.bits.p, words * sizeof(uint32_t), cudaMemcpyDeviceToHost, s.stream));
+            VB_CUDA(cudaStreamSynchronize(s.stream));
+        }
+    }
+    return vb_sync(ctx);
 }
 
 int vb_random_edge(vb_robot r, uint64_t seed, uint64_t index, float len_lo, float len_hi, float *a, float *b)
