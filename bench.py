@@ -208,8 +208,26 @@ def run_b200(args):
             dist.barrier()
         api._check(L.vb_sync(h))
 
+    # N > 1: the one exchange step of the path -- all-gather of the verdict words (NCCL over NVLink, issued
+    # by the library on its own stream right behind the kernel)
+    n_words = (n + 31) // 32
+    gathered_d = None
+    if world > 1:
+        uid = torch.zeros(128, dtype=torch.uint8)
+        if rank == 0:
+            buf = (C.c_ubyte * 128)()
+            api._check(L.vb_comm_unique_id(buf))
+            uid = torch.tensor(list(buf), dtype=torch.uint8)
+        uid = uid.to(dev)
+        dist.broadcast(uid, src=0)
+        raw = (C.c_ubyte * 128)(*uid.cpu().tolist())
+        api._check(L.vb_comm_init(h, world, rank, raw))
+        gathered_d = torch.zeros(n_words * world, device=dev, dtype=torch.int32)
+
     def step_device():
         api._check(L.vb_fkcc_d(h, 0, rid, None, eh, cfg_d.data_ptr(), n, bits_d.data_ptr(), None))
+        if world > 1:
+            api._check(L.vb_comm_allgather_bits_d(h, bits_d.data_ptr(), gathered_d.data_ptr(), n_words))
 
     def timed(fn, steps):
         ms = C.c_double()
@@ -231,6 +249,11 @@ def run_b200(args):
         ms_total = timed(step_device, args.steps)
     launches = ctx.launch_count() - launches0
     value = world * n * args.steps / (ms_total * 1e-3)
+    gather_ok = None
+    if world > 1:
+        # every rank holds every rank's words; rank r's block must equal what rank r computed
+        mine = gathered_d[rank * n_words:(rank + 1) * n_words]
+        gather_ok = bool(torch.equal(mine, bits_d))
     valid = C.c_uint64()
     api._check(L.vb_popcount_d(h, 0, bits_d.data_ptr(), n, C.byref(valid)))
 
@@ -318,7 +341,9 @@ def run_b200(args):
         "config": {"workload": WORKLOAD, "configs_per_gpu_per_step": n, "robot": "PandaBase<0,0,0>",
                    "environment": "MotionBenchMaker panda table_pick scene 1 (10 z-aligned cuboids + 2 z-aligned capsules)",
                    "l2": f"inputs {28 * n / 1e9:.2f} GB per step, larger than the 126 MB L2", "valid_fraction": valid.value / n,
-                   "sharding": "configurations sharded by rank, environment replicated, no data-path collective"},
+                   "sharding": "configurations sharded by rank (contiguous ranges), environment + grid replicated per GPU; "
+                               "one collective: ncclAllGather of the verdict words inside the timed step (N > 1)",
+                   "gather_verified": gather_ok},
         "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": 28 * n_e2e, "d2h_bytes_per_step": 4 * ((n_e2e + 31) // 32),
                 "steps": e2e_steps, "matches_device_path": same},
         "gpu_launches": int(launches),
