@@ -173,6 +173,7 @@ def run_reference(args):
 
 # ---- the B200 arm ----------------------------------------------------------------------------------
 def run_b200(args):
+    os.environ.setdefault("NCCL_DEBUG_FILE", "/dev/stderr")  # keep stdout to the one JSON line
     import torch
     import torch.distributed as dist
 
@@ -298,6 +299,9 @@ def run_b200(args):
     step_edges()
     ms_edges = timed(step_edges, 3)
     edges_value = world * n_edges * 3 / (ms_edges * 1e-3)
+    ecount = C.c_uint64()
+    api._check(L.vb_popcount_d(h, 0, ebits.data_ptr(), n_edges, C.byref(ecount)))
+    edge_valid = ecount.value / n_edges
 
     if rank != 0:
         if world > 1:
@@ -327,10 +331,22 @@ def run_b200(args):
             packed = time_reference(spec, sample, threads, True)
             n_b = max(8 * threads, n_cpu // 8)
             bcast = time_reference(spec, sample[:n_b], threads, False)
+            try:
+                ref_mod, renv = ref_env(spec)
+                n_ce = min(n_edges, 1 << 17)
+                ea_h, eb_h = ea[:n_ce].cpu().numpy(), eb[:n_ce].cpu().numpy()
+                ref_mod.validate_motion("panda_0_0", renv, ea_h[:4096], eb_h[:4096], threads)
+                t0 = time.perf_counter()
+                ev = ref_mod.validate_motion("panda_0_0", renv, ea_h, eb_h, threads)
+                cpu_edges = n_ce / (time.perf_counter() - t0)
+                edge_match = bool(np.array_equal(ev, api.unpack_bits(ebits[: (n_ce + 31) // 32].cpu().numpy().view(np.uint32), n_ce)))
+            except Exception:
+                cpu_edges, edge_match = None, None
             cpu = {"value": packed, "unit": UNIT, "cores": threads, "kind": "reference",
                    "sample": f"first {sample.shape[0]} configurations of the same stream, reference fkcc<8> with 8 distinct "
                              f"configurations per block (one verdict per block), {threads} threads",
-                   "per_config_verdicts_value": bcast}
+                   "per_config_verdicts_value": bcast, "edges_per_s": cpu_edges,
+                   "edge_verdicts_match_gpu": edge_match}
         except Exception as exc:  # the checker is optional for the number, never for the product
             cpu = {"value": None, "unit": UNIT, "cores": 0, "kind": "reference", "sample": f"unavailable: {exc}"}
 
@@ -355,7 +371,7 @@ def run_b200(args):
                              "bytes_per_config": 28.125}},
         "cpu_baseline": cpu,
         "extra": {"edges_per_s": edges_value, "edges_per_gpu": n_edges, "edge_lengths_rad": [0.05, 1.0],
-                  "edge_valid_fraction": None},
+                  "edge_valid_fraction": edge_valid},
     }
     print(json.dumps(line), flush=True)
     if world > 1:

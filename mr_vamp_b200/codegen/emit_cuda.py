@@ -247,7 +247,7 @@ def _slack(v: float) -> str:
     return "-1.0f" if v < 0 else _f32(v)
 
 
-def _tables(name: str, em: _Emitter, walk: bool = False) -> list[str]:
+def _tables(name: str, em: _Emitter, walk: bool = False, stride: int = 0) -> list[str]:
     """Constant-memory check tables; with `walk` also the global-memory mirrors and work-unit tables of
     the warp walk (vb_walk.cuh).  Returns (lines, table type, geometry dict)."""
     refs = list(em.refs)
@@ -262,11 +262,17 @@ def _tables(name: str, em: _Emitter, walk: bool = False) -> list[str]:
             g["ubegin"], g["ucount"] = g["begin"], g["count"]
             for k in range(g["count"]):
                 ref_group[g["begin"] + k] = gi
+    import numpy as np
+
+    F = np.float32
     units = []
     for gi, g in enumerate(em.selfg):
         g["unit0"] = len(units)
         for i in range(g["a"][1]):
-            units.append((g["a"][0] + i, gi))
+            sa, _, ra = em.refs[g["a"][0] + i]
+            sb, _, rb = g["gb"]
+            filt = float(F(F(ra) + F(rb)) + F(g["slack"])) if g["slack"] >= 0 else -1.0
+            units.append((3 * sa * stride, 3 * sb * stride, ra, filt, g["b"][0], g["b"][1]))
     assert len(refs) < 2048 and len(units) < 2048, (name, len(refs), len(units))
     ne, ns, na, nr = len(em.env), len(em.selfg), len(em.att), len(refs)
     t = f"Tables<{max(ne, 1)}, {max(ns, 1)}, {max(na, 1)}, {max(nr, 1)}>"
@@ -323,10 +329,16 @@ def _tables(name: str, em: _Emitter, walk: bool = False) -> list[str]:
         out.append(f"__device__ const SelfGroup {name}_gself[{max(ns, 1)}] = {{")
         out.extend(self_rows())
         out.append("};")
-        uu = units or [(0, 0)]
+        uu = units or [(0, 0, 0.0, -1.0, 0, 0)]
+        assert all(u[0] < 65536 and u[1] < 65536 for u in uu), name
         out.append(f"__device__ const SelfUnit {name}_units[{len(uu)}] = {{")
-        for i in range(0, len(uu), 8):
-            out.append("    " + ", ".join(f"{{{a}, {g}}}" for a, g in uu[i : i + 8]) + ",")
+        for i in range(0, len(uu), 4):
+            out.append("    " + ", ".join(f"{{{a}, {g}, {_f32(ra)}, {_f32(fr) if fr >= 0 else '-1.0f'}, {bb}, {bc}}}"
+                                          for a, g, ra, fr, bb, bc in uu[i : i + 4]) + ",")
+        out.append("};")
+        out.append(f"__device__ const BRef {name}_brefs[{len(rr)}] = {{")
+        for i in range(0, len(rr), 8):
+            out.append("    " + ", ".join(f"{{{3 * sl * stride}, {_f32(r) if r >= 0 else '-1.0f'}}}" for sl, _, r in rr[i : i + 8]) + ",")
         out.append("};")
         max_u = max([g["ucount"] for g in em.env] or [1])
         max_a = max([g["a"][1] for g in em.selfg if not g.get("dense")] or [1])
@@ -506,7 +518,10 @@ def emit_robot(ir: dict[str, Any]) -> str:
     w('#include "../csrc/vb_sdf.cuh"')
     w("namespace vb")
     w("{")
-    tab, ttype, geom = _tables(f"k_{robot}_tables", em, walk=True)
+    geom = {"env_q": 256, "self_q": 256, "pair_q": 256, "env_groups": max(len(em.env), 1)}
+    n_slots = max(len(em.slots), len(em_att.slots) if em_att else 0)
+    warps, ctas = _geometry(n_slots, geom)
+    tab, ttype, _ = _tables(f"k_{robot}_tables", em, walk=True, stride=32 * warps + 1)
     out.extend(tab)
     if em_att:
         tab2, ttype2, _ = _tables(f"k_{robot}_tables_attach", em_att)
@@ -518,8 +533,6 @@ def emit_robot(ir: dict[str, Any]) -> str:
     w(f"    static constexpr int kSpheres = {S};")
     w(f"    static constexpr int kResolution = {ir['resolution']};")
     w(f"    static constexpr bool kHasAttach = {'true' if has_attach else 'false'};")
-    n_slots = max(len(em.slots), len(em_att.slots) if em_att else 0)
-    warps, ctas = _geometry(n_slots, geom)
     w(f"    static constexpr int kSlots = {n_slots};  // distinct sphere centres used by the checks")
     w(f"    static constexpr int kBlock = {32 * warps};  // threads per CTA: {warps} warps x {ctas} CTA(s) per SM fill the shared memory")
     w("    static constexpr int kStride = kBlock + 1;  // slot-column stride in floats (odd: conflict free)")
@@ -531,7 +544,7 @@ def emit_robot(ir: dict[str, Any]) -> str:
     w(f"    __device__ __forceinline__ static const TablesT &tables() {{ return k_{robot}_tables; }}")
     w("    __device__ __forceinline__ static WalkTables walk_tables()")
     w("    {")
-    w(f"        return WalkTables{{k_{robot}_tables_grefs, k_{robot}_tables_ref_group, k_{robot}_tables_genv, k_{robot}_tables_gself, k_{robot}_tables_units}};")
+    w(f"        return WalkTables{{k_{robot}_tables_grefs, k_{robot}_tables_ref_group, k_{robot}_tables_genv, k_{robot}_tables_gself, k_{robot}_tables_units, k_{robot}_tables_brefs}};")
     w("    }")
     if em_att:
         w(f"    using TablesAttachT = {ttype2};")

@@ -42,11 +42,24 @@ namespace vb
         uint16_t unit0, dense;
     };
 
-    // one (self group, a_i) work unit of the warp walk
-    struct SelfUnit
+    // One (self group, a_i) work unit of the warp walk, flattened so that ONE 16-byte load gives the
+    // filter and the pair stage everything they need.  Offsets are float indices into a slot column:
+    // 3 * slot * kStride.
+    struct alignas(16) SelfUnit
     {
-        uint16_t a_ref;  // index into refs
-        uint16_t group;  // index into self
+        uint16_t a_off;    // column offset of a_i
+        uint16_t gb_off;   // column offset of the other link's bounding sphere
+        float a_r;         // radius of a_i
+        float filter_r;    // a_r + r(gb) + slack_b, or < 0: no containment bound (always passes)
+        uint16_t b_begin;  // the other link's fine spheres: brefs[b_begin .. b_begin + b_count)
+        uint16_t b_count;
+    };
+
+    // b-side sphere of a self group: pre-multiplied column offset + radius
+    struct alignas(8) BRef
+    {
+        uint32_t off;
+        float r;
     };
 
     template <int NE, int NS, int NA, int NR>
@@ -67,5 +80,6 @@ namespace vb
         const RefGroup *env;
         const SelfGroup *self;
         const SelfUnit *units;
+        const BRef *brefs;  // refs as (column offset, radius)
     };
 }  // namespace vb

@@ -80,19 +80,29 @@ namespace vb
             z = col[2 * S];
         }
 
+        VB_D static void at(const WalkCtx &c, int L, unsigned off, float &x, float &y, float &z)
+        {
+            const float *col = c.wcol + L + off;
+            x = col[0];
+            y = col[S];
+            z = col[2 * S];
+        }
+
         // a_i of configuration L against every b_j of its group
-        VB_D static bool pair_unit(const WalkCtx &c, const WalkTables &w, int L, const SlotRef &ar, int bb, int bc)
+        VB_D static bool pair_unit(const WalkCtx &c, const WalkTables &w, int L, const SelfUnit &u)
         {
             float ax, ay, az;
-            local(c, L, ar.slot, ax, ay, az);
+            at(c, L, u.a_off, ax, ay, az);
+            const BRef *B = w.brefs + u.b_begin;
+            const int bc = u.b_count;
             bool hit = false;
 #pragma unroll 4
             for (int j = 0; j < bc; ++j)
             {
-                const SlotRef br = w.refs[bb + j];
+                const BRef br = B[j];
                 float bx, by, bz;
-                local(c, L, br.slot, bx, by, bz);
-                const float dx = ax - bx, dy = ay - by, dz = az - bz, rs = ar.r + br.r;
+                at(c, L, br.off, bx, by, bz);
+                const float dx = ax - bx, dy = ay - by, dz = az - bz, rs = u.a_r + br.r;
                 hit = hit || (dx * dx + dy * dy + dz * dz - rs * rs < 0.f);
             }
             return hit;
@@ -112,14 +122,10 @@ namespace vb
                 {
                     const unsigned code = c.pairq[i];
                     const int L = code & 31;
-                    if (!done(c, L))
+                    const SelfUnit u = w.units[code >> 5];
+                    if (!done(c, L) && pair_unit(c, w, L, u))
                     {
-                        const SelfUnit su = w.units[code >> 5];
-                        const SelfGroup *G = w.self + su.group;
-                        if (pair_unit(c, w, L, w.refs[su.a_ref], G->b_begin, G->b_count))
-                        {
-                            atomicOr(c.cmask, 1u << L);
-                        }
+                        atomicOr(c.cmask, 1u << L);
                     }
                 }
             }
@@ -132,14 +138,14 @@ namespace vb
         }
 
         // queue one (configuration, a_i) unit; when the queue is full the lane runs the unit itself
-        VB_D static void push_pair(const WalkCtx &c, const WalkTables &w, int L, int unit, const SlotRef &ar, const SelfGroup *G)
+        VB_D static void push_pair(const WalkCtx &c, const WalkTables &w, int L, int unit, const SelfUnit &u)
         {
-            const unsigned at = atomicAdd(c.cmask + 1, 1u);
-            if (at < static_cast<unsigned>(Robot::kPairQ))
+            const unsigned at_ = atomicAdd(c.cmask + 1, 1u);
+            if (at_ < static_cast<unsigned>(Robot::kPairQ))
             {
-                c.pairq[at] = static_cast<uint16_t>(L | (unit << 5));
+                c.pairq[at_] = static_cast<uint16_t>(L | (unit << 5));
             }
-            else if (pair_unit(c, w, L, ar, G->b_begin, G->b_count))
+            else if (pair_unit(c, w, L, u))
             {
                 atomicOr(c.cmask, 1u << L);
             }
@@ -158,23 +164,23 @@ namespace vb
                 {
                     const unsigned code = c.selfq[i];
                     const int L = code & 31;
+                    const SelfGroup *G = w.self + (code >> 5);
+                    const int ac = G->a_count, u0 = G->unit0;
                     if (!done(c, L))
                     {
-                        const SelfGroup *G = w.self + (code >> 5);
-                        const float slack = G->slack_b, rb = G->gb.r;
-                        const int a0 = G->a_begin, ac = G->a_count, u0 = G->unit0;
+                        const SelfUnit *U = w.units + u0;
                         float gx, gy, gz;
-                        local(c, L, G->gb.slot, gx, gy, gz);
+                        at(c, L, U[0].gb_off, gx, gy, gz);
 #pragma unroll 2
                         for (int k = 0; k < ac; ++k)
                         {
-                            const SlotRef ar = w.refs[a0 + k];
+                            const SelfUnit u = U[k];
                             float ax, ay, az;
-                            local(c, L, ar.slot, ax, ay, az);
-                            const float dx = ax - gx, dy = ay - gy, dz = az - gz, R = ar.r + rb + slack;
-                            if (slack < 0.f || dx * dx + dy * dy + dz * dz - R * R < 0.f)
+                            at(c, L, u.a_off, ax, ay, az);
+                            const float dx = ax - gx, dy = ay - gy, dz = az - gz;
+                            if (u.filter_r < 0.f || dx * dx + dy * dy + dz * dz - u.filter_r * u.filter_r < 0.f)
                             {
-                                push_pair(c, w, L, u0 + k, ar, G);
+                                push_pair(c, w, L, u0 + k, u);
                             }
                         }
                     }

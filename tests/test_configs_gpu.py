@@ -1,0 +1,175 @@
+"""BASELINE.json configs beyond the bench line, as parity + measurement cases.
+Each case checks verdicts against the reference on a sample and prints device throughput next to the
+reference's CPU throughput on this box; the numbers are collected in gpurun_out/configs_r1.json (copied to
+profiles/ by hand).  These are NOT the bench line (bench.py measures configs[1])."""
+import json
+import os
+import time
+
+import numpy as np
+import pytest
+
+from mr_vamp_b200 import scenes
+from conftest import apply_ref
+
+pytestmark = pytest.mark.gpu
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+BAND = 1e-5
+RESULTS = {}
+
+
+def _cfgs(robot, seed, n):
+    rng = np.random.default_rng(seed)
+    return (robot.lower_bounds + rng.random((n, robot.dimension), dtype=np.float32) * robot.ranges).astype(np.float32)
+
+
+def _edges(robot, seed, n, lo=0.05, hi=1.0):
+    a = _cfgs(robot, seed, n)
+    rng = np.random.default_rng(seed + 1)
+    d = rng.normal(size=a.shape).astype(np.float32)
+    d *= (rng.uniform(lo, hi, (n, 1)) / np.linalg.norm(d, axis=1, keepdims=True)).astype(np.float32)
+    return a, np.clip(a + d, robot.lower_bounds, robot.lower_bounds + robot.ranges).astype(np.float32)
+
+
+def _timed(fn, reps=3):
+    fn()
+    best = 1e30
+    for _ in range(reps):
+        t0 = time.perf_counter()
+        fn()
+        best = min(best, time.perf_counter() - t0)
+    return best
+
+
+def _record(key, **kw):
+    RESULTS[key] = kw
+    os.makedirs(os.path.join(ROOT, "gpurun_out"), exist_ok=True)
+    with open(os.path.join(ROOT, "gpurun_out", "configs_r1.json"), "w") as fh:
+        json.dump(RESULTS, fh, indent=1)
+    print(key, json.dumps(kw))
+
+
+def _mbm(robot_name):
+    return scenes.load_mbm(os.path.join(scenes.GOLDEN_DIR, f"mbm_{robot_name}.json.gz"))
+
+
+def test_m1_all_panda_mbm_problems(vb, ref):
+    """configs[0]: every MotionBenchMaker Panda problem (7 scenarios x 100): start/goal verdicts, the straight
+    start->goal edge, 2000 random configurations and 500 RRTC-shaped edges per scene; verdicts must match the
+    reference on ALL of them outside the 1e-5 m band (north_star)."""
+    robot = vb.Robot("panda")
+    mbm = _mbm("panda")
+    n_q = n_e = hard = inband = 0
+    for name, problems in mbm["problems"].items():
+        for p in problems:
+            spec = scenes.problem_to_spec(p)
+            env = scenes.apply(spec, vb.Environment())
+            renv = apply_ref(spec, ref.Env())
+            q = np.concatenate([np.asarray([p["start"]] + p["goals"], np.float32), _cfgs(robot, p["index"], 2000)])
+            ok, mg = robot.fkcc_batch(q, env, margin=True)
+            ok0 = robot.fkcc_batch(q, env)
+            want = ref.fkcc("panda_0_0", renv, q, threads=8)
+            a, b = _edges(robot, 1000 + p["index"], 500)
+            a = np.concatenate([np.asarray([p["start"]], np.float32), a])
+            b = np.concatenate([np.asarray([p["goals"][0]], np.float32), b])
+            e_ok = robot.validate_motion_batch(a, b, env)
+            _, e_mg = robot.validate_motion_batch(a, b, env, margin=True)
+            e_want = ref.validate_motion("panda_0_0", renv, a, b, threads=8)
+            hard += int(((ok0 != want) & (mg > BAND)).sum() + ((ok != want) & (mg > BAND)).sum() + ((e_ok != e_want) & (e_mg > BAND)).sum())
+            inband += int(((ok0 != want) & (mg <= BAND)).sum() + ((e_ok != e_want) & (e_mg <= BAND)).sum())
+            n_q += q.shape[0]
+            n_e += a.shape[0]
+    _record("m1_panda_mbm", problems=700, configurations=n_q, edges=n_e, hard_mismatches=hard, within_band=inband)
+    assert hard == 0
+
+
+def test_m3_capt_100k_points_edge_validation(vb, ref):
+    """configs[2]: Panda vs a CAPT built (by the reference) from 100k points sampled on the surfaces of
+    table_pick scene 1; batched RRTC-shaped edge validation."""
+    robot = vb.Robot("panda")
+    p = _mbm("panda")["problems"]["table_pick"][0]
+    rng = np.random.default_rng(0)
+    pts = []
+    for o in p["box"]:
+        c = vb.Cuboid(o["position"], o["orientation_euler_xyz"], o["half_extents"]).raw()
+        ctr, axes, half = c[:3], c[3:12].reshape(3, 3), c[12:15]
+        u = rng.uniform(-1, 1, (8334, 3)).astype(np.float32)
+        face = rng.integers(0, 3, 8334)
+        u[np.arange(8334), face] = np.sign(u[np.arange(8334), face])
+        pts.append(ctr + (u * half) @ axes)
+    for o in p["cylinder"]:
+        c = vb.Cylinder(o["position"], o["orientation_euler_xyz"], o["radius"], o["length"]).raw()
+        t = rng.uniform(0, 1, 8334)[:, None]
+        ang = rng.uniform(0, 2 * np.pi, 8334)
+        v = c[3:6] / np.linalg.norm(c[3:6])
+        e1 = np.cross(v, [1.0, 0.0, 0.0])
+        e1 /= np.linalg.norm(e1)
+        e2 = np.cross(v, e1)
+        pts.append(c[:3] + t * c[3:6] + c[6] * (np.cos(ang)[:, None] * e1 + np.sin(ang)[:, None] * e2))
+    pts = np.concatenate(pts).astype(np.float32)[:100000]
+    renv = ref.Env()
+    build_ns = renv.add_pointcloud(pts, 0.012, 0.06, 0.0025)
+    c = renv.capt(0)
+    env = vb.Environment()
+    env.add_capt_buffers(c["tests"], c["aff_starts"], c["aff_x"], c["aff_y"], c["aff_z"], c["aabbs"], c["aabb_top"],
+                         c["r_point"], c["nlog2"])
+    n = 200_000
+    a, b = _edges(robot, 7, n)
+    ok = robot.validate_motion_batch(a, b, env)
+    m = 4000
+    _, mg = robot.validate_motion_batch(a[:m], b[:m], env, margin=True)
+    want = ref.validate_motion("panda_0_0", renv, a[:m], b[:m], threads=8)
+    hard = int(((ok[:m] != want) & (mg > BAND)).sum())
+    t_gpu = _timed(lambda: robot.validate_motion_batch(a, b, env))
+    threads = os.cpu_count() or 1
+    t0 = time.perf_counter()
+    ref.validate_motion("panda_0_0", renv, a[:20000], b[:20000], threads=threads)
+    t_cpu = time.perf_counter() - t0
+    _record("m3_capt_100k_edges", points=int(pts.shape[0]), affordance_mb=round(c["aff_x"].nbytes * 3 / 1e6, 1),
+            capt_build_ms=round(build_ns / 1e6, 1), edges=n, valid_fraction=float(ok.mean()), hard_mismatches=hard,
+            gpu_edges_per_s_host_buffers=n / t_gpu, cpu_edges_per_s=20000 / t_cpu, cpu_threads=threads)
+    assert hard == 0
+
+
+@pytest.mark.parametrize("name,problem", [("ur5", "table_pick"), ("fetch", "table_pick"), ("baxter", None)])
+def test_m4_other_robots_sweep(vb, ref, name, problem):
+    """configs[3]: UR5 / Fetch / Baxter fkcc + motion validation over batch sizes 1e3..1e6 (host buffers)."""
+    robot = vb.Robot(name)
+    mbm = _mbm(name)
+    probs = mbm["problems"][problem] if problem else next(iter(mbm["problems"].values()))
+    spec = scenes.problem_to_spec(probs[0])
+    env = scenes.apply(spec, vb.Environment())
+    renv = apply_ref(spec, ref.Env())
+    q = _cfgs(robot, 3, 1_000_000)
+    ok, mg = robot.fkcc_batch(q[:20000], env, margin=True)
+    want = ref.fkcc(name, renv, q[:20000], threads=8)
+    assert not ((robot.fkcc_batch(q[:20000], env) != want) & (mg > BAND)).any()
+    sweep = {}
+    for n in (1_000, 10_000, 100_000, 1_000_000):
+        sweep[str(n)] = n / _timed(lambda: robot.fkcc_batch(q[:n], env))
+    a, b = _edges(robot, 4, 100_000, hi={"ur5": 1.5, "fetch": 1.0, "baxter": 0.5}[name])
+    e_ok = robot.validate_motion_batch(a, b, env)
+    _, e_mg = robot.validate_motion_batch(a[:3000], b[:3000], env, margin=True)
+    e_want = ref.validate_motion(name, renv, a[:3000], b[:3000], threads=8)
+    assert not ((e_ok[:3000] != e_want) & (e_mg > BAND)).any()
+    t_e = _timed(lambda: robot.validate_motion_batch(a, b, env))
+    threads = os.cpu_count() or 1
+    t0 = time.perf_counter()
+    ref.fkcc_packed(name, renv, q[:800_000], threads=threads)
+    cpu = 800_000 / (time.perf_counter() - t0)
+    _record(f"m4_{name}", valid_fraction=float(want.mean()), fkcc_configs_per_s_host_buffers=sweep,
+            edges_per_s_host_buffers=100_000 / t_e, edge_valid_fraction=float(e_ok.mean()),
+            cpu_packed_configs_per_s=cpu, cpu_threads=threads)
+
+
+def test_m5_two_pandas(vb, ref):
+    """configs[4]: two Pandas 1 m apart, cage duplicated at both bases, composite validation."""
+    ra, rb = vb.robot("panda_0_0"), vb.robot("panda_1_0")
+    spec = scenes.cage(offset=ra.base) + scenes.cage(offset=rb.base)
+    env = scenes.apply(spec, vb.Environment())
+    n = 1_000_000
+    qa, qb = _cfgs(ra, 61, n), _cfgs(rb, 62, n)
+    ok = vb.validate_pairs_batch(ra, qa, rb, qb, env)
+    t = _timed(lambda: vb.validate_pairs_batch(ra, qa, rb, qb, env), reps=2)
+    _record("m5_two_pandas", composites=n, valid_fraction=float(ok.mean()), composites_per_s_host_buffers=n / t,
+            parity="unpinned (no reference implementation); checked against a CPU restatement in tests/test_pairs_gpu.py")
