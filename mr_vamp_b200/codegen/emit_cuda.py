@@ -481,7 +481,7 @@ def _geometry(n_slots: int, geom: dict) -> tuple[int, int]:
     """(warps per CTA, CTAs per SM) maximising resident warps within 227 KB of shared memory per SM."""
     queue = 2 * (geom["env_q"] + geom["self_q"] + geom["pair_q"]) + 128 * geom["env_groups"] + 16
     per_warp = 3 * n_slots * 4 * 32 + queue
-    fixed = 128 * 16 + 3 * n_slots * 4 + 16 + 1024  # staged records, stride padding, per-CTA reserve
+    fixed = 3 * n_slots * 4 + 16 + 1024  # stride padding, per-CTA reserve
     best = (1, 1)
     for ctas in (1, 2, 3, 4, 6, 8):
         w = min((227 * 1024 // ctas - fixed) // per_warp, 16, 32 // ctas)

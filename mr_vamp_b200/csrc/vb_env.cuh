@@ -211,20 +211,21 @@ namespace vb
         float x, y, z, r;
     };
 
-    // collision/validity.hh:46-150.  `P` points at the packed records (shared or global memory).
+    // collision/validity.hh:46-150.  `P` points at the packed records in global memory (read through the
+    // non-coherent path: a few hundred bytes shared by every thread, L1-resident).
     // Each loop stops at the first record whose min_distance is >= the sphere's largest distance
     // from the origin, as the reference does; with an exact sqrt the cut is conservative, so the
     // verdict equals the unpruned OR over all obstacles.
     template <class M>
-    VB_D bool env_hit(const EnvView &e, const float4 *P, float sx, float sy, float sz, float sr, M &mg)
+    __device__ __noinline__ bool env_hit(const EnvView &e, const float4 *P, float sx, float sy, float sz, float sr, M &mg)
     {
         const float ext = sqrtf(sx * sx + sy * sy + sz * sz) + sr;
         mg.count(9);
         const float4 *p = P;
         for (int i = 0; i < e.n_spheres; ++i, p += kSphereQ)
         {
-            const float4 a = p[0];
-            if (p[1].x >= ext)
+            const float4 a = __ldg(p + 0);
+            if (__ldg(p + 1).x >= ext)
             {
                 break;
             }
@@ -240,8 +241,8 @@ namespace vb
         p = P + kSphereQ * e.n_spheres;
         for (int i = 0; i < e.n_capsules; ++i, p += kCapsuleQ)
         {
-            const float4 a = p[0], b = p[1];
-            if (p[2].x >= ext)
+            const float4 a = __ldg(p + 0), b = __ldg(p + 1);
+            if (__ldg(p + 2).x >= ext)
             {
                 break;
             }
@@ -261,7 +262,7 @@ namespace vb
         p = P + kSphereQ * e.n_spheres + kCapsuleQ * e.n_capsules;
         for (int i = 0; i < e.n_zcapsules; ++i, p += kZCapsQ)
         {
-            const float4 a = p[0], b = p[1];
+            const float4 a = __ldg(p + 0), b = __ldg(p + 1);
             if (b.z >= ext)
             {
                 break;
@@ -283,14 +284,14 @@ namespace vb
         p = P + kSphereQ * e.n_spheres + kCapsuleQ * e.n_capsules + kZCapsQ * e.n_zcapsules;
         for (int i = 0; i < e.n_cuboids; ++i, p += kCuboidQ)
         {
-            const float4 c = p[0];
+            const float4 c = __ldg(p + 0);
             if (c.w >= ext)
             {
                 break;
             }
             // sphere_cuboid.hh:8-26
             mg.count(1 + 30);
-            const float4 a1 = p[1], a2 = p[2], a3 = p[3];
+            const float4 a1 = __ldg(p + 1), a2 = __ldg(p + 2), a3 = __ldg(p + 3);
             const float xs = sx - c.x, ys = sy - c.y, zs = sz - c.z;
             const float d1 = fmaxf(fabsf(a1.x * xs + a1.y * ys + a1.z * zs) - a1.w, 0.f);
             const float d2 = fmaxf(fabsf(a2.x * xs + a2.y * ys + a2.z * zs) - a2.w, 0.f);
@@ -306,14 +307,14 @@ namespace vb
             kCuboidQ * e.n_cuboids;
         for (int i = 0; i < e.n_zcuboids; ++i, p += kZCubQ)
         {
-            const float4 c = p[0];
+            const float4 c = __ldg(p + 0);
             if (c.w >= ext)
             {
                 break;
             }
             // sphere_cuboid.hh:35-52
             mg.count(1 + 21);
-            const float4 ax = p[1], hr = p[2];
+            const float4 ax = __ldg(p + 1), hr = __ldg(p + 2);
             const float xs = sx - c.x, ys = sy - c.y, zs = sz - c.z;
             const float d1 = fmaxf(fabsf(ax.x * xs + ax.y * ys) - hr.x, 0.f);
             const float d2 = fmaxf(fabsf(ax.z * xs + ax.w * ys) - hr.y, 0.f);

@@ -14,8 +14,6 @@
 
 namespace vb
 {
-    constexpr int kStageQuads = 128;  // obstacle records staged in shared memory when they fit (2 KB)
-
     struct LaunchArgs
     {
         EnvView env;
@@ -52,43 +50,31 @@ namespace vb
         return 2 * (Robot::kEnvQ + Robot::kSelfQ + Robot::kPairQ) + 128 * (Robot::kEnvGroups > 0 ? Robot::kEnvGroups : 1) + 16;
     }
 
+    // Shared memory is addressed by INDEX from the start of the dynamic window (see vb_walk.cuh: the compiler
+    // then emits LDS/STS instead of generic accesses).
     struct Scratch
     {
-        const float4 *prims;  // obstacle records (shared or global)
-        float *col;           // this thread's slot column
+        const float4 *prims;  // obstacle records (global memory, read through the non-coherent path)
+        unsigned col;         // float index of this thread's slot column
         int stride;
         float *att_col;       // this thread's column of posed attachment spheres (global memory)
         int att_stride;
-        unsigned char *queues;  // this warp's work queues
+        unsigned queues;      // byte offset of this warp's work queues
     };
 
-    // dynamic shared memory: [staged obstacle records][3 * kSlots * (blockDim + 1) floats][per-warp queues]
+    // dynamic shared memory: [3 * kSlots * (blockDim + 1) floats: one column per thread][per-warp queues]
     template <class Robot>
     VB_D Scratch stage_env(const LaunchArgs &a, bool with_queues)
     {
-        extern __shared__ float4 smem[];
-        const EnvView &env = a.env;
         Scratch s;
-        const bool staged = env.n_quads <= kStageQuads;
-        const int nq = staged ? env.n_quads : 0;
-        if (staged)
-        {
-            for (int i = threadIdx.x; i < nq; i += blockDim.x)
-            {
-                smem[i] = env.prims[i];
-            }
-            __syncthreads();
-        }
-        s.prims = staged ? smem : env.prims;  // large scenes: L1/L2-resident
-        float *slots = reinterpret_cast<float *>(smem + nq);
-        s.col = slots + threadIdx.x;
+        s.prims = a.env.prims;
+        s.col = threadIdx.x;
         s.stride = Robot::kStride;  // odd: a warp reading ONE column at 32 different slots is conflict free too
         s.att_stride = static_cast<int>(gridDim.x * blockDim.x);
         s.att_col = a.att_scratch ? a.att_scratch + static_cast<size_t>(blockIdx.x) * blockDim.x + threadIdx.x : nullptr;
         // 16-byte aligned start of the queues
-        const size_t slot_floats = (static_cast<size_t>(3 * Robot::kSlots * Robot::kStride) + 3) & ~static_cast<size_t>(3);
-        s.queues = with_queues ? reinterpret_cast<unsigned char *>(slots + slot_floats) + (threadIdx.x >> 5) * queue_bytes<Robot>()
-                               : nullptr;
+        const unsigned slot_floats = (3u * Robot::kSlots * Robot::kStride + 3u) & ~3u;
+        s.queues = with_queues ? 4u * slot_floats + (threadIdx.x >> 5) * queue_bytes<Robot>() : 0u;
         return s;
     }
 
@@ -102,9 +88,10 @@ namespace vb
         VB_D Center load(const SlotRef &ref) const
         {
             Center c;
-            c.x = sc.col[(3 * ref.slot + 0) * kStride];
-            c.y = sc.col[(3 * ref.slot + 1) * kStride];
-            c.z = sc.col[(3 * ref.slot + 2) * kStride];
+            const float *col = shm_f32() + sc.col;
+            c.x = col[(3 * ref.slot + 0) * kStride];
+            c.y = col[(3 * ref.slot + 1) * kStride];
+            c.z = col[(3 * ref.slot + 2) * kStride];
             if (ref.base & 1)
             {
                 c.x += bx;
@@ -275,12 +262,8 @@ namespace vb
         __syncwarp();
         WalkCtx wc;
         wc.wcol = sc.col - (threadIdx.x & 31);
+        wc.queues = sc.queues;
         wc.prims = sc.prims;
-        wc.envq = reinterpret_cast<uint16_t *>(sc.queues);
-        wc.selfq = wc.envq + Robot::kEnvQ;
-        wc.pairq = wc.selfq + Robot::kSelfQ;
-        wc.gmask = reinterpret_cast<uint32_t *>(wc.pairq + Robot::kPairQ);
-        wc.cmask = wc.gmask + 32 * (Robot::kEnvGroups > 0 ? Robot::kEnvGroups : 1);
         wc.bx = a.base[0];
         wc.by = a.base[1];
         wc.bz = a.base[2];
@@ -295,7 +278,7 @@ namespace vb
     // kMode 0: verdicts (warp-cooperative walk); 1: verdicts + margin (lane-serial reference-ordered walk);
     // 2: verdicts + algorithmic flops of the checks (same walk), written to the margin buffer
     template <class Robot, int kMode>
-    __global__ void __launch_bounds__(block_threads<Robot>()) fkcc_kernel(const LaunchArgs a)
+    __global__ void __launch_bounds__(block_threads<Robot>()) fkcc_kernel(const __grid_constant__ LaunchArgs a)
     {
         const Scratch prims = stage_env<Robot>(a, kMode == 0);
         int cstate = -1;
@@ -310,6 +293,14 @@ namespace vb
             for (int j = 0; j < Robot::kDim; ++j)
             {
                 q[j] = alive ? __ldg(a.cfg + i * Robot::kDim + j) : 0.f;
+            }
+            if (i + stride < a.n)
+            {
+                // pull the next iteration's configuration towards the SM while this one is processed (no
+                // register cost): with ~7 resident warps per SM nothing else hides the HBM latency
+                const float *nx = a.cfg + (i + stride) * Robot::kDim;
+                asm volatile("prefetch.global.L1 [%0];" ::"l"(nx));
+                asm volatile("prefetch.global.L1 [%0];" ::"l"(nx + Robot::kDim - 1));
             }
             if constexpr (kMode == 1)
             {
@@ -354,7 +345,7 @@ namespace vb
 
     // ---- K1r: fkcc over device-synthesised configurations (0 input bytes) -----------------------
     template <class Robot>
-    __global__ void __launch_bounds__(block_threads<Robot>()) fkcc_random_kernel(const LaunchArgs a, size_t first)
+    __global__ void __launch_bounds__(block_threads<Robot>()) fkcc_random_kernel(const __grid_constant__ LaunchArgs a, size_t first)
     {
         const Scratch prims = stage_env<Robot>(a, true);
         int cstate = -1;
@@ -487,7 +478,7 @@ namespace vb
     }
 
     template <class Robot, bool kMargin>
-    __global__ void __launch_bounds__(block_threads<Robot>()) motion_kernel(const LaunchArgs a)
+    __global__ void __launch_bounds__(block_threads<Robot>()) motion_kernel(const __grid_constant__ LaunchArgs a)
     {
         const Scratch prims = stage_env<Robot>(a, !kMargin);
         int cstate = -1;

@@ -9,12 +9,12 @@ namespace vb
 
     constexpr int kBlock = block_threads<R>();
 
-    // staged obstacle records + one slot column per thread (+ the per-warp work queues of the warp walk)
+    // one slot column per thread (+ the per-warp work queues of the warp walk)
     static size_t smem_bytes(const LaunchArgs &a, bool queues)
     {
-        const size_t quads = a.env.n_quads > kStageQuads ? 0 : static_cast<size_t>(a.env.n_quads);
+        (void)a;
         const size_t slot_floats = (static_cast<size_t>(3 * R::kSlots * R::kStride) + 3) & ~static_cast<size_t>(3);
-        return sizeof(float4) * quads + sizeof(float) * slot_floats +
+        return sizeof(float) * slot_floats +
                (queues ? static_cast<size_t>(kBlock / 32) * queue_bytes<R>() : 0);
     }
 

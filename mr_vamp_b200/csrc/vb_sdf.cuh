@@ -135,7 +135,7 @@ namespace vb
         if (o >= ix.first[4])
         {
             const float4 *p = P + ix.quad[4] + (o - ix.first[4]) * kZCubQ;
-            const float4 c = p[0], ax = p[1], hr = p[2];
+            const float4 c = __ldg(p + 0), ax = __ldg(p + 1), hr = __ldg(p + 2);
             const float xs = sx - c.x, ys = sy - c.y, zs = sz - c.z;
             const float d1 = fmaxf(fabsf(ax.x * xs + ax.y * ys) - hr.x, 0.f);
             const float d2 = fmaxf(fabsf(ax.z * xs + ax.w * ys) - hr.y, 0.f);
@@ -146,7 +146,7 @@ namespace vb
         else if (o >= ix.first[3])
         {
             const float4 *p = P + ix.quad[3] + (o - ix.first[3]) * kCuboidQ;
-            const float4 c = p[0], a1 = p[1], a2 = p[2], a3 = p[3];
+            const float4 c = __ldg(p + 0), a1 = __ldg(p + 1), a2 = __ldg(p + 2), a3 = __ldg(p + 3);
             const float xs = sx - c.x, ys = sy - c.y, zs = sz - c.z;
             const float d1 = fmaxf(fabsf(a1.x * xs + a1.y * ys + a1.z * zs) - a1.w, 0.f);
             const float d2 = fmaxf(fabsf(a2.x * xs + a2.y * ys + a2.z * zs) - a2.w, 0.f);
@@ -157,7 +157,7 @@ namespace vb
         else if (o >= ix.first[2])
         {
             const float4 *p = P + ix.quad[2] + (o - ix.first[2]) * kZCapsQ;
-            const float4 a = p[0], b = p[1];
+            const float4 a = __ldg(p + 0), b = __ldg(p + 1);
             const float dot = (sz - a.z) * b.x;
             const float cdf = fmaxf(fminf(dot * b.y, 1.f), 0.f);
             const float dx = sx - a.x, dy = sy - a.y, dz = sz - (a.z + b.x * cdf);
@@ -167,7 +167,7 @@ namespace vb
         else if (o >= ix.first[1])
         {
             const float4 *p = P + ix.quad[1] + (o - ix.first[1]) * kCapsuleQ;
-            const float4 a = p[0], b = p[1];
+            const float4 a = __ldg(p + 0), b = __ldg(p + 1);
             const float dot = (sx - a.x) * b.x + (sy - a.y) * b.y + (sz - a.z) * b.z;
             const float cdf = fmaxf(fminf(dot * b.w, 1.f), 0.f);
             const float dx = sx - (a.x + b.x * cdf), dy = sy - (a.y + b.y * cdf), dz = sz - (a.z + b.z * cdf);
@@ -176,7 +176,7 @@ namespace vb
         }
         else
         {
-            const float4 a = P[ix.quad[0] + o * kSphereQ];
+            const float4 a = __ldg(P + ix.quad[0] + o * kSphereQ);
             const float dx = a.x - sx, dy = a.y - sy, dz = a.z - sz;
             r.d2 = dx * dx + dy * dy + dz * dz;
             r.objr = a.w;

@@ -8,27 +8,36 @@ namespace vb
     // ---- chain output: sphere-centre slots in shared memory, one column per thread ---------------
     // slot s, coordinate c of thread t lives at col[(3 s + c) * stride] with col = slots + t: a warp
     // reading "its" slot touches 32 consecutive words (conflict free).
+    // `col` is a float INDEX from the start of the dynamic shared-memory window, so that the compiler emits
+    // STS (a generic store would resolve the shared window at run time).
     struct SlotSink
     {
-        float *col;
+        unsigned col;
         int stride;
         const AttachmentView *att;
         float *att_col;  // this thread's column of posed attachment spheres (global scratch)
         int att_stride;
 
+        VB_D static float *window()
+        {
+            extern __shared__ float4 vb_shared_window[];
+            return reinterpret_cast<float *>(vb_shared_window);
+        }
         VB_D void put(int slot, float x, float y, float z) const
         {
-            col[(3 * slot + 0) * stride] = x;
-            col[(3 * slot + 1) * stride] = y;
-            col[(3 * slot + 2) * stride] = z;
+            float *c = window() + col;
+            c[(3 * slot + 0) * stride] = x;
+            c[(3 * slot + 1) * stride] = y;
+            c[(3 * slot + 2) * stride] = z;
         }
         // compile-time stride: the stores of the straight-line chain get immediate offsets
         template <int kStride>
         VB_D void put_s(int slot, float x, float y, float z) const
         {
-            col[(3 * slot + 0) * kStride] = x;
-            col[(3 * slot + 1) * kStride] = y;
-            col[(3 * slot + 2) * kStride] = z;
+            float *c = window() + col;
+            c[(3 * slot + 0) * kStride] = x;
+            c[(3 * slot + 1) * kStride] = y;
+            c[(3 * slot + 2) * kStride] = z;
         }
         // collision/attachments.hh:75-122 (Attachment::pose); the posed centres go to the global scratch column
         VB_D void attach_pose(float p_tx, float p_ty, float p_tz, float p_rx, float p_ry, float p_rz, float p_rw) const

@@ -7,7 +7,7 @@
 
 namespace vb
 {
-    struct SlotRef
+    struct alignas(8) SlotRef
     {
         uint16_t slot;  // sphere-centre slot written by the chain
         uint16_t base;  // bit k set: add the robot base offset to coordinate k (Panda, robots/panda/fk.hh)
@@ -22,19 +22,20 @@ namespace vb
     // ubegin/ucount: the work units of the warp walk (vb_walk.cuh): refs[ubegin .. ubegin+ucount) are the
     // spheres to test once the guard may have fired (= the fine spheres; for a leaf group a copy of the
     // guard, appended behind the regular refs).
-    struct RefGroup
+    struct alignas(8) RefGroup
     {
         SlotRef guard;
         uint16_t begin, count;
         float slack;
         uint16_t ubegin, ucount;
+        uint32_t pad_;
     };
 
     // sphere_sphere_self_collision(ga, gb) { all pairs a_i x b_j }; a_count == 0: the guard is the test
     // slack_b: as above for the b-side fine spheres relative to the guard sphere gb
     // unit0: index of this group's first (group, a_i) work unit; dense: the guard fires for most
     // configurations (sampled at code-generation time), so the a-side filter runs lane-parallel
-    struct SelfGroup
+    struct alignas(16) SelfGroup
     {
         SlotRef ga, gb;
         uint16_t a_begin, a_count, b_begin, b_count;
@@ -71,6 +72,38 @@ namespace vb
         RefGroup att[NA];  // attachment_sphere_collision groups (robot sphere vs every attachment sphere)
         SlotRef refs[NR];
     };
+
+#ifdef __CUDACC__
+    // Table records are read with LDG through the non-coherent path in 8/16-byte pieces (a plain struct copy
+    // through a pointer of unknown address space compiles to generic loads).
+    template <class T>
+    __device__ __forceinline__ T ldg_record(const T *p)
+    {
+        static_assert(sizeof(T) % 8 == 0 && alignof(T) >= 8, "table records are 8-byte multiples");
+        T out;
+        if constexpr (sizeof(T) % 16 == 0 && alignof(T) >= 16)
+        {
+            const uint4 *src = reinterpret_cast<const uint4 *>(p);
+            uint4 *dst = reinterpret_cast<uint4 *>(&out);
+#pragma unroll
+            for (unsigned i = 0; i < sizeof(T) / 16; ++i)
+            {
+                dst[i] = __ldg(src + i);
+            }
+        }
+        else
+        {
+            const uint2 *src = reinterpret_cast<const uint2 *>(p);
+            uint2 *dst = reinterpret_cast<uint2 *>(&out);
+#pragma unroll
+            for (unsigned i = 0; i < sizeof(T) / 8; ++i)
+            {
+                dst[i] = __ldg(src + i);
+            }
+        }
+        return out;
+    }
+#endif
 
     // Global-memory mirrors for lane-dependent indices (constant memory serialises those).
     struct WalkTables

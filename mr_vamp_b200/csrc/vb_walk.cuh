@@ -29,14 +29,31 @@ namespace vb
 {
     constexpr unsigned kFull = 0xffffffffu;
 
-    // warp-uniform state of one walk
+    // The walk addresses its shared memory as INDICES from the start of the dynamic shared-memory window
+    // (not as pointers carried through structs): the compiler then knows the address space and emits
+    // LDS/STS/ATOMS instead of generic loads that resolve the window at run time.
+    VB_D float *shm_f32()
+    {
+        extern __shared__ float4 vb_shared_window[];
+        return reinterpret_cast<float *>(vb_shared_window);
+    }
+    VB_D uint16_t *shm_u16()
+    {
+        extern __shared__ float4 vb_shared_window[];
+        return reinterpret_cast<uint16_t *>(vb_shared_window);
+    }
+    VB_D unsigned *shm_u32()
+    {
+        extern __shared__ float4 vb_shared_window[];
+        return reinterpret_cast<unsigned *>(vb_shared_window);
+    }
+
+    // warp-uniform state of one walk (passed BY VALUE to the stages: 10 registers instead of a local-memory struct)
     struct WalkCtx
     {
-        const float *wcol;  // slot column of lane 0 of this warp
+        unsigned wcol;    // float index: slot column of lane 0 of this warp
+        unsigned queues;  // byte offset of this warp's queue block: [envq u16][selfq u16][pairq u16][gmask u32][cmask u32 x 4]
         const float4 *prims;
-        uint16_t *envq, *selfq, *pairq;
-        uint32_t *gmask;  // [group][lane]: candidate obstacles of the lane's guard sphere (vb_sdf.cuh)
-        unsigned *cmask;  // [0] bit L set: configuration of lane L collides; [1] pair-queue fill
         float bx, by, bz, radius;
         // Motion validation: the 8 lanes of an octet are the 8 interpolants of one rake block of the
         // reference (planning/validate.hh:36-60), whose `if (guard collides in ANY lane)` opens the fine
@@ -49,6 +66,13 @@ namespace vb
     struct Walk
     {
         static constexpr int S = Robot::kStride;
+        static constexpr unsigned kGroups = Robot::kEnvGroups > 0 ? Robot::kEnvGroups : 1;
+
+        VB_D static uint16_t *envq(const WalkCtx &c) { return shm_u16() + c.queues / 2; }
+        VB_D static uint16_t *selfq(const WalkCtx &c) { return envq(c) + Robot::kEnvQ; }
+        VB_D static uint16_t *pairq(const WalkCtx &c) { return selfq(c) + Robot::kSelfQ; }
+        VB_D static unsigned *gmask(const WalkCtx &c) { return shm_u32() + (c.queues + 2 * (Robot::kEnvQ + Robot::kSelfQ + Robot::kPairQ)) / 4; }
+        VB_D static unsigned *cmask(const WalkCtx &c) { return gmask(c) + 32 * kGroups; }
 
         VB_D static unsigned vol(const unsigned *p)
         {
@@ -57,12 +81,12 @@ namespace vb
 
         VB_D static bool done(const WalkCtx &c, int L)
         {
-            return (vol(c.cmask) >> L) & 1u;
+            return (vol(cmask(c)) >> L) & 1u;
         }
 
         VB_D static Center centre(const WalkCtx &c, int L, const SlotRef &ref)
         {
-            const float *col = c.wcol + L + 3 * static_cast<int>(ref.slot) * S;
+            const float *col = shm_f32() + c.wcol + L + 3 * static_cast<int>(ref.slot) * S;
             Center s;
             s.x = col[0] + ((ref.base & 1) ? c.bx : 0.f);
             s.y = col[S] + ((ref.base & 2) ? c.by : 0.f);
@@ -74,7 +98,7 @@ namespace vb
         // local frame (self collision: no base offset, fixed radii)
         VB_D static void local(const WalkCtx &c, int L, int slot, float &x, float &y, float &z)
         {
-            const float *col = c.wcol + L + 3 * slot * S;
+            const float *col = shm_f32() + c.wcol + L + 3 * slot * S;
             x = col[0];
             y = col[S];
             z = col[2 * S];
@@ -82,7 +106,7 @@ namespace vb
 
         VB_D static void at(const WalkCtx &c, int L, unsigned off, float &x, float &y, float &z)
         {
-            const float *col = c.wcol + L + off;
+            const float *col = shm_f32() + c.wcol + L + off;
             x = col[0];
             y = col[S];
             z = col[2 * S];
@@ -99,7 +123,7 @@ namespace vb
 #pragma unroll 4
             for (int j = 0; j < bc; ++j)
             {
-                const BRef br = B[j];
+                const BRef br = ldg_record(B + j);
                 float bx, by, bz;
                 at(c, L, br.off, bx, by, bz);
                 const float dx = ax - bx, dy = ay - by, dz = az - bz, rs = u.a_r + br.r;
@@ -109,30 +133,30 @@ namespace vb
         }
 
         // ---- self collision, stage 2: queued (configuration, a_i) units ----------------------------
-        __device__ __noinline__ static void pair_stage(const WalkCtx &c)
+        __device__ __noinline__ static void pair_stage(const WalkCtx c)
         {
             const WalkTables w = Robot::walk_tables();
             const int lane = threadIdx.x & 31;
             __syncwarp();
-            const int np = min(static_cast<int>(vol(c.cmask + 1)), Robot::kPairQ);
+            const int np = min(static_cast<int>(vol(cmask(c) + 1)), Robot::kPairQ);
             for (int base = 0; base < np; base += 32)
             {
                 const int i = base + lane;
                 if (i < np)
                 {
-                    const unsigned code = c.pairq[i];
+                    const unsigned code = pairq(c)[i];
                     const int L = code & 31;
-                    const SelfUnit u = w.units[code >> 5];
+                    const SelfUnit u = ldg_record(w.units + (code >> 5));
                     if (!done(c, L) && pair_unit(c, w, L, u))
                     {
-                        atomicOr(c.cmask, 1u << L);
+                        atomicOr(cmask(c), 1u << L);
                     }
                 }
             }
             __syncwarp();
             if (lane == 0)
             {
-                c.cmask[1] = 0u;
+                cmask(c)[1] = 0u;
             }
             __syncwarp();
         }
@@ -140,20 +164,20 @@ namespace vb
         // queue one (configuration, a_i) unit; when the queue is full the lane runs the unit itself
         VB_D static void push_pair(const WalkCtx &c, const WalkTables &w, int L, int unit, const SelfUnit &u)
         {
-            const unsigned at_ = atomicAdd(c.cmask + 1, 1u);
+            const unsigned at_ = atomicAdd(cmask(c) + 1, 1u);
             if (at_ < static_cast<unsigned>(Robot::kPairQ))
             {
-                c.pairq[at_] = static_cast<uint16_t>(L | (unit << 5));
+                pairq(c)[at_] = static_cast<uint16_t>(L | (unit << 5));
             }
             else if (pair_unit(c, w, L, u))
             {
-                atomicOr(c.cmask, 1u << L);
+                atomicOr(cmask(c), 1u << L);
             }
         }
 
         // ---- self collision, stage 1: one (configuration, group) item per lane ------------------------
         // every a_i of the item against the inflated bounding sphere of the other link
-        __device__ __noinline__ static void filter_stage(const WalkCtx &c, int nq)
+        __device__ __noinline__ static void filter_stage(const WalkCtx c, int nq)
         {
             const WalkTables w = Robot::walk_tables();
             const int lane = threadIdx.x & 31;
@@ -162,19 +186,19 @@ namespace vb
                 const int i = base + lane;
                 if (i < nq)
                 {
-                    const unsigned code = c.selfq[i];
+                    const unsigned code = selfq(c)[i];
                     const int L = code & 31;
-                    const SelfGroup *G = w.self + (code >> 5);
-                    const int ac = G->a_count, u0 = G->unit0;
+                    const SelfGroup G = ldg_record(w.self + (code >> 5));
+                    const int ac = G.a_count, u0 = G.unit0;
                     if (!done(c, L))
                     {
                         const SelfUnit *U = w.units + u0;
                         float gx, gy, gz;
-                        at(c, L, U[0].gb_off, gx, gy, gz);
+                        at(c, L, ldg_record(U).gb_off, gx, gy, gz);
 #pragma unroll 2
                         for (int k = 0; k < ac; ++k)
                         {
-                            const SelfUnit u = U[k];
+                            const SelfUnit u = ldg_record(U + k);
                             float ax, ay, az;
                             at(c, L, u.a_off, ax, ay, az);
                             const float dx = ax - gx, dy = ay - gy, dz = az - gz;
@@ -186,7 +210,7 @@ namespace vb
                     }
                 }
                 __syncwarp();
-                if (vol(c.cmask + 1) >= static_cast<unsigned>(Robot::kPairQ) / 2)
+                if (vol(cmask(c) + 1) >= static_cast<unsigned>(Robot::kPairQ) / 2)
                 {
                     pair_stage(c);
                 }
@@ -199,7 +223,7 @@ namespace vb
         {
             const int lane = threadIdx.x & 31;
             const unsigned m = __ballot_sync(kFull, on);
-            unsigned base = vol(c.cmask + 1);
+            unsigned base = vol(cmask(c) + 1);
             if (base + 32u > static_cast<unsigned>(Robot::kPairQ))
             {
                 pair_stage(c);
@@ -207,12 +231,12 @@ namespace vb
             }
             if (on)
             {
-                c.pairq[base + __popc(m & ((1u << lane) - 1u))] = static_cast<uint16_t>(code);
+                pairq(c)[base + __popc(m & ((1u << lane) - 1u))] = static_cast<uint16_t>(code);
             }
             __syncwarp();
             if (lane == 0)
             {
-                c.cmask[1] = base + __popc(m);
+                cmask(c)[1] = base + __popc(m);
             }
             __syncwarp();
         }
@@ -220,11 +244,11 @@ namespace vb
         // one fine sphere refs[idx] of configuration L against the tight candidates of its group
         VB_D static bool fine_unit(const WalkCtx &c, const WalkTables &w, const PrimIndex &ix, int L, int idx)
         {
-            const int g = w.ref_group[idx] & 0x7fff;
-            uint32_t tight = c.gmask[32 * g + L];
+            const int g = __ldg(w.ref_group + idx) & 0x7fff;
+            uint32_t tight = gmask(c)[32 * g + L];
             const bool thigh = (tight >> 31) != 0u;
             tight &= 0x7fffffffu;
-            const Center s = centre(c, L, w.refs[idx]);
+            const Center s = centre(c, L, ldg_record(w.refs + idx));
             bool hit = false;
             int cur = 0;
             for (int o = next_candidate(tight, thigh, ix.first[5], cur); o >= 0 && !hit;
@@ -236,30 +260,30 @@ namespace vb
         }
 
         // ---- environment, stage 2: queued (configuration, fine sphere) units ---------------------------
-        __device__ __noinline__ static void fine_stage(const EnvView &env, const WalkCtx &c)
+        __device__ __noinline__ static void fine_stage(const EnvView &env, const WalkCtx c)
         {
             const WalkTables w = Robot::walk_tables();
             const int lane = threadIdx.x & 31;
             const PrimIndex ix = prim_index(env);
             __syncwarp();
-            const int nu = min(static_cast<int>(vol(c.cmask + 1)), Robot::kPairQ);
+            const int nu = min(static_cast<int>(vol(cmask(c) + 1)), Robot::kPairQ);
             for (int base = 0; base < nu; base += 32)
             {
                 const int i = base + lane;
                 if (i < nu)
                 {
-                    const unsigned code = c.pairq[i];
+                    const unsigned code = pairq(c)[i];
                     const int L = code & 31;
                     if (!done(c, L) && fine_unit(c, w, ix, L, code >> 5))
                     {
-                        atomicOr(c.cmask, 1u << L);
+                        atomicOr(cmask(c), 1u << L);
                     }
                 }
             }
             __syncwarp();
             if (lane == 0)
             {
-                c.cmask[1] = 0u;
+                cmask(c)[1] = 0u;
             }
             __syncwarp();
         }
@@ -270,7 +294,7 @@ namespace vb
         // that touch the guard sphere inflated by the group's static slack.  The fine spheres of a fired
         // guard become units of stage 2 (the pair queue is free at this point and is reused), where they
         // are tested, with the exact primitive arithmetic of the reference, against those few obstacles.
-        __device__ __noinline__ static void env_stage(const EnvView &env, const WalkCtx &c, int ne)
+        __device__ __noinline__ static void env_stage(const EnvView &env, const WalkCtx c, int ne)
         {
             const WalkTables w = Robot::walk_tables();
             const int lane = threadIdx.x & 31;
@@ -282,16 +306,17 @@ namespace vb
                 const int i = base + lane;
                 if (i < ne)
                 {
-                    const unsigned code = c.envq[i];
+                    const unsigned code = envq(c)[i];
                     const int L = code & 31, g = code >> 5;
                     if (!done(c, L))
                     {
-                        const RefGroup *G = w.env + g;
+                        const RefGroup Gr = ldg_record(w.env + g);
+                        const RefGroup *G = &Gr;
                         const int u0 = G->ubegin, uc = G->ucount;
                         bool hit = false;
                         if (!has_other)
                         {
-                            const uint32_t mask = c.gmask[32 * g + L];
+                            const uint32_t mask = gmask(c)[32 * g + L];
                             const Center b = centre(c, L, G->guard);
                             const float slack = G->slack;
                             uint32_t low = mask & 0x7fffffffu, tight = 0u;
@@ -318,13 +343,13 @@ namespace vb
                             }
                             else if (ghit)
                             {
-                                c.gmask[32 * g + L] = tight;
-                                const unsigned at = atomicAdd(c.cmask + 1, static_cast<unsigned>(uc));
+                                gmask(c)[32 * g + L] = tight;
+                                const unsigned at = atomicAdd(cmask(c) + 1, static_cast<unsigned>(uc));
                                 for (int k = 0; k < uc; ++k)
                                 {
                                     if (at + k < static_cast<unsigned>(Robot::kPairQ))
                                     {
-                                        c.pairq[at + k] = static_cast<uint16_t>(L | ((u0 + k) << 5));
+                                        pairq(c)[at + k] = static_cast<uint16_t>(L | ((u0 + k) << 5));
                                     }
                                     else
                                     {
@@ -339,18 +364,18 @@ namespace vb
                             NoMargin mg;
                             for (int k = 0; k < uc && !hit; ++k)
                             {
-                                const Center s = centre(c, L, w.refs[u0 + k]);
+                                const Center s = centre(c, L, ldg_record(w.refs + u0 + k));
                                 hit = env_hit(env, c.prims, s.x, s.y, s.z, s.r, mg);
                             }
                         }
                         if (hit)
                         {
-                            atomicOr(c.cmask, 1u << L);
+                            atomicOr(cmask(c), 1u << L);
                         }
                     }
                 }
                 __syncwarp();
-                if (vol(c.cmask + 1) >= static_cast<unsigned>(Robot::kPairQ) / 2)
+                if (vol(cmask(c) + 1) >= static_cast<unsigned>(Robot::kPairQ) / 2)
                 {
                     fine_stage(env, c);
                 }
@@ -368,10 +393,10 @@ namespace vb
             const auto &t = Robot::tables();
             const int lane = threadIdx.x & 31;
             const unsigned lt = (1u << lane) - 1u;
-            const float *col = c.wcol + lane;
+            const float *col = shm_f32() + c.wcol + lane;
             if (lane < 2)
             {
-                c.cmask[lane] = 0u;
+                cmask(c)[lane] = 0u;
             }
             __syncwarp();
             if (Robot::kEnvConstAny && (env.n_quads > 0 || ((env.n_heightfields | env.n_capts) != 0)))
@@ -468,7 +493,7 @@ namespace vb
                         }
                         if (on)
                         {
-                            c.selfq[nq + __popc(m & lt)] = static_cast<uint16_t>(lane | ((wi * 32 + b) << 5));
+                            selfq(c)[nq + __popc(m & lt)] = static_cast<uint16_t>(lane | ((wi * 32 + b) << 5));
                         }
                         nq += __popc(m);
                     }
@@ -491,7 +516,7 @@ namespace vb
             uint32_t maybe[Robot::kEnvWords], cert[Robot::kEnvWords];
             if (grid)
             {
-                Robot::env_classify(cells, inside, c.radius, env.sdf, maybe, cert, c.gmask + lane);
+                Robot::env_classify(cells, inside, c.radius, env.sdf, maybe, cert, gmask(c) + lane);
             }
             else
             {
@@ -507,7 +532,7 @@ namespace vb
                     const Center b = centre(c, lane, grp.guard);
                     NoMargin mg;
                     const bool hit = !collided && env_hit(env, c.prims, b.x, b.y, b.z, b.r, mg);
-                    c.gmask[32 * g + lane] = 0xffffffffu;
+                    gmask(c)[32 * g + lane] = 0xffffffffu;
 #pragma unroll
                     for (int wi = 0; wi < Robot::kEnvWords; ++wi)
                     {
@@ -552,7 +577,7 @@ namespace vb
                     }
                     if (on)
                     {
-                        c.envq[ne + __popc(m & lt)] = static_cast<uint16_t>(lane | ((wi * 32 + b) << 5));
+                        envq(c)[ne + __popc(m & lt)] = static_cast<uint16_t>(lane | ((wi * 32 + b) << 5));
                     }
                     ne += __popc(m);
                 }
