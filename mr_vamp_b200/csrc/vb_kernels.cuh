@@ -14,6 +14,9 @@
 
 namespace vb
 {
+    // the warps of a CTA are kept on one instruction stream with CTA barriers (the hot code is ~75 KB of mostly
+    // straight-line SASS; seven independent streams per SM thrash the instruction caches)
+    constexpr bool kLockstep = true;
     struct LaunchArgs
     {
         EnvView env;
@@ -284,8 +287,15 @@ namespace vb
         int cstate = -1;
         const size_t stride = static_cast<size_t>(gridDim.x) * blockDim.x;
         const size_t n_round = (a.n + 31) / 32 * 32;
-        for (size_t i = static_cast<size_t>(blockIdx.x) * blockDim.x + threadIdx.x; i < n_round; i += stride)
+        // CTA-uniform trip count with a barrier per iteration: the warps of a CTA walk the (large, mostly
+        // straight-line) code together, so the instruction cache serves one stream instead of seven
+        for (size_t base = static_cast<size_t>(blockIdx.x) * blockDim.x; base < n_round; base += stride)
         {
+            const size_t i = base + threadIdx.x;
+            if (kLockstep)
+            {
+                __syncthreads();
+            }
             bool ok = false;
             const bool alive = i < a.n;
             float q[Robot::kDim];
@@ -325,7 +335,7 @@ namespace vb
                 ok = check_warp<Robot>(a, prims, q, alive, a.attach != 0, cstate);
             }
             const uint32_t word = __ballot_sync(0xffffffffu, ok);
-            if ((threadIdx.x & 31) == 0)
+            if ((threadIdx.x & 31) == 0 && i < n_round)
             {
                 a.bits[i >> 5] = word;
             }
@@ -351,14 +361,21 @@ namespace vb
         int cstate = -1;
         const size_t stride = static_cast<size_t>(gridDim.x) * blockDim.x;
         const size_t n_round = (a.n + 31) / 32 * 32;
-        for (size_t i = static_cast<size_t>(blockIdx.x) * blockDim.x + threadIdx.x; i < n_round; i += stride)
+        // CTA-uniform trip count with a barrier per iteration: the warps of a CTA walk the (large, mostly
+        // straight-line) code together, so the instruction cache serves one stream instead of seven
+        for (size_t base = static_cast<size_t>(blockIdx.x) * blockDim.x; base < n_round; base += stride)
         {
+            const size_t i = base + threadIdx.x;
+            if (kLockstep)
+            {
+                __syncthreads();
+            }
             const bool alive = i < a.n;
             float q[Robot::kDim];
             random_config<Robot>(a.seed, first + i, q);
             const bool ok = check_warp<Robot>(a, prims, q, alive, a.attach != 0, cstate);
             const uint32_t word = __ballot_sync(0xffffffffu, ok);
-            if ((threadIdx.x & 31) == 0)
+            if ((threadIdx.x & 31) == 0 && i < n_round)
             {
                 a.bits[i >> 5] = word;
             }
