@@ -54,6 +54,18 @@ def _f64(c: float) -> str:
 
 
 
+CONST_SLOT = 0x4000  # slot code of a configuration-independent centre: CONST_SLOT | index
+
+
+def slot_offset(slot: int, stride: int, const_row: int) -> int:
+    """Float offset of a slot's x coordinate from the warp's first column (y, z follow at +stride each).
+    Regular slots add the lane; constant slots (offset >= 3 * const_row * stride) do not."""
+    if slot & CONST_SLOT:
+        j = slot & (CONST_SLOT - 1)
+        return 3 * (const_row + j // 32) * stride + j % 32
+    return 3 * slot * stride
+
+
 class _Emitter:
     """Lowers one traced function to (chain lines, check tables)."""
 
@@ -64,6 +76,8 @@ class _Emitter:
         self.lines: list[str] = []
         self.slots: dict[tuple, int] = {}
         self.const_slots: set[int] = set()
+        self.const_xyz: dict[int, list[str]] = {}
+        self.n_rows = 0  # per-thread slot rows (configuration-dependent centres)
         self.refs: list[tuple[int, int, float]] = []  # (slot, base mask, radius)
         self.env: list[dict[str, Any]] = []
         self.selfg: list[dict[str, Any]] = []
@@ -94,12 +108,18 @@ class _Emitter:
         """Sphere argument list [x, y, z, r] -> (slot, base mask, radius); emits the put on first use."""
         key = tuple((a["v"] if a["v"] is not None else ("c", a["c"])) for a in s[:3])
         if key not in self.slots:
-            self.slots[key] = len(self.slots)
+            xyz = [self.coord(a) for a in s[:3]]
             if all(a["v"] is None for a in s[:3]):
+                # configuration-independent centre: ONE copy per warp in the constant rows (see vb_sinks.cuh)
+                j = len(self.const_slots)
+                self.slots[key] = CONST_SLOT | j
                 self.const_slots.add(self.slots[key])
-            self.lines.append(
-                f"p.put_s<kStride>({self.slots[key]}, {self.coord(s[0])}, {self.coord(s[1])}, {self.coord(s[2])});"
-            )
+                self.const_xyz[self.slots[key]] = xyz
+                self.lines.append(f"p.put_c<kStride>(kConstRow + {j // 32}, {j % 32}, {xyz[0]}, {xyz[1]}, {xyz[2]});")
+            else:
+                self.slots[key] = self.n_rows
+                self.n_rows += 1
+                self.lines.append(f"p.put_s<kStride>({self.slots[key]}, {xyz[0]}, {xyz[1]}, {xyz[2]});")
         mask = sum((1 << i) for i, a in enumerate(s[:3]) if a.get("base"))
         for i, a in enumerate(s[:3]):
             assert a.get("base") in (None, "xyz"[i]), s
@@ -247,7 +267,7 @@ def _slack(v: float) -> str:
     return "-1.0f" if v < 0 else _f32(v)
 
 
-def _tables(name: str, em: _Emitter, walk: bool = False, stride: int = 0) -> list[str]:
+def _tables(name: str, em: _Emitter, walk: bool = False, stride: int = 0, const_row: int = 0) -> list[str]:
     """Constant-memory check tables; with `walk` also the global-memory mirrors and work-unit tables of
     the warp walk (vb_walk.cuh).  Returns (lines, table type, geometry dict)."""
     refs = list(em.refs)
@@ -272,7 +292,7 @@ def _tables(name: str, em: _Emitter, walk: bool = False, stride: int = 0) -> lis
             sa, _, ra = em.refs[g["a"][0] + i]
             sb, _, rb = g["gb"]
             filt = float(F(F(ra) + F(rb)) + F(g["slack"])) if g["slack"] >= 0 else -1.0
-            units.append((3 * sa * stride, 3 * sb * stride, ra, filt, g["b"][0], g["b"][1]))
+            units.append((slot_offset(sa, stride, const_row), slot_offset(sb, stride, const_row), ra, filt, g["b"][0], g["b"][1]))
     assert len(refs) < 2048 and len(units) < 2048, (name, len(refs), len(units))
     ne, ns, na, nr = len(em.env), len(em.selfg), len(em.att), len(refs)
     t = f"Tables<{max(ne, 1)}, {max(ns, 1)}, {max(na, 1)}, {max(nr, 1)}>"
@@ -297,7 +317,7 @@ def _tables(name: str, em: _Emitter, walk: bool = False, stride: int = 0) -> lis
 
     rr = refs or [(0, 0, 0.0)]
     out = [f"__constant__ {t} {name} = {{"]
-    out.append(f"    {len(em.slots)}, {ne}, {ns}, {na}, {em.att_env},")
+    out.append(f"    {em.n_rows}, {ne}, {ns}, {na}, {em.att_env},")
     out.append("    {")
     out.extend("    " + r for r in env_rows())
     out.append("    },")
@@ -338,7 +358,7 @@ def _tables(name: str, em: _Emitter, walk: bool = False, stride: int = 0) -> lis
         out.append("};")
         out.append(f"__device__ const BRef {name}_brefs[{len(rr)}] = {{")
         for i in range(0, len(rr), 8):
-            out.append("    " + ", ".join(f"{{{3 * sl * stride}, {_f32(r) if r >= 0 else '-1.0f'}}}" for sl, _, r in rr[i : i + 8]) + ",")
+            out.append("    " + ", ".join(f"{{{slot_offset(sl, stride, const_row)}, {_f32(r) if r >= 0 else '-1.0f'}}}" for sl, _, r in rr[i : i + 8]) + ",")
         out.append("};")
         max_u = max([g["ucount"] for g in em.env] or [1])
         max_a = max([g["a"][1] for g in em.selfg if not g.get("dense")] or [1])
@@ -394,6 +414,10 @@ def _uniform(em: _Emitter) -> list[str]:
     def need(slot: int):
         if slot not in loaded:
             loaded.add(slot)
+            if slot & CONST_SLOT:
+                x, y, z = em.const_xyz[slot]
+                body.append(f"const float s{slot}x = {x}, s{slot}y = {y}, s{slot}z = {z};")
+                return
             body.append(
                 f"const float s{slot}x = col[{3 * slot} * kStride], s{slot}y = col[{3 * slot + 1} * kStride], s{slot}z = col[{3 * slot + 2} * kStride];"
             )
@@ -443,7 +467,7 @@ def _uniform(em: _Emitter) -> list[str]:
         slot, mask, r = g["guard"]
         xyz = []
         for c in range(3):
-            e = f"col[{3 * slot + c} * kStride]"
+            e = em.const_xyz[slot][c] if slot & CONST_SLOT else f"col[{3 * slot + c} * kStride]"
             if mask & (1 << c):
                 e += f" + b{'xyz'[c]}"
             xyz.append(e)
@@ -477,9 +501,14 @@ def _uniform(em: _Emitter) -> list[str]:
     return out
 
 
+def _queue_bytes(geom: dict) -> int:
+    # item queue (self items, then environment items: never live together) + pair/fine-unit queue + candidate masks + state
+    return 2 * (max(geom["env_q"], geom["self_q"]) + geom["pair_q"]) + 128 * geom["env_groups"] + 16
+
+
 def _geometry(n_slots: int, geom: dict) -> tuple[int, int]:
     """(warps per CTA, CTAs per SM) maximising resident warps within 227 KB of shared memory per SM."""
-    queue = 2 * (geom["env_q"] + geom["self_q"] + geom["pair_q"]) + 128 * geom["env_groups"] + 16
+    queue = _queue_bytes(geom)
     per_warp = 3 * n_slots * 4 * 32 + queue
     fixed = 3 * n_slots * 4 + 16 + 1024  # stride padding, per-CTA reserve
     best = (1, 1)
@@ -519,12 +548,16 @@ def emit_robot(ir: dict[str, Any]) -> str:
     w("namespace vb")
     w("{")
     geom = {"env_q": 256, "self_q": 256, "pair_q": 256, "env_groups": max(len(em.env), 1)}
-    n_slots = max(len(em.slots), len(em_att.slots) if em_att else 0)
+    # shared-memory rows: one per configuration-dependent centre (a column per thread), then the constant rows
+    # (one copy per warp, 32 constants per row)
+    const_row = max(em.n_rows, em_att.n_rows if em_att else 0)
+    n_const = max(len(em.const_slots), len(em_att.const_slots) if em_att else 0)
+    n_slots = const_row + (n_const + 31) // 32
     warps, ctas = _geometry(n_slots, geom)
-    tab, ttype, _ = _tables(f"k_{robot}_tables", em, walk=True, stride=32 * warps + 1)
+    tab, ttype, _ = _tables(f"k_{robot}_tables", em, walk=True, stride=32 * warps + 1, const_row=const_row)
     out.extend(tab)
     if em_att:
-        tab2, ttype2, _ = _tables(f"k_{robot}_tables_attach", em_att)
+        tab2, ttype2, _ = _tables(f"k_{robot}_tables_attach", em_att, const_row=const_row)
         out.extend(tab2)
     w(f"struct {cls}")
     w("{")
@@ -533,7 +566,8 @@ def emit_robot(ir: dict[str, Any]) -> str:
     w(f"    static constexpr int kSpheres = {S};")
     w(f"    static constexpr int kResolution = {ir['resolution']};")
     w(f"    static constexpr bool kHasAttach = {'true' if has_attach else 'false'};")
-    w(f"    static constexpr int kSlots = {n_slots};  // distinct sphere centres used by the checks")
+    w(f"    static constexpr int kSlots = {n_slots};  // shared-memory slot rows: {const_row} per-thread + {n_slots - const_row} of per-warp constants")
+    w(f"    static constexpr int kConstRow = {const_row};  // first constant row ({n_const} configuration-independent centres)")
     w(f"    static constexpr int kBlock = {32 * warps};  // threads per CTA: {warps} warps x {ctas} CTA(s) per SM fill the shared memory")
     w("    static constexpr int kStride = kBlock + 1;  // slot-column stride in floats (odd: conflict free)")
     w(f"    static constexpr int kEnvQ = {geom['env_q']}, kSelfQ = {geom['self_q']}, kPairQ = {geom['pair_q']};  // work-queue capacities (units)")

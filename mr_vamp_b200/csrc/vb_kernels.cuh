@@ -50,7 +50,8 @@ namespace vb
     template <class Robot>
     __host__ __device__ constexpr int queue_bytes()
     {
-        return 2 * (Robot::kEnvQ + Robot::kSelfQ + Robot::kPairQ) + 128 * (Robot::kEnvGroups > 0 ? Robot::kEnvGroups : 1) + 16;
+        return 2 * ((Robot::kEnvQ > Robot::kSelfQ ? Robot::kEnvQ : Robot::kSelfQ) + Robot::kPairQ) +
+               128 * (Robot::kEnvGroups > 0 ? Robot::kEnvGroups : 1) + 16;
     }
 
     // Shared memory is addressed by INDEX from the start of the dynamic window (see vb_walk.cuh: the compiler
@@ -65,7 +66,7 @@ namespace vb
         unsigned queues;      // byte offset of this warp's work queues
     };
 
-    // dynamic shared memory: [3 * kSlots * (blockDim + 1) floats: one column per thread][per-warp queues]
+    // dynamic shared memory: [3 * kSlots rows of (blockDim + 1) floats: one column per thread][per-warp queues]
     template <class Robot>
     VB_D Scratch stage_env(const LaunchArgs &a, bool with_queues)
     {
@@ -82,7 +83,7 @@ namespace vb
     }
 
     // ---- the table walk: every collision test of one configuration -------------------------------
-    template <int kStride>
+    template <int kStride, int kConstRow>
     struct TableCtx
     {
         const EnvView &env;
@@ -91,10 +92,10 @@ namespace vb
         VB_D Center load(const SlotRef &ref) const
         {
             Center c;
-            const float *col = shm_f32() + sc.col;
-            c.x = col[(3 * ref.slot + 0) * kStride];
-            c.y = col[(3 * ref.slot + 1) * kStride];
-            c.z = col[(3 * ref.slot + 2) * kStride];
+            const float *col = shm_f32() + slot_index<kStride, kConstRow>(sc.col & ~31u, sc.col & 31u, ref.slot);
+            c.x = col[0];
+            c.y = col[kStride];
+            c.z = col[2 * kStride];
             if (ref.base & 1)
             {
                 c.x += bx;
@@ -133,8 +134,8 @@ namespace vb
         return v < 0.f;
     }
 
-    template <class T, class M, int kStride>
-    VB_D bool walk_tables(const T &t, const TableCtx<kStride> &c, M &mg)
+    template <class T, class M, int kStride, int kConstRow>
+    VB_D bool walk_tables(const T &t, const TableCtx<kStride, kConstRow> &c, M &mg)
     {
         // environment groups (robots/<robot>/fk.hh: `if (sphere_environment_in_collision(bounding)) {...}`)
         for (int g = 0; g < t.n_env; ++g)
@@ -230,7 +231,7 @@ namespace vb
     VB_D bool check_config(const LaunchArgs &a, const Scratch &sc, const float *q, bool attach, M &mg)
     {
         SlotSink sink{sc.col, sc.stride, &a.env.attach, sc.att_col, sc.att_stride};
-        const TableCtx<Robot::kStride> ctx{a.env, sc, a.base[0], a.base[1], a.base[2], a.sphere_radius};
+        const TableCtx<Robot::kStride, Robot::kConstRow> ctx{a.env, sc, a.base[0], a.base[1], a.base[2], a.sphere_radius};
         if (Robot::kHasAttach && attach)
         {
             Robot::chain_attach(sink, q);

@@ -7,7 +7,9 @@ namespace vb
 {
     // ---- chain output: sphere-centre slots in shared memory, one column per thread ---------------
     // slot s, coordinate c of thread t lives at col[(3 s + c) * stride] with col = slots + t: a warp
-    // reading "its" slot touches 32 consecutive words (conflict free).
+    // reading "its" slot touches 32 consecutive words (conflict free).  Centres that do not depend on the
+    // configuration are not replicated per thread: they live once per warp in the rows behind the
+    // per-thread slots (put_c; slot code kConstSlot | j in the tables).
     // `col` is a float INDEX from the start of the dynamic shared-memory window, so that the compiler emits
     // STS (a generic store would resolve the shared window at run time).
     struct SlotSink
@@ -38,6 +40,16 @@ namespace vb
             c[(3 * slot + 0) * kStride] = x;
             c[(3 * slot + 1) * kStride] = y;
             c[(3 * slot + 2) * kStride] = z;
+        }
+        // configuration-independent centre (e.g. the base link): one copy per WARP, constant j of row-triple `row`
+        // lives in column (warp's first column + j); every lane stores the same value
+        template <int kStride>
+        VB_D void put_c(int row, int j, float x, float y, float z) const
+        {
+            float *c = window() + (col & ~31u) + j;
+            c[(3 * row + 0) * kStride] = x;
+            c[(3 * row + 1) * kStride] = y;
+            c[(3 * row + 2) * kStride] = z;
         }
         // collision/attachments.hh:75-122 (Attachment::pose); the posed centres go to the global scratch column
         VB_D void attach_pose(float p_tx, float p_ty, float p_tz, float p_rx, float p_ry, float p_rz, float p_rw) const

@@ -7,9 +7,12 @@
 
 namespace vb
 {
+    // slot code of a configuration-independent centre: kConstSlot | j (codegen/emit_cuda.py: CONST_SLOT)
+    constexpr unsigned kConstSlot = 0x4000u;
+
     struct alignas(8) SlotRef
     {
-        uint16_t slot;  // sphere-centre slot written by the chain
+        uint16_t slot;  // sphere-centre slot written by the chain (or kConstSlot | j)
         uint16_t base;  // bit k set: add the robot base offset to coordinate k (Panda, robots/panda/fk.hh)
         float r;        // radius; < 0: the run-time radius of robots::sphere
     };
@@ -44,8 +47,9 @@ namespace vb
     };
 
     // One (self group, a_i) work unit of the warp walk, flattened so that ONE 16-byte load gives the
-    // filter and the pair stage everything they need.  Offsets are float indices into a slot column:
-    // 3 * slot * kStride.
+    // filter and the pair stage everything they need.  Offsets are float indices from the warp's first
+    // column: 3 * slot * kStride for a per-thread slot (the lane is added), >= 3 * kConstRow * kStride for a
+    // per-warp constant (no lane term).
     struct alignas(16) SelfUnit
     {
         uint16_t a_off;    // column offset of a_i
@@ -74,6 +78,15 @@ namespace vb
     };
 
 #ifdef __CUDACC__
+    // float index of a slot's x coordinate (y, z at +kStride each): `wcol` = first column of the warp, L = lane
+    // whose configuration is addressed
+    template <int kStride, int kConstRow>
+    __device__ __forceinline__ unsigned slot_index(unsigned wcol, int L, unsigned slot)
+    {
+        const unsigned j = slot & (kConstSlot - 1u);
+        return (slot & kConstSlot) ? 3u * (kConstRow + (j >> 5)) * kStride + wcol + (j & 31u) : 3u * slot * kStride + wcol + L;
+    }
+
     // Table records are read with LDG through the non-coherent path in 8/16-byte pieces (a plain struct copy
     // through a pointer of unknown address space compiles to generic loads).
     template <class T>

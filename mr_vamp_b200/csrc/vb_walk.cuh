@@ -52,7 +52,7 @@ namespace vb
     struct WalkCtx
     {
         unsigned wcol;    // float index: slot column of lane 0 of this warp
-        unsigned queues;  // byte offset of this warp's queue block: [envq u16][selfq u16][pairq u16][gmask u32][cmask u32 x 4]
+        unsigned queues;  // byte offset of this warp's queue block: [item queue u16][pairq u16][gmask u32][cmask u32 x 4]
         const float4 *prims;
         float bx, by, bz, radius;
         // Motion validation: the 8 lanes of an octet are the 8 interpolants of one rake block of the
@@ -68,10 +68,14 @@ namespace vb
         static constexpr int S = Robot::kStride;
         static constexpr unsigned kGroups = Robot::kEnvGroups > 0 ? Robot::kEnvGroups : 1;
 
+        static constexpr unsigned kConstOff = 3u * Robot::kConstRow * S;
+        static constexpr int kItemQ = Robot::kEnvQ > Robot::kSelfQ ? Robot::kEnvQ : Robot::kSelfQ;
+
+        // self items and environment items are never queued at the same time: one array serves both
         VB_D static uint16_t *envq(const WalkCtx &c) { return shm_u16() + c.queues / 2; }
-        VB_D static uint16_t *selfq(const WalkCtx &c) { return envq(c) + Robot::kEnvQ; }
-        VB_D static uint16_t *pairq(const WalkCtx &c) { return selfq(c) + Robot::kSelfQ; }
-        VB_D static unsigned *gmask(const WalkCtx &c) { return shm_u32() + (c.queues + 2 * (Robot::kEnvQ + Robot::kSelfQ + Robot::kPairQ)) / 4; }
+        VB_D static uint16_t *selfq(const WalkCtx &c) { return envq(c); }
+        VB_D static uint16_t *pairq(const WalkCtx &c) { return envq(c) + kItemQ; }
+        VB_D static unsigned *gmask(const WalkCtx &c) { return shm_u32() + (c.queues + 2 * (kItemQ + Robot::kPairQ)) / 4; }
         VB_D static unsigned *cmask(const WalkCtx &c) { return gmask(c) + 32 * kGroups; }
 
         VB_D static unsigned vol(const unsigned *p)
@@ -86,7 +90,7 @@ namespace vb
 
         VB_D static Center centre(const WalkCtx &c, int L, const SlotRef &ref)
         {
-            const float *col = shm_f32() + c.wcol + L + 3 * static_cast<int>(ref.slot) * S;
+            const float *col = shm_f32() + slot_index<S, Robot::kConstRow>(c.wcol, L, ref.slot);
             Center s;
             s.x = col[0] + ((ref.base & 1) ? c.bx : 0.f);
             s.y = col[S] + ((ref.base & 2) ? c.by : 0.f);
@@ -95,18 +99,10 @@ namespace vb
             return s;
         }
 
-        // local frame (self collision: no base offset, fixed radii)
-        VB_D static void local(const WalkCtx &c, int L, int slot, float &x, float &y, float &z)
-        {
-            const float *col = shm_f32() + c.wcol + L + 3 * slot * S;
-            x = col[0];
-            y = col[S];
-            z = col[2 * S];
-        }
-
+        // pre-multiplied offset (SelfUnit / BRef): per-thread slots add the lane, per-warp constants do not
         VB_D static void at(const WalkCtx &c, int L, unsigned off, float &x, float &y, float &z)
         {
-            const float *col = shm_f32() + c.wcol + L + off;
+            const float *col = shm_f32() + c.wcol + off + (off >= kConstOff ? 0u : static_cast<unsigned>(L));
             x = col[0];
             y = col[S];
             z = col[2 * S];
