@@ -32,7 +32,7 @@ import struct
 import sys
 from typing import Any
 
-from . import ir_eval, trace_parser
+from . import ir_eval, pair_tables, trace_parser
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
 GEN_DIR = os.path.join(os.path.dirname(_HERE), "_gen")
@@ -537,6 +537,11 @@ def emit_robot(ir: dict[str, Any]) -> str:
 
     em = _Emitter(fns["interleaved_sphere_fk"], sampled(fns["interleaved_sphere_fk"])).run_checks()
     em_att = _Emitter(fns["interleaved_sphere_fk_attachment"]).run_checks() if has_attach else None
+    # self groups decided by a two-joint table are rare work for the walk, whatever their guard's fire rate
+    ptabs = pair_tables.build(ir, fns["interleaved_sphere_fk"])
+    for t in ptabs:
+        for g in t["groups"]:
+            em.selfg[g]["dense"] = False
     out: list[str] = []
     w = out.append
     w(f"// GENERATED by mr_vamp_b200/codegen/emit_cuda.py from {ir['source']} of the VAMP checkout")
@@ -559,6 +564,8 @@ def emit_robot(ir: dict[str, Any]) -> str:
     if em_att:
         tab2, ttype2, _ = _tables(f"k_{robot}_tables_attach", em_att, const_row=const_row)
         out.extend(tab2)
+    pt_head, pt_body = pair_tables.emit(robot, ir, ptabs, max((len(em.selfg) + 31) // 32, 1))
+    out.extend(pt_head)
     w(f"struct {cls}")
     w("{")
     w(f'    static constexpr const char *kName = "{robot}";')
@@ -615,6 +622,7 @@ def emit_robot(ir: dict[str, Any]) -> str:
         w("    }")
 
     out.extend(_uniform(em))
+    out.extend(pt_body)
     fn("chain", em.lines)
     fn("chain_attach", em_att.lines if em_att else ["chain(p, q);"])
     fn("sphere_fk", _Emitter(fns["sphere_fk"]).run_spheres(), "SphereSink")

@@ -258,6 +258,21 @@ namespace vb
             __syncwarp();
             return ok;
         }
+        // joint-pair tables (codegen/pair_tables.py): the load is issued ahead of the chain, which hides its latency
+        uint32_t pfree[Robot::kSelfWords];
+        bool phit = false;
+        if (Robot::kPairTables > 0 && alive)
+        {
+            phit = Robot::pair_lookup(q, pfree);
+        }
+        else
+        {
+#pragma unroll
+            for (int wi = 0; wi < Robot::kSelfWords; ++wi)
+            {
+                pfree[wi] = 0u;
+            }
+        }
         if (alive)
         {
             SlotSink sink{sc.col, sc.stride, &a.env.attach, sc.att_col, sc.att_stride};
@@ -273,7 +288,7 @@ namespace vb
         wc.bz = a.base[2];
         wc.radius = a.sphere_radius;
         wc.octet = octet;
-        const bool ok = Walk<Robot>::run(a.env, wc, !alive, cstate);
+        const bool ok = Walk<Robot>::run(a.env, wc, !alive || phit, cstate, pfree);
         __syncwarp();  // columns are rewritten by the next configuration
         return ok;
     }

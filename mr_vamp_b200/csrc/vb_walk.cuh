@@ -384,7 +384,8 @@ namespace vb
         // configuration.  Returns this lane's verdict (true = collision free).
         // `cstate` is the warp's cached verdict of the configuration-independent environment groups
         // (-1 unknown, 0 free, 1 colliding): a property of (environment, base), evaluated once.
-        VB_D static bool run(const EnvView &env, const WalkCtx &c, bool collided, int &cstate)
+        // `pfree`: bit g set = self group g cannot collide at this lane's configuration (joint-pair tables).
+        VB_D static bool run(const EnvView &env, const WalkCtx &c, bool collided, int &cstate, const uint32_t *pfree)
         {
             const auto &t = Robot::tables();
             const int lane = threadIdx.x & 31;
@@ -449,7 +450,7 @@ namespace vb
 #pragma unroll
                 for (int wi = 0; wi < Robot::kSelfWords; ++wi)
                 {
-                    fired[wi] &= live;
+                    fired[wi] &= live & ~pfree[wi];
                     collided = collided || (fired[wi] & Robot::self_leaf_mask(wi)) != 0u;
                 }
                 const WalkTables w = Robot::walk_tables();
