@@ -20,7 +20,7 @@ all: $(LIB)
 
 # The traces are generated from the VAMP checkout the library is built against; without a checkout
 # (e.g. on a GPU box that received prebuilt files) existing generated headers are used as they are.
-$(GEN)/.stamp: $(PKG)/codegen/emit_cuda.py $(PKG)/codegen/trace_parser.py
+$(GEN)/.stamp: $(wildcard $(PKG)/codegen/*.py)
 	@if [ -d $(VAMP_SRC)/src/impl/vamp ]; then VAMP_SRC=$(VAMP_SRC) $(PYTHON) -m $(PKG).codegen.emit_cuda >/dev/null; \
 	 elif [ ! -f $(GEN)/panda_trace.cuh ]; then echo "no VAMP checkout at $(VAMP_SRC) and no generated traces"; exit 1; fi
 	@mkdir -p $(GEN) && touch $@

@@ -17,7 +17,7 @@ from typing import Iterable, Optional, Sequence
 import numpy as np
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "lib", "libvamp_b200.so")
+LIB_PATH = os.environ.get("VAMP_B200_LIB") or os.path.join(_HERE, "lib", "libvamp_b200.so")  # override: development A/B builds
 
 _f32p = C.POINTER(C.c_float)
 _u32p = C.POINTER(C.c_uint32)

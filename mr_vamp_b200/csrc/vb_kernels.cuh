@@ -17,6 +17,10 @@ namespace vb
     // the warps of a CTA are kept on one instruction stream with CTA barriers (the hot code is ~75 KB of mostly
     // straight-line SASS; seven independent streams per SM thrash the instruction caches)
     constexpr bool kLockstep = true;
+#ifndef VB_LOCKSTEP_EVERY
+#define VB_LOCKSTEP_EVERY 1
+#endif
+    constexpr unsigned kLockstepEvery = VB_LOCKSTEP_EVERY;
     struct LaunchArgs
     {
         EnvView env;
@@ -258,6 +262,7 @@ namespace vb
             __syncwarp();
             return ok;
         }
+        VB_TICK_BEGIN;
         // joint-pair tables (codegen/pair_tables.py): the load is issued ahead of the chain, which hides its latency
         uint32_t pfree[Robot::kSelfWords];
         bool phit = false;
@@ -276,9 +281,11 @@ namespace vb
         if (alive)
         {
             SlotSink sink{sc.col, sc.stride, &a.env.attach, sc.att_col, sc.att_stride};
+            VB_TICK(0);
             Robot::chain(sink, q);
         }
         __syncwarp();
+        VB_TICK(1);
         WalkCtx wc;
         wc.wcol = sc.col - (threadIdx.x & 31);
         wc.queues = sc.queues;
@@ -305,10 +312,11 @@ namespace vb
         const size_t n_round = (a.n + 31) / 32 * 32;
         // CTA-uniform trip count with a barrier per iteration: the warps of a CTA walk the (large, mostly
         // straight-line) code together, so the instruction cache serves one stream instead of seven
+        unsigned iter = 0;
         for (size_t base = static_cast<size_t>(blockIdx.x) * blockDim.x; base < n_round; base += stride)
         {
             const size_t i = base + threadIdx.x;
-            if (kLockstep)
+            if (kLockstep && (iter++ % kLockstepEvery) == 0)
             {
                 __syncthreads();
             }
@@ -379,17 +387,22 @@ namespace vb
         const size_t n_round = (a.n + 31) / 32 * 32;
         // CTA-uniform trip count with a barrier per iteration: the warps of a CTA walk the (large, mostly
         // straight-line) code together, so the instruction cache serves one stream instead of seven
+        unsigned iter = 0;
         for (size_t base = static_cast<size_t>(blockIdx.x) * blockDim.x; base < n_round; base += stride)
         {
             const size_t i = base + threadIdx.x;
-            if (kLockstep)
+            VB_TICK_BEGIN;
+            if (kLockstep && (iter++ % kLockstepEvery) == 0)
             {
                 __syncthreads();
             }
+            VB_TICK(10);
             const bool alive = i < a.n;
             float q[Robot::kDim];
             random_config<Robot>(a.seed, first + i, q);
+            VB_TICK(11);
             const bool ok = check_warp<Robot>(a, prims, q, alive, a.attach != 0, cstate);
+            VB_TICK(12);
             const uint32_t word = __ballot_sync(0xffffffffu, ok);
             if ((threadIdx.x & 31) == 0 && i < n_round)
             {

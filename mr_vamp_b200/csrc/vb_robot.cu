@@ -122,6 +122,18 @@ namespace vb
         random_config<R>(seed, index, q);
     }
 
+#ifdef VB_PHASE_CLOCKS
+    extern "C" int vb_debug_phase_clocks(unsigned long long *out16, int reset)
+    {
+        if (reset)
+        {
+            unsigned long long z[16] = {};
+            return cudaMemcpyToSymbol(vb_phase_clocks, z, sizeof(z));
+        }
+        return cudaMemcpyFromSymbol(out16, vb_phase_clocks, 16 * sizeof(unsigned long long));
+    }
+#endif
+
     const RobotOps *VB_OPS()
     {
         static RobotOps ops = [] {

@@ -29,6 +29,32 @@ namespace vb
 {
     constexpr unsigned kFull = 0xffffffffu;
 
+    // The stages of the walk are inlined into the kernel: as separate functions every call spills the caller's
+    // live state to local memory (ABI), ~170 local loads/stores per warp and iteration that also evict the
+    // tables from the small L1 left beside 224 KB of shared memory.
+#ifndef VB_STAGE
+#define VB_STAGE __device__ __forceinline__
+#endif
+
+    // development aid (-DVB_PHASE_CLOCKS): cycles per phase of the walk, summed over warps (lane 0's clock)
+#ifdef VB_PHASE_CLOCKS
+    __device__ unsigned long long vb_phase_clocks[16];
+#define VB_TICK_BEGIN long long vb_last_ = clock64()
+#define VB_TICK(k)                                                                               \
+    do                                                                                           \
+    {                                                                                            \
+        const long long now_ = clock64();                                                        \
+        if ((threadIdx.x & 31) == 0)                                                             \
+        {                                                                                        \
+            atomicAdd(&vb_phase_clocks[k], static_cast<unsigned long long>(now_ - vb_last_));    \
+        }                                                                                        \
+        vb_last_ = clock64();                                                                    \
+    } while (0)
+#else
+#define VB_TICK_BEGIN
+#define VB_TICK(k)
+#endif
+
     // The walk addresses its shared memory as INDICES from the start of the dynamic shared-memory window
     // (not as pointers carried through structs): the compiler then knows the address space and emits
     // LDS/STS/ATOMS instead of generic loads that resolve the window at run time.
@@ -129,7 +155,7 @@ namespace vb
         }
 
         // ---- self collision, stage 2: queued (configuration, a_i) units ----------------------------
-        __device__ __noinline__ static void pair_stage(const WalkCtx c)
+        VB_STAGE static void pair_stage(const WalkCtx c)
         {
             const WalkTables w = Robot::walk_tables();
             const int lane = threadIdx.x & 31;
@@ -173,7 +199,7 @@ namespace vb
 
         // ---- self collision, stage 1: one (configuration, group) item per lane ------------------------
         // every a_i of the item against the inflated bounding sphere of the other link
-        __device__ __noinline__ static void filter_stage(const WalkCtx c, int nq)
+        VB_STAGE static void filter_stage(const WalkCtx c, int nq)
         {
             const WalkTables w = Robot::walk_tables();
             const int lane = threadIdx.x & 31;
@@ -256,7 +282,7 @@ namespace vb
         }
 
         // ---- environment, stage 2: queued (configuration, fine sphere) units ---------------------------
-        __device__ __noinline__ static void fine_stage(const EnvView &env, const WalkCtx c)
+        VB_STAGE static void fine_stage(const EnvView &env, const WalkCtx c)
         {
             const WalkTables w = Robot::walk_tables();
             const int lane = threadIdx.x & 31;
@@ -290,7 +316,7 @@ namespace vb
         // that touch the guard sphere inflated by the group's static slack.  The fine spheres of a fired
         // guard become units of stage 2 (the pair queue is free at this point and is reused), where they
         // are tested, with the exact primitive arithmetic of the reference, against those few obstacles.
-        __device__ __noinline__ static void env_stage(const EnvView &env, const WalkCtx c, int ne)
+        VB_STAGE static void env_stage(const EnvView &env, const WalkCtx c, int ne)
         {
             const WalkTables w = Robot::walk_tables();
             const int lane = threadIdx.x & 31;
@@ -387,6 +413,7 @@ namespace vb
         // `pfree`: bit g set = self group g cannot collide at this lane's configuration (joint-pair tables).
         VB_D static bool run(const EnvView &env, const WalkCtx &c, bool collided, int &cstate, const uint32_t *pfree)
         {
+            VB_TICK_BEGIN;
             const auto &t = Robot::tables();
             const int lane = threadIdx.x & 31;
             const unsigned lt = (1u << lane) - 1u;
@@ -435,7 +462,8 @@ namespace vb
             const bool has_other = (env.n_heightfields | env.n_capts) != 0;
             const bool grid = env.sdf.cell != nullptr && !has_other;
             uint2 cells[Robot::kEnvGroups > 0 ? Robot::kEnvGroups : 1];
-            uint32_t inside[Robot::kEnvWords];
+            uint32_t inside[Robot::kEnvWords], maybe[Robot::kEnvWords], cert[Robot::kEnvWords];
+            bool classified = false;
             if (grid)
             {
                 Robot::env_fetch(col, c.bx, c.by, c.bz, env.sdf, cells, inside);
@@ -445,7 +473,17 @@ namespace vb
             if (t.n_self > 0)
             {
                 uint32_t fired[Robot::kSelfWords], dpass[Robot::kDenseN];
+                VB_TICK(2);
                 Robot::self_guards(col, fired, dpass);
+                VB_TICK(3);
+                if (grid)
+                {
+                    // consumed here, not after the stages below: 22 registers of in-flight loads held across
+                    // their calls would be spilled, i.e. waited for, at the first call
+                    Robot::env_classify(cells, inside, c.radius, env.sdf, maybe, cert, gmask(c) + lane);
+                    classified = true;
+                }
+                VB_TICK(7);
                 const uint32_t live = collided ? 0u : 0xffffffffu;
 #pragma unroll
                 for (int wi = 0; wi < Robot::kSelfWords; ++wi)
@@ -496,8 +534,11 @@ namespace vb
                     }
                 }
                 __syncwarp();
+                VB_TICK(4);
                 filter_stage(c, nq);
+                VB_TICK(5);
                 pair_stage(c);
+                VB_TICK(6);
                 collided = collided || done(c, lane);
             }
             if (__all_sync(kFull, collided))
@@ -510,10 +551,12 @@ namespace vb
             {
                 return !collided;
             }
-            uint32_t maybe[Robot::kEnvWords], cert[Robot::kEnvWords];
             if (grid)
             {
-                Robot::env_classify(cells, inside, c.radius, env.sdf, maybe, cert, gmask(c) + lane);
+                if (!classified)
+                {
+                    Robot::env_classify(cells, inside, c.radius, env.sdf, maybe, cert, gmask(c) + lane);
+                }
             }
             else
             {
@@ -580,7 +623,9 @@ namespace vb
                 }
             }
             __syncwarp();
+            VB_TICK(8);
             env_stage(env, c, ne);
+            VB_TICK(9);
             return !(collided || done(c, lane));
         }
     };
