@@ -376,16 +376,13 @@ def _uniform(em: _Emitter) -> list[str]:
     F = np.float32
     ns, ne = len(em.selfg), len(em.env)
     sw, ew = max((ns + 31) // 32, 1), max((ne + 31) // 32, 1)
-    dense = [gi for gi, g in enumerate(em.selfg) if g.get("dense")]
-    leaf_mask, dense_mask = [0] * sw, [0] * sw
+    leaf_mask = [0] * sw
     for gi, g in enumerate(em.selfg):
         if g["a"][1] == 0:
             leaf_mask[gi // 32] |= 1 << (gi % 32)
-        if g.get("dense"):
-            dense_mask[gi // 32] |= 1 << (gi % 32)
     out: list[str] = []
     w = out.append
-    w(f"    static constexpr int kSelfWords = {sw}, kEnvWords = {ew}, kDenseN = {max(len(dense), 1)}, kDenseUsed = {len(dense)};")
+    w(f"    static constexpr int kSelfWords = {sw}, kEnvWords = {ew};")
 
     def table(name, typ, vals):
         w(f"    VB_D static {typ} {name}(int i)")
@@ -405,28 +402,28 @@ def _uniform(em: _Emitter) -> list[str]:
     table("env_const_mask", "uint32_t", const_mask)
     w(f"    static constexpr bool kEnvConstAny = {'true' if any(const_mask) else 'false'};")
     table("self_leaf_mask", "uint32_t", leaf_mask)
-    table("self_dense_mask", "uint32_t", dense_mask)
-    table("dense_group", "int", dense or [0])
 
-    loaded: set[int] = set()
+    def sphere_loads(loaded: set[int], body: list[str]):
+        def need(slot: int):
+            if slot not in loaded:
+                loaded.add(slot)
+                if slot & CONST_SLOT:
+                    x, y, z = em.const_xyz[slot]
+                    body.append(f"const float s{slot}x = {x}, s{slot}y = {y}, s{slot}z = {z};")
+                    return
+                body.append(
+                    f"const float s{slot}x = col[{3 * slot} * kStride], s{slot}y = col[{3 * slot + 1} * kStride], s{slot}z = col[{3 * slot + 2} * kStride];"
+                )
+
+        def d2(a: int, b: int) -> str:
+            need(a)
+            need(b)
+            return f"sqd(s{a}x - s{b}x, s{a}y - s{b}y, s{a}z - s{b}z)"
+
+        return d2
+
     body: list[str] = []
-
-    def need(slot: int):
-        if slot not in loaded:
-            loaded.add(slot)
-            if slot & CONST_SLOT:
-                x, y, z = em.const_xyz[slot]
-                body.append(f"const float s{slot}x = {x}, s{slot}y = {y}, s{slot}z = {z};")
-                return
-            body.append(
-                f"const float s{slot}x = col[{3 * slot} * kStride], s{slot}y = col[{3 * slot + 1} * kStride], s{slot}z = col[{3 * slot + 2} * kStride];"
-            )
-
-    def d2(a: int, b: int) -> str:
-        need(a)
-        need(b)
-        return (f"sqd(s{a}x - s{b}x, s{a}y - s{b}y, s{a}z - s{b}z)")
-
+    d2 = sphere_loads(set(), body)
     for wi in range(sw):
         body.append(f"uint32_t f{wi} = 0u;")
     for gi, g in enumerate(em.selfg):
@@ -436,24 +433,55 @@ def _uniform(em: _Emitter) -> list[str]:
         body.append(f"f{gi // 32} |= ({d2(sa, sb)} < {_f32(float(rs2))}) ? {1 << (gi % 32)}u : 0u;  // {g['name']}")
     for wi in range(sw):
         body.append(f"fired[{wi}] = f{wi};")
-    for di, gi in enumerate(dense):
-        g = em.selfg[gi]
-        sb, rb = g["gb"][0], g["gb"][2]
-        terms = []
-        for i in range(g["a"][1]):
-            sa, _, ra = em.refs[g["a"][0] + i]
-            if g["slack"] < 0:
-                terms.append(f"{1 << i}u")
-                continue
-            R = F(F(ra) + F(rb)) + F(g["slack"])
-            terms.append(f"(({d2(sa, sb)} < {_f32(float(F(R * R)))}) ? {1 << i}u : 0u)")
-        body.append(f"dpass[{di}] = " + " | ".join(terms) + f";  // {g['name']}")
-    w("    // self-collision guard pairs (bit g of fired[]) and a-side filters of the dense groups (bit i of dpass[d])")
-    w("    __device__ __forceinline__ static void self_guards(const float *__restrict__ col, uint32_t *__restrict__ fired, uint32_t *__restrict__ dpass)")
+    w("    // self-collision guard pairs (bit g of fired[])")
+    w("    __device__ __forceinline__ static void self_guards(const float *__restrict__ col, uint32_t *__restrict__ fired)")
     w("    {")
     w("        auto sqd = [](float dx, float dy, float dz) { return dx * dx + dy * dy + dz * dz; };")
     for ln in body:
         w("        " + ln)
+    w("    }")
+
+    # a-side filters: unit (g, a_i) survives when a_i touches the other link's bounding sphere inflated by the
+    # group's static slack.  A group is evaluated when its guard fired in any lane of the warp (warp-uniform
+    # branch), with immediate offsets and radii; bit `unit` of ubits[] = unit to be run by the pair stage.
+    n_units = sum(g["a"][1] for g in em.selfg)
+    uw = max((n_units + 31) // 32, 1)
+    w(f"    static constexpr int kUnitWords = {uw};  // {n_units} (group, a_i) work units")
+    w("    // fired[]: this lane's guard hits (collided / tabulated-free groups already cleared)")
+    w("    __device__ __forceinline__ static void self_filters(const float *__restrict__ col, const uint32_t *__restrict__ fired, uint32_t *__restrict__ ubits)")
+    w("    {")
+    w("        auto sqd = [](float dx, float dy, float dz) { return dx * dx + dy * dy + dz * dz; };")
+    for wi in range(uw):
+        w(f"        uint32_t u{wi} = 0u;")
+    unit = 0
+    for gi, g in enumerate(em.selfg):
+        ac = g["a"][1]
+        if ac == 0:
+            continue
+        assert g["unit0"] == unit, (g["name"], g["unit0"], unit)
+        sb, rb = g["gb"][0], g["gb"][2]
+        blk: list[str] = []
+        d2g = sphere_loads(set(), blk)
+        for i in range(ac):
+            sa, _, ra = em.refs[g["a"][0] + i]
+            pos = unit + i
+            if g["slack"] < 0:
+                blk.append(f"u{pos // 32} |= {1 << (pos % 32)}u;")
+            else:
+                R = F(F(ra) + F(rb)) + F(g["slack"])
+                blk.append(f"u{pos // 32} |= ({d2g(sa, sb)} < {_f32(float(F(R * R)))}) ? {1 << (pos % 32)}u : 0u;")
+        bit = f"(fired[{gi // 32}] & {1 << (gi % 32)}u)"
+        w(f"        if (__any_sync(0xffffffffu, {bit} != 0u))  // {g['name']}")
+        w("        {")
+        w(f"            if ({bit} != 0u)")
+        w("            {")
+        for ln in blk:
+            w("                " + ln)
+        w("            }")
+        w("        }")
+        unit += ac
+    for wi in range(uw):
+        w(f"        ubits[{wi}] = u{wi};")
     w("    }")
     # environment guards: one branch-free grid fetch each, classified after the self-collision phase
     w("    // issues the grid-cell load of every environment guard sphere (bit g of inside[]: centre inside the grid)")

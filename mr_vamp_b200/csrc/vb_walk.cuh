@@ -99,7 +99,6 @@ namespace vb
 
         // self items and environment items are never queued at the same time: one array serves both
         VB_D static uint16_t *envq(const WalkCtx &c) { return shm_u16() + c.queues / 2; }
-        VB_D static uint16_t *selfq(const WalkCtx &c) { return envq(c); }
         VB_D static uint16_t *pairq(const WalkCtx &c) { return envq(c) + kItemQ; }
         VB_D static unsigned *gmask(const WalkCtx &c) { return shm_u32() + (c.queues + 2 * (kItemQ + Robot::kPairQ)) / 4; }
         VB_D static unsigned *cmask(const WalkCtx &c) { return gmask(c) + 32 * kGroups; }
@@ -154,13 +153,11 @@ namespace vb
             return hit;
         }
 
-        // ---- self collision, stage 2: queued (configuration, a_i) units ----------------------------
-        VB_STAGE static void pair_stage(const WalkCtx c)
+        // ---- self collision: queued (configuration, a_i) units, one per lane -----------------------------
+        VB_STAGE static void pair_stage(const WalkCtx c, int np)
         {
             const WalkTables w = Robot::walk_tables();
             const int lane = threadIdx.x & 31;
-            __syncwarp();
-            const int np = min(static_cast<int>(vol(cmask(c) + 1)), Robot::kPairQ);
             for (int base = 0; base < np; base += 32)
             {
                 const int i = base + lane;
@@ -176,89 +173,66 @@ namespace vb
                 }
             }
             __syncwarp();
-            if (lane == 0)
-            {
-                cmask(c)[1] = 0u;
-            }
-            __syncwarp();
         }
 
-        // queue one (configuration, a_i) unit; when the queue is full the lane runs the unit itself
-        VB_D static void push_pair(const WalkCtx &c, const WalkTables &w, int L, int unit, const SelfUnit &u)
+        // Queues the units of this lane's bit set (bit = unit index) behind those of the lower lanes and runs
+        // the pair stage.  All 32 lanes call.
+        VB_STAGE static void run_units(const WalkCtx c, const uint32_t *ubits)
         {
-            const unsigned at_ = atomicAdd(cmask(c) + 1, 1u);
-            if (at_ < static_cast<unsigned>(Robot::kPairQ))
-            {
-                pairq(c)[at_] = static_cast<uint16_t>(L | (unit << 5));
-            }
-            else if (pair_unit(c, w, L, u))
-            {
-                atomicOr(cmask(c), 1u << L);
-            }
-        }
-
-        // ---- self collision, stage 1: one (configuration, group) item per lane ------------------------
-        // every a_i of the item against the inflated bounding sphere of the other link
-        VB_STAGE static void filter_stage(const WalkCtx c, int nq)
-        {
-            const WalkTables w = Robot::walk_tables();
             const int lane = threadIdx.x & 31;
-            for (int base = 0; base < nq; base += 32)
+            int cnt = 0;
+#pragma unroll
+            for (int wi = 0; wi < Robot::kUnitWords; ++wi)
             {
-                const int i = base + lane;
-                if (i < nq)
+                cnt += __popc(ubits[wi]);
+            }
+            int incl = cnt;
+#pragma unroll
+            for (int d = 1; d < 32; d <<= 1)
+            {
+                const int v = __shfl_up_sync(kFull, incl, d);
+                incl += lane >= d ? v : 0;
+            }
+            const int total = __shfl_sync(kFull, incl, 31);
+            if (total == 0)
+            {
+                return;
+            }
+            if (total <= Robot::kPairQ)
+            {
+                int at_ = incl - cnt;
+#pragma unroll
+                for (int wi = 0; wi < Robot::kUnitWords; ++wi)
                 {
-                    const unsigned code = selfq(c)[i];
-                    const int L = code & 31;
-                    const SelfGroup G = ldg_record(w.self + (code >> 5));
-                    const int ac = G.a_count, u0 = G.unit0;
-                    if (!done(c, L))
+                    uint32_t m = ubits[wi];
+                    while (m)
                     {
-                        const SelfUnit *U = w.units + u0;
-                        float gx, gy, gz;
-                        at(c, L, ldg_record(U).gb_off, gx, gy, gz);
-#pragma unroll 2
-                        for (int k = 0; k < ac; ++k)
-                        {
-                            const SelfUnit u = ldg_record(U + k);
-                            float ax, ay, az;
-                            at(c, L, u.a_off, ax, ay, az);
-                            const float dx = ax - gx, dy = ay - gy, dz = az - gz;
-                            if (u.filter_r < 0.f || dx * dx + dy * dy + dz * dz - u.filter_r * u.filter_r < 0.f)
-                            {
-                                push_pair(c, w, L, u0 + k, u);
-                            }
-                        }
+                        const int b = __ffs(m) - 1;
+                        m &= m - 1u;
+                        pairq(c)[at_++] = static_cast<uint16_t>(lane | ((wi * 32 + b) << 5));
                     }
                 }
                 __syncwarp();
-                if (vol(cmask(c) + 1) >= static_cast<unsigned>(Robot::kPairQ) / 2)
+                pair_stage(c, total);
+                return;
+            }
+            // more units than the queue holds (rare): every lane runs its own units
+            const WalkTables w = Robot::walk_tables();
+            bool hit = false;
+#pragma unroll
+            for (int wi = 0; wi < Robot::kUnitWords; ++wi)
+            {
+                uint32_t m = ubits[wi];
+                while (m && !hit)
                 {
-                    pair_stage(c);
+                    const int b = __ffs(m) - 1;
+                    m &= m - 1u;
+                    hit = pair_unit(c, w, lane, ldg_record(w.units + wi * 32 + b));
                 }
             }
-            __syncwarp();
-        }
-
-        // convergent variant of push_pair: all 32 lanes call, lanes with `on` queue one unit each
-        VB_D static void push_pairs(const WalkCtx &c, bool on, unsigned code)
-        {
-            const int lane = threadIdx.x & 31;
-            const unsigned m = __ballot_sync(kFull, on);
-            unsigned base = vol(cmask(c) + 1);
-            if (base + 32u > static_cast<unsigned>(Robot::kPairQ))
+            if (hit)
             {
-                pair_stage(c);
-                base = 0u;
-            }
-            if (on)
-            {
-                pairq(c)[base + __popc(m & ((1u << lane) - 1u))] = static_cast<uint16_t>(code);
-            }
-            __syncwarp();
-            if (lane == 0)
-            {
-                cmask(c)[1] = base + __popc(m);
+                atomicOr(cmask(c), 1u << lane);
             }
             __syncwarp();
         }
@@ -472,9 +446,9 @@ namespace vb
             // ---------------- self collision ----------------
             if (t.n_self > 0)
             {
-                uint32_t fired[Robot::kSelfWords], dpass[Robot::kDenseN];
+                uint32_t fired[Robot::kSelfWords];
                 VB_TICK(2);
-                Robot::self_guards(col, fired, dpass);
+                Robot::self_guards(col, fired);
                 VB_TICK(3);
                 if (grid)
                 {
@@ -491,53 +465,18 @@ namespace vb
                     fired[wi] &= live & ~pfree[wi];
                     collided = collided || (fired[wi] & Robot::self_leaf_mask(wi)) != 0u;
                 }
-                const WalkTables w = Robot::walk_tables();
-                // dense groups: the a-side filter ran lane-parallel in the guard phase; queue the survivors
-#pragma unroll
-                for (int d = 0; d < Robot::kDenseUsed; ++d)
-                {
-                    const int g = Robot::dense_group(d);
-                    uint32_t todo = ((fired[g >> 5] >> (g & 31)) & 1u) && !collided ? dpass[d] : 0u;
-                    const int unit0 = t.self[g].unit0;
-                    while (__any_sync(kFull, todo != 0u))
-                    {
-                        const bool on = todo != 0u;
-                        const int k = on ? __ffs(todo) - 1 : 0;
-                        todo &= todo - 1u;
-                        push_pairs(c, on, lane | ((unit0 + k) << 5));
-                    }
-                }
-                // rare groups: one item per (lane, fired group), appended group by group
-                int nq = 0;
+                VB_TICK(4);
+                // a-side filters of the fired groups, lane-parallel and straight-line; the surviving (group, a_i)
+                // units of all 32 configurations are then spread over the lanes
+                uint32_t ubits[Robot::kUnitWords];
 #pragma unroll
                 for (int wi = 0; wi < Robot::kSelfWords; ++wi)
                 {
-                    const uint32_t mine = collided ? 0u : (fired[wi] & ~Robot::self_leaf_mask(wi) & ~Robot::self_dense_mask(wi));
-                    uint32_t any = __reduce_or_sync(kFull, mine);
-                    while (any)
-                    {
-                        const int b = __ffs(any) - 1;
-                        any &= any - 1u;
-                        const bool on = (mine >> b) & 1u;
-                        const unsigned m = __ballot_sync(kFull, on);
-                        if (nq + 32 > Robot::kSelfQ)
-                        {
-                            filter_stage(c, nq);
-                            pair_stage(c);
-                            nq = 0;
-                        }
-                        if (on)
-                        {
-                            selfq(c)[nq + __popc(m & lt)] = static_cast<uint16_t>(lane | ((wi * 32 + b) << 5));
-                        }
-                        nq += __popc(m);
-                    }
+                    fired[wi] = collided ? 0u : (fired[wi] & ~Robot::self_leaf_mask(wi));
                 }
-                __syncwarp();
-                VB_TICK(4);
-                filter_stage(c, nq);
+                Robot::self_filters(col, fired, ubits);
                 VB_TICK(5);
-                pair_stage(c);
+                run_units(c, ubits);
                 VB_TICK(6);
                 collided = collided || done(c, lane);
             }
