@@ -153,6 +153,10 @@ uint64_t vb_launch_count(const vb_ctx *);
 /* counts set bits of a device bitmask with n valid bits */
 int vb_popcount_d(vb_ctx *, int slot, const uint32_t *bits_d, size_t n, uint64_t *count);
 
+/* measured FP32 FMA throughput of the slot's device (roofline denominator of the fkcc kernels);
+   best of 3 timed launches of 8 independent FMA chains per thread, in TFLOP/s */
+int vb_fp32_peak_d(vb_ctx *, int slot, double *tflops);
+
 /* ---- multi-process gather (one process per GPU, NCCL over NVLink) ------------------------- */
 /* id_bytes: 128-byte ncclUniqueId created by rank 0 with vb_comm_unique_id and distributed by the caller */
 int vb_comm_unique_id(void *id_bytes_128);

@@ -69,6 +69,7 @@ _SIGNATURES = [
     ("vb_timer_start", C.c_int, [_vp, C.c_int]),
     ("vb_timer_stop", C.c_int, [_vp, C.c_int, C.POINTER(C.c_double)]),
     ("vb_launch_count", C.c_uint64, [_vp]),
+    ("vb_fp32_peak_d", C.c_int, [_vp, C.c_int, C.POINTER(C.c_double)]),
     ("vb_popcount_d", C.c_int, [_vp, C.c_int, _vp, C.c_size_t, C.POINTER(C.c_uint64)]),
     ("vb_comm_unique_id", C.c_int, [_vp]),
     ("vb_comm_init", C.c_int, [_vp, C.c_int, C.c_int, _vp]),

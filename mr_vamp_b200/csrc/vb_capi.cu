@@ -1043,6 +1043,28 @@ namespace
         }
     }
 
+
+    // FP32 roofline denominator: 8 independent FMA chains per thread, 2 flops per FMA
+    __global__ void __launch_bounds__(256) fma_peak_kernel(float *sink, int iters, float a, float b)
+    {
+        float x0 = threadIdx.x * 1e-3f, x1 = x0 + 1.f, x2 = x0 + 2.f, x3 = x0 + 3.f;
+        float x4 = x0 + 4.f, x5 = x0 + 5.f, x6 = x0 + 6.f, x7 = x0 + 7.f;
+        for (int i = 0; i < iters; ++i)
+        {
+#pragma unroll
+            for (int k = 0; k < 8; ++k)
+            {
+                x0 = fmaf(x0, a, b); x1 = fmaf(x1, a, b); x2 = fmaf(x2, a, b); x3 = fmaf(x3, a, b);
+                x4 = fmaf(x4, a, b); x5 = fmaf(x5, a, b); x6 = fmaf(x6, a, b); x7 = fmaf(x7, a, b);
+            }
+        }
+        const float v = ((x0 + x1) + (x2 + x3)) + ((x4 + x5) + (x6 + x7));
+        if (v == 12345.678f)
+        {
+            sink[0] = v;  // never true in practice: keeps the chains alive
+        }
+    }
+
     struct Query
     {
         vb_ctx *ctx;
@@ -1265,6 +1287,38 @@ int vb_popcount_d(vb_ctx *ctx, int slot, const uint32_t *bits_d, size_t n, uint6
     if (count)
     {
         *count = host;
+    }
+    return VB_OK;
+}
+
+
+int vb_fp32_peak_d(vb_ctx *ctx, int slot, double *tflops)
+{
+    VB_TRY(check_slot(ctx, slot));
+    Slot &s = ctx->slots[slot];
+    VB_CUDA(cudaSetDevice(s.device));
+    VB_CUDA(s.scan_tmp.reserve(sizeof(unsigned long long)));
+    const int iters = 4096, ctas = s.sm_count * 8;
+    double best = 0.0;
+    for (int rep = 0; rep < 4; ++rep)
+    {
+        VB_CUDA(cudaEventRecord(s.ev0, s.stream));
+        fma_peak_kernel<<<ctas, 256, 0, s.stream>>>(s.scan_tmp.as<float>(), iters, 0.999f, 1e-3f);
+        VB_CUDA(cudaGetLastError());
+        VB_CUDA(cudaEventRecord(s.ev1, s.stream));
+        VB_CUDA(cudaEventSynchronize(s.ev1));
+        ctx->launches += 1;
+        float ms = 0.f;
+        VB_CUDA(cudaEventElapsedTime(&ms, s.ev0, s.ev1));
+        const double flops = 2.0 * 64.0 * iters * 256.0 * ctas;
+        if (rep > 0 && ms > 0.f)
+        {
+            best = std::max(best, flops / (ms * 1e-3) / 1e12);
+        }
+    }
+    if (tflops)
+    {
+        *tflops = best;
     }
     return VB_OK;
 }
