@@ -534,14 +534,15 @@ def _queue_bytes(geom: dict) -> int:
     return 2 * (max(geom["env_q"], geom["self_q"]) + geom["pair_q"]) + 128 * geom["env_groups"] + 16
 
 
-def _geometry(n_slots: int, geom: dict) -> tuple[int, int]:
+def _geometry(n_slots: int, geom: dict, dim: int = 0) -> tuple[int, int]:
     """(warps per CTA, CTAs per SM) maximising resident warps within 227 KB of shared memory per SM."""
     queue = _queue_bytes(geom)
-    per_warp = 3 * n_slots * 4 * 32 + queue
-    fixed = 3 * n_slots * 4 + 16 + 1024  # stride padding, per-CTA reserve
+    per_warp = 3 * n_slots * 4 * 32 + queue + 4 * dim * 32  # columns + queues + staged configurations (vb_kernels.cuh)
+    fixed = 3 * n_slots * 4 + 16 + 16  # stride padding, staging mbarrier
     best = (1, 1)
     for ctas in (1, 2, 3, 4, 6, 8):
-        w = min((227 * 1024 // ctas - fixed) // per_warp, 16, 32 // ctas)
+        # 228 KB per SM, 1 KB of it reserved per resident CTA
+        w = min((228 * 1024 // ctas - 1024 - fixed) // per_warp, 16, 32 // ctas)
         if w >= 1 and w * ctas > best[0] * best[1]:
             best = (int(w), ctas)
     return best
@@ -586,7 +587,16 @@ def emit_robot(ir: dict[str, Any]) -> str:
     const_row = max(em.n_rows, em_att.n_rows if em_att else 0)
     n_const = max(len(em.const_slots), len(em_att.const_slots) if em_att else 0)
     n_slots = const_row + (n_const + 31) // 32
+    # Staged configurations (vb_kernels.cuh) are worth their shared memory only if they do not cost a resident
+    # warp; queue capacities shrink first (overflowing units run in place, vb_walk.cuh).
     warps, ctas = _geometry(n_slots, geom)
+    stage_cfg = False
+    for cap in (256, 192, 128):
+        smaller = dict(geom, pair_q=cap, env_q=max(cap, 192), self_q=max(cap, 192))
+        w2, c2 = _geometry(n_slots, smaller, dim)
+        if w2 * c2 >= warps * ctas:
+            geom, warps, ctas, stage_cfg = smaller, w2, c2, True
+            break
     tab, ttype, _ = _tables(f"k_{robot}_tables", em, walk=True, stride=32 * warps + 1, const_row=const_row)
     out.extend(tab)
     if em_att:
@@ -604,7 +614,9 @@ def emit_robot(ir: dict[str, Any]) -> str:
     w(f"    static constexpr int kSlots = {n_slots};  // shared-memory slot rows: {const_row} per-thread + {n_slots - const_row} of per-warp constants")
     w(f"    static constexpr int kConstRow = {const_row};  // first constant row ({n_const} configuration-independent centres)")
     w(f"    static constexpr int kBlock = {32 * warps};  // threads per CTA: {warps} warps x {ctas} CTA(s) per SM fill the shared memory")
+    w(f"    static constexpr int kCtasPerSm = {ctas};  // resident CTAs per SM (second argument of __launch_bounds__)")
     w("    static constexpr int kStride = kBlock + 1;  // slot-column stride in floats (odd: conflict free)")
+    w(f"    static constexpr bool kStageCfg = {'true' if stage_cfg else 'false'};  // configurations staged in shared memory by bulk copy")
     w(f"    static constexpr int kEnvQ = {geom['env_q']}, kSelfQ = {geom['self_q']}, kPairQ = {geom['pair_q']};  // work-queue capacities (units)")
     w(f"    static constexpr int kChainFlops = {st['chain_flops']};")
     w(f"    static constexpr int kEnvGroups = {st['env_groups']}, kEnvFine = {st['env_fine']};")
@@ -643,7 +655,7 @@ def emit_robot(ir: dict[str, Any]) -> str:
     w("    }")
 
     def fn(name: str, body: list[str], sink: str = "SlotSink"):
-        w(f"    __device__ __noinline__ static void {name}(const {sink} &p, const float *__restrict__ q)")
+        w(f"    __device__ VB_CHAIN_ATTR static void {name}(const {sink} &p, const float *__restrict__ q)")
         w("    {")
         for ln in body:
             w("        " + ln)

@@ -7,6 +7,13 @@
 // quarter of a box; every lane of a warp walks the same record at the same time, so the loads
 // are broadcasts.
 #pragma once
+// inlining policy of the two large device functions (A/B switchable at build time)
+#ifndef VB_CHAIN_ATTR
+#define VB_CHAIN_ATTR __forceinline__
+#endif
+#ifndef VB_ENVHIT_ATTR
+#define VB_ENVHIT_ATTR __noinline__
+#endif
 #include "vb_numerics.cuh"
 
 namespace vb
@@ -217,7 +224,7 @@ namespace vb
     // from the origin, as the reference does; with an exact sqrt the cut is conservative, so the
     // verdict equals the unpruned OR over all obstacles.
     template <class M>
-    __device__ __noinline__ bool env_hit(const EnvView &e, const float4 *P, float sx, float sy, float sz, float sr, M &mg)
+    __device__ VB_ENVHIT_ATTR bool env_hit(const EnvView &e, const float4 *P, float sx, float sy, float sz, float sr, M &mg)
     {
         const float ext = sqrtf(sx * sx + sy * sy + sz * sz) + sr;
         mg.count(9);

@@ -16,11 +16,23 @@ namespace vb
 {
     // the warps of a CTA are kept on one instruction stream with CTA barriers (the hot code is ~75 KB of mostly
     // straight-line SASS; seven independent streams per SM thrash the instruction caches)
+#ifdef VB_NO_LOCKSTEP
+    constexpr bool kLockstep = false;
+#else
     constexpr bool kLockstep = true;
+#endif
+#ifdef VB_NO_STAGE
+    constexpr bool kStageAllowed = false;
+#else
+    constexpr bool kStageAllowed = true;
+#endif
 #ifndef VB_LOCKSTEP_EVERY
 #define VB_LOCKSTEP_EVERY 1
 #endif
     constexpr unsigned kLockstepEvery = VB_LOCKSTEP_EVERY;
+    // Every fkcc / motion kernel states its resident CTAs per SM (Robot::kCtasPerSm, fixed by the shared-memory
+    // columns) as the second __launch_bounds__ argument: without it ptxas plans for 4 CTAs of kBlock threads,
+    // caps the kernels at 64 registers and spills the in-flight grid cells (i.e. waits for every L2 load).
     struct LaunchArgs
     {
         EnvView env;
@@ -300,41 +312,124 @@ namespace vb
         return ok;
     }
 
+    // ---- configuration staging: TMA bulk copy (global -> shared) one grid-stride step ahead ------------
+    // With ~8 resident warps per SM nothing hides the HBM latency of the next configurations, and registers
+    // loaded ahead would be spilled around the chain's call.  One elected thread therefore issues a 1-D bulk
+    // copy (cp.async.bulk, completion on an mbarrier) of the CTA's next kBlock configurations (contiguous,
+    // kBlock * 4 * dim bytes) right after the previous ones were consumed; a full walk later they are in
+    // shared memory.
+    template <class Robot>
+    __host__ __device__ constexpr unsigned cfg_stage_bytes()
+    {
+        return Robot::kStageCfg ? static_cast<unsigned>(Robot::kBlock) * Robot::kDim * 4u + 16u : 0u;  // + the mbarrier
+    }
+    VB_D uint32_t shm_addr(unsigned byte_offset)
+    {
+        extern __shared__ float4 vb_shared_window[];
+        return static_cast<uint32_t>(__cvta_generic_to_shared(vb_shared_window)) + byte_offset;
+    }
+    VB_D void mbar_init(uint32_t mbar, uint32_t count)
+    {
+        asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(mbar), "r"(count) : "memory");
+    }
+    VB_D void mbar_expect_tx(uint32_t mbar, uint32_t bytes)
+    {
+        asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(mbar), "r"(bytes) : "memory");
+    }
+    VB_D void bulk_global_to_shared(uint32_t dst, const void *src, uint32_t bytes, uint32_t mbar)
+    {
+        asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(dst),
+                     "l"(src), "r"(bytes), "r"(mbar)
+                     : "memory");
+    }
+    VB_D void mbar_wait(uint32_t mbar, uint32_t parity)
+    {
+        uint32_t ok;
+        do
+        {
+            asm volatile("{\n.reg .pred p;\nmbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\nselp.u32 %0, 1, 0, p;\n}"
+                         : "=r"(ok)
+                         : "r"(mbar), "r"(parity)
+                         : "memory");
+        } while (!ok);
+    }
+
     // ---- K1: batched fkcc over explicit configurations -----------------------------------------
     // kMode 0: verdicts (warp-cooperative walk); 1: verdicts + margin (lane-serial reference-ordered walk);
     // 2: verdicts + algorithmic flops of the checks (same walk), written to the margin buffer
     template <class Robot, int kMode>
-    __global__ void __launch_bounds__(block_threads<Robot>()) fkcc_kernel(const __grid_constant__ LaunchArgs a)
+    __global__ void __launch_bounds__(block_threads<Robot>(), Robot::kCtasPerSm) fkcc_kernel(const __grid_constant__ LaunchArgs a)
     {
         const Scratch prims = stage_env<Robot>(a, kMode == 0);
         int cstate = -1;
         const size_t stride = static_cast<size_t>(gridDim.x) * blockDim.x;
         const size_t n_round = (a.n + 31) / 32 * 32;
+        // configuration staging (verdict mode): [slot columns][queues][kBlock x dim floats][mbarrier]
+        constexpr unsigned kCfgBytes = static_cast<unsigned>(Robot::kBlock) * Robot::kDim * 4u;
+        const unsigned stage_off = 4u * ((3u * Robot::kSlots * Robot::kStride + 3u) & ~3u) +
+                                   static_cast<unsigned>(Robot::kBlock / 32) * queue_bytes<Robot>();
+        const bool staged = kMode == 0 && kStageAllowed && Robot::kStageCfg && kCfgBytes % 16u == 0u && (reinterpret_cast<uintptr_t>(a.cfg) & 15u) == 0u;
+        const uint32_t stage_buf = shm_addr(stage_off), stage_bar = stage_buf + kCfgBytes;
+        uint32_t stage_parity = 0u;
+        if (staged)
+        {
+            if (threadIdx.x == 0)
+            {
+                mbar_init(stage_bar, 1u);
+                asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+                const size_t first = static_cast<size_t>(blockIdx.x) * blockDim.x;
+                if (first + blockDim.x <= a.n)
+                {
+                    mbar_expect_tx(stage_bar, kCfgBytes);
+                    bulk_global_to_shared(stage_buf, a.cfg + first * Robot::kDim, kCfgBytes, stage_bar);
+                }
+            }
+            __syncthreads();
+        }
         // CTA-uniform trip count with a barrier per iteration: the warps of a CTA walk the (large, mostly
         // straight-line) code together, so the instruction cache serves one stream instead of seven
         unsigned iter = 0;
         for (size_t base = static_cast<size_t>(blockIdx.x) * blockDim.x; base < n_round; base += stride)
         {
             const size_t i = base + threadIdx.x;
-            if (kLockstep && (iter++ % kLockstepEvery) == 0)
-            {
-                __syncthreads();
-            }
             bool ok = false;
             const bool alive = i < a.n;
             float q[Robot::kDim];
+            const bool full = staged && base + blockDim.x <= a.n;  // CTA-uniform: this step's configurations were staged
+            if (full)
+            {
+                mbar_wait(stage_bar, stage_parity);
+                stage_parity ^= 1u;
+                const float *row = shm_f32() + stage_off / 4u + threadIdx.x * Robot::kDim;  // odd stride: conflict free
 #pragma unroll
-            for (int j = 0; j < Robot::kDim; ++j)
-            {
-                q[j] = alive ? __ldg(a.cfg + i * Robot::kDim + j) : 0.f;
+                for (int j = 0; j < Robot::kDim; ++j)
+                {
+                    q[j] = row[j];
+                }
             }
-            if (i + stride < a.n)
+            else
             {
-                // pull the next iteration's configuration towards the SM while this one is processed (no
-                // register cost): with ~7 resident warps per SM nothing else hides the HBM latency
-                const float *nx = a.cfg + (i + stride) * Robot::kDim;
-                asm volatile("prefetch.global.L1 [%0];" ::"l"(nx));
-                asm volatile("prefetch.global.L1 [%0];" ::"l"(nx + Robot::kDim - 1));
+#pragma unroll
+                for (int j = 0; j < Robot::kDim; ++j)
+                {
+                    q[j] = alive ? __ldg(a.cfg + i * Robot::kDim + j) : 0.f;
+                }
+                if (!staged && i + stride < a.n)
+                {
+                    // pull the next step's configuration towards the SM while this one is processed
+                    const float *nx = a.cfg + (i + stride) * Robot::kDim;
+                    asm volatile("prefetch.global.L1 [%0];" ::"l"(nx));
+                    asm volatile("prefetch.global.L1 [%0];" ::"l"(nx + Robot::kDim - 1));
+                }
+            }
+            if (staged || (kLockstep && (iter++ % kLockstepEvery) == 0))
+            {
+                __syncthreads();  // (staging: every thread has taken its configuration out of the buffer)
+            }
+            if (staged && threadIdx.x == 0 && base + stride + blockDim.x <= a.n)
+            {
+                mbar_expect_tx(stage_bar, kCfgBytes);
+                bulk_global_to_shared(stage_buf, a.cfg + (base + stride) * Robot::kDim, kCfgBytes, stage_bar);
             }
             if constexpr (kMode == 1)
             {
@@ -379,7 +474,7 @@ namespace vb
 
     // ---- K1r: fkcc over device-synthesised configurations (0 input bytes) -----------------------
     template <class Robot>
-    __global__ void __launch_bounds__(block_threads<Robot>()) fkcc_random_kernel(const __grid_constant__ LaunchArgs a, size_t first)
+    __global__ void __launch_bounds__(block_threads<Robot>(), Robot::kCtasPerSm) fkcc_random_kernel(const __grid_constant__ LaunchArgs a, size_t first)
     {
         const Scratch prims = stage_env<Robot>(a, true);
         int cstate = -1;
@@ -413,7 +508,7 @@ namespace vb
 
     // ---- K2: sphere_fk ---------------------------------------------------------------------------
     template <class Robot>
-    __global__ void __launch_bounds__(block_threads<Robot>()) sphere_fk_kernel(const LaunchArgs a)
+    __global__ void __launch_bounds__(block_threads<Robot>(), Robot::kCtasPerSm) sphere_fk_kernel(const LaunchArgs a)
     {
         const size_t i = static_cast<size_t>(blockIdx.x) * blockDim.x + threadIdx.x;
         if (i >= a.n)
@@ -524,7 +619,7 @@ namespace vb
     }
 
     template <class Robot, bool kMargin>
-    __global__ void __launch_bounds__(block_threads<Robot>()) motion_kernel(const __grid_constant__ LaunchArgs a)
+    __global__ void __launch_bounds__(block_threads<Robot>(), Robot::kCtasPerSm) motion_kernel(const __grid_constant__ LaunchArgs a)
     {
         const Scratch prims = stage_env<Robot>(a, !kMargin);
         int cstate = -1;
