@@ -324,6 +324,15 @@ def run_b200(args):
     hbm_peak = float(peaks.get("hbm_gbs", 6650.0))
     hbm_achieved = (28.0 + 0.125) * n / (ms_step * 1e-3) / 1e9
 
+    # DRAM traffic of the fkcc kernel per launch, from the committed ncu --set full capture (bytes per configuration
+    # there x the configurations of one launch here); None when the profile is absent
+    traffic = None
+    try:
+        with open(os.path.join(ROOT, "profiles", "r1_panda_fkcc_mbm_traffic.json")) as fh:
+            traffic = float(json.load(fh)["bytes_per_config"]) * n
+    except Exception:
+        pass
+
     # ---- CPU baseline on this box's host cores (bounded sample of the same workload)
     cpu = None
     if world == 1:
@@ -370,7 +379,8 @@ def run_b200(args):
         "gpu_launches": int(launches),
         "clocks": clocks.summary(),
         "roofline": {"bound": "fp32", "achieved": achieved, "peak": fp32_peak, "unit": "TFLOP/s", "frac": achieved / fp32_peak,
-                     "traffic": None, "flops_per_config": w_mean,
+                     "traffic": traffic, "traffic_unit": "bytes per launch (dram read + write; HBM-side, the path is FP32-bound)",
+                     "flops_per_config": w_mean,
                      "peak_source": f"148 SMs x 128 FP32 lanes x 2 x {sm_max_mhz:.0f} MHz (nominal; MEASURED_PEAKS.json has no FP32 entry)",
                      "peak_measured": fp32_measured.value, "frac_measured": achieved / fp32_measured.value if fp32_measured.value else None,
                      "peak_measured_source": "vb_fp32_peak_d: 8 independent FMA chains per thread, 8 x 256-thread CTAs per SM, best of 3, same run",

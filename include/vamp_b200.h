@@ -26,6 +26,8 @@
  *   vb_validate             Helper::validate_configuration, bindings/common.hh:172-182 (joint limits + fkcc)
  *   vb_validate_motion      planning::validate_motion / validate_vector, planning/validate.hh:23-75,
  *                           and Path::validate, planning/plan.hh:155-168 (edges of a path in one call)
+ *   vb_validate_path        Path::validate, planning/plan.hh:155-168 (first invalid edge)
+ *   vb_shortcut_path        planning::shortcut_path, planning/simplify.hh:115-140 (all candidates in one batch)
  *   vb_validate_pairs       the fork's planned MultiRobotEnvironment::check_inter_robot_collisions
  *                           (MR_DEV_PLAN.md:176-198; no reference implementation exists)
  */
@@ -123,6 +125,16 @@ int vb_validate(vb_ctx *, vb_robot, const float *base_xyz, const vb_env *, const
 int vb_validate_motion(vb_ctx *, vb_robot, const float *base_xyz, const vb_env *, const float *starts,
                        const float *goals, size_t n_edges, int resolution, uint32_t *valid_bits,
                        float *margin_or_null);
+/* Batch edge callers.
+ * vb_validate_path: Path::validate, planning/plan.hh:155-168 -- all consecutive edges of `waypoints` [n][dim] in one
+ *   batch; *first_invalid_edge = index of the first invalid edge, -1 if the path is valid.
+ * vb_shortcut_path: planning::shortcut_path, planning/simplify.hh:115-140 -- all (n-1)(n-2)/2 shortcut candidates in
+ *   one batch, then the reference's scan on the verdicts; keep[i] = 1 iff waypoint i survives (same waypoints
+ *   as the reference leaves in the path), *n_kept = how many. */
+int vb_validate_path(vb_ctx *, vb_robot, const float *base_xyz, const vb_env *, const float *waypoints, size_t n,
+                     int resolution, int64_t *first_invalid_edge);
+int vb_shortcut_path(vb_ctx *, vb_robot, const float *base_xyz, const vb_env *, const float *waypoints, size_t n,
+                     int resolution, uint8_t *keep, size_t *n_kept_or_null);
 /* composite validity of two robots sharing one environment: fkcc(a) && fkcc(b) && no sphere of a
  * overlaps a sphere of b (world frame). */
 int vb_validate_pairs(vb_ctx *, vb_robot robot_a, const float *base_a, vb_robot robot_b, const float *base_b,

@@ -69,6 +69,9 @@ _SIGNATURES = [
     ("vb_timer_start", C.c_int, [_vp, C.c_int]),
     ("vb_timer_stop", C.c_int, [_vp, C.c_int, C.POINTER(C.c_double)]),
     ("vb_launch_count", C.c_uint64, [_vp]),
+    ("vb_validate_path", C.c_int, [_vp, C.c_int, _f32p, _vp, _f32p, C.c_size_t, C.c_int, C.POINTER(C.c_int64)]),
+    ("vb_shortcut_path", C.c_int, [_vp, C.c_int, _f32p, _vp, _f32p, C.c_size_t, C.c_int, C.POINTER(C.c_uint8),
+                          C.POINTER(C.c_size_t)]),
     ("vb_fp32_peak_d", C.c_int, [_vp, C.c_int, C.POINTER(C.c_double)]),
     ("vb_popcount_d", C.c_int, [_vp, C.c_int, _vp, C.c_size_t, C.POINTER(C.c_uint64)]),
     ("vb_comm_unique_id", C.c_int, [_vp]),
@@ -451,10 +454,27 @@ class Robot:
 
     def validate_path(self, waypoints, environment: Optional[Environment] = None) -> bool:
         """Path.validate(env) (planning/plan.hh:155-168): every consecutive edge in ONE batch call."""
+        return self.first_invalid_edge(waypoints, environment) < 0
+
+    def first_invalid_edge(self, waypoints, environment: Optional[Environment] = None, resolution: int = 0) -> int:
+        """Index of the edge at which Path::validate's loop returns false (planning/plan.hh:155-168), or -1."""
         w = self._configs(waypoints)
-        if w.shape[0] < 2:
-            return True
-        return bool(self.validate_motion_batch(w[:-1], w[1:], environment).all())
+        first = C.c_int64(-1)
+        _check(lib().vb_validate_path(self.ctx.handle, self.robot_id, _ptr(self.base), self._env(environment).handle,
+                                      _ptr(w), w.shape[0], resolution, C.byref(first)))
+        return int(first.value)
+
+    def shortcut_path(self, waypoints, environment: Optional[Environment] = None, resolution: int = 0) -> np.ndarray:
+        """planning::shortcut_path (planning/simplify.hh:115-140): the waypoints the reference's greedy scan keeps,
+        with all (n-1)(n-2)/2 candidate shortcuts validated in ONE batch call."""
+        w = self._configs(waypoints)
+        keep = np.ones(w.shape[0], dtype=np.uint8)
+        kept = C.c_size_t(0)
+        _check(lib().vb_shortcut_path(self.ctx.handle, self.robot_id, _ptr(self.base), self._env(environment).handle,
+                                      _ptr(w), w.shape[0], resolution, keep.ctypes.data_as(C.POINTER(C.c_uint8)),
+                                      C.byref(kept)))
+        assert int(keep.sum()) == kept.value
+        return w[keep.astype(bool)]
 
     # -- synthetic streams shared with the device-side generators ---------------------------------
     def random_configs(self, seed: int, first: int, n: int) -> np.ndarray:

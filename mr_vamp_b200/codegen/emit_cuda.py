@@ -540,7 +540,8 @@ def _geometry(n_slots: int, geom: dict, dim: int = 0) -> tuple[int, int]:
     per_warp = 3 * n_slots * 4 * 32 + queue + 4 * dim * 32  # columns + queues + staged configurations (vb_kernels.cuh)
     fixed = 3 * n_slots * 4 + 16 + 16  # stride padding, staging mbarrier
     best = (1, 1)
-    for ctas in (1, 2, 3, 4, 6, 8):
+    forced = int(os.environ.get("VB_FORCE_CTAS", "0"))  # development: A/B of the CTA geometry
+    for ctas in ((forced,) if forced else (1, 2, 3, 4, 6, 8)):
         # 228 KB per SM, 1 KB of it reserved per resident CTA
         w = min((228 * 1024 // ctas - 1024 - fixed) // per_warp, 16, 32 // ctas)
         if w >= 1 and w * ctas > best[0] * best[1]:
@@ -597,6 +598,9 @@ def emit_robot(ir: dict[str, Any]) -> str:
         if w2 * c2 >= warps * ctas:
             geom, warps, ctas, stage_cfg = smaller, w2, c2, True
             break
+    if os.environ.get("VB_FORCE_Q"):  # development: "env,self,pair" capacities, to exercise the overflow paths
+        e_, s_, p_ = (int(v) for v in os.environ["VB_FORCE_Q"].split(","))
+        geom = dict(geom, env_q=e_, self_q=s_, pair_q=p_)
     tab, ttype, _ = _tables(f"k_{robot}_tables", em, walk=True, stride=32 * warps + 1, const_row=const_row)
     out.extend(tab)
     if em_att:

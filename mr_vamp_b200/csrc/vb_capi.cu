@@ -1347,6 +1347,116 @@ int vb_fkcc_work_d(vb_ctx *ctx, int slot, vb_robot robot, const float *base, con
     return run_fkcc_d(q, configs_d, n, valid_bits_d, work_d, 2);
 }
 
+
+/* ---- batch edge callers ---------------------------------------------------- */
+// Path::validate (planning/plan.hh:155-168): every consecutive edge in one batch; the index of the first
+// invalid edge (the reference's loop stops there), or -1.
+int vb_validate_path(vb_ctx *ctx, vb_robot robot, const float *base, const vb_env *env, const float *waypoints, size_t n,
+                     int resolution, int64_t *first_invalid_edge)
+{
+    if (!ctx || !env || !first_invalid_edge || (n && !waypoints))
+    {
+        return fail(VB_ERR_ARG, "vb_validate_path: null argument");
+    }
+    const vb::RobotOps *ops = ops_of(robot);
+    if (!ops)
+    {
+        return fail(VB_ERR_ARG, "unknown robot id %d", static_cast<int>(robot));
+    }
+    *first_invalid_edge = -1;
+    if (n < 2)
+    {
+        return VB_OK;
+    }
+    const size_t edges = n - 1;
+    std::vector<uint32_t> bits((edges + 31) / 32);
+    VB_TRY(vb_validate_motion(ctx, robot, base, env, waypoints, waypoints + ops->dim, edges, resolution, bits.data(), nullptr));
+    for (size_t e = 0; e < edges; ++e)
+    {
+        if (!((bits[e >> 5] >> (e & 31)) & 1u))
+        {
+            *first_invalid_edge = static_cast<int64_t>(e);
+            break;
+        }
+    }
+    return VB_OK;
+}
+
+// planning::shortcut_path (planning/simplify.hh:115-140).  The reference scans i ascending, j descending and
+// calls validate_motion once per candidate; here ALL candidates (a, b > a + 1) of the original path are
+// validated in one batch and the same scan is replayed on the verdict matrix.  Erasing waypoints never
+// creates a new candidate pair, so the surviving waypoints are exactly the reference's.
+int vb_shortcut_path(vb_ctx *ctx, vb_robot robot, const float *base, const vb_env *env, const float *waypoints, size_t n,
+                     int resolution, uint8_t *keep, size_t *n_kept)
+{
+    if (!ctx || !env || (n && (!waypoints || !keep)))
+    {
+        return fail(VB_ERR_ARG, "vb_shortcut_path: null argument");
+    }
+    const vb::RobotOps *ops = ops_of(robot);
+    if (!ops)
+    {
+        return fail(VB_ERR_ARG, "unknown robot id %d", static_cast<int>(robot));
+    }
+    for (size_t i = 0; i < n; ++i)
+    {
+        keep[i] = 1;
+    }
+    if (n_kept)
+    {
+        *n_kept = n;
+    }
+    if (n < 3)
+    {
+        return VB_OK;
+    }
+    const size_t dim = static_cast<size_t>(ops->dim);
+    const size_t pairs = (n - 1) * (n - 2) / 2;
+    // pair (a, b), b >= a + 2, at index offset(a) + (b - a - 2), offset(a) = sum_{k<a} (n - 2 - k)
+    auto offset = [n](size_t a) { return a * (n - 2) - a * (a - 1) / 2; };
+    std::vector<float> starts(pairs * dim), goals(pairs * dim);
+    for (size_t a = 0; a + 2 < n; ++a)
+    {
+        for (size_t b = a + 2; b < n; ++b)
+        {
+            const size_t e = offset(a) + (b - a - 2);
+            std::copy(waypoints + a * dim, waypoints + (a + 1) * dim, starts.begin() + e * dim);
+            std::copy(waypoints + b * dim, waypoints + (b + 1) * dim, goals.begin() + e * dim);
+        }
+    }
+    std::vector<uint32_t> bits((pairs + 31) / 32);
+    VB_TRY(vb_validate_motion(ctx, robot, base, env, starts.data(), goals.data(), pairs, resolution, bits.data(), nullptr));
+    auto valid = [&](size_t a, size_t b) {
+        const size_t e = offset(a) + (b - a - 2);
+        return ((bits[e >> 5] >> (e & 31)) & 1u) != 0u;
+    };
+    std::vector<size_t> path(n);
+    for (size_t i = 0; i < n; ++i)
+    {
+        path[i] = i;
+    }
+    for (size_t i = 0; i + 2 < path.size(); ++i)
+    {
+        for (size_t j = path.size() - 1; j > i + 1; --j)
+        {
+            if (valid(path[i], path[j]))
+            {
+                for (size_t k = i + 1; k < j; ++k)
+                {
+                    keep[path[k]] = 0;
+                }
+                path.erase(path.begin() + static_cast<std::ptrdiff_t>(i) + 1, path.begin() + static_cast<std::ptrdiff_t>(j));
+                break;
+            }
+        }
+    }
+    if (n_kept)
+    {
+        *n_kept = path.size();
+    }
+    return VB_OK;
+}
+
 int vb_validate_motion_d(vb_ctx *ctx, int slot, vb_robot robot, const float *base, const vb_env *env,
                          const float *starts_d, const float *goals_d, size_t n, int resolution,
                          uint32_t *valid_bits_d, float *margin_d)
