@@ -9,7 +9,7 @@ GEN := $(PKG)/_gen
 OBJ := build/obj
 LIB := $(PKG)/lib/libvamp_b200.so
 ARCH := -gencode arch=compute_100a,code=sm_100a
-NVFLAGS := -std=c++17 -O3 $(ARCH) -lineinfo -Xcompiler -fPIC -Xptxas -v
+NVFLAGS := -std=c++17 -O3 -diag-suppress 177 $(ARCH) -lineinfo -Xcompiler -fPIC -Xptxas -v
 ROBOTS := sphere ur5 panda fetch baxter
 CSRC := $(PKG)/csrc
 HDRS := $(wildcard $(CSRC)/*.cuh) $(wildcard $(CSRC)/*.h) include/vamp_b200.h

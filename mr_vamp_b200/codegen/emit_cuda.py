@@ -57,6 +57,15 @@ def _f64(c: float) -> str:
 CONST_SLOT = 0x4000  # slot code of a configuration-independent centre: CONST_SLOT | index
 
 
+DERIVED_SLOT = 0x2000  # slot code of a centre that is NOT stored: DERIVED_SLOT | index into the derived table
+# Rigid-link reduction (plan_links) is a per-robot build decision, taken from measurements on B200 (MotionBenchMaker
+# table_pick scene 1, 33.5 M uniform configurations, Gcfg/s without -> with): panda 2.44 -> 2.92, ur5 3.02 -> 3.32,
+# fetch 0.73 -> 0.46 (its reduced links are on both sides of most of its 465 pair units; rebuilding them costs more
+# than the four extra resident warps give back), baxter: no link has more than four spheres.
+LINK_REDUCTION_OFF = {"fetch"}
+MIN_LINK_SPHERES = int(os.environ.get("VB_MIN_LINK_SPHERES", "5"))  # links with at least this many fine spheres keep <= 4 of them in shared memory
+
+
 def slot_offset(slot: int, stride: int, const_row: int) -> int:
     """Float offset of a slot's x coordinate from the warp's first column (y, z follow at +stride each).
     Regular slots add the lane; constant slots (offset >= 3 * const_row * stride) do not."""
@@ -69,7 +78,8 @@ def slot_offset(slot: int, stride: int, const_row: int) -> int:
 class _Emitter:
     """Lowers one traced function to (chain lines, check tables)."""
 
-    def __init__(self, fn: dict[str, Any], samples=None):
+    def __init__(self, fn: dict[str, Any], samples=None, reduce_links: bool = True):
+        self.reduce_links = reduce_links
         self.values = fn["values"]
         self.program = fn["program"]
         self.samples = samples  # (vals, n) from ir_eval, for the static containment slack
@@ -84,6 +94,11 @@ class _Emitter:
         self.att: list[dict[str, Any]] = []
         self.att_env = 0
         self.has_pose = False
+        # rigid-link reduction: key -> (basis spheres [4 argument lists], weights [4]); see plan_links
+        self.plan: dict[tuple, tuple[list, list[float]]] = {}
+        self.derived: list[dict[str, Any]] = []  # {"basis": [slot x 4], "w": [float x 4]}
+        self.link_weights: dict[tuple, tuple[list, list[float]]] = {}  # stored non-basis spheres of reduced links
+        self.slot_weights: dict[int, list[float]] = {}  # their slot -> weights over the link's basis
 
     # -- operands -----------------------------------------------------------------------------
     def opnd(self, o) -> str:
@@ -106,7 +121,11 @@ class _Emitter:
 
     def ref(self, s) -> tuple[int, int, float]:
         """Sphere argument list [x, y, z, r] -> (slot, base mask, radius); emits the put on first use."""
-        key = tuple((a["v"] if a["v"] is not None else ("c", a["c"])) for a in s[:3])
+        key = self.key(s)
+        if key not in self.slots and key in self.plan:
+            basis, wts = self.plan[key]
+            self.slots[key] = DERIVED_SLOT | len(self.derived)
+            self.derived.append({"basis": [self.ref(b)[0] for b in basis], "w": list(wts)})
         if key not in self.slots:
             xyz = [self.coord(a) for a in s[:3]]
             if all(a["v"] is None for a in s[:3]):
@@ -119,6 +138,8 @@ class _Emitter:
             else:
                 self.slots[key] = self.n_rows
                 self.n_rows += 1
+                if key in self.link_weights:
+                    self.slot_weights[self.slots[key]] = list(self.link_weights[key][1])
                 self.lines.append(f"p.put_s<kStride>({self.slots[key]}, {xyz[0]}, {xyz[1]}, {xyz[2]});")
         mask = sum((1 << i) for i, a in enumerate(s[:3]) if a.get("base"))
         for i, a in enumerate(s[:3]):
@@ -127,6 +148,87 @@ class _Emitter:
         radius = -1.0 if r.get("sym") == "radius" else float(r["c"])
         assert r.get("sym") == "radius" or r["v"] is None
         return (self.slots[key], mask, radius)
+
+    @staticmethod
+    def key(s) -> tuple:
+        return tuple((a["v"] if a["v"] is not None else ("c", a["c"])) for a in s[:3])
+
+    def plan_links(self):
+        """Rigid-link reduction of the shared-memory columns.  The fine spheres of one environment group sit on
+        one rigid link, so each centre is a constant affine combination of (at most) four of them.  For links
+        with >= MIN_LINK_SPHERES fine spheres only that basis is stored by the chain; the others are rebuilt
+        where a fired group needs them (<= 1e-6 m from the traced value, checked here over the sampled
+        configurations in float32), and their chain arithmetic becomes dead code.  Fewer slot rows = more
+        resident warps per SM, which is what bounds the fkcc kernels."""
+        if self.samples is None or not self.reduce_links:
+            return self
+        import numpy as np
+
+        vals, n = self.samples
+        # guard spheres are read by every configuration (straight-line guard phase): always stored
+        guards = set()
+        for it in self.program:
+            if it.get("k") in ("env", "attach_self"):
+                guards.add(self.key(it["guard"]))
+            elif it.get("k") == "self":
+                guards.add(self.key(it["guard"][0]))
+                guards.add(self.key(it["guard"][1]))
+        for it in self.program:
+            if it.get("k") != "env":
+                continue
+            fine = it["fine"]
+            if len(fine) < MIN_LINK_SPHERES or fine == [it["guard"]]:
+                continue
+            if any(all(a["v"] is None for a in s[:3]) for s in fine):
+                continue  # configuration-independent centres live in the constant rows
+            if len({tuple(a.get("base") for a in s[:3]) for s in fine}) != 1:
+                continue
+            C = [ir_eval.centre(vals, s, n) for s in fine]  # float64 copies of the float32 samples
+            # greedy basis on the first sample: farthest pair, then farthest from the line, then from the plane
+            P = np.stack([c[0] for c in C])
+            d = np.linalg.norm(P[:, None] - P[None], axis=2)
+            i0, i1 = np.unravel_index(np.argmax(d), d.shape)
+            basis = [int(i0), int(i1)]
+            for _ in range(2):
+                B = P[basis[1:]] - P[basis[0]]
+                Q, _ = np.linalg.qr(B.T)
+                R = (P - P[basis[0]]) - (P - P[basis[0]]) @ Q @ Q.T
+                dist = np.linalg.norm(R, axis=1)
+                k = int(np.argmax(dist))
+                if dist[k] < 5e-3:
+                    break
+                basis.append(k)
+            ok = True
+            plan = {}
+            m = min(n, 128)
+            lw = {}
+            for j, sj in enumerate(fine):
+                if j in basis:
+                    continue
+                # affine weights: c_j - c_b0 = sum_k w_k (c_bk - c_b0), stacked over the samples
+                A = np.concatenate([np.stack([C[b][t] - C[basis[0]][t] for b in basis[1:]], axis=1) for t in range(m)])
+                y = np.concatenate([C[j][t] - C[basis[0]][t] for t in range(m)])
+                wk, *_ = np.linalg.lstsq(A, y, rcond=None)
+                wts = [1.0 - float(wk.sum())] + [float(v) for v in wk]
+                wts32 = [np.float32(v) for v in wts]
+                rec = np.zeros((n, 3), np.float32)
+                for wv, b in zip(wts32, basis):
+                    rec = (rec + wv * C[b].astype(np.float32)).astype(np.float32)
+                err = float(np.abs(rec.astype(np.float64) - C[j]).max())
+                if err > 1e-6:
+                    ok = False
+                    break
+                while len(wts) < 4:
+                    wts.append(0.0)
+                entry = ([fine[b] for b in basis] + [fine[basis[0]]] * (4 - len(basis)), wts)
+                if self.key(sj) in guards:
+                    lw[self.key(sj)] = entry  # stays stored; the weights serve the b-side loop of the pair stage
+                else:
+                    plan[self.key(sj)] = entry
+            if ok:
+                self.plan.update(plan)
+                self.link_weights.update(lw)
+        return self
 
     def slack(self, fine_spheres, guard) -> float:
         """Largest overhang of the fine spheres beyond the guard sphere (+1e-4 m), or -1 if unknown."""
@@ -220,6 +322,7 @@ class _Emitter:
         raise ValueError(k)
 
     def run_checks(self):
+        self.plan_links()
         for it in self.program:
             if it["k"] == "val":
                 self.value(it["id"])
@@ -286,13 +389,48 @@ def _tables(name: str, em: _Emitter, walk: bool = False, stride: int = 0, const_
 
     F = np.float32
     units = []
+    # b-side lists of the pair stage, one copy per distinct list (the groups of one link share it): the pair
+    # stage is bound by the latency of these reads, and the L1 beside the slot columns is small
+    blist_at: dict[tuple, int] = {}
+    blist: list[tuple[int, float, list[float]]] = []  # (slot, radius, weights over the link's basis or None)
+
+    def b_list(g) -> int:
+        entries = [em.refs[g["b"][0] + j] for j in range(g["b"][1])]
+        key = tuple((sl, r) for sl, _, r in entries)
+        if key not in blist_at:
+            blist_at[key] = len(blist)
+            slots = [sl for sl, _, _ in entries]
+            der = [sl & (DERIVED_SLOT - 1) for sl in slots if sl & DERIVED_SLOT]
+            basis = em.derived[der[0]]["basis"] if der else None
+            for sl, _, r in entries:
+                wts = None
+                if basis is not None:
+                    if sl & DERIVED_SLOT:
+                        wts = em.derived[sl & (DERIVED_SLOT - 1)]["w"]
+                    elif sl in basis:
+                        wts = [1.0 if b == sl and basis.index(sl) == k else 0.0 for k, b in enumerate(basis)]
+                    else:
+                        wts = em.slot_weights[sl]
+                blist.append((sl, r, wts))
+        return blist_at[key]
+
     for gi, g in enumerate(em.selfg):
         g["unit0"] = len(units)
         for i in range(g["a"][1]):
             sa, _, ra = em.refs[g["a"][0] + i]
             sb, _, rb = g["gb"]
             filt = float(F(F(ra) + F(rb)) + F(g["slack"])) if g["slack"] >= 0 else -1.0
-            units.append((slot_offset(sa, stride, const_row), slot_offset(sb, stride, const_row), ra, filt, g["b"][0], g["b"][1]))
+            b_slots = [em.refs[g["b"][0] + j][0] for j in range(g["b"][1])]
+            b_der = [sl & (DERIVED_SLOT - 1) for sl in b_slots if sl & DERIVED_SLOT]
+            if b_der:
+                # every b_j sits on the link whose basis the derived ones share
+                bases = {tuple(em.derived[d]["basis"]) for d in b_der}
+                assert len(bases) == 1, g["name"]
+                assert all((sl & DERIVED_SLOT) or sl in em.derived[b_der[0]]["basis"] or sl in em.slot_weights for sl in b_slots), g["name"]
+            assert g["b"][1] < 64 and len(em.derived) < 511, g["name"]
+            pack = g["b"][1] | (((b_der[0] + 1) if b_der else 0) << 6) | ((1 << 15) if sa & DERIVED_SLOT else 0)
+            units.append(((sa & (DERIVED_SLOT - 1)) if sa & DERIVED_SLOT else slot_offset(sa, stride, const_row),
+                          slot_offset(sb, stride, const_row), ra, filt, b_list(g), pack))
     assert len(refs) < 2048 and len(units) < 2048, (name, len(refs), len(units))
     ne, ns, na, nr = len(em.env), len(em.selfg), len(em.att), len(refs)
     t = f"Tables<{max(ne, 1)}, {max(ns, 1)}, {max(na, 1)}, {max(nr, 1)}>"
@@ -316,7 +454,16 @@ def _tables(name: str, em: _Emitter, walk: bool = False, stride: int = 0, const_
         return ["    " + ", ".join(_ref(r) for r in rr[i : i + 6]) + "," for i in range(0, len(rr), 6)]
 
     rr = refs or [(0, 0, 0.0)]
-    out = [f"__constant__ {t} {name} = {{"]
+    # centres the chain does not store (plan_links): pre-multiplied basis offsets + weights
+    dd = em.derived or [{"basis": [0, 0, 0, 0], "w": [0.0, 0.0, 0.0, 0.0]}]
+    assert all(not (b & DERIVED_SLOT) for d in dd for b in d["basis"])
+    assert all(slot_offset(b, stride or 1, const_row) < 65536 for d in dd for b in d["basis"]), name
+    out = [f"__device__ const DerivedRec {name}_ders[{len(dd)}] = {{"]
+    for d in dd:
+        offs = ", ".join(str(slot_offset(b, stride, const_row)) for b in d["basis"])
+        out.append(f"    {{{{{offs}}}, {{{', '.join(_f32(v) for v in d['w'])}}}}},")
+    out.append("};")
+    out.append(f"__constant__ {t} {name} = {{")
     out.append(f"    {em.n_rows}, {ne}, {ns}, {na}, {em.att_env},")
     out.append("    {")
     out.extend("    " + r for r in env_rows())
@@ -356,9 +503,16 @@ def _tables(name: str, em: _Emitter, walk: bool = False, stride: int = 0, const_
             out.append("    " + ", ".join(f"{{{a}, {g}, {_f32(ra)}, {_f32(fr) if fr >= 0 else '-1.0f'}, {bb}, {bc}}}"
                                           for a, g, ra, fr, bb, bc in uu[i : i + 4]) + ",")
         out.append("};")
-        out.append(f"__device__ const BRef {name}_brefs[{len(rr)}] = {{")
-        for i in range(0, len(rr), 8):
-            out.append("    " + ", ".join(f"{{{slot_offset(sl, stride, const_row)}, {_f32(r) if r >= 0 else '-1.0f'}}}" for sl, _, r in rr[i : i + 8]) + ",")
+        bl = blist or [(0, 0.0, None)]
+        out.append(f"__device__ const BRef {name}_brefs[{len(bl)}] = {{")
+        for i in range(0, len(bl), 8):
+            out.append("    " + ", ".join(f"{{{0 if sl & DERIVED_SLOT else slot_offset(sl, stride, const_row)}, {_f32(r) if r >= 0 else '-1.0f'}}}" for sl, r, _ in bl[i : i + 8]) + ",")
+        out.append("};")
+        # b-side spheres of reduced links as weights over the link's basis (stored basis spheres: one-hot)
+        bw_rows = [f"{{{{{', '.join(_f32(v) for v in (wts or [0.0, 0.0, 0.0, 0.0]))}}}, {_f32(r) if r >= 0 else '-1.0f'}, 0u}}" for _, r, wts in bl]
+        out.append(f"__device__ const BWeights {name}_bws[{len(bl)}] = {{")
+        for i in range(0, len(bw_rows), 4):
+            out.append("    " + ", ".join(bw_rows[i : i + 4]) + ",")
         out.append("};")
         max_u = max([g["ucount"] for g in em.env] or [1])
         max_a = max([g["a"][1] for g in em.selfg if not g.get("dense")] or [1])
@@ -407,6 +561,15 @@ def _uniform(em: _Emitter) -> list[str]:
         def need(slot: int):
             if slot not in loaded:
                 loaded.add(slot)
+                if slot & DERIVED_SLOT:
+                    d = em.derived[slot & (DERIVED_SLOT - 1)]
+                    terms = [(wv, b) for wv, b in zip(d["w"], d["basis"]) if wv != 0.0]
+                    for _, b in terms:
+                        need(b)
+                    for c in "xyz":
+                        expr = " + ".join(f"{_f32(wv)} * s{b}{c}" for wv, b in terms)
+                        body.append(f"const float s{slot}{c} = {expr};")
+                    return
                 if slot & CONST_SLOT:
                     x, y, z = em.const_xyz[slot]
                     body.append(f"const float s{slot}x = {x}, s{slot}y = {y}, s{slot}z = {z};")
@@ -493,6 +656,7 @@ def _uniform(em: _Emitter) -> list[str]:
         w(f"        uint32_t i{wi} = 0u;")
     for gi, g in enumerate(em.env):
         slot, mask, r = g["guard"]
+        assert not (slot & DERIVED_SLOT), g["name"]
         xyz = []
         for c in range(3):
             e = em.const_xyz[slot][c] if slot & CONST_SLOT else f"col[{3 * slot + c} * kStride]"
@@ -565,8 +729,10 @@ def emit_robot(ir: dict[str, Any]) -> str:
         q = (lo + rng.random((n, dim)) * rg).astype(np.float32)
         return ir_eval.evaluate(fn, q), n
 
-    em = _Emitter(fns["interleaved_sphere_fk"], sampled(fns["interleaved_sphere_fk"])).run_checks()
-    em_att = _Emitter(fns["interleaved_sphere_fk_attachment"]).run_checks() if has_attach else None
+    reduce_links = robot not in LINK_REDUCTION_OFF
+    em = _Emitter(fns["interleaved_sphere_fk"], sampled(fns["interleaved_sphere_fk"]), reduce_links).run_checks()
+    em_att = (_Emitter(fns["interleaved_sphere_fk_attachment"], sampled(fns["interleaved_sphere_fk_attachment"]), reduce_links).run_checks()
+              if has_attach else None)
     # self groups decided by a two-joint table are rare work for the walk, whatever their guard's fire rate
     ptabs = pair_tables.build(ir, fns["interleaved_sphere_fk"])
     for t in ptabs:
@@ -604,7 +770,7 @@ def emit_robot(ir: dict[str, Any]) -> str:
     tab, ttype, _ = _tables(f"k_{robot}_tables", em, walk=True, stride=32 * warps + 1, const_row=const_row)
     out.extend(tab)
     if em_att:
-        tab2, ttype2, _ = _tables(f"k_{robot}_tables_attach", em_att, const_row=const_row)
+        tab2, ttype2, _ = _tables(f"k_{robot}_tables_attach", em_att, stride=32 * warps + 1, const_row=const_row)
         out.extend(tab2)
     pt_head, pt_body = pair_tables.emit(robot, ir, ptabs, max((len(em.selfg) + 31) // 32, 1))
     out.extend(pt_head)
@@ -629,8 +795,11 @@ def emit_robot(ir: dict[str, Any]) -> str:
     w(f"    __device__ __forceinline__ static const TablesT &tables() {{ return k_{robot}_tables; }}")
     w("    __device__ __forceinline__ static WalkTables walk_tables()")
     w("    {")
-    w(f"        return WalkTables{{k_{robot}_tables_grefs, k_{robot}_tables_ref_group, k_{robot}_tables_genv, k_{robot}_tables_gself, k_{robot}_tables_units, k_{robot}_tables_brefs}};")
+    w(f"        return WalkTables{{k_{robot}_tables_grefs, k_{robot}_tables_ref_group, k_{robot}_tables_genv, k_{robot}_tables_gself, k_{robot}_tables_units, k_{robot}_tables_brefs, k_{robot}_tables_ders, k_{robot}_tables_bws}};")
     w("    }")
+    w(f"    __device__ __forceinline__ static const DerivedRec *ders() {{ return k_{robot}_tables_ders; }}")
+    w(f"    __device__ __forceinline__ static const DerivedRec *ders_attach() {{ return k_{robot}_tables{'_attach' if em_att else ''}_ders; }}")
+    w(f"    static constexpr int kDerived = {len(em.derived)};  // centres rebuilt from their link's basis instead of stored")
     if em_att:
         w(f"    using TablesAttachT = {ttype2};")
         w(f"    __device__ __forceinline__ static const TablesAttachT &tables_attach() {{ return k_{robot}_tables_attach; }}")

@@ -105,13 +105,32 @@ namespace vb
         const EnvView &env;
         Scratch sc;
         float bx, by, bz, radius;
+        const DerivedRec *ders;  // centres rebuilt from their link's basis (vb_tables.cuh)
         VB_D Center load(const SlotRef &ref) const
         {
             Center c;
-            const float *col = shm_f32() + slot_index<kStride, kConstRow>(sc.col & ~31u, sc.col & 31u, ref.slot);
-            c.x = col[0];
-            c.y = col[kStride];
-            c.z = col[2 * kStride];
+            if (ref.slot & kDerivedSlot)
+            {
+                const DerivedRec d = ldg_record(ders + (ref.slot & (kDerivedSlot - 1u)));
+                c.x = c.y = c.z = 0.f;
+                constexpr unsigned kConstOff = 3u * kConstRow * kStride;
+#pragma unroll
+                for (int k = 0; k < 4; ++k)
+                {
+                    const unsigned off = d.off[k];
+                    const float *col = shm_f32() + (sc.col & ~31u) + off + (off >= kConstOff ? 0u : (sc.col & 31u));
+                    c.x += d.w[k] * col[0];
+                    c.y += d.w[k] * col[kStride];
+                    c.z += d.w[k] * col[2 * kStride];
+                }
+            }
+            else
+            {
+                const float *col = shm_f32() + slot_index<kStride, kConstRow>(sc.col & ~31u, sc.col & 31u, ref.slot);
+                c.x = col[0];
+                c.y = col[kStride];
+                c.z = col[2 * kStride];
+            }
             if (ref.base & 1)
             {
                 c.x += bx;
@@ -247,12 +266,14 @@ namespace vb
     VB_D bool check_config(const LaunchArgs &a, const Scratch &sc, const float *q, bool attach, M &mg)
     {
         SlotSink sink{sc.col, sc.stride, &a.env.attach, sc.att_col, sc.att_stride};
-        const TableCtx<Robot::kStride, Robot::kConstRow> ctx{a.env, sc, a.base[0], a.base[1], a.base[2], a.sphere_radius};
         if (Robot::kHasAttach && attach)
         {
+            const TableCtx<Robot::kStride, Robot::kConstRow> ctx{a.env, sc, a.base[0], a.base[1], a.base[2], a.sphere_radius,
+                                                                 Robot::ders_attach()};
             Robot::chain_attach(sink, q);
             return walk_tables(Robot::tables_attach(), ctx, mg);
         }
+        const TableCtx<Robot::kStride, Robot::kConstRow> ctx{a.env, sc, a.base[0], a.base[1], a.base[2], a.sphere_radius, Robot::ders()};
         Robot::chain(sink, q);
         return walk_tables(Robot::tables(), ctx, mg);
     }

@@ -10,6 +10,17 @@ namespace vb
     // slot code of a configuration-independent centre: kConstSlot | j (codegen/emit_cuda.py: CONST_SLOT)
     constexpr unsigned kConstSlot = 0x4000u;
 
+    // slot code of a centre the chain does not store: kDerivedSlot | index into the DerivedRec table.  Such a
+    // centre is a constant affine combination of <= 4 stored centres of the same rigid link (codegen/emit_cuda.py:
+    // plan_links); it is rebuilt where a fired group needs it.
+    constexpr unsigned kDerivedSlot = 0x2000u;
+
+    struct alignas(8) DerivedRec
+    {
+        uint16_t off[4];  // pre-multiplied column offsets of the link's basis centres (as SelfUnit::a_off)
+        float w[4];       // weights, sum 1; unused entries 0 (their offset repeats off[0])
+    };
+
     struct alignas(8) SlotRef
     {
         uint16_t slot;  // sphere-centre slot written by the chain (or kConstSlot | j)
@@ -56,8 +67,21 @@ namespace vb
         uint16_t gb_off;   // column offset of the other link's bounding sphere
         float a_r;         // radius of a_i
         float filter_r;    // a_r + r(gb) + slack_b, or < 0: no containment bound (always passes)
-        uint16_t b_begin;  // the other link's fine spheres: brefs[b_begin .. b_begin + b_count)
-        uint16_t b_count;
+        uint16_t b_begin;  // the other link's fine spheres: brefs[b_begin .. b_begin + b_count()) (bws[] for a reduced link)
+        uint16_t b_pack;   // bits 0-5: b count; bits 6-14: 1 + index of a DerivedRec whose off[] is the b-link's basis
+                           // (0: every b_j is stored); bit 15: a_i is not stored, a_off is the index of its DerivedRec
+        __host__ __device__ int b_count() const { return b_pack & 63; }
+        __host__ __device__ int b_basis() const { return ((b_pack >> 6) & 511) - 1; }
+        __host__ __device__ bool a_derived() const { return (b_pack >> 15) != 0; }
+    };
+    static_assert(sizeof(SelfUnit) == 16, "SelfUnit is read as one 16-byte load");
+
+    // b-side sphere of a reduced link: weights over the link's basis + radius
+    struct alignas(8) BWeights
+    {
+        float w[4];
+        float r;
+        uint32_t pad_;
     };
 
     // b-side sphere of a self group: pre-multiplied column offset + radius
@@ -127,5 +151,7 @@ namespace vb
         const SelfGroup *self;
         const SelfUnit *units;
         const BRef *brefs;  // refs as (column offset, radius)
+        const DerivedRec *ders;
+        const BWeights *bws;  // refs of reduced links as (basis weights, radius)
     };
 }  // namespace vb

@@ -115,13 +115,37 @@ namespace vb
 
         VB_D static Center centre(const WalkCtx &c, int L, const SlotRef &ref)
         {
-            const float *col = shm_f32() + slot_index<S, Robot::kConstRow>(c.wcol, L, ref.slot);
             Center s;
-            s.x = col[0] + ((ref.base & 1) ? c.bx : 0.f);
-            s.y = col[S] + ((ref.base & 2) ? c.by : 0.f);
-            s.z = col[2 * S] + ((ref.base & 4) ? c.bz : 0.f);
+            if (Robot::kDerived > 0 && (ref.slot & kDerivedSlot))
+            {
+                derived(c, L, ldg_record(Robot::ders() + (ref.slot & (kDerivedSlot - 1u))), s.x, s.y, s.z);
+            }
+            else
+            {
+                const float *col = shm_f32() + slot_index<S, Robot::kConstRow>(c.wcol, L, ref.slot);
+                s.x = col[0];
+                s.y = col[S];
+                s.z = col[2 * S];
+            }
+            s.x += (ref.base & 1) ? c.bx : 0.f;
+            s.y += (ref.base & 2) ? c.by : 0.f;
+            s.z += (ref.base & 4) ? c.bz : 0.f;
             s.r = ref.r < 0.f ? c.radius : ref.r;
             return s;
+        }
+
+        // centre rebuilt from its link's basis (vb_tables.cuh: DerivedRec)
+        VB_D static void derived(const WalkCtx &c, int L, const DerivedRec &d, float &x, float &y, float &z)
+        {
+            float bx[4], by[4], bz[4];
+#pragma unroll
+            for (int k = 0; k < 4; ++k)
+            {
+                at(c, L, d.off[k], bx[k], by[k], bz[k]);
+            }
+            x = d.w[0] * bx[0] + d.w[1] * bx[1] + d.w[2] * bx[2] + d.w[3] * bx[3];
+            y = d.w[0] * by[0] + d.w[1] * by[1] + d.w[2] * by[2] + d.w[3] * by[3];
+            z = d.w[0] * bz[0] + d.w[1] * bz[1] + d.w[2] * bz[2] + d.w[3] * bz[3];
         }
 
         // pre-multiplied offset (SelfUnit / BRef): per-thread slots add the lane, per-warp constants do not
@@ -137,10 +161,40 @@ namespace vb
         VB_D static bool pair_unit(const WalkCtx &c, const WalkTables &w, int L, const SelfUnit &u)
         {
             float ax, ay, az;
-            at(c, L, u.a_off, ax, ay, az);
-            const BRef *B = w.brefs + u.b_begin;
-            const int bc = u.b_count;
+            if (Robot::kDerived > 0 && u.a_derived())
+            {
+                derived(c, L, ldg_record(w.ders + u.a_off), ax, ay, az);
+            }
+            else
+            {
+                at(c, L, u.a_off, ax, ay, az);
+            }
+            const int bc = u.b_count();
             bool hit = false;
+            if (Robot::kDerived > 0 && u.b_basis() >= 0)
+            {
+                // reduced b-link: its basis once, then every b_j from its weights (no shared-memory access in the loop)
+                const DerivedRec bd = ldg_record(w.ders + u.b_basis());
+                float px[4], py[4], pz[4];
+#pragma unroll
+                for (int k = 0; k < 4; ++k)
+                {
+                    at(c, L, bd.off[k], px[k], py[k], pz[k]);
+                }
+                const BWeights *B = w.bws + u.b_begin;
+#pragma unroll 2
+                for (int j = 0; j < bc; ++j)
+                {
+                    const BWeights bw = ldg_record(B + j);
+                    const float bx = bw.w[0] * px[0] + bw.w[1] * px[1] + bw.w[2] * px[2] + bw.w[3] * px[3];
+                    const float by = bw.w[0] * py[0] + bw.w[1] * py[1] + bw.w[2] * py[2] + bw.w[3] * py[3];
+                    const float bz = bw.w[0] * pz[0] + bw.w[1] * pz[1] + bw.w[2] * pz[2] + bw.w[3] * pz[3];
+                    const float dx = ax - bx, dy = ay - by, dz = az - bz, rs = u.a_r + bw.r;
+                    hit = hit || (dx * dx + dy * dy + dz * dz - rs * rs < 0.f);
+                }
+                return hit;
+            }
+            const BRef *B = w.brefs + u.b_begin;
 #pragma unroll 4
             for (int j = 0; j < bc; ++j)
             {
