@@ -516,7 +516,10 @@ def _tables(name: str, em: _Emitter, walk: bool = False, stride: int = 0, const_
         out.append("};")
         max_u = max([g["ucount"] for g in em.env] or [1])
         max_a = max([g["a"][1] for g in em.selfg if not g.get("dense")] or [1])
-        geom = {"env_q": 256, "self_q": 256, "pair_q": 256, "env_groups": max(ne, 1)}
+        geom = {"env_q": 256, "self_q": 256, "pair_q": 256, "env_groups": max(ne, 1),
+                # records of the warp walk that may live in shared memory (vb_walk.cuh: WT): (name, count, bytes each)
+                "tab": [("Units", len(uu), 16), ("Brefs", len(bl), 8), ("Bws", len(bl), 24), ("Ders", len(dd), 24),
+                        ("Env", max(ne, 1), 24), ("Refs", len(rr), 8), ("RefGroup", len(rg), 2)]}
     return out, t, geom
 
 
@@ -767,8 +770,17 @@ def emit_robot(ir: dict[str, Any]) -> str:
     if os.environ.get("VB_FORCE_Q"):  # development: "env,self,pair" capacities, to exercise the overflow paths
         e_, s_, p_ = (int(v) for v in os.environ["VB_FORCE_Q"].split(","))
         geom = dict(geom, env_q=e_, self_q=s_, pair_q=p_)
-    tab, ttype, _ = _tables(f"k_{robot}_tables", em, walk=True, stride=32 * warps + 1, const_row=const_row)
+    tab, ttype, tgeom = _tables(f"k_{robot}_tables", em, walk=True, stride=32 * warps + 1, const_row=const_row)
     out.extend(tab)
+    # check tables behind the staged configurations when the window has room for them (no resident warp is given up)
+    tab_off, tab_lines = 0, []
+    for tname, cnt, size in tgeom["tab"]:
+        tab_lines.append(f"    static constexpr unsigned kTab{tname} = {tab_off}, kTab{tname}Bytes = {cnt * size};")
+        tab_off = (tab_off + cnt * size + 15) & ~15
+    stride_ = 32 * warps + 1
+    used = 4 * ((3 * n_slots * stride_ + 3) & ~3) + warps * _queue_bytes(geom) + ((32 * warps * dim * 4 + 16) if stage_cfg else 0)
+    used = (used + 15) & ~15
+    tables_in_shared = used + tab_off <= 228 * 1024 // ctas - 1024
     if em_att:
         tab2, ttype2, _ = _tables(f"k_{robot}_tables_attach", em_att, stride=32 * warps + 1, const_row=const_row)
         out.extend(tab2)
@@ -784,6 +796,10 @@ def emit_robot(ir: dict[str, Any]) -> str:
     w(f"    static constexpr int kSlots = {n_slots};  // shared-memory slot rows: {const_row} per-thread + {n_slots - const_row} of per-warp constants")
     w(f"    static constexpr int kConstRow = {const_row};  // first constant row ({n_const} configuration-independent centres)")
     w(f"    static constexpr int kBlock = {32 * warps};  // threads per CTA: {warps} warps x {ctas} CTA(s) per SM fill the shared memory")
+    w(f"    static constexpr bool kTablesInShared = {'true' if tables_in_shared else 'false'};  // check tables of the warp walk in shared memory ({tab_off} bytes)")
+    w(f"    static constexpr unsigned kTabBytes = {tab_off};")
+    for ln in tab_lines:
+        w(ln)
     w(f"    static constexpr int kCtasPerSm = {ctas};  // resident CTAs per SM (second argument of __launch_bounds__)")
     w("    static constexpr int kStride = kBlock + 1;  // slot-column stride in floats (odd: conflict free)")
     w(f"    static constexpr bool kStageCfg = {'true' if stage_cfg else 'false'};  // configurations staged in shared memory by bulk copy")

@@ -62,14 +62,6 @@ namespace vb
         return Robot::kBlock;
     }
 
-    // bytes of the per-warp work queues of the warp walk (vb_walk.cuh)
-    template <class Robot>
-    __host__ __device__ constexpr int queue_bytes()
-    {
-        return 2 * ((Robot::kEnvQ > Robot::kSelfQ ? Robot::kEnvQ : Robot::kSelfQ) + Robot::kPairQ) +
-               128 * (Robot::kEnvGroups > 0 ? Robot::kEnvGroups : 1) + 16;
-    }
-
     // Shared memory is addressed by INDEX from the start of the dynamic window (see vb_walk.cuh: the compiler
     // then emits LDS/STS instead of generic accesses).
     struct Scratch
@@ -95,6 +87,11 @@ namespace vb
         // 16-byte aligned start of the queues
         const unsigned slot_floats = (3u * Robot::kSlots * Robot::kStride + 3u) & ~3u;
         s.queues = with_queues ? 4u * slot_floats + (threadIdx.x >> 5) * queue_bytes<Robot>() : 0u;
+        if (with_queues)
+        {
+            WT<Robot>::stage();  // check tables of the warp walk into shared memory (when the generator found room)
+            __syncthreads();
+        }
         return s;
     }
 
@@ -339,11 +336,6 @@ namespace vb
     // copy (cp.async.bulk, completion on an mbarrier) of the CTA's next kBlock configurations (contiguous,
     // kBlock * 4 * dim bytes) right after the previous ones were consumed; a full walk later they are in
     // shared memory.
-    template <class Robot>
-    __host__ __device__ constexpr unsigned cfg_stage_bytes()
-    {
-        return Robot::kStageCfg ? static_cast<unsigned>(Robot::kBlock) * Robot::kDim * 4u + 16u : 0u;  // + the mbarrier
-    }
     VB_D uint32_t shm_addr(unsigned byte_offset)
     {
         extern __shared__ float4 vb_shared_window[];
@@ -387,8 +379,7 @@ namespace vb
         const size_t n_round = (a.n + 31) / 32 * 32;
         // configuration staging (verdict mode): [slot columns][queues][kBlock x dim floats][mbarrier]
         constexpr unsigned kCfgBytes = static_cast<unsigned>(Robot::kBlock) * Robot::kDim * 4u;
-        const unsigned stage_off = 4u * ((3u * Robot::kSlots * Robot::kStride + 3u) & ~3u) +
-                                   static_cast<unsigned>(Robot::kBlock / 32) * queue_bytes<Robot>();
+        constexpr unsigned stage_off = cfg_stage_offset<Robot>();
         const bool staged = kMode == 0 && kStageAllowed && Robot::kStageCfg && kCfgBytes % 16u == 0u && (reinterpret_cast<uintptr_t>(a.cfg) & 15u) == 0u;
         const uint32_t stage_buf = shm_addr(stage_off), stage_bar = stage_buf + kCfgBytes;
         uint32_t stage_parity = 0u;

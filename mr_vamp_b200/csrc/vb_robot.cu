@@ -14,8 +14,7 @@ namespace vb
     {
         (void)a;
         const size_t slot_floats = (static_cast<size_t>(3 * R::kSlots * R::kStride) + 3) & ~static_cast<size_t>(3);
-        return sizeof(float) * slot_floats +
-               (queues ? static_cast<size_t>(kBlock / 32) * queue_bytes<R>() + cfg_stage_bytes<R>() : 0);
+        return queues ? static_cast<size_t>(walk_smem_bytes<R>()) : sizeof(float) * slot_floats;
     }
 
     template <class K>

@@ -88,9 +88,129 @@ namespace vb
         bool octet;
     };
 
+    // ---- layout of the dynamic shared-memory window (bytes) -------------------------------------------------
+    //   [3 * kSlots rows of kStride floats: one column per thread][per-warp work queues][staged configurations +
+    //   mbarrier][check tables]
+    template <class Robot>
+    __host__ __device__ constexpr int queue_bytes()
+    {
+        return 2 * ((Robot::kEnvQ > Robot::kSelfQ ? Robot::kEnvQ : Robot::kSelfQ) + Robot::kPairQ) +
+               128 * (Robot::kEnvGroups > 0 ? Robot::kEnvGroups : 1) + 16;
+    }
+    template <class Robot>
+    __host__ __device__ constexpr unsigned cfg_stage_bytes()
+    {
+        return Robot::kStageCfg ? static_cast<unsigned>(Robot::kBlock) * Robot::kDim * 4u + 16u : 0u;  // + the mbarrier
+    }
+    template <class Robot>
+    __host__ __device__ constexpr unsigned cfg_stage_offset()
+    {
+        return 4u * ((3u * Robot::kSlots * Robot::kStride + 3u) & ~3u) + static_cast<unsigned>(Robot::kBlock / 32) * queue_bytes<Robot>();
+    }
+    template <class Robot>
+    __host__ __device__ constexpr unsigned tab_base()
+    {
+        return (cfg_stage_offset<Robot>() + cfg_stage_bytes<Robot>() + 15u) & ~15u;
+    }
+    template <class Robot>
+    __host__ __device__ constexpr unsigned walk_smem_bytes()
+    {
+        return tab_base<Robot>() + (Robot::kTablesInShared ? static_cast<unsigned>(Robot::kTabBytes) : 0u);
+    }
+
+    // Check-table records of the warp walk.  Robot::kTablesInShared: the code generator found room for them behind
+    // the slot columns (Robot::stage_tables() copies them in at kernel start) and they are read with LDS at fixed
+    // window offsets; otherwise through the non-coherent global path.  The unit stages are chains of dependent table
+    // reads, and the L1 left beside ~220 KB of shared memory is small.
+    template <class Robot>
+    struct WT
+    {
+        template <class T>
+        VB_D static T get(const T *global, unsigned window_bytes, unsigned i)
+        {
+            if constexpr (Robot::kTablesInShared)
+            {
+                extern __shared__ float4 vb_shared_window[];
+                const T *base = reinterpret_cast<const T *>(reinterpret_cast<const unsigned char *>(vb_shared_window) + tab_base<Robot>() + window_bytes);
+                T out;
+                if constexpr (sizeof(T) % 16 == 0 && alignof(T) >= 16)
+                {
+                    const uint4 *src = reinterpret_cast<const uint4 *>(base + i);
+                    uint4 *dst = reinterpret_cast<uint4 *>(&out);
+#pragma unroll
+                    for (unsigned k = 0; k < sizeof(T) / 16; ++k)
+                    {
+                        dst[k] = src[k];
+                    }
+                }
+                else if constexpr (sizeof(T) % 8 == 0)
+                {
+                    const uint2 *src = reinterpret_cast<const uint2 *>(base + i);
+                    uint2 *dst = reinterpret_cast<uint2 *>(&out);
+#pragma unroll
+                    for (unsigned k = 0; k < sizeof(T) / 8; ++k)
+                    {
+                        dst[k] = src[k];
+                    }
+                }
+                else
+                {
+                    out = base[i];
+                }
+                return out;
+            }
+            else
+            {
+                if constexpr (sizeof(T) % 8 == 0)
+                {
+                    return ldg_record(global + i);
+                }
+                else
+                {
+                    return __ldg(global + i);
+                }
+            }
+        }
+        // all threads of the CTA: copy the tables behind the staged configurations (caller synchronises)
+        VB_D static void stage()
+        {
+            if constexpr (Robot::kTablesInShared)
+            {
+                extern __shared__ float4 vb_shared_window[];
+                unsigned char *base = reinterpret_cast<unsigned char *>(vb_shared_window) + tab_base<Robot>();
+                const WalkTables w = Robot::walk_tables();
+                copy(base + Robot::kTabUnits, w.units, Robot::kTabUnitsBytes);
+                copy(base + Robot::kTabBrefs, w.brefs, Robot::kTabBrefsBytes);
+                copy(base + Robot::kTabBws, w.bws, Robot::kTabBwsBytes);
+                copy(base + Robot::kTabDers, w.ders, Robot::kTabDersBytes);
+                copy(base + Robot::kTabEnv, w.env, Robot::kTabEnvBytes);
+                copy(base + Robot::kTabRefs, w.refs, Robot::kTabRefsBytes);
+                copy(base + Robot::kTabRefGroup, w.ref_group, Robot::kTabRefGroupBytes);
+            }
+        }
+        // tables are arrays of 2-byte-multiple records at 16-byte aligned window offsets
+        VB_D static void copy(unsigned char *dst, const void *src, unsigned bytes)
+        {
+            const uint16_t *s16 = static_cast<const uint16_t *>(src);
+            uint16_t *d16 = reinterpret_cast<uint16_t *>(dst);
+            for (unsigned i = threadIdx.x; i < bytes / 2u; i += blockDim.x)
+            {
+                d16[i] = __ldg(s16 + i);
+            }
+        }
+        VB_D static SelfUnit unit(unsigned i) { return get(Robot::walk_tables().units, Robot::kTabUnits, i); }
+        VB_D static BRef bref(unsigned i) { return get(Robot::walk_tables().brefs, Robot::kTabBrefs, i); }
+        VB_D static BWeights bw(unsigned i) { return get(Robot::walk_tables().bws, Robot::kTabBws, i); }
+        VB_D static DerivedRec der(unsigned i) { return get(Robot::walk_tables().ders, Robot::kTabDers, i); }
+        VB_D static RefGroup env(unsigned g) { return get(Robot::walk_tables().env, Robot::kTabEnv, g); }
+        VB_D static SlotRef ref(unsigned i) { return get(Robot::walk_tables().refs, Robot::kTabRefs, i); }
+        VB_D static uint16_t ref_group(unsigned i) { return get(Robot::walk_tables().ref_group, Robot::kTabRefGroup, i); }
+    };
+
     template <class Robot>
     struct Walk
     {
+        using T = WT<Robot>;
         static constexpr int S = Robot::kStride;
         static constexpr unsigned kGroups = Robot::kEnvGroups > 0 ? Robot::kEnvGroups : 1;
 
@@ -118,7 +238,7 @@ namespace vb
             Center s;
             if (Robot::kDerived > 0 && (ref.slot & kDerivedSlot))
             {
-                derived(c, L, ldg_record(Robot::ders() + (ref.slot & (kDerivedSlot - 1u))), s.x, s.y, s.z);
+                derived(c, L, T::der(ref.slot & (kDerivedSlot - 1u)), s.x, s.y, s.z);
             }
             else
             {
@@ -163,7 +283,7 @@ namespace vb
             float ax, ay, az;
             if (Robot::kDerived > 0 && u.a_derived())
             {
-                derived(c, L, ldg_record(w.ders + u.a_off), ax, ay, az);
+                derived(c, L, T::der(u.a_off), ax, ay, az);
             }
             else
             {
@@ -174,18 +294,17 @@ namespace vb
             if (Robot::kDerived > 0 && u.b_basis() >= 0)
             {
                 // reduced b-link: its basis once, then every b_j from its weights (no shared-memory access in the loop)
-                const DerivedRec bd = ldg_record(w.ders + u.b_basis());
+                const DerivedRec bd = T::der(u.b_basis());
                 float px[4], py[4], pz[4];
 #pragma unroll
                 for (int k = 0; k < 4; ++k)
                 {
                     at(c, L, bd.off[k], px[k], py[k], pz[k]);
                 }
-                const BWeights *B = w.bws + u.b_begin;
 #pragma unroll 2
                 for (int j = 0; j < bc; ++j)
                 {
-                    const BWeights bw = ldg_record(B + j);
+                    const BWeights bw = T::bw(u.b_begin + j);
                     const float bx = bw.w[0] * px[0] + bw.w[1] * px[1] + bw.w[2] * px[2] + bw.w[3] * px[3];
                     const float by = bw.w[0] * py[0] + bw.w[1] * py[1] + bw.w[2] * py[2] + bw.w[3] * py[3];
                     const float bz = bw.w[0] * pz[0] + bw.w[1] * pz[1] + bw.w[2] * pz[2] + bw.w[3] * pz[3];
@@ -194,11 +313,10 @@ namespace vb
                 }
                 return hit;
             }
-            const BRef *B = w.brefs + u.b_begin;
 #pragma unroll 4
             for (int j = 0; j < bc; ++j)
             {
-                const BRef br = ldg_record(B + j);
+                const BRef br = T::bref(u.b_begin + j);
                 float bx, by, bz;
                 at(c, L, br.off, bx, by, bz);
                 const float dx = ax - bx, dy = ay - by, dz = az - bz, rs = u.a_r + br.r;
@@ -219,7 +337,7 @@ namespace vb
                 {
                     const unsigned code = pairq(c)[i];
                     const int L = code & 31;
-                    const SelfUnit u = ldg_record(w.units + (code >> 5));
+                    const SelfUnit u = T::unit(code >> 5);
                     if (!done(c, L) && pair_unit(c, w, L, u))
                     {
                         atomicOr(cmask(c), 1u << L);
@@ -281,7 +399,7 @@ namespace vb
                 {
                     const int b = __ffs(m) - 1;
                     m &= m - 1u;
-                    hit = pair_unit(c, w, lane, ldg_record(w.units + wi * 32 + b));
+                    hit = pair_unit(c, w, lane, T::unit(wi * 32 + b));
                 }
             }
             if (hit)
@@ -294,11 +412,11 @@ namespace vb
         // one fine sphere refs[idx] of configuration L against the tight candidates of its group
         VB_D static bool fine_unit(const WalkCtx &c, const WalkTables &w, const PrimIndex &ix, int L, int idx)
         {
-            const int g = __ldg(w.ref_group + idx) & 0x7fff;
+            const int g = T::ref_group(idx) & 0x7fff;
             uint32_t tight = gmask(c)[32 * g + L];
             const bool thigh = (tight >> 31) != 0u;
             tight &= 0x7fffffffu;
-            const Center s = centre(c, L, ldg_record(w.refs + idx));
+            const Center s = centre(c, L, T::ref(idx));
             bool hit = false;
             int cur = 0;
             for (int o = next_candidate(tight, thigh, ix.first[5], cur); o >= 0 && !hit;
@@ -360,7 +478,7 @@ namespace vb
                     const int L = code & 31, g = code >> 5;
                     if (!done(c, L))
                     {
-                        const RefGroup Gr = ldg_record(w.env + g);
+                        const RefGroup Gr = T::env(g);
                         const RefGroup *G = &Gr;
                         const int u0 = G->ubegin, uc = G->ucount;
                         bool hit = false;
@@ -414,7 +532,7 @@ namespace vb
                             NoMargin mg;
                             for (int k = 0; k < uc && !hit; ++k)
                             {
-                                const Center s = centre(c, L, ldg_record(w.refs + u0 + k));
+                                const Center s = centre(c, L, T::ref(u0 + k));
                                 hit = env_hit(env, c.prims, s.x, s.y, s.z, s.r, mg);
                             }
                         }
