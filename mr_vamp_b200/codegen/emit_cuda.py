@@ -781,6 +781,11 @@ def emit_robot(ir: dict[str, Any]) -> str:
     used = 4 * ((3 * n_slots * stride_ + 3) & ~3) + warps * _queue_bytes(geom) + ((32 * warps * dim * 4 + 16) if stage_cfg else 0)
     used = (used + 15) & ~15
     tables_in_shared = used + tab_off <= 228 * 1024 // ctas - 1024
+    if not tables_in_shared and stage_cfg:
+        # the tables are worth more than the staged configurations (measured on Panda: +5 % against +3 %)
+        bare = (4 * ((3 * n_slots * stride_ + 3) & ~3) + warps * _queue_bytes(geom) + 15) & ~15
+        if bare + tab_off <= 228 * 1024 // ctas - 1024:
+            stage_cfg, tables_in_shared = False, True
     if em_att:
         tab2, ttype2, _ = _tables(f"k_{robot}_tables_attach", em_att, stride=32 * warps + 1, const_row=const_row)
         out.extend(tab2)

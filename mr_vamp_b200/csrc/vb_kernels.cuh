@@ -21,7 +21,7 @@ namespace vb
 #else
     constexpr bool kLockstep = true;
 #endif
-#ifdef VB_NO_STAGE
+#if defined(VB_NO_STAGE) || defined(VB_SPLIT_BARRIER)
     constexpr bool kStageAllowed = false;
 #else
     constexpr bool kStageAllowed = true;
@@ -398,6 +398,19 @@ namespace vb
             }
             __syncthreads();
         }
+#ifdef VB_SPLIT_BARRIER
+        // experiment: warps may drift one grid-stride step apart (two alternating mbarriers in the staging area)
+        if (kMode == 0)
+        {
+            if (threadIdx.x == 0)
+            {
+                mbar_init(stage_buf, blockDim.x / 32u);
+                mbar_init(stage_buf + 8u, blockDim.x / 32u);
+                asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+            }
+            __syncthreads();
+        }
+#endif
         // CTA-uniform trip count with a barrier per iteration: the warps of a CTA walk the (large, mostly
         // straight-line) code together, so the instruction cache serves one stream instead of seven
         unsigned iter = 0;
@@ -434,6 +447,21 @@ namespace vb
                     asm volatile("prefetch.global.L1 [%0];" ::"l"(nx + Robot::kDim - 1));
                 }
             }
+#ifdef VB_SPLIT_BARRIER
+            if (kMode == 0)
+            {
+                const unsigned k = iter++;
+                if ((threadIdx.x & 31) == 0)
+                {
+                    asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(stage_buf + 8u * (k & 1u)) : "memory");
+                }
+                if (k > 0)
+                {
+                    mbar_wait(stage_buf + 8u * ((k - 1u) & 1u), ((k - 1u) >> 1) & 1u);
+                }
+            }
+            else
+#endif
             if (staged || (kLockstep && (iter++ % kLockstepEvery) == 0))
             {
                 __syncthreads();  // (staging: every thread has taken its configuration out of the buffer)
@@ -638,8 +666,15 @@ namespace vb
         const size_t stride = static_cast<size_t>(gridDim.x) * blockDim.x;
         const size_t n_points = __ldg(a.prefix + a.n);  // total interpolants, left on the device by the scan
         const size_t n_round = (n_points + 31) / 32 * 32;
-        for (size_t t = static_cast<size_t>(blockIdx.x) * blockDim.x + threadIdx.x; t < n_round; t += stride)
+        // CTA-uniform trip count with a barrier per step, as in the fkcc kernels: the warps of a CTA stream the
+        // (large, straight-line) walk code together
+        for (size_t base = static_cast<size_t>(blockIdx.x) * blockDim.x; base < n_round; base += stride)
         {
+            const size_t t = base + threadIdx.x;
+            if (kLockstep && !kMargin)
+            {
+                __syncthreads();
+            }
             bool alive = t < n_points;
             size_t e = 0;
             uint32_t pass = 0;
