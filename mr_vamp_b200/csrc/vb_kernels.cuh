@@ -21,6 +21,11 @@ namespace vb
 #else
     constexpr bool kLockstep = true;
 #endif
+#ifdef VB_MID_BARRIER
+    constexpr bool kMidBarrier = true;
+#else
+    constexpr bool kMidBarrier = false;
+#endif
 #if defined(VB_NO_STAGE) || defined(VB_SPLIT_BARRIER)
     constexpr bool kStageAllowed = false;
 #else
@@ -277,12 +282,17 @@ namespace vb
 
     // Verdicts of 32 configurations, one per lane (all lanes must call; `alive` = lane has a configuration).
     // Attachment traces keep the lane-serial walk (rare, first rake pass only).
-    template <class Robot>
+    template <class Robot, bool kSync = false>
     VB_D bool check_warp(const LaunchArgs &a, const Scratch &sc, const float *q, bool alive, bool attach, int &cstate,
                          bool octet = false)
     {
-        if (Robot::kHasAttach && __any_sync(kFull, attach && alive))
+        // kSync (CTA-uniform callers, `attach` uniform): the attachment decision must not depend on the warp
+        if (Robot::kHasAttach && (kSync ? attach : __any_sync(kFull, attach && alive)))
         {
+            if (kSync)
+            {
+                __syncthreads();  // the one mid-step barrier of Walk::run
+            }
             bool ok = false;
             if (alive)
             {
@@ -325,7 +335,7 @@ namespace vb
         wc.bz = a.base[2];
         wc.radius = a.sphere_radius;
         wc.octet = octet;
-        const bool ok = Walk<Robot>::run(a.env, wc, !alive || phit, cstate, pfree);
+        const bool ok = Walk<Robot>::template run<kSync>(a.env, wc, !alive || phit, cstate, pfree);
         __syncwarp();  // columns are rewritten by the next configuration
         return ok;
     }
@@ -491,7 +501,7 @@ namespace vb
             }
             else
             {
-                ok = check_warp<Robot>(a, prims, q, alive, a.attach != 0, cstate);
+                ok = check_warp<Robot, kMidBarrier>(a, prims, q, alive, a.attach != 0, cstate);
             }
             const uint32_t word = __ballot_sync(0xffffffffu, ok);
             if ((threadIdx.x & 31) == 0 && i < n_round)
@@ -536,7 +546,7 @@ namespace vb
             float q[Robot::kDim];
             random_config<Robot>(a.seed, first + i, q);
             VB_TICK(11);
-            const bool ok = check_warp<Robot>(a, prims, q, alive, a.attach != 0, cstate);
+            const bool ok = check_warp<Robot, kMidBarrier>(a, prims, q, alive, a.attach != 0, cstate);
             VB_TICK(12);
             const uint32_t word = __ballot_sync(0xffffffffu, ok);
             if ((threadIdx.x & 31) == 0 && i < n_round)

@@ -557,6 +557,9 @@ namespace vb
         // `cstate` is the warp's cached verdict of the configuration-independent environment groups
         // (-1 unknown, 0 free, 1 colliding): a property of (environment, base), evaluated once.
         // `pfree`: bit g set = self group g cannot collide at this lane's configuration (joint-pair tables).
+        // kSync: the caller's loop is CTA-uniform (fkcc kernels); every path through run() then passes exactly one CTA
+        // barrier between the self-collision and the environment part, which re-aligns the warps' instruction streams
+        template <bool kSync>
         VB_D static bool run(const EnvView &env, const WalkCtx &c, bool collided, int &cstate, const uint32_t *pfree)
         {
             VB_TICK_BEGIN;
@@ -600,6 +603,10 @@ namespace vb
                 }
                 if (cstate > 0)
                 {
+                    if (kSync)
+                    {
+                        __syncthreads();
+                    }
                     return false;
                 }
             }
@@ -651,6 +658,10 @@ namespace vb
                 run_units(c, ubits);
                 VB_TICK(6);
                 collided = collided || done(c, lane);
+            }
+            if (kSync)
+            {
+                __syncthreads();
             }
             if (__all_sync(kFull, collided))
             {
