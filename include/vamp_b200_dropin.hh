@@ -11,7 +11,7 @@
 //   vamp::b200::sphere_fk<Robot, rake>(block, s)  <- Robot::sphere_fk<rake>(block, s)   robots/panda_base.hh:67-71
 //   vamp::b200::validate_motion<Robot>(a, b, denv)<- planning::validate_motion<Robot, rake, res>(a, b, env)
 //                                                    planning/validate.hh:67-75
-//   vamp::b200::validate_batch / validate_motion_batch / validate_path
+//   vamp::b200::validate_batch / validate_motion_batch / validate_path / shortcut_path
 //                                                 <- the batch calls README.md:308 lists as a TODO, and
 //                                                    Path::validate (planning/plan.hh:155-168) in one launch
 //
@@ -214,15 +214,26 @@ namespace vamp::b200
         {
             return true;
         }
-        const auto ok = validate_motion_batch<Robot>(env, waypoints, waypoints + Robot::dimension, n_waypoints - 1);
-        for (bool b : ok)
-        {
-            if (!b)
-            {
-                return false;
-            }
-        }
-        return true;
+        int64_t first = -1;
+        const auto base = base_of<Robot>::get();
+        check(vb_validate_path(env.ctx(), robot_id<Robot>(), base.data(), env.get(), waypoints, n_waypoints, Robot::resolution,
+                               &first));
+        return first < 0;
+    }
+
+    // planning::shortcut_path (planning/simplify.hh:115-140): every candidate shortcut of the path validated in one
+    // batch, the reference's scan replayed on the verdicts.  keep[i] != 0: waypoint i stays in the path.  Returns
+    // true when at least one waypoint was removed (the reference's return value).
+    template <typename Robot>
+    inline bool shortcut_path(const DeviceEnvironment &env, const float *waypoints, std::size_t n_waypoints,
+                              std::vector<uint8_t> &keep)
+    {
+        keep.assign(n_waypoints, 1);
+        std::size_t kept = n_waypoints;
+        const auto base = base_of<Robot>::get();
+        check(vb_shortcut_path(env.ctx(), robot_id<Robot>(), base.data(), env.get(), waypoints, n_waypoints, Robot::resolution,
+                               keep.data(), &kept));
+        return kept != n_waypoints;
     }
 
     // ---- the reference's own signatures -------------------------------------------------------------------
