@@ -63,7 +63,8 @@ DERIVED_SLOT = 0x2000  # slot code of a centre that is NOT stored: DERIVED_SLOT 
 # fetch 0.73 -> 0.46 (its reduced links are on both sides of most of its 465 pair units; rebuilding them costs more
 # than the four extra resident warps give back), baxter: no link has more than four spheres.
 LINK_REDUCTION_OFF = {"fetch"}
-MIN_LINK_SPHERES = int(os.environ.get("VB_MIN_LINK_SPHERES", "5"))  # links with at least this many fine spheres keep <= 4 of them in shared memory
+MIN_LINK_SPHERES = int(os.environ.get("VB_MIN_LINK_SPHERES", "2"))  # links with fewer fine spheres are left alone
+DERIVE_GUARDS = os.environ.get("VB_DERIVE_GUARDS", "1") != "0"  # bounding spheres rebuilt from the link basis too
 
 
 def slot_offset(slot: int, stride: int, const_row: int) -> int:
@@ -185,11 +186,14 @@ class _Emitter:
                 continue
             C = [ir_eval.centre(vals, s, n) for s in fine]  # float64 copies of the float32 samples
             # greedy basis on the first sample: farthest pair, then farthest from the line, then from the plane
+            # (many links carry collinear or coplanar sphere sets: 2 or 3 basis centres then suffice)
             P = np.stack([c[0] for c in C])
             d = np.linalg.norm(P[:, None] - P[None], axis=2)
             i0, i1 = np.unravel_index(np.argmax(d), d.shape)
             basis = [int(i0), int(i1)]
             for _ in range(2):
+                if len(basis) >= len(fine):
+                    break
                 B = P[basis[1:]] - P[basis[0]]
                 Q, _ = np.linalg.qr(B.T)
                 R = (P - P[basis[0]]) - (P - P[basis[0]]) @ Q @ Q.T
@@ -198,34 +202,46 @@ class _Emitter:
                 if dist[k] < 5e-3:
                     break
                 basis.append(k)
+            m = min(n, 128)
+            A = np.concatenate([np.stack([C[b][t] - C[basis[0]][t] for b in basis[1:]], axis=1) for t in range(m)])
+
+            def weights(Cj):
+                """Affine weights of a centre over the basis and the float32 reconstruction error over all samples."""
+                y = np.concatenate([Cj[t] - C[basis[0]][t] for t in range(m)])
+                wk, *_ = np.linalg.lstsq(A, y, rcond=None)
+                wts = [1.0 - float(wk.sum())] + [float(v) for v in wk]
+                rec = np.zeros((n, 3), np.float32)
+                for wv, b in zip(wts, basis):
+                    rec = (rec + np.float32(wv) * C[b].astype(np.float32)).astype(np.float32)
+                err = float(np.abs(rec.astype(np.float64) - Cj).max())
+                return wts + [0.0] * (4 - len(wts)), err
+
+            basis_args = [fine[b] for b in basis] + [fine[basis[0]]] * (4 - len(basis))
             ok = True
             plan = {}
-            m = min(n, 128)
             lw = {}
             for j, sj in enumerate(fine):
                 if j in basis:
                     continue
-                # affine weights: c_j - c_b0 = sum_k w_k (c_bk - c_b0), stacked over the samples
-                A = np.concatenate([np.stack([C[b][t] - C[basis[0]][t] for b in basis[1:]], axis=1) for t in range(m)])
-                y = np.concatenate([C[j][t] - C[basis[0]][t] for t in range(m)])
-                wk, *_ = np.linalg.lstsq(A, y, rcond=None)
-                wts = [1.0 - float(wk.sum())] + [float(v) for v in wk]
-                wts32 = [np.float32(v) for v in wts]
-                rec = np.zeros((n, 3), np.float32)
-                for wv, b in zip(wts32, basis):
-                    rec = (rec + wv * C[b].astype(np.float32)).astype(np.float32)
-                err = float(np.abs(rec.astype(np.float64) - C[j]).max())
+                wts, err = weights(C[j])
                 if err > 1e-6:
                     ok = False
                     break
-                while len(wts) < 4:
-                    wts.append(0.0)
-                entry = ([fine[b] for b in basis] + [fine[basis[0]]] * (4 - len(basis)), wts)
                 if self.key(sj) in guards:
-                    lw[self.key(sj)] = entry  # stays stored; the weights serve the b-side loop of the pair stage
+                    lw[self.key(sj)] = (basis_args, wts)  # stays stored; the weights serve the b-side loop of the pair stage
                 else:
-                    plan[self.key(sj)] = entry
-            if ok:
+                    plan[self.key(sj)] = (basis_args, wts)
+            if not ok:
+                continue
+            # the link's bounding sphere (guard of this group and of its self-collision groups) is rigid with the
+            # link too: rebuilt from the basis where it lies in its affine span
+            gkey = self.key(it["guard"])
+            if (DERIVE_GUARDS and gkey not in {self.key(sj) for sj in fine} and not all(a["v"] is None for a in it["guard"][:3])
+                    and gkey not in self.plan):
+                wts, err = weights(ir_eval.centre(vals, it["guard"], n))
+                if err <= 1e-6:
+                    plan[gkey] = (basis_args, wts)
+            if plan:
                 self.plan.update(plan)
                 self.link_weights.update(lw)
         return self
@@ -430,7 +446,7 @@ def _tables(name: str, em: _Emitter, walk: bool = False, stride: int = 0, const_
             assert g["b"][1] < 64 and len(em.derived) < 511, g["name"]
             pack = g["b"][1] | (((b_der[0] + 1) if b_der else 0) << 6) | ((1 << 15) if sa & DERIVED_SLOT else 0)
             units.append(((sa & (DERIVED_SLOT - 1)) if sa & DERIVED_SLOT else slot_offset(sa, stride, const_row),
-                          slot_offset(sb, stride, const_row), ra, filt, b_list(g), pack))
+                          0 if sb & DERIVED_SLOT else slot_offset(sb, stride, const_row), ra, filt, b_list(g), pack))
     assert len(refs) < 2048 and len(units) < 2048, (name, len(refs), len(units))
     ne, ns, na, nr = len(em.env), len(em.selfg), len(em.att), len(refs)
     t = f"Tables<{max(ne, 1)}, {max(ns, 1)}, {max(na, 1)}, {max(nr, 1)}>"
@@ -586,6 +602,7 @@ def _uniform(em: _Emitter) -> list[str]:
             need(b)
             return f"sqd(s{a}x - s{b}x, s{a}y - s{b}y, s{a}z - s{b}z)"
 
+        d2.need = need
         return d2
 
     body: list[str] = []
@@ -657,12 +674,19 @@ def _uniform(em: _Emitter) -> list[str]:
     w("        bool in;")
     for wi in range(ew):
         w(f"        uint32_t i{wi} = 0u;")
+    fetch_body: list[str] = []
+    fetch_need = sphere_loads(set(), fetch_body).need
     for gi, g in enumerate(em.env):
         slot, mask, r = g["guard"]
-        assert not (slot & DERIVED_SLOT), g["name"]
+        if slot & DERIVED_SLOT:
+            fetch_need(slot)
+            for ln in fetch_body:
+                w("        " + ln)
+            fetch_body.clear()
         xyz = []
         for c in range(3):
-            e = em.const_xyz[slot][c] if slot & CONST_SLOT else f"col[{3 * slot + c} * kStride]"
+            e = (f"s{slot}{'xyz'[c]}" if slot & DERIVED_SLOT else em.const_xyz[slot][c] if slot & CONST_SLOT
+                 else f"col[{3 * slot + c} * kStride]")
             if mask & (1 << c):
                 e += f" + b{'xyz'[c]}"
             xyz.append(e)
@@ -732,7 +756,7 @@ def emit_robot(ir: dict[str, Any]) -> str:
         q = (lo + rng.random((n, dim)) * rg).astype(np.float32)
         return ir_eval.evaluate(fn, q), n
 
-    reduce_links = robot not in LINK_REDUCTION_OFF
+    reduce_links = robot not in LINK_REDUCTION_OFF or os.environ.get("VB_REDUCE_ALL") == "1"
     em = _Emitter(fns["interleaved_sphere_fk"], sampled(fns["interleaved_sphere_fk"]), reduce_links).run_checks()
     em_att = (_Emitter(fns["interleaved_sphere_fk_attachment"], sampled(fns["interleaved_sphere_fk_attachment"]), reduce_links).run_checks()
               if has_attach else None)
@@ -757,35 +781,48 @@ def emit_robot(ir: dict[str, Any]) -> str:
     const_row = max(em.n_rows, em_att.n_rows if em_att else 0)
     n_const = max(len(em.const_slots), len(em_att.const_slots) if em_att else 0)
     n_slots = const_row + (n_const + 31) // 32
-    # Staged configurations (vb_kernels.cuh) are worth their shared memory only if they do not cost a resident
-    # warp; queue capacities shrink first (overflowing units run in place, vb_walk.cuh).
-    warps, ctas = _geometry(n_slots, geom)
-    stage_cfg = False
-    for cap in (256, 192, 128):
-        smaller = dict(geom, pair_q=cap, env_q=max(cap, 192), self_q=max(cap, 192))
-        w2, c2 = _geometry(n_slots, smaller, dim)
-        if w2 * c2 >= warps * ctas:
-            geom, warps, ctas, stage_cfg = smaller, w2, c2, True
-            break
+    # Window plan: resident warps, queue capacities, and which of {staged configurations, check tables} go behind
+    # the columns.  Scored with the effects measured on B200 (Panda, MBM scene): throughput ~ warps^0.4 (8 -> 11
+    # warps: +14 %), staged configurations +3 %, tables in shared memory +5 %.  Overflowing queue units run in
+    # place (vb_walk.cuh): correct, but slow when it happens often, so the capacities stay >= 192.
+    _, _, tgeom0 = _tables(f"k_{robot}_tables", em, walk=True, stride=33, const_row=const_row)
+    tab_bytes = 0
+    for _, cnt, size in tgeom0["tab"]:
+        tab_bytes = (tab_bytes + cnt * size + 15) & ~15
+
+    def window_bytes(g, w_, stage):
+        st = 32 * w_ + 1
+        b = 4 * ((3 * n_slots * st + 3) & ~3) + w_ * _queue_bytes(g) + ((32 * w_ * dim * 4 + 16) if stage else 0)
+        return (b + 15) & ~15
+
+    best = None
+    for cap in (256, 192):  # (128 was measured on Fetch: queue overflow, 0.73 -> 0.46 Gcfg/s)
+        g = dict(geom, pair_q=cap, env_q=cap, self_q=cap)
+        for stage in (False, True):
+            w_, c_ = _geometry(n_slots, g, dim if stage else 0)
+            for drop in (0, 1):  # one warp less can buy both extras
+                ww = w_ - drop
+                if ww < 1:
+                    continue
+                avail = 228 * 1024 // c_ - 1024
+                if window_bytes(g, ww, stage) > avail:
+                    continue
+                tabs = window_bytes(g, ww, stage) + tab_bytes <= avail
+                score = (ww * c_) ** 0.4 * (1.03 if stage else 1.0) * (1.05 if tabs else 1.0)
+                if best is None or score > best[0] + 1e-9:
+                    best = (score, g, ww, c_, stage, tabs)
+    _, geom, warps, ctas, stage_cfg, tables_in_shared = best
     if os.environ.get("VB_FORCE_Q"):  # development: "env,self,pair" capacities, to exercise the overflow paths
         e_, s_, p_ = (int(v) for v in os.environ["VB_FORCE_Q"].split(","))
         geom = dict(geom, env_q=e_, self_q=s_, pair_q=p_)
+        tables_in_shared = False
     tab, ttype, tgeom = _tables(f"k_{robot}_tables", em, walk=True, stride=32 * warps + 1, const_row=const_row)
     out.extend(tab)
-    # check tables behind the staged configurations when the window has room for them (no resident warp is given up)
     tab_off, tab_lines = 0, []
     for tname, cnt, size in tgeom["tab"]:
         tab_lines.append(f"    static constexpr unsigned kTab{tname} = {tab_off}, kTab{tname}Bytes = {cnt * size};")
         tab_off = (tab_off + cnt * size + 15) & ~15
-    stride_ = 32 * warps + 1
-    used = 4 * ((3 * n_slots * stride_ + 3) & ~3) + warps * _queue_bytes(geom) + ((32 * warps * dim * 4 + 16) if stage_cfg else 0)
-    used = (used + 15) & ~15
-    tables_in_shared = used + tab_off <= 228 * 1024 // ctas - 1024
-    if not tables_in_shared and stage_cfg:
-        # the tables are worth more than the staged configurations (measured on Panda: +5 % against +3 %)
-        bare = (4 * ((3 * n_slots * stride_ + 3) & ~3) + warps * _queue_bytes(geom) + 15) & ~15
-        if bare + tab_off <= 228 * 1024 // ctas - 1024:
-            stage_cfg, tables_in_shared = False, True
+    assert tab_off == tab_bytes
     if em_att:
         tab2, ttype2, _ = _tables(f"k_{robot}_tables_attach", em_att, stride=32 * warps + 1, const_row=const_row)
         out.extend(tab2)
