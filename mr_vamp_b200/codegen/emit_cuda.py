@@ -100,6 +100,7 @@ class _Emitter:
         self.derived: list[dict[str, Any]] = []  # {"basis": [slot x 4], "w": [float x 4]}
         self.link_weights: dict[tuple, tuple[list, list[float]]] = {}  # stored non-basis spheres of reduced links
         self.slot_weights: dict[int, list[float]] = {}  # their slot -> weights over the link's basis
+        self.link_gram: dict[tuple, list[list[float]]] = {}  # basis keys -> Gram matrix of the basis edges
 
     # -- operands -----------------------------------------------------------------------------
     def opnd(self, o) -> str:
@@ -126,7 +127,8 @@ class _Emitter:
         if key not in self.slots and key in self.plan:
             basis, wts = self.plan[key]
             self.slots[key] = DERIVED_SLOT | len(self.derived)
-            self.derived.append({"basis": [self.ref(b)[0] for b in basis], "w": list(wts)})
+            self.derived.append({"basis": [self.ref(b)[0] for b in basis], "w": list(wts),
+                                 "gram": self.link_gram[tuple(self.key(b) for b in basis)]})
         if key not in self.slots:
             xyz = [self.coord(a) for a in s[:3]]
             if all(a["v"] is None for a in s[:3]):
@@ -217,6 +219,11 @@ class _Emitter:
                 return wts + [0.0] * (4 - len(wts)), err
 
             basis_args = [fine[b] for b in basis] + [fine[basis[0]]] * (4 - len(basis))
+            # Gram matrix of the basis edges e_k = c_bk - c_b0 (a rigid-motion invariant): lets the pair stage
+            # evaluate |a - b_j|^2 = |a - c_b0|^2 - 2 sum_k w_k (a - c_b0).e_k + w^T G w with w^T G w a constant
+            E = [C[b] - C[basis[0]] for b in basis[1:]] + [np.zeros_like(C[0])] * (4 - len(basis))
+            gram = [[float((E[k] * E[l]).sum(axis=1).mean()) for l in range(3)] for k in range(3)]
+            self.link_gram[tuple(self.key(b) for b in basis_args)] = gram
             ok = True
             plan = {}
             lw = {}
@@ -418,6 +425,7 @@ def _tables(name: str, em: _Emitter, walk: bool = False, stride: int = 0, const_
             slots = [sl for sl, _, _ in entries]
             der = [sl & (DERIVED_SLOT - 1) for sl in slots if sl & DERIVED_SLOT]
             basis = em.derived[der[0]]["basis"] if der else None
+            gram = em.derived[der[0]]["gram"] if der else None
             for sl, _, r in entries:
                 wts = None
                 if basis is not None:
@@ -427,7 +435,7 @@ def _tables(name: str, em: _Emitter, walk: bool = False, stride: int = 0, const_
                         wts = [1.0 if b == sl and basis.index(sl) == k else 0.0 for k, b in enumerate(basis)]
                     else:
                         wts = em.slot_weights[sl]
-                blist.append((sl, r, wts))
+                blist.append((sl, r, wts, gram))
         return blist_at[key]
 
     for gi, g in enumerate(em.selfg):
@@ -519,13 +527,20 @@ def _tables(name: str, em: _Emitter, walk: bool = False, stride: int = 0, const_
             out.append("    " + ", ".join(f"{{{a}, {g}, {_f32(ra)}, {_f32(fr) if fr >= 0 else '-1.0f'}, {bb}, {bc}}}"
                                           for a, g, ra, fr, bb, bc in uu[i : i + 4]) + ",")
         out.append("};")
-        bl = blist or [(0, 0.0, None)]
+        bl = blist or [(0, 0.0, None, None)]
         out.append(f"__device__ const BRef {name}_brefs[{len(bl)}] = {{")
         for i in range(0, len(bl), 8):
-            out.append("    " + ", ".join(f"{{{0 if sl & DERIVED_SLOT else slot_offset(sl, stride, const_row)}, {_f32(r) if r >= 0 else '-1.0f'}}}" for sl, r, _ in bl[i : i + 8]) + ",")
+            out.append("    " + ", ".join(f"{{{0 if sl & DERIVED_SLOT else slot_offset(sl, stride, const_row)}, {_f32(r) if r >= 0 else '-1.0f'}}}" for sl, r, _, _ in bl[i : i + 8]) + ",")
         out.append("};")
         # b-side spheres of reduced links as weights over the link's basis (stored basis spheres: one-hot)
-        bw_rows = [f"{{{{{', '.join(_f32(v) for v in (wts or [0.0, 0.0, 0.0, 0.0]))}}}, {_f32(r) if r >= 0 else '-1.0f'}, 0u}}" for _, r, wts in bl]
+        def edge_form(wts, gram):
+            if wts is None:
+                return [0.0, 0.0, 0.0, 0.0]
+            wk = wts[1:4]
+            g = sum(wk[k] * wk[l] * gram[k][l] for k in range(3) for l in range(3))
+            return [wk[0], wk[1], wk[2], g]
+
+        bw_rows = [f"{{{{{', '.join(_f32(v) for v in edge_form(wts, gram))}}}, {_f32(r) if r >= 0 else '-1.0f'}, 0u}}" for _, r, wts, gram in bl]
         out.append(f"__device__ const BWeights {name}_bws[{len(bl)}] = {{")
         for i in range(0, len(bw_rows), 4):
             out.append("    " + ", ".join(bw_rows[i : i + 4]) + ",")

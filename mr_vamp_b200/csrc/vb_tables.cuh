@@ -76,7 +76,9 @@ namespace vb
     };
     static_assert(sizeof(SelfUnit) == 16, "SelfUnit is read as one 16-byte load");
 
-    // b-side sphere of a reduced link: weights over the link's basis + radius
+    // b-side sphere of a reduced link: w[0..2] = weights over the basis EDGES e_k = c_k - c_0 of the link, w[3] =
+    // w^T G w with G the (rigid-motion invariant) Gram matrix of the edges, + radius.  With u = a - c_0:
+    //   |a - b|^2 = |u|^2 - 2 sum_k w_k (u . e_k) + w^T G w        (3 FMAs per b sphere once u . e_k are known)
     struct alignas(8) BWeights
     {
         float w[4];

@@ -28,6 +28,8 @@
 namespace vb
 {
     constexpr unsigned kFull = 0xffffffffu;
+    // pair stage, reduced b-links: |d^2 - (ra + rb)^2| below this (m^2) is decided by the direct formula
+    constexpr float kGramBand = 1.6e-5f;
 
     // The stages of the walk are inlined into the kernel: as separate functions every call spills the caller's
     // live state to local memory (ABI), ~170 local loads/stores per warp and iteration that also evict the
@@ -293,7 +295,7 @@ namespace vb
             bool hit = false;
             if (Robot::kDerived > 0 && u.b_basis() >= 0)
             {
-                // reduced b-link: its basis once, then every b_j from its weights (no shared-memory access in the loop)
+                // reduced b-link: a_i relative to the link's basis once, then 3 FMAs per b_j (vb_tables.cuh: BWeights)
                 const DerivedRec bd = T::der(u.b_basis());
                 float px[4], py[4], pz[4];
 #pragma unroll
@@ -301,15 +303,32 @@ namespace vb
                 {
                     at(c, L, bd.off[k], px[k], py[k], pz[k]);
                 }
-#pragma unroll 2
+                const float ux = ax - px[0], uy = ay - py[0], uz = az - pz[0];
+                const float s0 = ux * ux + uy * uy + uz * uz;
+                float q[3];
+#pragma unroll
+                for (int k = 0; k < 3; ++k)
+                {
+                    q[k] = -2.f * (ux * (px[k + 1] - px[0]) + uy * (py[k + 1] - py[0]) + uz * (pz[k + 1] - pz[0]));
+                }
+#pragma unroll 4
                 for (int j = 0; j < bc; ++j)
                 {
                     const BWeights bw = T::bw(u.b_begin + j);
-                    const float bx = bw.w[0] * px[0] + bw.w[1] * px[1] + bw.w[2] * px[2] + bw.w[3] * px[3];
-                    const float by = bw.w[0] * py[0] + bw.w[1] * py[1] + bw.w[2] * py[2] + bw.w[3] * py[3];
-                    const float bz = bw.w[0] * pz[0] + bw.w[1] * pz[1] + bw.w[2] * pz[2] + bw.w[3] * pz[3];
-                    const float dx = ax - bx, dy = ay - by, dz = az - bz, rs = u.a_r + bw.r;
-                    hit = hit || (dx * dx + dy * dy + dz * dz - rs * rs < 0.f);
+                    const float d2 = s0 + bw.w[0] * q[0] + bw.w[1] * q[1] + bw.w[2] * q[2] + bw.w[3];
+                    const float rs = u.a_r + bw.r;
+                    float v = d2 - rs * rs;
+                    if (fabsf(v) < kGramBand)
+                    {
+                        // |u|^2 and the dot products cancel (up to ~3e-7 m^2 of rounding): near contact the sphere is
+                        // rebuilt from the basis edges and tested directly, as the stored b-loop does
+                        const float bx = px[0] + bw.w[0] * (px[1] - px[0]) + bw.w[1] * (px[2] - px[0]) + bw.w[2] * (px[3] - px[0]);
+                        const float by = py[0] + bw.w[0] * (py[1] - py[0]) + bw.w[1] * (py[2] - py[0]) + bw.w[2] * (py[3] - py[0]);
+                        const float bz = pz[0] + bw.w[0] * (pz[1] - pz[0]) + bw.w[1] * (pz[2] - pz[0]) + bw.w[2] * (pz[3] - pz[0]);
+                        const float dx = ax - bx, dy = ay - by, dz = az - bz;
+                        v = dx * dx + dy * dy + dz * dz - rs * rs;
+                    }
+                    hit = hit || (v < 0.f);
                 }
                 return hit;
             }
