@@ -29,7 +29,7 @@ namespace vb
 {
     constexpr unsigned kFull = 0xffffffffu;
     // pair stage, reduced b-links: |d^2 - (ra + rb)^2| below this (m^2) is decided by the direct formula
-    constexpr float kGramBand = 1.6e-5f;
+    constexpr float kGramBand = 4e-5f;
 
     // The stages of the walk are inlined into the kernel: as separate functions every call spills the caller's
     // live state to local memory (ABI), ~170 local loads/stores per warp and iteration that also evict the
