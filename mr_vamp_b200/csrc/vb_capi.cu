@@ -875,9 +875,9 @@ namespace
         g.oy = lo[1];
         g.oz = lo[2];
         g.inv_h = 1.f / h;
-        g.fnx = static_cast<float>(g.nx);
-        g.fny = static_cast<float>(g.ny);
-        g.fnz = static_cast<float>(g.nz);
+        g.fnx = std::nextafterf(static_cast<float>(g.nx), 0.f);
+        g.fny = std::nextafterf(static_cast<float>(g.ny), 0.f);
+        g.fnz = std::nextafterf(static_cast<float>(g.nz), 0.f);
         g.pad = 0.5f * std::sqrt(3.f) * h * 1.001f + vb::kSdfMargin;
         g.cover = clipped ? 0.f : vb::kSdfCover;
         return true;

@@ -61,7 +61,7 @@ namespace vb
         const uint2 *cell;     // [nz][ny][nx]: x = float bits of the signed distance at the voxel centre, y = candidate mask
         float ox, oy, oz;      // lower corner
         float inv_h;           // 1 / voxel edge
-        float fnx, fny, fnz;   // float(nx), float(ny), float(nz)
+        float fnx, fny, fnz;   // the largest floats below nx, ny, nz (voxel coordinates are clamped to [0, fn*])
         int nx, ny, nz;
         float pad;             // half voxel diagonal + safety margin
         float cover;           // outside the grid every obstacle is at least this far away (0: unknown)

@@ -29,9 +29,10 @@ namespace vb
     VB_D uint2 grid_fetch(const SdfView &g, float x, float y, float z, bool &in)
     {
         const float fx = (x - g.ox) * g.inv_h, fy = (y - g.oy) * g.inv_h, fz = (z - g.oz) * g.inv_h;
-        in = fx >= 0.f && fy >= 0.f && fz >= 0.f && fx < g.fnx && fy < g.fny && fz < g.fnz;
-        const int ix = min(max(static_cast<int>(fx), 0), g.nx - 1), iy = min(max(static_cast<int>(fy), 0), g.ny - 1),
-                  iz = min(max(static_cast<int>(fz), 0), g.nz - 1);
+        // clamped in the float domain (inside the grid the clamp is the identity; NaN clamps to 0 and is "outside")
+        const float cx = fminf(fmaxf(fx, 0.f), g.fnx), cy = fminf(fmaxf(fy, 0.f), g.fny), cz = fminf(fmaxf(fz, 0.f), g.fnz);
+        in = cx == fx && cy == fy && cz == fz;
+        const int ix = static_cast<int>(cx), iy = static_cast<int>(cy), iz = static_cast<int>(cz);
         return __ldg(g.cell + (iz * g.ny + iy) * g.nx + ix);
     }
 

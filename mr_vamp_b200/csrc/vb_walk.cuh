@@ -311,24 +311,31 @@ namespace vb
                 {
                     q[k] = -2.f * (ux * (px[k + 1] - px[0]) + uy * (py[k + 1] - py[0]) + uz * (pz[k + 1] - pz[0]));
                 }
+                bool near = false;
 #pragma unroll 4
                 for (int j = 0; j < bc; ++j)
                 {
                     const BWeights bw = T::bw(u.b_begin + j);
                     const float d2 = s0 + bw.w[0] * q[0] + bw.w[1] * q[1] + bw.w[2] * q[2] + bw.w[3];
                     const float rs = u.a_r + bw.r;
-                    float v = d2 - rs * rs;
-                    if (fabsf(v) < kGramBand)
+                    const float v = d2 - rs * rs;
+                    near = near || fabsf(v) < kGramBand;
+                    hit = hit || v < -kGramBand;
+                }
+                if (near && !hit)
+                {
+                    // |u|^2 and the dot products cancel (a few 1e-6 m^2 of rounding): a unit with a sphere that close to
+                    // contact is decided by rebuilding the b spheres from the basis edges and testing them directly, as
+                    // the stored b-loop does
+                    for (int j = 0; j < bc; ++j)
                     {
-                        // |u|^2 and the dot products cancel (up to ~3e-7 m^2 of rounding): near contact the sphere is
-                        // rebuilt from the basis edges and tested directly, as the stored b-loop does
+                        const BWeights bw = T::bw(u.b_begin + j);
                         const float bx = px[0] + bw.w[0] * (px[1] - px[0]) + bw.w[1] * (px[2] - px[0]) + bw.w[2] * (px[3] - px[0]);
                         const float by = py[0] + bw.w[0] * (py[1] - py[0]) + bw.w[1] * (py[2] - py[0]) + bw.w[2] * (py[3] - py[0]);
                         const float bz = pz[0] + bw.w[0] * (pz[1] - pz[0]) + bw.w[1] * (pz[2] - pz[0]) + bw.w[2] * (pz[3] - pz[0]);
-                        const float dx = ax - bx, dy = ay - by, dz = az - bz;
-                        v = dx * dx + dy * dy + dz * dz - rs * rs;
+                        const float dx = ax - bx, dy = ay - by, dz = az - bz, rs = u.a_r + bw.r;
+                        hit = hit || (dx * dx + dy * dy + dz * dz - rs * rs < 0.f);
                     }
-                    hit = hit || (v < 0.f);
                 }
                 return hit;
             }
