@@ -827,6 +827,8 @@ def emit_robot(ir: dict[str, Any]) -> str:
                 if best is None or score > best[0] + 1e-9:
                     best = (score, g, ww, c_, stage, tabs)
     _, geom, warps, ctas, stage_cfg, tables_in_shared = best
+    if os.environ.get("VB_FORCE_STAGE") == "1":  # development: staged configurations whatever the plan says
+        stage_cfg, tables_in_shared = True, False
     if os.environ.get("VB_FORCE_Q"):  # development: "env,self,pair" capacities, to exercise the overflow paths
         e_, s_, p_ = (int(v) for v in os.environ["VB_FORCE_Q"].split(","))
         geom = dict(geom, env_q=e_, self_q=s_, pair_q=p_)

@@ -472,12 +472,21 @@ namespace vb
             }
             else
 #endif
+            if (full)
+            {
+                // The reads of the staging buffer above are generic-proxy accesses, the next bulk copy writes it through
+                // the async proxy: without a proxy fence the copy may overtake shared-memory loads that are still in
+                // flight when the CTA barrier completes (observed with 2 CTAs per SM: a warp then walked the NEXT
+                // step's configurations).  Every reader fences before the barrier, the issuing thread after it.
+                asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+            }
             if (staged || (kLockstep && (iter++ % kLockstepEvery) == 0))
             {
                 __syncthreads();  // (staging: every thread has taken its configuration out of the buffer)
             }
             if (staged && threadIdx.x == 0 && base + stride + blockDim.x <= a.n)
             {
+                asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
                 mbar_expect_tx(stage_bar, kCfgBytes);
                 bulk_global_to_shared(stage_buf, a.cfg + (base + stride) * Robot::kDim, kCfgBytes, stage_bar);
             }

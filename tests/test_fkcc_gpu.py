@@ -69,6 +69,26 @@ def test_fkcc_verdicts(vb, ref, name, scene):
     _compare(ok, mg, ref.fkcc(REF_NAME.get(name, name), renv, q, threads=8), f"{name}/{scene}")
 
 
+@pytest.mark.parametrize("name", ROBOTS)
+def test_many_grid_stride_steps(vb, ref, name):
+    """Several grid-stride steps per CTA (the batches above fit in one): the staged-configuration pipeline (TMA bulk copy
+    one step ahead, vb_kernels.cuh) must hand every step ITS configurations.  A missing proxy fence between the reads of
+    the staging buffer and the next bulk copy once let a warp walk the next step's configurations (non-deterministic,
+    ~0.1 % of the steps with 2 CTAs per SM); the lane-serial kernel reads its configurations directly."""
+    robot = vb.Robot(name)
+    spec = scenes.random_scene(7) if name in ("sphere", "ur5", "panda") else []  # (the clutter sits inside Fetch's / Baxter's base)
+    env = scenes.apply(spec, vb.Environment())
+    n = 1_500_000 if name != "sphere" else 6_000_000
+    q = _cfgs(robot, 17, n)
+    ok_serial, mg = robot.fkcc_batch(q, env, margin=True)
+    for rep in range(3):
+        ok = robot.fkcc_batch(q, env)
+        hard = (ok != ok_serial) & (mg > BAND)
+        assert not hard.any(), f"{name}: {int(hard.sum())} verdicts of the warp walk differ from the lane-serial walk (pass {rep})"
+    sub = slice(0, n, max(1, n // 60000))
+    _compare(ok[sub], mg[sub], ref.fkcc(REF_NAME.get(name, name), apply_ref(spec, ref.Env()), q[sub], threads=8), f"{name}/many steps")
+
+
 def test_cage_known_answers(vb):
     # scripts/sphere_cage_example.py:10-13,67: start and goal are valid in the nominal cage
     robot = vb.Robot("panda")
