@@ -10,6 +10,7 @@
 #include <algorithm>
 #include <atomic>
 #include <cmath>
+#include <cstdlib>
 #include <cstdarg>
 #include <cstdio>
 #include <cstring>
@@ -462,7 +463,7 @@ namespace
 
     struct Replica
     {
-        DevBuf prims, hf_desc, capt_desc, att_local, sdf;
+        DevBuf prims, hf_desc, capt_desc, att_local, sdf, sdf_c;
         std::vector<DevBuf> blobs;  // heightfield data and CAPT arrays
         vb::EnvView view{};
     };
@@ -497,6 +498,7 @@ namespace
             r.capt_desc.release();
             r.att_local.release();
             r.sdf.release();
+            r.sdf_c.release();
             for (auto &b : r.blobs)
             {
                 b.release();
@@ -772,12 +774,11 @@ namespace
     }
 
     // one thread per voxel of the distance / candidate grid (vb_sdf.cuh)
-    __global__ void sdf_build_kernel(const vb::EnvView e, uint2 *cell)
+    __global__ void sdf_build_kernel(const vb::EnvView e, const vb::SdfView g, uint2 *cell)
     {
-        const vb::SdfView &g = e.sdf;
         const size_t n = static_cast<size_t>(g.nx) * g.ny * g.nz;
         const float h = 1.f / g.inv_h;
-        const float reach = vb::kMaskReach + g.pad;
+        const float reach = g.mask_reach + g.pad;
         for (size_t v = static_cast<size_t>(blockIdx.x) * blockDim.x + threadIdx.x; v < n;
              v += static_cast<size_t>(gridDim.x) * blockDim.x)
         {
@@ -804,7 +805,9 @@ namespace
     constexpr size_t kSdfMaxVoxels = size_t(4) << 20;
     constexpr float kSdfMinVoxel = 0.015f;
 
-    bool sdf_geometry(const vb_env *env, vb::SdfView &g)
+    constexpr float kSdfCoarseVoxel = 0.08f;  // coarse level of the two-level guard lookup (vb_sdf.cuh)
+
+    bool sdf_geometry(const vb_env *env, vb::SdfView &g, float min_voxel_arg = kSdfMinVoxel)
     {
         float lo[3] = {3e38f, 3e38f, 3e38f}, hi[3] = {-3e38f, -3e38f, -3e38f};
         auto grow = [&](const float *c, const float *e) {
@@ -859,7 +862,15 @@ namespace
             }
             ext[k] = hi[k] - lo[k];
         }
-        float h = std::max(kSdfMinVoxel, std::cbrt(ext[0] * ext[1] * ext[2] / static_cast<float>(kSdfMaxVoxels)));
+        float min_voxel = min_voxel_arg;
+        if (const char *v = std::getenv("VB_SDF_VOXEL"))  // development: voxel edge of the fine grid in metres
+        {
+            if (min_voxel_arg == kSdfMinVoxel)
+            {
+                min_voxel = std::max(1e-3f, static_cast<float>(std::atof(v)));
+            }
+        }
+        float h = std::max(min_voxel, std::cbrt(ext[0] * ext[1] * ext[2] / static_cast<float>(kSdfMaxVoxels)));
         for (;;)
         {
             g.nx = static_cast<int>(std::ceil(ext[0] / h));
@@ -880,6 +891,11 @@ namespace
         g.fnz = std::nextafterf(static_cast<float>(g.nz), 0.f);
         g.pad = 0.5f * std::sqrt(3.f) * h * 1.001f + vb::kSdfMargin;
         g.cover = clipped ? 0.f : vb::kSdfCover;
+        g.mask_reach = vb::kMaskReach;
+        if (const char *v = std::getenv("VB_SDF_REACH"))  // development: candidate-mask reach in metres
+        {
+            g.mask_reach = std::max(0.05f, static_cast<float>(std::atof(v)));
+        }
         return true;
     }
 
@@ -963,8 +979,19 @@ namespace
             const size_t voxels = static_cast<size_t>(v.sdf.nx) * v.sdf.ny * v.sdf.nz;
             VB_CUDA(rep.sdf.reserve(voxels * sizeof(uint2)));
             v.sdf.cell = rep.sdf.as<uint2>();
-            sdf_build_kernel<<<slot.sm_count * 8, 256, 0, slot.stream>>>(v, rep.sdf.as<uint2>());
+            sdf_build_kernel<<<slot.sm_count * 8, 256, 0, slot.stream>>>(v, v.sdf, rep.sdf.as<uint2>());
             VB_CUDA(cudaGetLastError());
+            // coarse level: the same box at 8 cm voxels, when the fine grid is much finer than that
+            v.sdf_c = vb::SdfView{};
+            const bool want_coarse = !std::getenv("VB_SDF_NO_COARSE") && 1.f / v.sdf.inv_h < 0.5f * kSdfCoarseVoxel;
+            if (want_coarse && sdf_geometry(env, v.sdf_c, kSdfCoarseVoxel))
+            {
+                const size_t cv = static_cast<size_t>(v.sdf_c.nx) * v.sdf_c.ny * v.sdf_c.nz;
+                VB_CUDA(rep.sdf_c.reserve(cv * sizeof(uint2)));
+                v.sdf_c.cell = rep.sdf_c.as<uint2>();
+                sdf_build_kernel<<<slot.sm_count * 8, 256, 0, slot.stream>>>(v, v.sdf_c, rep.sdf_c.as<uint2>());
+                VB_CUDA(cudaGetLastError());
+            }
         }
         VB_CUDA(cudaStreamSynchronize(slot.stream));
         return VB_OK;

@@ -65,6 +65,7 @@ namespace vb
         int nx, ny, nz;
         float pad;             // half voxel diagonal + safety margin
         float cover;           // outside the grid every obstacle is at least this far away (0: unknown)
+        float mask_reach;      // candidate masks hold every obstacle within mask_reach + pad of the voxel centre
     };
 
     // Passed by value to every kernel (lives in the parameter constant bank).
@@ -78,6 +79,7 @@ namespace vb
         const CaptView *capts;
         AttachmentView attach;
         SdfView sdf;
+        SdfView sdf_c;  // coarse level of the two-level guard lookup (cell == nullptr: none)
     };
 
     // Margin bookkeeping: smallest |signed clearance| (metres) over every test that decided control

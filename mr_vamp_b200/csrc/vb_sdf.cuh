@@ -36,6 +36,13 @@ namespace vb
         return __ldg(g.cell + (iz * g.ny + iy) * g.nx + ix);
     }
 
+    // coarse level of the two-level lookup: true iff the coarse cell alone proves that no primitive touches a sphere
+    // of radius r centred in it (same test as grid_class's `free`, with the coarse grid's pad)
+    VB_D bool grid_coarse_free(const SdfView &g, uint2 cell, bool in, float r)
+    {
+        return in ? (__uint_as_float(cell.x) - g.pad > r) : (r < g.cover);
+    }
+
     // Classification of a sphere of radius r whose cell was fetched with grid_fetch; `reach` = radius of
     // the ball around the sphere centre that contains every sphere that will be tested against `mask`
     // (< 0: unknown).  Outside the grid every obstacle is at least `cover` away (cover == 0: unknown).
@@ -45,7 +52,7 @@ namespace vb
         const bool free_ = in ? (d - g.pad > r) : (r < g.cover);
         maybe = !free_;
         cert = in && (d + g.pad < r);
-        const bool covered = reach >= 0.f && reach + g.pad < kMaskReach;
+        const bool covered = reach >= 0.f && reach + g.pad < g.mask_reach;
         mask = !covered ? 0xffffffffu : (in ? cell.y : (reach < g.cover ? 0u : 0xffffffffu));
     }
 

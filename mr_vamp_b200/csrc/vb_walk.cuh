@@ -645,7 +645,7 @@ namespace vb
             bool classified = false;
             if (grid)
             {
-                Robot::env_fetch(col, c.bx, c.by, c.bz, env.sdf, cells, inside);
+                Robot::env_fetch(col, c.bx, c.by, c.bz, env.sdf, env.sdf_c, c.radius, cells, inside);
             }
 
             // ---------------- self collision ----------------
