@@ -805,7 +805,7 @@ namespace
     constexpr size_t kSdfMaxVoxels = size_t(4) << 20;
     constexpr float kSdfMinVoxel = 0.015f;
 
-    constexpr float kSdfCoarseVoxel = 0.08f;  // coarse level of the two-level guard lookup (vb_sdf.cuh)
+    constexpr float kSdfCoarseVoxel = 0.15f;  // coarse level of the two-level guard lookup (vb_sdf.cuh); swept 0.05 .. 0.3 m on B200
 
     bool sdf_geometry(const vb_env *env, vb::SdfView &g, float min_voxel_arg = kSdfMinVoxel)
     {
@@ -983,8 +983,13 @@ namespace
             VB_CUDA(cudaGetLastError());
             // coarse level: the same box at 8 cm voxels, when the fine grid is much finer than that
             v.sdf_c = vb::SdfView{};
-            const bool want_coarse = !std::getenv("VB_SDF_NO_COARSE") && 1.f / v.sdf.inv_h < 0.5f * kSdfCoarseVoxel;
-            if (want_coarse && sdf_geometry(env, v.sdf_c, kSdfCoarseVoxel))
+            float coarse_voxel = kSdfCoarseVoxel;
+            if (const char *cv = std::getenv("VB_SDF_COARSE"))  // development: voxel edge of the coarse level in metres
+            {
+                coarse_voxel = std::max(0.02f, static_cast<float>(std::atof(cv)));
+            }
+            const bool want_coarse = !std::getenv("VB_SDF_NO_COARSE") && 1.f / v.sdf.inv_h < 0.5f * coarse_voxel;
+            if (want_coarse && sdf_geometry(env, v.sdf_c, coarse_voxel))
             {
                 const size_t cv = static_cast<size_t>(v.sdf_c.nx) * v.sdf_c.ny * v.sdf_c.nz;
                 VB_CUDA(rep.sdf_c.reserve(cv * sizeof(uint2)));
