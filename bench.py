@@ -91,7 +91,7 @@ class ClockSampler:
                     self.rows.append([c.strip() for c in out.split(",")])
             except Exception:
                 pass
-            self._stop.wait(0.2)
+            self._stop.wait(0.03)
 
     def __enter__(self):
         self._t.start()
