@@ -154,6 +154,20 @@ int vb_fkcc_work_d(vb_ctx *, int slot, vb_robot, const float *base_xyz, const vb
 int vb_validate_motion_d(vb_ctx *, int slot, vb_robot, const float *base_xyz, const vb_env *, const float *starts_d,
                          const float *goals_d, size_t n_edges, int resolution, uint32_t *valid_bits_d,
                          float *margin_d_or_null);
+/* vb_validate_motion_noalloc_d: vb_validate_motion_d (verdicts only) for callers that cannot call cudaMalloc --
+ * code under CUDA graph capture, tight serving loops, harnesses that forbid allocation.  It has NO counterpart in
+ * the reference.  Its scratch memory (interpolant counts, their
+ * prefix, the scan's temporary storage) is a file-scope `static __device__` array of
+ * 2 * (VB_NOALLOC_MAX_EDGES + 64) * 4 + 65536 bytes (about 2.1 MB) that every GPU loading the library holds until
+ * exit; the call allocates and frees nothing.  n_edges > VB_NOALLOC_MAX_EDGES (also returned by
+ * vb_noalloc_max_edges()) is rejected with VB_ERR_ARG, an environment with an attachment with VB_ERR_STATE.  All
+ * calls share the one array per device: calls that overlap on the GPU (other streams, other contexts, other host
+ * threads) race on it -- serialise them.  Asynchronous on the slot's stream like the other _d entry points. */
+#define VB_NOALLOC_MAX_EDGES 262144
+size_t vb_noalloc_max_edges(void);
+int vb_validate_motion_noalloc_d(vb_ctx *, int slot, vb_robot, const float *base_xyz, const vb_env *,
+                                 const float *starts_d, const float *goals_d, size_t n_edges, int resolution,
+                                 uint32_t *valid_bits_d);
 /* configurations first .. first+n-1 of the synthetic stream, generated in registers (0 input bytes) */
 int vb_fkcc_random_d(vb_ctx *, int slot, vb_robot, const float *base_xyz, const vb_env *, uint64_t seed,
                      uint64_t first, size_t n, uint32_t *valid_bits_d);

@@ -65,6 +65,8 @@ _SIGNATURES = [
     ("vb_fkcc_d", C.c_int, [_vp, C.c_int, C.c_int, _f32p, _vp, _vp, C.c_size_t, _vp, _vp]),
     ("vb_fkcc_work_d", C.c_int, [_vp, C.c_int, C.c_int, _f32p, _vp, _vp, C.c_size_t, _vp, _vp]),
     ("vb_validate_motion_d", C.c_int, [_vp, C.c_int, C.c_int, _f32p, _vp, _vp, _vp, C.c_size_t, C.c_int, _vp, _vp]),
+    ("vb_noalloc_max_edges", C.c_size_t, []),
+    ("vb_validate_motion_noalloc_d", C.c_int, [_vp, C.c_int, C.c_int, _f32p, _vp, _vp, _vp, C.c_size_t, C.c_int, _vp]),
     ("vb_fkcc_random_d", C.c_int, [_vp, C.c_int, C.c_int, _f32p, _vp, C.c_uint64, C.c_uint64, C.c_size_t, _vp]),
     ("vb_timer_start", C.c_int, [_vp, C.c_int]),
     ("vb_timer_stop", C.c_int, [_vp, C.c_int, C.POINTER(C.c_double)]),

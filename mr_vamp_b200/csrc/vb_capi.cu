@@ -1502,6 +1502,116 @@ int vb_validate_motion_d(vb_ctx *ctx, int slot, vb_robot robot, const float *bas
     return run_motion_d(q, starts_d, goals_d, n, resolution, valid_bits_d, margin_d);
 }
 
+}  // extern "C"
+
+/* ---- allocation-free motion validation ---------------------------------------------------------- */
+// vb_validate_motion_d keeps its interpolant counts, their exclusive prefix and the scan's temporary storage in
+// grow-only cudaMalloc'ed buffers of the slot.  Callers that must not allocate (CUDA graph capture, tight serving
+// loops) get the same kernels over a fixed file-scope device array instead.  Every device that loads the library
+// holds the array until exit; every call shares it, so calls that overlap on the GPU race on it.
+namespace
+{
+    constexpr size_t kNoAllocMaxEdges = VB_NOALLOC_MAX_EDGES;
+    constexpr size_t kNoAllocWords = (kNoAllocMaxEdges + 1 + 63) / 64 * 64;  // counts / prefix: 256-byte multiples
+    constexpr size_t kNoAllocScanBytes = size_t(64) << 10;                   // cub::DeviceScan temporary storage
+    constexpr size_t kNoAllocBytes = 2 * kNoAllocWords * sizeof(uint32_t) + kNoAllocScanBytes;
+
+    static __device__ __align__(256) unsigned char vb_noalloc_scratch[kNoAllocBytes];
+
+    // In host code `vb_noalloc_scratch` is only a handle for the runtime's symbol table; the device address is looked
+    // up once per device, with that device current.
+    constexpr int kNoAllocMaxDevices = 64;
+    std::atomic<unsigned char *> g_noalloc_addr[kNoAllocMaxDevices];
+
+    int noalloc_scratch(int device, unsigned char **out)
+    {
+        if (device < 0 || device >= kNoAllocMaxDevices)
+        {
+            return fail(VB_ERR_ARG, "device id %d beyond the %d the static scratch table covers", device, kNoAllocMaxDevices);
+        }
+        unsigned char *p = g_noalloc_addr[device].load(std::memory_order_acquire);
+        if (!p)
+        {
+            VB_CUDA(cudaSetDevice(device));
+            void *addr = nullptr;
+            VB_CUDA(cudaGetSymbolAddress(&addr, vb_noalloc_scratch));
+            if (!addr)
+            {
+                return fail(VB_ERR_CUDA, "cudaGetSymbolAddress returned a null address for the static scratch array");
+            }
+            p = static_cast<unsigned char *>(addr);
+            g_noalloc_addr[device].store(p, std::memory_order_release);  // same value from every thread: a benign race
+        }
+        *out = p;
+        return VB_OK;
+    }
+}  // namespace
+
+extern "C" {
+
+size_t vb_noalloc_max_edges(void)
+{
+    return kNoAllocMaxEdges;
+}
+
+int vb_validate_motion_noalloc_d(vb_ctx *ctx, int slot, vb_robot robot, const float *base, const vb_env *env,
+                                 const float *starts_d, const float *goals_d, size_t n, int resolution,
+                                 uint32_t *valid_bits_d)
+{
+    if (!env || (n && (!starts_d || !goals_d || !valid_bits_d)))
+    {
+        return fail(VB_ERR_ARG, "vb_validate_motion_noalloc_d: null argument");
+    }
+    if (n > kNoAllocMaxEdges)
+    {
+        return fail(VB_ERR_ARG, "vb_validate_motion_noalloc_d: %zu edges exceed the static scratch array's maximum of %zu "
+                                "per call (split the batch, or use vb_validate_motion_d)", n, kNoAllocMaxEdges);
+    }
+    Query q;
+    VB_TRY(begin_query(ctx, slot, robot, base, env, q));
+    if (q.args.attach)
+    {
+        return fail(VB_ERR_STATE, "vb_validate_motion_noalloc_d: environments with an attachment need a per-launch scratch "
+                                  "column that is allocated on demand; use vb_validate_motion_d");
+    }
+    if (n == 0)
+    {
+        return VB_OK;
+    }
+    Slot &s = *q.slot;
+    unsigned char *scratch = nullptr;
+    VB_TRY(noalloc_scratch(s.device, &scratch));
+    uint32_t *counts = reinterpret_cast<uint32_t *>(scratch);
+    uint32_t *prefix = counts + kNoAllocWords;
+    void *scan_tmp = prefix + kNoAllocWords;
+    q.args.cfg = starts_d;
+    q.args.cfg_b = goals_d;
+    q.args.n = n;
+    q.args.bits = valid_bits_d;
+    q.args.margin = nullptr;
+    q.args.resolution = resolution > 0 ? resolution : q.ops->resolution;
+    // the array keeps the previous call's contents: the terminating count must start at zero, everything else the
+    // kernels read is rewritten first (counts[0..n) by edge_count, prefix[0..n] by the scan)
+    VB_CUDA(cudaMemsetAsync(counts + n, 0, sizeof(uint32_t), s.stream));
+    VB_CUDA(q.ops->edge_count(q.args, counts));
+    size_t tmp_bytes = 0;
+    VB_CUDA(cub::DeviceScan::ExclusiveSum(nullptr, tmp_bytes, counts, prefix, static_cast<int>(n + 1), s.stream));
+    if (tmp_bytes > kNoAllocScanBytes)
+    {
+        return fail(VB_ERR_STATE, "vb_validate_motion_noalloc_d: the scan wants %zu bytes of temporary storage, the static "
+                                  "array reserves %zu", tmp_bytes, kNoAllocScanBytes);
+    }
+    VB_CUDA(cub::DeviceScan::ExclusiveSum(scan_tmp, tmp_bytes, counts, prefix, static_cast<int>(n + 1), s.stream));
+    q.args.prefix = prefix;
+    fill_bits_kernel<<<static_cast<unsigned>(((n + 31) / 32 + 255) / 256), 256, 0, s.stream>>>(valid_bits_d, n);
+    VB_CUDA(cudaGetLastError());
+    int grid = 1;
+    VB_TRY(grid_for(q, n * 8 * 4, &grid));
+    VB_CUDA(q.ops->motion(q.args, false, grid));
+    ctx->launches += 4;
+    return VB_OK;
+}
+
 int vb_fkcc_random_d(vb_ctx *ctx, int slot, vb_robot robot, const float *base, const vb_env *env, uint64_t seed,
                      uint64_t first, size_t n, uint32_t *valid_bits_d)
 {
