@@ -26,6 +26,10 @@
  *   vb_validate             Helper::validate_configuration, bindings/common.hh:172-182 (joint limits + fkcc)
  *   vb_validate_motion      planning::validate_motion / validate_vector, planning/validate.hh:23-75,
  *                           and Path::validate, planning/plan.hh:155-168 (edges of a path in one call)
+ *   vb_validate_vector      planning::validate_vector(start, vector, distance, env), planning/validate.hh:23-65 --
+ *                           the form the planners' inner loops call (rrtc.hh:139,180; prm.hh; fcit.hh)
+ *   vb_connect_increments   RRTC's connect loop, planning/rrtc.hh:172-194 (all n_extensions increments of many
+ *                           attempts in one batch, first failing increment per attempt)
  *   vb_validate_path        Path::validate, planning/plan.hh:155-168 (first invalid edge)
  *   vb_shortcut_path        planning::shortcut_path, planning/simplify.hh:115-140 (all candidates in one batch)
  *   vb_validate_pairs       the fork's planned MultiRobotEnvironment::check_inter_robot_collisions
@@ -125,6 +129,20 @@ int vb_validate(vb_ctx *, vb_robot, const float *base_xyz, const vb_env *, const
 int vb_validate_motion(vb_ctx *, vb_robot, const float *base_xyz, const vb_env *, const float *starts,
                        const float *goals, size_t n_edges, int resolution, uint32_t *valid_bits,
                        float *margin_or_null);
+/* (start, vector, distance) form of an edge: validate_vector, planning/validate.hh:23-65.  The number of passes
+ * comes from `distances` exactly as in the reference (n = max(ceil(distance / 8 * resolution), 1)); the interpolants
+ * are start + vector * k/8 - i * vector / (8 n).  vb_validate_motion is the special case vector = goal - start,
+ * distance = |vector|. */
+int vb_validate_vector(vb_ctx *, vb_robot, const float *base_xyz, const vb_env *, const float *starts,
+                       const float *vectors, const float *distances, size_t n_edges, int resolution,
+                       uint32_t *valid_bits, float *margin_or_null);
+/* RRTC connect loop (planning/rrtc.hh:172-194) for n attempts: attempt i walks from from[i] towards to[i]
+ * (distances[i] = their distance as the caller's nearest-neighbour query returned it) in n_ext = ceil(distance /
+ * range) increments, prior += increment accumulated in float as the reference does.  n_valid[i] = number of
+ * increments validated before the first failure (the reference's i_extension at loop exit; == n_ext iff connected). */
+int vb_connect_increments(vb_ctx *, vb_robot, const float *base_xyz, const vb_env *, const float *from, const float *to,
+                          const float *distances, size_t n, float range, int resolution, uint32_t *n_valid,
+                          uint32_t *n_ext_or_null);
 /* Batch edge callers.
  * vb_validate_path: Path::validate, planning/plan.hh:155-168 -- all consecutive edges of `waypoints` [n][dim] in one
  *   batch; *first_invalid_edge = index of the first invalid edge, -1 if the path is valid.
@@ -154,10 +172,14 @@ int vb_fkcc_work_d(vb_ctx *, int slot, vb_robot, const float *base_xyz, const vb
 int vb_validate_motion_d(vb_ctx *, int slot, vb_robot, const float *base_xyz, const vb_env *, const float *starts_d,
                          const float *goals_d, size_t n_edges, int resolution, uint32_t *valid_bits_d,
                          float *margin_d_or_null);
+int vb_validate_vector_d(vb_ctx *, int slot, vb_robot, const float *base_xyz, const vb_env *, const float *starts_d,
+                         const float *vectors_d, const float *distances_d, size_t n_edges, int resolution,
+                         uint32_t *valid_bits_d, float *margin_d_or_null);
 /* vb_validate_motion_noalloc_d: vb_validate_motion_d (verdicts only) for callers that cannot call cudaMalloc --
  * code under CUDA graph capture, tight serving loops, harnesses that forbid allocation.  It has NO counterpart in
- * the reference.  Its scratch memory (interpolant counts, their
- * prefix, the scan's temporary storage) is a file-scope `static __device__` array of
+ * the reference.  It runs the prefix-array form of the motion
+ * kernels (one thread per interpolant), whose scratch memory (interpolant counts, their prefix, the scan's temporary
+ * storage) is a file-scope `static __device__` array of
  * 2 * (VB_NOALLOC_MAX_EDGES + 64) * 4 + 65536 bytes (about 2.1 MB) that every GPU loading the library holds until
  * exit; the call allocates and frees nothing.  n_edges > VB_NOALLOC_MAX_EDGES (also returned by
  * vb_noalloc_max_edges()) is rejected with VB_ERR_ARG, an environment with an attachment with VB_ERR_STATE.  All

@@ -57,6 +57,9 @@ _SIGNATURES = [
     ("vb_fkcc", C.c_int, [_vp, C.c_int, _f32p, _vp, _f32p, C.c_size_t, _u32p, _f32p]),
     ("vb_validate", C.c_int, [_vp, C.c_int, _f32p, _vp, _f32p, C.c_size_t, _u32p]),
     ("vb_validate_motion", C.c_int, [_vp, C.c_int, _f32p, _vp, _f32p, _f32p, C.c_size_t, C.c_int, _u32p, _f32p]),
+    ("vb_validate_vector", C.c_int, [_vp, C.c_int, _f32p, _vp, _f32p, _f32p, _f32p, C.c_size_t, C.c_int, _u32p, _f32p]),
+    ("vb_connect_increments", C.c_int, [_vp, C.c_int, _f32p, _vp, _f32p, _f32p, _f32p, C.c_size_t, C.c_float, C.c_int,
+                                        _u32p, _u32p]),
     ("vb_validate_pairs", C.c_int, [_vp, C.c_int, _f32p, C.c_int, _f32p, _vp, _f32p, _f32p, C.c_size_t, _u32p]),
     ("vb_dev_alloc", C.c_int, [_vp, C.c_int, C.c_size_t, C.POINTER(_vp)]),
     ("vb_dev_free", C.c_int, [_vp, C.c_int, _vp]),
@@ -65,6 +68,7 @@ _SIGNATURES = [
     ("vb_fkcc_d", C.c_int, [_vp, C.c_int, C.c_int, _f32p, _vp, _vp, C.c_size_t, _vp, _vp]),
     ("vb_fkcc_work_d", C.c_int, [_vp, C.c_int, C.c_int, _f32p, _vp, _vp, C.c_size_t, _vp, _vp]),
     ("vb_validate_motion_d", C.c_int, [_vp, C.c_int, C.c_int, _f32p, _vp, _vp, _vp, C.c_size_t, C.c_int, _vp, _vp]),
+    ("vb_validate_vector_d", C.c_int, [_vp, C.c_int, C.c_int, _f32p, _vp, _vp, _vp, _vp, C.c_size_t, C.c_int, _vp, _vp]),
     ("vb_noalloc_max_edges", C.c_size_t, []),
     ("vb_validate_motion_noalloc_d", C.c_int, [_vp, C.c_int, C.c_int, _f32p, _vp, _vp, _vp, C.c_size_t, C.c_int, _vp]),
     ("vb_fkcc_random_d", C.c_int, [_vp, C.c_int, C.c_int, _f32p, _vp, C.c_uint64, C.c_uint64, C.c_size_t, _vp]),
@@ -437,6 +441,33 @@ class Robot:
                                         _ptr(a), _ptr(b), n, resolution, _ptr(bits, _u32p), _ptr(mg)))
         ok = unpack_bits(bits, n)
         return (ok, mg) if margin else ok
+
+    def validate_vector_batch(self, starts, vectors, distances, env: Optional[Environment] = None, resolution: int = 0,
+                              margin: bool = False):
+        """planning::validate_vector(start, vector, distance, env) per edge (planning/validate.hh:23-65) -> bool[n]."""
+        a, v = self._configs(starts), self._configs(vectors)
+        d = _f32(distances).reshape(-1)
+        if a.shape != v.shape or d.shape[0] != a.shape[0]:
+            raise ValueError("starts, vectors and distances differ in shape")
+        n = a.shape[0]
+        bits = np.zeros((n + 31) // 32, dtype=np.uint32)
+        mg = np.zeros(n, dtype=np.float32) if margin else None
+        _check(lib().vb_validate_vector(self.ctx.handle, self.robot_id, _ptr(self.base), self._env(env).handle,
+                                        _ptr(a), _ptr(v), _ptr(d), n, resolution, _ptr(bits, _u32p), _ptr(mg)))
+        ok = unpack_bits(bits, n)
+        return (ok, mg) if margin else ok
+
+    def connect_increments(self, from_, to, distances, range_: float, env: Optional[Environment] = None, resolution: int = 0):
+        """RRTC's connect loop (planning/rrtc.hh:172-194) for many attempts in one batch ->
+        (n_valid uint32[n], n_ext uint32[n]); attempt i connects iff n_valid[i] == n_ext[i]."""
+        a, b = self._configs(from_), self._configs(to)
+        d = _f32(distances).reshape(-1)
+        n = a.shape[0]
+        n_valid = np.zeros(n, dtype=np.uint32)
+        n_ext = np.zeros(n, dtype=np.uint32)
+        _check(lib().vb_connect_increments(self.ctx.handle, self.robot_id, _ptr(self.base), self._env(env).handle, _ptr(a),
+                                           _ptr(b), _ptr(d), n, range_, resolution, _ptr(n_valid, _u32p), _ptr(n_ext, _u32p)))
+        return n_valid, n_ext
 
     def fk_batch(self, configs) -> np.ndarray:
         """Robot::sphere_fk -> float32[n, n_spheres, 4] (x, y, z, r), world frame."""

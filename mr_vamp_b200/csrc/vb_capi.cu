@@ -134,7 +134,7 @@ namespace
         cudaStream_t stream = nullptr;
         cudaStream_t stream2 = nullptr;  // second lane of the host-buffer pipeline (copy of chunk k+1 under the kernel of chunk k)
         cudaEvent_t ev0 = nullptr, ev1 = nullptr, evj = nullptr;
-        DevBuf in_a, in_a2, in_b, bits, margin, out, counts, prefix, scan_tmp, att;
+        DevBuf in_a, in_a2, in_b, in_b2, in_d, in_d2, bits, margin, out, scan_tmp, att;
     };
 }  // namespace
 
@@ -271,7 +271,7 @@ void vb_ctx_destroy(vb_ctx *ctx)
         cudaStreamSynchronize(s.stream2);
         cudaStreamDestroy(s.stream2);
         cudaEventDestroy(s.evj);
-        for (DevBuf *b : {&s.in_a, &s.in_a2, &s.in_b, &s.bits, &s.margin, &s.out, &s.counts, &s.prefix, &s.scan_tmp, &s.att})
+        for (DevBuf *b : {&s.in_a, &s.in_a2, &s.in_b, &s.in_b2, &s.in_d, &s.in_d2, &s.bits, &s.margin, &s.out, &s.scan_tmp, &s.att})
         {
             b->release();
         }
@@ -1177,47 +1177,29 @@ namespace
         return VB_OK;
     }
 
-    int run_motion_d(Query &q, const float *a_d, const float *b_d, size_t n, int resolution, uint32_t *bits_d,
-                     float *margin_d)
+    // Edges in (start, goal) form, or (start, vector, distance) form when vector_form (planning/validate.hh:23-65).
+    // One launch of the rake kernel (vb_kernels.cuh: motion_rake_kernel); it presets and writes the verdict words
+    // (and margins) itself and needs no scratch memory.
+    int run_motion_d(Query &q, const float *a_d, const float *b_d, const float *dist_d, bool vector_form, size_t n,
+                     int resolution, uint32_t *bits_d, float *margin_d)
     {
         if (n == 0)
         {
             return VB_OK;
         }
-        if (n >= (size_t(1) << 31))
-        {
-            return fail(VB_ERR_ARG, "at most 2^31 edges per call");
-        }
-        Slot &s = *q.slot;
         q.args.cfg = a_d;
         q.args.cfg_b = b_d;
+        q.args.dist = dist_d;
+        q.args.vector_form = vector_form ? 1 : 0;
         q.args.n = n;
         q.args.bits = bits_d;
         q.args.margin = margin_d;
         q.args.resolution = resolution > 0 ? resolution : q.ops->resolution;
-        // interpolants per edge -> exclusive prefix (prefix[n] = total, read by the kernel itself)
-        VB_CUDA(s.counts.reserve((n + 1) * sizeof(uint32_t)));
-        VB_CUDA(s.prefix.reserve((n + 1) * sizeof(uint32_t)));
-        VB_CUDA(cudaMemsetAsync(s.counts.as<uint32_t>() + n, 0, sizeof(uint32_t), s.stream));
-        VB_CUDA(q.ops->edge_count(q.args, s.counts.as<uint32_t>()));
-        size_t tmp_bytes = 0;
-        VB_CUDA(cub::DeviceScan::ExclusiveSum(nullptr, tmp_bytes, s.counts.as<uint32_t>(), s.prefix.as<uint32_t>(),
-                                              static_cast<int>(n + 1), s.stream));
-        VB_CUDA(s.scan_tmp.reserve(tmp_bytes));
-        VB_CUDA(cub::DeviceScan::ExclusiveSum(s.scan_tmp.p, tmp_bytes, s.counts.as<uint32_t>(),
-                                              s.prefix.as<uint32_t>(), static_cast<int>(n + 1), s.stream));
-        q.args.prefix = s.prefix.as<uint32_t>();
-        const unsigned fill_grid = static_cast<unsigned>(((n + 31) / 32 + 255) / 256);
-        fill_bits_kernel<<<fill_grid, 256, 0, s.stream>>>(bits_d, n);
-        if (margin_d)
-        {
-            fill_float_kernel<<<static_cast<unsigned>((n + 255) / 256), 256, 0, s.stream>>>(margin_d, n, 3.0e38f);
-        }
         int grid = 1;
-        // at least 8 interpolants per edge; the exact total stays on the device
-        VB_TRY(grid_for(q, n * 8 * 4, &grid));
-        VB_CUDA(q.ops->motion(q.args, margin_d != nullptr, grid));
-        q.ctx->launches += 4 + (margin_d ? 1 : 0);
+        // one edge per octet of 8 lanes at a time
+        VB_TRY(grid_for(q, n * 8, &grid));
+        VB_CUDA(q.ops->motion_rake(q.args, margin_d != nullptr, grid));
+        q.ctx->launches += 1;
         return VB_OK;
     }
 
@@ -1499,15 +1481,29 @@ int vb_validate_motion_d(vb_ctx *ctx, int slot, vb_robot robot, const float *bas
     }
     Query q;
     VB_TRY(begin_query(ctx, slot, robot, base, env, q));
-    return run_motion_d(q, starts_d, goals_d, n, resolution, valid_bits_d, margin_d);
+    return run_motion_d(q, starts_d, goals_d, nullptr, false, n, resolution, valid_bits_d, margin_d);
+}
+
+int vb_validate_vector_d(vb_ctx *ctx, int slot, vb_robot robot, const float *base, const vb_env *env,
+                         const float *starts_d, const float *vectors_d, const float *distances_d, size_t n,
+                         int resolution, uint32_t *valid_bits_d, float *margin_d)
+{
+    if (!env || (n && (!starts_d || !vectors_d || !distances_d || !valid_bits_d)))
+    {
+        return fail(VB_ERR_ARG, "vb_validate_vector_d: null argument");
+    }
+    Query q;
+    VB_TRY(begin_query(ctx, slot, robot, base, env, q));
+    return run_motion_d(q, starts_d, vectors_d, distances_d, true, n, resolution, valid_bits_d, margin_d);
 }
 
 }  // extern "C"
 
 /* ---- allocation-free motion validation ---------------------------------------------------------- */
-// vb_validate_motion_d keeps its interpolant counts, their exclusive prefix and the scan's temporary storage in
-// grow-only cudaMalloc'ed buffers of the slot.  Callers that must not allocate (CUDA graph capture, tight serving
-// loops) get the same kernels over a fixed file-scope device array instead.  Every device that loads the library
+// The prefix-array form of motion validation (edge_count_kernel -> exclusive scan -> motion_kernel: one thread per
+// interpolant) needs scratch memory: the interpolant counts, their exclusive prefix and the scan's temporary storage.
+// Callers that must not allocate (CUDA graph capture, tight serving loops) get it over a fixed file-scope device
+// array.  Every device that loads the library
 // holds the array until exit; every call shares it, so calls that overlap on the GPU race on it.
 namespace
 {
@@ -1593,7 +1589,9 @@ int vb_validate_motion_noalloc_d(vb_ctx *ctx, int slot, vb_robot robot, const fl
     // the array keeps the previous call's contents: the terminating count must start at zero, everything else the
     // kernels read is rewritten first (counts[0..n) by edge_count, prefix[0..n] by the scan)
     VB_CUDA(cudaMemsetAsync(counts + n, 0, sizeof(uint32_t), s.stream));
-    VB_CUDA(q.ops->edge_count(q.args, counts));
+    fill_bits_kernel<<<static_cast<unsigned>(((n + 31) / 32 + 255) / 256), 256, 0, s.stream>>>(valid_bits_d, n);
+    VB_CUDA(cudaGetLastError());
+    VB_CUDA(q.ops->edge_count(q.args, counts));  // (clears the verdict bit of edges too long for the 32-bit prefix)
     size_t tmp_bytes = 0;
     VB_CUDA(cub::DeviceScan::ExclusiveSum(nullptr, tmp_bytes, counts, prefix, static_cast<int>(n + 1), s.stream));
     if (tmp_bytes > kNoAllocScanBytes)
@@ -1603,8 +1601,6 @@ int vb_validate_motion_noalloc_d(vb_ctx *ctx, int slot, vb_robot robot, const fl
     }
     VB_CUDA(cub::DeviceScan::ExclusiveSum(scan_tmp, tmp_bytes, counts, prefix, static_cast<int>(n + 1), s.stream));
     q.args.prefix = prefix;
-    fill_bits_kernel<<<static_cast<unsigned>(((n + 31) / 32 + 255) / 256), 256, 0, s.stream>>>(valid_bits_d, n);
-    VB_CUDA(cudaGetLastError());
     int grid = 1;
     VB_TRY(grid_for(q, n * 8 * 4, &grid));
     VB_CUDA(q.ops->motion(q.args, false, grid));
@@ -1756,12 +1752,17 @@ int vb_validate(vb_ctx *ctx, vb_robot robot, const float *base, const vb_env *en
     return fkcc_host(ctx, robot, base, env, configs, n, valid_bits, nullptr, true);
 }
 
-int vb_validate_motion(vb_ctx *ctx, vb_robot robot, const float *base, const vb_env *env, const float *starts,
-                       const float *goals, size_t n, int resolution, uint32_t *valid_bits, float *margin)
+// Host-buffer edges: chunks on two streams per device like fkcc_host, so that the copies of chunk k+1 run under the
+// kernel of chunk k.  second = goals, or vectors when dist != nullptr.
+static constexpr size_t kEdgeChunk = size_t(1) << 19;  // edges per chunk (multiple of 32)
+
+static int motion_host(vb_ctx *ctx, vb_robot robot, const float *base, const vb_env *env, const float *starts,
+                       const float *second, const float *dist, size_t n, int resolution, uint32_t *valid_bits, float *margin,
+                       const char *who)
 {
-    if (!ctx || !env || (n && (!starts || !goals || !valid_bits)))
+    if (!ctx || !env || (n && (!starts || !second || !valid_bits)))
     {
-        return fail(VB_ERR_ARG, "vb_validate_motion: null argument");
+        return fail(VB_ERR_ARG, "%s: null argument", who);
     }
     const vb::RobotOps *ops = ops_of(robot);
     if (!ops)
@@ -1779,27 +1780,149 @@ int vb_validate_motion(vb_ctx *ctx, vb_robot robot, const float *base, const vb_
         Query q;
         VB_TRY(begin_query(ctx, static_cast<int>(i), robot, base, env, q));
         Slot &s = *q.slot;
-        const size_t words = (m + 31) / 32, bytes = m * ops->dim * sizeof(float);
-        VB_CUDA(s.in_a.reserve(bytes));
-        VB_CUDA(s.in_b.reserve(bytes));
-        VB_CUDA(s.bits.reserve(words * sizeof(uint32_t)));
+        const size_t chunk = std::min(m, kEdgeChunk), row = ops->dim * sizeof(float);
+        const bool two = m > chunk && !q.args.attach;  // attachment runs share one scratch buffer: one stream
+        VB_CUDA(s.in_a.reserve(chunk * row));
+        VB_CUDA(s.in_b.reserve(chunk * row));
+        if (dist)
+        {
+            VB_CUDA(s.in_d.reserve(chunk * sizeof(float)));
+        }
+        if (two)
+        {
+            VB_CUDA(s.in_a2.reserve(chunk * row));
+            VB_CUDA(s.in_b2.reserve(chunk * row));
+            if (dist)
+            {
+                VB_CUDA(s.in_d2.reserve(chunk * sizeof(float)));
+            }
+        }
+        VB_CUDA(s.bits.reserve((m + 31) / 32 * sizeof(uint32_t)));
         if (margin)
         {
             VB_CUDA(s.margin.reserve(m * sizeof(float)));
         }
-        VB_CUDA(cudaMemcpyAsync(s.in_a.p, starts + shards[i].lo * ops->dim, bytes, cudaMemcpyHostToDevice, s.stream));
-        VB_CUDA(cudaMemcpyAsync(s.in_b.p, goals + shards[i].lo * ops->dim, bytes, cudaMemcpyHostToDevice, s.stream));
-        VB_TRY(run_motion_d(q, s.in_a.as<float>(), s.in_b.as<float>(), m, resolution, s.bits.as<uint32_t>(),
-                            margin ? s.margin.as<float>() : nullptr));
-        VB_CUDA(cudaMemcpyAsync(valid_bits + shards[i].lo / 32, s.bits.p, words * sizeof(uint32_t),
-                                cudaMemcpyDeviceToHost, s.stream));
-        if (margin)
+        VB_CUDA(cudaEventRecord(s.evj, s.stream));
+        VB_CUDA(cudaStreamWaitEvent(s.stream2, s.evj, 0));
+        size_t k = 0;
+        for (size_t lo = 0; lo < m; lo += chunk, ++k)
         {
-            VB_CUDA(cudaMemcpyAsync(margin + shards[i].lo, s.margin.p, m * sizeof(float), cudaMemcpyDeviceToHost,
-                                    s.stream));
+            const size_t c = std::min(chunk, m - lo), g0 = shards[i].lo + lo;
+            const bool alt = two && (k & 1);
+            cudaStream_t st = alt ? s.stream2 : s.stream;
+            float *a_d = (alt ? s.in_a2 : s.in_a).as<float>(), *b_d = (alt ? s.in_b2 : s.in_b).as<float>();
+            float *d_d = dist ? (alt ? s.in_d2 : s.in_d).as<float>() : nullptr;
+            uint32_t *bits_d = s.bits.as<uint32_t>() + lo / 32;
+            float *margin_d = margin ? s.margin.as<float>() + lo : nullptr;
+            q.args.stream = st;
+            VB_CUDA(cudaMemcpyAsync(a_d, starts + g0 * ops->dim, c * row, cudaMemcpyHostToDevice, st));
+            VB_CUDA(cudaMemcpyAsync(b_d, second + g0 * ops->dim, c * row, cudaMemcpyHostToDevice, st));
+            if (dist)
+            {
+                VB_CUDA(cudaMemcpyAsync(d_d, dist + g0, c * sizeof(float), cudaMemcpyHostToDevice, st));
+            }
+            VB_TRY(run_motion_d(q, a_d, b_d, d_d, dist != nullptr, c, resolution, bits_d, margin_d));
+            VB_CUDA(cudaMemcpyAsync(valid_bits + g0 / 32, bits_d, (c + 31) / 32 * sizeof(uint32_t), cudaMemcpyDeviceToHost, st));
+            if (margin)
+            {
+                VB_CUDA(cudaMemcpyAsync(margin + g0, margin_d, c * sizeof(float), cudaMemcpyDeviceToHost, st));
+            }
         }
     }
     return vb_sync(ctx);
+}
+
+int vb_validate_motion(vb_ctx *ctx, vb_robot robot, const float *base, const vb_env *env, const float *starts,
+                       const float *goals, size_t n, int resolution, uint32_t *valid_bits, float *margin)
+{
+    return motion_host(ctx, robot, base, env, starts, goals, nullptr, n, resolution, valid_bits, margin, "vb_validate_motion");
+}
+
+int vb_validate_vector(vb_ctx *ctx, vb_robot robot, const float *base, const vb_env *env, const float *starts,
+                       const float *vectors, const float *distances, size_t n, int resolution, uint32_t *valid_bits,
+                       float *margin)
+{
+    if (n && !distances)
+    {
+        return fail(VB_ERR_ARG, "vb_validate_vector: null distances");
+    }
+    return motion_host(ctx, robot, base, env, starts, vectors, distances, n, resolution, valid_bits, margin, "vb_validate_vector");
+}
+
+// RRTC's connect loop (planning/rrtc.hh:172-194): from `from` towards `to` in n_ext = ceil(dist / range) equal
+// increments, each validated with validate_vector(prior, increment, increment_length) and prior += increment
+// accumulated in float exactly as the reference does; stops at the first failing increment.  All increments of all
+// attempts go to the device in ONE batch; n_valid[i] = the reference's i_extension when its loop ends (== n_ext[i]
+// iff the trees connect).  The reference's free_index < max_samples condition is the caller's to apply.
+int vb_connect_increments(vb_ctx *ctx, vb_robot robot, const float *base, const vb_env *env, const float *from,
+                          const float *to, const float *distances, size_t n, float range, int resolution,
+                          uint32_t *n_valid, uint32_t *n_ext_or_null)
+{
+    if (!ctx || !env || (n && (!from || !to || !distances || !n_valid)) || !(range > 0.f))
+    {
+        return fail(VB_ERR_ARG, "vb_connect_increments: bad arguments");
+    }
+    const vb::RobotOps *ops = ops_of(robot);
+    if (!ops)
+    {
+        return fail(VB_ERR_ARG, "unknown robot id %d", static_cast<int>(robot));
+    }
+    const size_t dim = static_cast<size_t>(ops->dim);
+    std::vector<size_t> first(n + 1, 0);
+    for (size_t i = 0; i < n; ++i)
+    {
+        const float ne = std::ceil(distances[i] / range);
+        if (!(ne < 1048576.f))
+        {
+            return fail(VB_ERR_ARG, "vb_connect_increments: attempt %zu needs %g extensions", i, static_cast<double>(ne));
+        }
+        first[i + 1] = first[i] + static_cast<size_t>(ne < 0.f ? 0.f : ne);
+    }
+    const size_t total = first[n];
+    std::vector<float> priors(total * dim), incs(total * dim), lens(total);
+    for (size_t i = 0; i < n; ++i)
+    {
+        const size_t ne = first[i + 1] - first[i];
+        if (ne == 0)
+        {
+            continue;
+        }
+        const float inv = 1.0F / static_cast<float>(ne), len = distances[i] / static_cast<float>(ne);
+        float prior[16], inc[16];
+        for (size_t j = 0; j < dim; ++j)
+        {
+            prior[j] = from[i * dim + j];
+            inc[j] = (to[i * dim + j] - from[i * dim + j]) * inv;
+        }
+        for (size_t k = 0; k < ne; ++k)
+        {
+            float *p = priors.data() + (first[i] + k) * dim, *v = incs.data() + (first[i] + k) * dim;
+            for (size_t j = 0; j < dim; ++j)
+            {
+                p[j] = prior[j];
+                v[j] = inc[j];
+                prior[j] = prior[j] + inc[j];
+            }
+            lens[first[i] + k] = len;
+        }
+    }
+    std::vector<uint32_t> bits((total + 31) / 32);
+    VB_TRY(motion_host(ctx, robot, base, env, priors.data(), incs.data(), lens.data(), total, resolution, bits.data(), nullptr,
+                       "vb_connect_increments"));
+    for (size_t i = 0; i < n; ++i)
+    {
+        size_t k = first[i];
+        while (k < first[i + 1] && ((bits[k >> 5] >> (k & 31)) & 1u))
+        {
+            ++k;
+        }
+        n_valid[i] = static_cast<uint32_t>(k - first[i]);
+        if (n_ext_or_null)
+        {
+            n_ext_or_null[i] = static_cast<uint32_t>(first[i + 1] - first[i]);
+        }
+    }
+    return VB_OK;
 }
 
 }  // extern "C"

@@ -57,6 +57,8 @@ namespace vb
         int attach;            // use the attachment trace
         float sphere_radius;   // robots::sphere global radius (robots/sphere/fk.hh:16)
         float edge_len[2];     // synthetic edges: length range
+        const float *dist;     // edges in (start, vector, distance) form: distances [n] (validate_vector), else null
+        int vector_form;       // cfg_b holds vectors (goal - start) instead of goals
         cudaStream_t stream;
     };
 
@@ -624,8 +626,9 @@ namespace vb
     // long edge simply occupies more threads; verdicts are AND-reduced with atomicAnd.
     constexpr int kRake = 8;
 
+    // number of rake passes as a float (not yet cast: the caller rejects values the cast cannot hold)
     template <int D>
-    VB_HD uint32_t edge_passes(const float *qa, const float *qb, int resolution)
+    VB_HD float edge_passes(const float *qa, const float *qb, int resolution)
     {
         // squared_l2_norm (vector/interface.hh:407-410): rows are added first, then the 8 lanes are
         // folded as ((s0+s4)+(s2+s6)) + ((s1+s5)+(s3+s7)) (vector/avx.hh:442-452)
@@ -637,9 +640,14 @@ namespace vb
         }
         const float ss = VB_ADD(VB_ADD(VB_ADD(s[0], s[4]), VB_ADD(s[2], s[6])), VB_ADD(VB_ADD(s[1], s[5]), VB_ADD(s[3], s[7])));
         const float dist = sqrtf(ss);
-        const float nf = fmaxf(ceilf(dist / static_cast<float>(kRake) * static_cast<float>(resolution)), 1.f);
-        return static_cast<uint32_t>(nf);
+        return fmaxf(ceilf(dist / static_cast<float>(kRake) * static_cast<float>(resolution)), 1.f);
     }
+
+    // Prefix-array form of the motion kernels (only the allocation-free entry point still uses it: at most 2^18 edges
+    // per launch).  An edge of kMaxPrefixPasses passes or more (> 255 rad at resolution 32; also NaN / Inf lengths)
+    // would overflow the 32-bit interpolant prefix: it gets no interpolants and is reported invalid.  The verdict
+    // words must have been preset before this kernel runs.
+    constexpr float kMaxPrefixPasses = 1024.f;
 
     template <class Robot>
     __global__ void edge_count_kernel(const LaunchArgs a, uint32_t *counts)
@@ -655,7 +663,14 @@ namespace vb
             qa[j] = a.cfg[e * Robot::kDim + j];
             qb[j] = a.cfg_b[e * Robot::kDim + j];
         }
-        counts[e] = kRake * edge_passes<Robot::kDim>(qa, qb, a.resolution);
+        const float nf = edge_passes<Robot::kDim>(qa, qb, a.resolution);
+        if (!(nf < kMaxPrefixPasses))
+        {
+            counts[e] = 0u;
+            atomicAnd(a.bits + (e >> 5), ~(1u << (e & 31)));
+            return;
+        }
+        counts[e] = kRake * static_cast<uint32_t>(nf);
     }
 
     template <class Robot>
@@ -755,6 +770,169 @@ namespace vb
             if (alive && !ok)
             {
                 atomicAnd(a.bits + (e >> 5), ~(1u << (e & 31)));
+            }
+        }
+    }
+    // ---- K3r: motion validation, one rake block per octet, passes in the reference's order ---------------
+    // planning/validate.hh:23-65 (validate_vector).  The 8 lanes of an octet are the 8 interpolants of one rake
+    // block of ONE edge; the octet walks that edge's passes one after the other exactly as the reference's loop
+    // does (block = start + vector * percents, then block -= backstep per pass; same recurrence, bit-identical
+    // interpolants), stops at the first colliding pass and then takes the next edge of its CTA's range from a
+    // shared-memory counter.  Refuted edges therefore never run their later passes, no lane waits for an edge
+    // that is longer than its neighbours', and there is neither a prefix array nor a search: one launch, no
+    // scratch memory.  a.cfg = starts; a.cfg_b = goals, or vectors when a.vector_form (then a.dist = distances).
+    // Edges whose length is not finite (or beyond 2^31 passes) are reported invalid; the reference's cast is
+    // undefined there.
+    template <int D>
+    VB_HD float edge_norm(const float *v)
+    {
+        // squared_l2_norm (vector/interface.hh:407-410): rows are added first, then the 8 lanes are
+        // folded as ((s0+s4)+(s2+s6)) + ((s1+s5)+(s3+s7)) (vector/avx.hh:442-452)
+        float s[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
+        for (int j = 0; j < D; ++j)
+        {
+            s[j & 7] = (j < 8) ? VB_MUL(v[j], v[j]) : VB_ADD(s[j & 7], VB_MUL(v[j], v[j]));
+        }
+        const float ss = VB_ADD(VB_ADD(VB_ADD(s[0], s[4]), VB_ADD(s[2], s[6])), VB_ADD(VB_ADD(s[1], s[5]), VB_ADD(s[3], s[7])));
+        return sqrtf(ss);
+    }
+
+    // kMargin: the lane-serial reference-ordered walk, min |clearance| over the executed interpolants per edge
+    template <class Robot, bool kMargin>
+    __global__ void __launch_bounds__(block_threads<Robot>(), Robot::kCtasPerSm) motion_rake_kernel(const __grid_constant__ LaunchArgs a)
+    {
+        __shared__ unsigned next_edge;  // edges of this CTA's range handed out so far
+        const Scratch prims = stage_env<Robot>(a, !kMargin);
+        int cstate = -1;
+        const int lane = threadIdx.x & 31;
+        const unsigned oct_bit = 1u << (lane & ~7);
+        // contiguous range of edges per CTA, boundaries on multiples of 32: the CTA owns its verdict words
+        const size_t per = ((a.n + gridDim.x - 1) / gridDim.x + 31) / 32 * 32;
+        const size_t e_lo = min(a.n, static_cast<size_t>(blockIdx.x) * per), e_hi = min(a.n, e_lo + per);
+        const unsigned count = static_cast<unsigned>(e_hi - e_lo);
+        for (size_t w = e_lo / 32 + threadIdx.x; w * 32 < e_hi; w += blockDim.x)
+        {
+            const size_t rem = a.n - w * 32;
+            a.bits[w] = rem >= 32 ? 0xffffffffu : ((1u << rem) - 1u);
+        }
+        if constexpr (kMargin)
+        {
+            for (size_t i = e_lo + threadIdx.x; i < e_hi; i += blockDim.x)
+            {
+                a.margin[i] = 3.0e38f;
+            }
+        }
+        if (threadIdx.x == 0)
+        {
+            next_edge = 0u;
+        }
+        __syncthreads();
+        constexpr unsigned kNone = 0xffffffffu;
+        unsigned e = kNone;  // octet-uniform: edge (offset in the CTA's range) this octet is walking
+        uint32_t pass = 0, n_pass = 1;
+        float x[Robot::kDim], back[Robot::kDim];
+#pragma unroll
+        for (int j = 0; j < Robot::kDim; ++j)
+        {
+            x[j] = back[j] = 0.f;
+        }
+        bool more = count > 0u;  // warp-uniform: the range may still hold edges nobody has taken
+        const float pct = static_cast<float>((lane & 7) + 1) / static_cast<float>(kRake);
+        for (;;)
+        {
+            const unsigned want = __ballot_sync(0xffffffffu, e == kNone) & 0x01010101u;
+            if (more && want)
+            {
+                unsigned first = 0u;
+                if (lane == 0)
+                {
+                    first = atomicAdd(&next_edge, static_cast<unsigned>(__popc(want)));
+                }
+                first = __shfl_sync(0xffffffffu, first, 0);
+                more = first + static_cast<unsigned>(__popc(want)) < count;
+                const unsigned mine = first + static_cast<unsigned>(__popc(want & (oct_bit - 1u)));
+                if (e == kNone && mine < count)
+                {
+                    const size_t g = e_lo + mine;
+                    float qa[Robot::kDim], v[Robot::kDim];
+#pragma unroll
+                    for (int j = 0; j < Robot::kDim; ++j)
+                    {
+                        qa[j] = __ldg(a.cfg + g * Robot::kDim + j);
+                        const float second = __ldg(a.cfg_b + g * Robot::kDim + j);
+                        v[j] = a.vector_form ? second : VB_ADD(second, -qa[j]);
+                    }
+                    const float dist = a.dist ? __ldg(a.dist + g) : edge_norm<Robot::kDim>(v);
+                    const float nf = fmaxf(ceilf(dist / static_cast<float>(kRake) * static_cast<float>(a.resolution)), 1.f);
+                    if (!(nf < 2147483648.f))
+                    {
+                        if ((lane & 7) == 0)
+                        {
+                            atomicAnd(a.bits + (g >> 5), ~(1u << (g & 31)));
+                        }
+                    }
+                    else
+                    {
+                        e = mine;
+                        pass = 0u;
+                        n_pass = static_cast<uint32_t>(nf);
+                        const float denom = static_cast<float>(kRake * n_pass);
+#pragma unroll
+                        for (int j = 0; j < Robot::kDim; ++j)
+                        {
+                            x[j] = fmaf(v[j], pct, qa[j]);
+                            back[j] = v[j] / denom;
+                        }
+                    }
+                }
+            }
+            const bool alive = e != kNone;
+            // CTA-uniform exit, and the barrier that keeps the warps of the CTA on one instruction stream
+            if (!__syncthreads_or(alive || more))
+            {
+                break;
+            }
+            // the attachment trace is only used for the first pass (validate.hh:43-44 vs :58)
+            const bool attach = a.attach && pass == 0u;
+            bool ok = true;
+            if constexpr (kMargin)
+            {
+                if (alive)
+                {
+                    MinMargin mg;
+                    ok = check_config<Robot>(a, prims, x, attach, mg);
+                    atomicMin(reinterpret_cast<int *>(a.margin + e_lo + e), __float_as_int(mg.m));
+                }
+                __syncwarp();
+            }
+            else
+            {
+                ok = check_warp<Robot>(a, prims, x, alive, attach, cstate, true) || !alive;
+            }
+            const unsigned okm = __ballot_sync(0xffffffffu, ok);
+            if (alive)
+            {
+                if (((okm >> (lane & ~7)) & 0xffu) != 0xffu)
+                {
+                    if ((lane & 7) == 0)
+                    {
+                        const size_t g = e_lo + e;
+                        atomicAnd(a.bits + (g >> 5), ~(1u << (g & 31)));
+                    }
+                    e = kNone;
+                }
+                else if (++pass == n_pass)
+                {
+                    e = kNone;
+                }
+                else
+                {
+#pragma unroll
+                    for (int j = 0; j < Robot::kDim; ++j)
+                    {
+                        x[j] = VB_ADD(x[j], -back[j]);
+                    }
+                }
             }
         }
     }

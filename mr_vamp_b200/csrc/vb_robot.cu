@@ -3,6 +3,8 @@
 #include VB_TRACE_HEADER
 #include "vb_robot_ops.h"
 
+#include <atomic>
+
 namespace vb
 {
     using R = VB_TRACE;
@@ -20,21 +22,43 @@ namespace vb
     template <class K>
     static cudaError_t allow_smem(K kernel)
     {
-        return cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024);
+        // static + dynamic shared memory of a CTA may not exceed 227 KB
+        cudaFuncAttributes attr;
+        if (cudaError_t e = cudaFuncGetAttributes(&attr, kernel); e != cudaSuccess)
+        {
+            return e;
+        }
+        return cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                    227 * 1024 - static_cast<int>(attr.sharedSizeBytes));
     }
 
+    // cudaFuncAttributeMaxDynamicSharedMemorySize is a per-device attribute of the kernel: it is raised once for every
+    // device a launch is about to run on (the caller has made that device current), not once per process.
     static cudaError_t prepare()
     {
-        static cudaError_t once = [] {
-            cudaError_t e = allow_smem(fkcc_kernel<R, 0>);
-            if (e == cudaSuccess) e = allow_smem(fkcc_kernel<R, 1>);
-            if (e == cudaSuccess) e = allow_smem(fkcc_kernel<R, 2>);
-            if (e == cudaSuccess) e = allow_smem(fkcc_random_kernel<R>);
-            if (e == cudaSuccess) e = allow_smem(motion_kernel<R, true>);
-            if (e == cudaSuccess) e = allow_smem(motion_kernel<R, false>);
+        constexpr int kMaxDevices = 64;
+        static std::atomic<int> ready[kMaxDevices];
+        int dev = 0;
+        if (cudaError_t e = cudaGetDevice(&dev); e != cudaSuccess)
+        {
             return e;
-        }();
-        return once;
+        }
+        if (dev >= 0 && dev < kMaxDevices && ready[dev].load(std::memory_order_acquire))
+        {
+            return cudaSuccess;
+        }
+        cudaError_t e = allow_smem(fkcc_kernel<R, 0>);
+        if (e == cudaSuccess) e = allow_smem(fkcc_kernel<R, 1>);
+        if (e == cudaSuccess) e = allow_smem(fkcc_kernel<R, 2>);
+        if (e == cudaSuccess) e = allow_smem(fkcc_random_kernel<R>);
+        if (e == cudaSuccess) e = allow_smem(motion_kernel<R, false>);
+        if (e == cudaSuccess) e = allow_smem(motion_rake_kernel<R, false>);
+        if (e == cudaSuccess) e = allow_smem(motion_rake_kernel<R, true>);
+        if (e == cudaSuccess && dev >= 0 && dev < kMaxDevices)
+        {
+            ready[dev].store(1, std::memory_order_release);
+        }
+        return e;
     }
 
     static cudaError_t launch_fkcc(const LaunchArgs &a, int mode, int grid)
@@ -95,13 +119,24 @@ namespace vb
         {
             return e;
         }
+        (void)margin;  // the prefix-array kernel only serves the allocation-free entry point (verdicts)
+        motion_kernel<R, false><<<grid, kBlock, smem_bytes(a, true), a.stream>>>(a);
+        return cudaGetLastError();
+    }
+
+    static cudaError_t launch_motion_rake(const LaunchArgs &a, bool margin, int grid)
+    {
+        if (cudaError_t e = prepare(); e != cudaSuccess)
+        {
+            return e;
+        }
         if (margin)
         {
-            motion_kernel<R, true><<<grid, kBlock, smem_bytes(a, false), a.stream>>>(a);
+            motion_rake_kernel<R, true><<<grid, kBlock, smem_bytes(a, false), a.stream>>>(a);
         }
         else
         {
-            motion_kernel<R, false><<<grid, kBlock, smem_bytes(a, true), a.stream>>>(a);
+            motion_rake_kernel<R, false><<<grid, kBlock, smem_bytes(a, true), a.stream>>>(a);
         }
         return cudaGetLastError();
     }
@@ -158,6 +193,7 @@ namespace vb
             o.sphere_fk = &launch_sphere_fk;
             o.edge_count = &launch_edge_count;
             o.motion = &launch_motion;
+            o.motion_rake = &launch_motion_rake;
             o.limits = &launch_limits;
             o.occupancy = &occupancy;
             o.random_config = &host_random_config;

@@ -16,6 +16,7 @@ namespace vb
         cudaError_t (*sphere_fk)(const LaunchArgs &);
         cudaError_t (*edge_count)(const LaunchArgs &, uint32_t *counts_d);
         cudaError_t (*motion)(const LaunchArgs &, bool margin, int grid);
+        cudaError_t (*motion_rake)(const LaunchArgs &, bool margin, int grid);  // one rake block per octet, no scratch
         cudaError_t (*limits)(const LaunchArgs &);
         cudaError_t (*occupancy)(const LaunchArgs &, int *blocks_per_sm, int *threads);  // of the fkcc kernel
         void (*random_config)(uint64_t seed, uint64_t index, float *q);

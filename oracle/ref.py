@@ -14,7 +14,9 @@ import numpy as np
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
 _SO = os.path.join(_HERE, "_ref", "libvamp_ref.so")
+_SO_CLEAR = os.path.join(_HERE, "_ref", "libvamp_ref_clear.so")  # instrumented primitives (oracle/clear/)
 _lib = None
+_clear = None
 
 _f32p = C.POINTER(C.c_float)
 _u8p = C.POINTER(C.c_uint8)
@@ -25,7 +27,7 @@ def build(force: bool = False) -> bool:
     src = os.environ.get("VAMP_SRC", "/root/reference")
     if not os.path.isdir(os.path.join(src, "src", "impl", "vamp")):
         return os.path.exists(_SO)
-    args = ["make", "-C", _HERE, "-j8", f"VAMP_SRC={src}", "_ref/libvamp_ref.so"]
+    args = ["make", "-C", _HERE, "-j8", f"VAMP_SRC={src}", "all"]
     if force:
         args.insert(1, "-B")
     subprocess.run(args, check=True, stdout=subprocess.DEVNULL)
@@ -33,7 +35,7 @@ def build(force: bool = False) -> bool:
 
 
 def available() -> bool:
-    return os.path.exists(_SO)
+    return os.path.exists(_SO) and os.path.exists(_SO_CLEAR)
 
 
 class CaptView(C.Structure):
@@ -84,11 +86,27 @@ def lib():
         for fn in (L.vref_fkcc, L.vref_fkcc_packed, L.vref_fkcc_attach):
             fn.argtypes = [C.c_char_p, C.c_void_p, _f32p, C.c_size_t, _u8p, C.c_int]
         L.vref_validate_motion.argtypes = [C.c_char_p, C.c_void_p, _f32p, _f32p, C.c_size_t, _u8p, C.c_int]
+        L.vref_validate_vector.argtypes = [C.c_char_p, C.c_void_p, _f32p, _f32p, _f32p, C.c_size_t, _u8p, C.c_int]
+        L.vref_env_float_ptr.argtypes = [C.c_void_p]
+        L.vref_env_float_ptr.restype = C.c_void_p
         L.vref_validate.argtypes = [C.c_char_p, C.c_void_p, _f32p, C.c_size_t, _u8p]
         L.vref_scale.argtypes = [C.c_char_p, _f32p, C.c_size_t]
         L.vref_sphere_robot_set_radius.argtypes = [C.c_float]
         _lib = L
     return _lib
+
+
+def clear_lib():
+    """libvamp_ref_clear.so: the reference with instrumented primitives (min |signed clearance| per query)."""
+    global _clear
+    if _clear is None:
+        if not os.path.exists(_SO_CLEAR):
+            raise FileNotFoundError(f"{_SO_CLEAR} missing: run `make -C oracle` where the reference checkout is present")
+        L = C.CDLL(_SO_CLEAR)
+        L.vrefc_fkcc_clearance.argtypes = [C.c_char_p, C.c_void_p, _f32p, C.c_size_t, _u8p, _f32p, C.c_int]
+        L.vrefc_motion_clearance.argtypes = [C.c_char_p, C.c_void_p, _f32p, _f32p, _f32p, C.c_size_t, _u8p, _f32p, C.c_int]
+        _clear = L
+    return _clear
 
 
 def _f(a):
@@ -250,6 +268,53 @@ def validate_motion(robot, env, a, b, threads=1):
     if rc:
         raise RuntimeError(f"reference call failed ({rc})")
     return out.astype(bool)
+
+
+def validate_vector(robot, env, a, v, dist, threads=1):
+    """planning::validate_vector(start, vector, distance, env) per row."""
+    a, pa = _f(a)
+    v, pv = _f(v)
+    d, pd = _f(dist)
+    dim, _, _ = robot_info(robot)
+    n = a.reshape(-1, dim).shape[0]
+    out = np.zeros(n, dtype=np.uint8)
+    rc = lib().vref_validate_vector(robot.encode(), env.h, pa, pv, pd, n, out.ctypes.data_as(_u8p), threads)
+    if rc:
+        raise RuntimeError(f"reference call failed ({rc})")
+    return out.astype(bool)
+
+
+def fkcc_clearance(robot, env, cfg, threads=1):
+    """Reference verdict per configuration AND the smallest |signed clearance| (metres) over every collision test the
+    reference executed for it (fkcc_attach when the environment carries an attachment)."""
+    a, p = _f(cfg)
+    dim, _, _ = robot_info(robot)
+    n = a.reshape(-1, dim).shape[0]
+    ok = np.zeros(n, dtype=np.uint8)
+    clr = np.zeros(n, dtype=np.float32)
+    rc = clear_lib().vrefc_fkcc_clearance(robot.encode(), lib().vref_env_float_ptr(env.h), p, n, ok.ctypes.data_as(_u8p),
+                                          clr.ctypes.data_as(_f32p), threads)
+    if rc:
+        raise RuntimeError(f"clearance oracle call failed ({rc})")
+    return ok.astype(bool), clr
+
+
+def motion_clearance(robot, env, a, second, dist=None, threads=1):
+    """validate_motion (dist None: second = goals) or validate_vector (second = vectors): verdict and min |clearance|."""
+    a, pa = _f(a)
+    b, pb = _f(second)
+    dim, _, _ = robot_info(robot)
+    n = a.reshape(-1, dim).shape[0]
+    pd = None
+    if dist is not None:
+        d, pd = _f(dist)
+    ok = np.zeros(n, dtype=np.uint8)
+    clr = np.zeros(n, dtype=np.float32)
+    rc = clear_lib().vrefc_motion_clearance(robot.encode(), lib().vref_env_float_ptr(env.h), pa, pb, pd, n,
+                                            ok.ctypes.data_as(_u8p), clr.ctypes.data_as(_f32p), threads)
+    if rc:
+        raise RuntimeError(f"clearance oracle call failed ({rc})")
+    return ok.astype(bool), clr
 
 
 def validate(robot, env, cfg):

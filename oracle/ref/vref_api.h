@@ -77,6 +77,11 @@ int vref_fkcc_attach(const char *robot, const vref_env *, const float *cfg, size
 /* planning::validate_motion<Robot, 8, Robot::resolution>(a, b, env) (planning/validate.hh:67-75) */
 int vref_validate_motion(const char *robot, const vref_env *, const float *a, const float *b, size_t n,
                          uint8_t *valid, int threads);
+/* planning::validate_vector<Robot, 8, Robot::resolution>(start, vector, distance, env) (planning/validate.hh:23-65) */
+int vref_validate_vector(const char *robot, const vref_env *, const float *a, const float *v, const float *dist,
+                         size_t n, uint8_t *valid, int threads);
+/* the collision::Environment<float> inside a vref_env (handed to libvamp_ref_clear.so, oracle/clear/vrefc_api.h) */
+const void *vref_env_float_ptr(const vref_env *);
 /* Helper::validate_configuration: joint-limit test && validate_motion<Robot,8,1>(q,q) */
 int vref_validate(const char *robot, const vref_env *, const float *cfg, size_t n, uint8_t *valid);
 /* scale_configuration: [0,1]^d -> joint ranges, in place */

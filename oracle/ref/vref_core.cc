@@ -379,6 +379,23 @@ int vref_validate_motion(
     return 0;
 }
 
+int vref_validate_vector(const char *robot, const vref_env *env, const float *a, const float *v, const float *dist,
+                         size_t n, uint8_t *valid, int threads)
+{
+    const auto *vt = vref::find(robot);
+    if (not vt)
+    {
+        return -1;
+    }
+    vref::parallel(n, threads, env, [&](const vref::EnvV &ev, size_t lo, size_t hi) { vt->vector(ev, a, v, dist, lo, hi, valid); });
+    return 0;
+}
+
+const void *vref_env_float_ptr(const vref_env *env)
+{
+    return &env->f;
+}
+
 int vref_validate(const char *robot, const vref_env *env, const float *cfg, size_t n, uint8_t *valid)
 {
     const auto *vt = vref::find(robot);

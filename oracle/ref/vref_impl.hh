@@ -32,6 +32,7 @@ namespace vref
         void (*fkcc_packed)(const EnvV &, const float *, std::size_t, std::size_t, uint8_t *);
         void (*fkcc_attach)(const EnvV &, const float *, std::size_t, std::size_t, uint8_t *);
         void (*motion)(const EnvV &, const float *, const float *, std::size_t, std::size_t, uint8_t *);
+        void (*vector)(const EnvV &, const float *, const float *, const float *, std::size_t, std::size_t, uint8_t *);
         void (*validate)(const EnvV &, const float *, std::size_t, uint8_t *);
         void (*scale)(float *, std::size_t);
     };
@@ -132,6 +133,18 @@ namespace vref
             }
         }
 
+        static void vector(const EnvV &env, const float *a, const float *v, const float *dist, std::size_t lo,
+                           std::size_t hi, uint8_t *valid)
+        {
+            for (std::size_t i = lo; i < hi; ++i)
+            {
+                valid[i] = vamp::planning::validate_vector<Robot, rake, Robot::resolution>(
+                               make_config(a + i * dim), make_config(v + i * dim), dist[i], env) ?
+                               1 :
+                               0;
+            }
+        }
+
         // bindings/common.hh:172-182
         static void validate(const EnvV &env, const float *cfg, std::size_t n, uint8_t *valid)
         {
@@ -169,6 +182,7 @@ namespace vref
                 &fkcc_packed,
                 &fkcc_attach,
                 &motion,
+                &vector,
                 &validate,
                 &scale};
         }

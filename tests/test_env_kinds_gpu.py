@@ -6,9 +6,9 @@ import numpy as np
 import pytest
 
 from mr_vamp_b200 import scenes
+from conftest import apply_ref, judge
 
 pytestmark = pytest.mark.gpu
-BAND = 1e-5
 
 
 def _cfgs(robot, seed, n):
@@ -47,22 +47,18 @@ def test_capt_pointcloud_fkcc_and_edges(vb, ref, n_points):
     q = _cfgs(robot, 21, 20000)
     ok, mg = robot.fkcc_batch(q, env, margin=True)
     ok2 = robot.fkcc_batch(q, env)
-    want = ref.fkcc("panda_0_0", renv, q, threads=8)
-    hard = (ok != want) & (mg > BAND)
-    print(f"capt {n_points} pts: valid_ref={want.mean():.3f} differ={int((ok != want).sum())} hard={int(hard.sum())}")
-    assert hard.sum() == 0
-    assert not ((ok2 != ok) & (mg > BAND)).any()
+    want, clr = ref.fkcc_clearance("panda_0_0", renv, q, threads=8)
+    judge(f"capt {n_points} pts fkcc lane-serial", ok, want, clr)
+    judge(f"capt {n_points} pts fkcc warp walk", ok2, want, clr)
     a, b = q[:2000], np.clip(q[:2000] + np.float32(0.15), robot.lower_bounds, robot.lower_bounds + robot.ranges)
     # The reference checks 8 interpolants per block and opens a group's fine tests for ALL lanes when the
     # guard fires in ANY lane; with a point cloud the guard query is unreliable (bounding-sphere radius >
     # the tree's r_max), so block verdicts are not the AND of per-configuration verdicts.  The verdict
     # kernel reproduces the block coupling; the margin kernel keeps per-configuration semantics and only
-    # classifies disagreements.
-    _, e_mg = robot.validate_motion_batch(a, b, env, margin=True)
+    # has no use here: the band is judged by the oracle.
     e_ok = robot.validate_motion_batch(a, b, env)
-    e_want = ref.validate_motion("panda_0_0", renv, a, b, threads=8)
-    print(f"capt {n_points} pts edges: valid_ref={e_want.mean():.3f} differ={int((e_ok != e_want).sum())}")
-    assert not ((e_ok != e_want) & (e_mg > BAND)).any()
+    e_want, e_clr = ref.motion_clearance("panda_0_0", renv, a, b, threads=8)
+    judge(f"capt {n_points} pts edges", e_ok, e_want, e_clr)
 
 
 def test_capt_with_primitives(vb, ref):
@@ -70,9 +66,9 @@ def test_capt_with_primitives(vb, ref):
     env, renv = _upload_capt(vb, ref, _surface_cloud(3, 5000), extra_spec=scenes.cage()[:6])
     q = _cfgs(robot, 22, 10000)
     ok, mg = robot.fkcc_batch(q, env, margin=True)
-    want = ref.fkcc("ur5", renv, q, threads=8)
-    assert not ((ok != want) & (mg > BAND)).any()
-    assert not ((robot.fkcc_batch(q, env) != ok) & (mg > BAND)).any()
+    want, clr = ref.fkcc_clearance("ur5", renv, q, threads=8)
+    judge("capt + primitives ur5 lane-serial", ok, want, clr)
+    judge("capt + primitives ur5 warp walk", robot.fkcc_batch(q, env), want, clr)
 
 
 def test_capt_sphere_queries_match_collides_simd(vb, ref):
@@ -100,18 +96,15 @@ def test_heightfield(vb, ref):
     hf = vb.HeightField([0.0, 0.0, -0.45], [0.05, 0.05, 1.0], data)
     spec = [("heightfield", hf.off_scale, data), ("sphere", 0.9, 0.0, 0.9, 0.15), ("sphere", 0.5, 0.6, 1.0, 0.15)]
     env = scenes.apply(spec, vb.Environment())
-    from conftest import apply_ref
-
     renv = apply_ref(spec, ref.Env())
     for name in ("panda", "fetch"):
         robot = vb.Robot(name)
         q = _cfgs(robot, 31, 10000)
         ok, mg = robot.fkcc_batch(q, env, margin=True)
-        want = ref.fkcc("panda_0_0" if name == "panda" else name, renv, q, threads=8)
-        print(f"heightfield {name}: valid_ref={want.mean():.3f} differ={int((ok != want).sum())}")
+        want, clr = ref.fkcc_clearance("panda_0_0" if name == "panda" else name, renv, q, threads=8)
         assert name != "panda" or 0.02 < want.mean() < 0.98
-        assert not ((ok != want) & (mg > BAND)).any()
-        assert not ((robot.fkcc_batch(q, env) != ok) & (mg > BAND)).any()
+        judge(f"heightfield {name} lane-serial", ok, want, clr, mg)
+        judge(f"heightfield {name} warp walk", robot.fkcc_batch(q, env), want, clr)
 
 
 @pytest.mark.parametrize("name", ["panda", "ur5", "fetch"])
@@ -121,8 +114,6 @@ def test_attachment(vb, ref, name):
     spec = scenes.cage() if name != "fetch" else [("sphere", 0.95, 0.0, 0.9, 0.15), ("sphere", 0.7, 0.55, 1.2, 0.15),
                                                   ("sphere", 0.7, -0.5, 0.6, 0.2), ("sphere", 1.0, 0.3, 0.5, 0.2)]
     env = scenes.apply(spec, vb.Environment())
-    from conftest import apply_ref
-
     renv = apply_ref(spec, ref.Env())
     att = vb.Attachment([0.0, 0.0, 0.08], [0.0, 0.0, 0.0, 1.0])
     att.add_spheres([vb.Sphere([0.0, 0.0, 0.0], 0.04), vb.Sphere([0.0, 0.0, 0.07], 0.03), vb.Sphere([0.03, 0.0, 0.12], 0.025)])
@@ -131,16 +122,19 @@ def test_attachment(vb, ref, name):
     rn = "panda_0_0" if name == "panda" else name
     q = _cfgs(robot, 41, 10000)
     ok, mg = robot.fkcc_batch(q, env, margin=True)
-    want = ref.fkcc_attach(rn, renv, q, threads=8)
-    plain = ref.fkcc(rn, apply_ref(spec, ref.Env()), q, threads=8)
-    print(f"attach {name}: valid_ref={want.mean():.3f} (without attachment {plain.mean():.3f}) differ={int((ok != want).sum())}")
+    want, clr = ref.fkcc_clearance(rn, renv, q, threads=8)
+    assert np.array_equal(want, ref.fkcc_attach(rn, renv, q, threads=8)), "clearance oracle and reference disagree"
+    plain, plain_clr = ref.fkcc_clearance(rn, apply_ref(spec, ref.Env()), q, threads=8)
     assert (want != plain).any(), "the attachment must matter for this test to mean anything"
-    assert not ((ok != want) & (mg > BAND)).any()
-    assert not ((robot.fkcc_batch(q, env) != ok) & (mg > BAND)).any()
+    # (no cross-check of the library's margin output here: with an attachment it is not the same quantity as the oracle's
+    # figure -- up to 1.4 cm apart on ~4 % of the valid configurations although all 10 000 verdicts agree)
+    judge(f"attach {name} lane-serial", ok, want, clr)
+    judge(f"attach {name} fkcc", robot.fkcc_batch(q, env), want, clr)
     # edges: the attachment trace is used for the first rake pass only (planning/validate.hh:43-44 vs :58)
     a, b = q[:1500], np.clip(q[:1500] + np.float32(0.1), robot.lower_bounds, robot.lower_bounds + robot.ranges)
-    e_ok, e_mg = robot.validate_motion_batch(a, b, env, margin=True)
-    e_want = ref.validate_motion(rn, renv, a, b, threads=8)
-    assert not ((e_ok != e_want) & (e_mg > BAND)).any()
+    e_want, e_clr = ref.motion_clearance(rn, renv, a, b, threads=8)
+    assert np.array_equal(e_want, ref.validate_motion(rn, renv, a, b, threads=8)), "clearance oracle and reference disagree"
+    judge(f"attach {name} edges", robot.validate_motion_batch(a, b, env), e_want, e_clr)
+    judge(f"attach {name} edges lane-serial", robot.validate_motion_batch(a, b, env, margin=True)[0], e_want, e_clr)
     env.detach()
-    assert not ((robot.fkcc_batch(q, env) != plain) & (mg > BAND)).any()
+    judge(f"attach {name} detached", robot.fkcc_batch(q, env), plain, plain_clr)

@@ -7,11 +7,10 @@ import numpy as np
 import pytest
 
 from mr_vamp_b200 import scenes
-from conftest import apply_ref
+from conftest import apply_ref, judge, BAND
 
 pytestmark = pytest.mark.gpu
 
-BAND = 1e-5
 ROBOTS = ["sphere", "ur5", "panda", "fetch", "baxter"]
 REF_NAME = {"panda": "panda_0_0"}
 
@@ -19,14 +18,6 @@ REF_NAME = {"panda": "panda_0_0"}
 def _cfgs(robot, seed, n):
     rng = np.random.default_rng(seed)
     return (robot.lower_bounds + rng.random((n, robot.dimension), dtype=np.float32) * robot.ranges).astype(np.float32)
-
-
-def _compare(ok_gpu, margin, ok_ref, what):
-    diff = ok_gpu != ok_ref
-    hard = diff & (margin > BAND)
-    print(f"{what}: n={ok_ref.size} valid_ref={ok_ref.mean():.3f} differ={int(diff.sum())} "
-          f"in-band={int((diff & ~hard).sum())} hard={int(hard.sum())}")
-    assert hard.sum() == 0, f"{what}: {int(hard.sum())} verdict mismatches outside the {BAND} m band"
 
 
 @pytest.mark.parametrize("name", ROBOTS)
@@ -52,7 +43,8 @@ def test_panda_base_variants(vb, ref, base):
     env = scenes.apply(spec, vb.Environment())
     renv = apply_ref(spec, ref.Env())
     ok, mg = robot.fkcc_batch(q, env, margin=True)
-    _compare(ok, mg, ref.fkcc(base, renv, q), f"{base} cage")
+    want, clr = ref.fkcc_clearance(base, renv, q)
+    judge(f"{base} cage", ok, want, clr, mg)
 
 
 @pytest.mark.parametrize("name", ROBOTS)
@@ -65,8 +57,9 @@ def test_fkcc_verdicts(vb, ref, name, scene):
     q = _cfgs(robot, 3, 20000)
     ok, mg = robot.fkcc_batch(q, env, margin=True)
     ok2 = robot.fkcc_batch(q, env)
-    assert not ((ok != ok2) & (mg > BAND)).any(), "cooperative and lane-serial kernels disagree outside the band"
-    _compare(ok, mg, ref.fkcc(REF_NAME.get(name, name), renv, q, threads=8), f"{name}/{scene}")
+    want, clr = ref.fkcc_clearance(REF_NAME.get(name, name), renv, q, threads=8)
+    judge(f"{name}/{scene} lane-serial", ok, want, clr, mg)
+    judge(f"{name}/{scene} warp walk", ok2, want, clr)
 
 
 @pytest.mark.parametrize("name", ROBOTS)
@@ -80,13 +73,9 @@ def test_many_grid_stride_steps(vb, ref, name):
     env = scenes.apply(spec, vb.Environment())
     n = 1_500_000 if name != "sphere" else 6_000_000
     q = _cfgs(robot, 17, n)
-    ok_serial, mg = robot.fkcc_batch(q, env, margin=True)
+    want, clr = ref.fkcc_clearance(REF_NAME.get(name, name), apply_ref(spec, ref.Env()), q, threads=8)
     for rep in range(3):
-        ok = robot.fkcc_batch(q, env)
-        hard = (ok != ok_serial) & (mg > BAND)
-        assert not hard.any(), f"{name}: {int(hard.sum())} verdicts of the warp walk differ from the lane-serial walk (pass {rep})"
-    sub = slice(0, n, max(1, n // 60000))
-    _compare(ok[sub], mg[sub], ref.fkcc(REF_NAME.get(name, name), apply_ref(spec, ref.Env()), q[sub], threads=8), f"{name}/many steps")
+        judge(f"{name}/many steps (pass {rep})", robot.fkcc_batch(q, env), want, clr)
 
 
 def test_cage_known_answers(vb):
@@ -127,8 +116,18 @@ def test_validate_motion(vb, ref, name, scene):
     b[: n // 10] = _cfgs(robot, 8, n // 10)  # some long (PRM-shaped) edges
     ok, mg = robot.validate_motion_batch(a, b, env, margin=True)
     ok2 = robot.validate_motion_batch(a, b, env)
-    assert not ((ok != ok2) & (mg > BAND)).any(), "cooperative and lane-serial kernels disagree outside the band"
-    _compare(ok, mg, ref.validate_motion(REF_NAME.get(name, name), renv, a, b, threads=8), f"{name}/{scene} edges")
+    want, clr = ref.motion_clearance(REF_NAME.get(name, name), renv, a, b, threads=8)
+    # (the margin output is not cross-checked on edges: the reference walks 8 interpolants as one block, whose joint
+    # pruning and guard coupling execute tests a per-interpolant walk does not, and its approximate-sqrt pruning skips
+    # obstacles the exact pruning visits: the two figures are minima over different sets of tests)
+    judge(f"{name}/{scene} edges lane-serial", ok, want, clr)
+    judge(f"{name}/{scene} edges warp walk", ok2, want, clr)
+    # the (start, vector, distance) form the planners call (planning/validate.hh:23-65), with the distance as a
+    # planner passes it (its own float, not recomputed from the vector)
+    v = (b - a).astype(np.float32)
+    d = (np.linalg.norm(v.astype(np.float64), axis=1) * rng.uniform(0.97, 1.03, n)).astype(np.float32)
+    want_v, clr_v = ref.motion_clearance(REF_NAME.get(name, name), renv, a, v, d, threads=8)
+    judge(f"{name}/{scene} validate_vector", robot.validate_vector_batch(a, v, d, env), want_v, clr_v)
 
 
 def test_validate_joint_limits(vb, ref):

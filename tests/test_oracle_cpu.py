@@ -127,3 +127,50 @@ def test_port_interpolants_follow_the_rake(ref):
     assert pts.shape == (8 * n, 7)
     assert np.allclose(pts[7], b)
     assert np.allclose(sorted(pts[:, 0]), np.arange(1, 8 * n + 1) * 0.3 / (8 * n), atol=1e-6)
+
+
+# ---- the clearance oracle (oracle/clear): the judge of the 1e-5 m band -------------------------------------------
+@pytest.mark.parametrize("name,rn", [("panda", "panda_0_0"), ("ur5", "ur5"), ("fetch", "fetch"), ("baxter", "baxter"),
+                                     ("sphere", "sphere")])
+def test_clearance_oracle_gives_the_reference_verdicts(ref, name, rn):
+    """libvamp_ref_clear.so runs the same reference walk with wrapped primitives: its verdicts must be the
+    unmodified reference's, for fkcc, validate_motion and validate_vector."""
+    from mr_vamp_b200 import scenes
+    from conftest import apply_ref
+
+    dim = ref.robot_info(rn)[0]
+    rng = np.random.default_rng(5)
+    q = ref.scale(rn, rng.random((6000, dim), dtype=np.float32))
+    for spec in (scenes.cage(), scenes.random_scene(7)):
+        renv = apply_ref(spec, ref.Env())
+        ok, clr = ref.fkcc_clearance(rn, renv, q, threads=4)
+        assert np.array_equal(ok, ref.fkcc(rn, renv, q, threads=4))
+        assert (clr >= 0).all() and np.isfinite(clr[~ok]).all()
+        a, b = q[:800], q[800:1600]
+        okm, _ = ref.motion_clearance(rn, renv, a, b, threads=4)
+        assert np.array_equal(okm, ref.validate_motion(rn, renv, a, b, threads=4))
+        v = (b - a).astype(np.float32)
+        d = (np.linalg.norm(v, axis=1) * 1.01).astype(np.float32)
+        okv, _ = ref.motion_clearance(rn, renv, a, v, d, threads=4)
+        assert np.array_equal(okv, ref.validate_vector(rn, renv, a, v, d, threads=4))
+
+
+def test_clearance_oracle_known_answers(ref):
+    """robots::sphere (one sphere of radius 0.2 at q) against one obstacle sphere: the only test executed is that pair,
+    so the oracle's figure must be | |q - c| - (0.2 + R) |; same for a z-aligned box face and a height field."""
+    ref.lib().vref_sphere_robot_set_radius(0.2)
+    renv = ref.Env()
+    renv.add_sphere(0.0, 0.0, 0.0, 0.3)
+    q = np.array([[0.7, 0.0, 0.0], [0.0, 0.5000051, 0.0], [0.3, 0.0, 0.0], [0.0, 0.0, 0.49], [2.0, 1.0, 0.5]], np.float32)
+    ok, clr = ref.fkcc_clearance("sphere", renv, q)
+    want = np.abs(np.linalg.norm(q.astype(np.float64), axis=1) - 0.5)
+    assert list(ok) == [True, True, False, False, True]
+    assert np.allclose(clr, want, atol=2e-6), (clr, want)
+    assert clr[1] <= 1e-5 < clr[0]  # the second query is inside the band, the first is not
+    # z-aligned cuboid: unit axes, half extents (0.5, 0.5, 0.1) centred at z = -0.1 (top face at z = 0)
+    renv = ref.Env()
+    renv.add_cuboid(np.array([0, 0, -0.1, 1, 0, 0, 0, 1, 0, 0, 0, 1, 0.5, 0.5, 0.1], np.float32))
+    q = np.array([[0.1, 0.2, 0.25], [0.0, 0.0, 0.199995], [0.0, 0.0, 0.15]], np.float32)
+    ok, clr = ref.fkcc_clearance("sphere", renv, q)
+    assert list(ok) == [True, False, False]
+    assert np.allclose(clr, np.abs(q[:, 2] - 0.2), atol=2e-6), clr

@@ -52,12 +52,13 @@ def _ref_shortcut(ref, name, renv, w):
     return path
 
 
-def _band_edges(robot, env, w):
-    """Candidate edges whose verdict is decided within the 1e-5 m band (either answer is acceptable there)."""
+def _band_edges(ref, name, renv, w):
+    """Candidate edges whose verdict is decided within the 1e-5 m band (either answer is acceptable there), as judged
+    by the oracle's clearance (oracle/clear)."""
     n = len(w)
     ia, ib = np.triu_indices(n, k=1)
-    _, mg = robot.validate_motion_batch(w[ia], w[ib], env, margin=True)
-    return {(int(a), int(b)) for a, b, m in zip(ia, ib, mg) if m <= BAND}
+    _, clr = ref.motion_clearance(REF_NAME.get(name, name), renv, w[ia], w[ib], threads=8)
+    return {(int(a), int(b)) for a, b, m in zip(ia, ib, clr) if m <= BAND}
 
 
 @pytest.mark.parametrize("name", ["panda", "ur5"])
@@ -72,7 +73,7 @@ def test_shortcut_path_matches_reference(vb, ref, name, scene):
         got = robot.shortcut_path(w, env)
         want = w[_ref_shortcut(ref, name, renv, w)]
         if got.shape != want.shape or not np.array_equal(got, want):
-            assert _band_edges(robot, env, w), f"{name}/{scene}: shortcut_path differs from the reference outside the band"
+            assert _band_edges(ref, name, renv, w), f"{name}/{scene}: shortcut_path differs from the reference outside the band"
             continue
         checked += 1
     assert checked >= 7
@@ -94,8 +95,56 @@ def test_first_invalid_edge_matches_reference(vb, ref, name):
                 want = e
                 break
         if got != want:
-            assert _band_edges(robot, env, w), f"{name}: Path::validate differs from the reference outside the band"
+            assert _band_edges(ref, name, renv, w), f"{name}: Path::validate differs from the reference outside the band"
             continue
         seen_invalid += want >= 0
         assert robot.validate_path(w, env) == (want < 0)
     assert seen_invalid >= 1
+
+
+def _ref_connect(ref, rn, renv, a, b, dist, rng_range):
+    """planning/rrtc.hh:172-194 replayed with one reference validate_vector call per increment (float32 arithmetic
+    as the reference's vector ops: increment = vector * (1 / n_ext), prior += increment)."""
+    n_ext = int(np.ceil(np.float32(dist) / np.float32(rng_range)))
+    inc_len = np.float32(dist) / np.float32(n_ext)
+    inc = ((b - a).astype(np.float32) * (np.float32(1.0) / np.float32(n_ext))).astype(np.float32)
+    prior = a.astype(np.float32).copy()
+    i = 0
+    while i < n_ext and ref.validate_vector(rn, renv, prior[None, :], inc[None, :], np.array([inc_len], np.float32))[0]:
+        prior = (prior + inc).astype(np.float32)
+        i += 1
+    return i, n_ext
+
+
+@pytest.mark.parametrize("name,rng_range", [("panda", 1.0), ("ur5", 1.5)])
+def test_connect_increments_match_the_rrtc_loop(vb, ref, name, rng_range):
+    """vb_connect_increments: all n_extensions increments of many connect attempts in one batch; per attempt the number
+    of increments the reference's loop (planning/rrtc.hh:172-194) validates before it stops."""
+    robot = vb.Robot(name)
+    rn = REF_NAME.get(name, name)
+    spec = scenes.random_scene(11)
+    env = scenes.apply(spec, vb.Environment())
+    renv = apply_ref(spec, ref.Env())
+    rng = np.random.default_rng(77)
+    n = 300
+    lo = robot.lower_bounds
+    a = (lo + rng.random((n, robot.dimension), dtype=np.float32) * robot.ranges).astype(np.float32)
+    b = (lo + rng.random((n, robot.dimension), dtype=np.float32) * robot.ranges).astype(np.float32)
+    b[: n // 2] = np.clip(a[: n // 2] + rng.normal(0, 0.25, (n // 2, robot.dimension)), lo, lo + robot.ranges).astype(np.float32)
+    dist = np.linalg.norm((b - a).astype(np.float32), axis=1).astype(np.float32)  # what the NN query returns
+    n_valid, n_ext = robot.connect_increments(a, b, dist, rng_range, env)
+    want = [_ref_connect(ref, rn, renv, a[i], b[i], dist[i], rng_range) for i in range(n)]
+    assert np.array_equal(n_ext, [w[1] for w in want])
+    differ = [i for i in range(n) if n_valid[i] != want[i][0]]
+    for i in differ:
+        # either answer is acceptable only when an increment's verdict is decided inside the band
+        ne = int(n_ext[i])
+        inc = ((b[i] - a[i]) * (np.float32(1.0) / np.float32(ne))).astype(np.float32)
+        priors = np.stack([a[i]] * ne).astype(np.float32)
+        for k in range(1, ne):
+            priors[k] = (priors[k - 1] + inc).astype(np.float32)
+        _, clr = ref.motion_clearance(rn, renv, priors, np.stack([inc] * ne), np.full(ne, dist[i] / np.float32(ne), np.float32))
+        assert (clr <= BAND).any(), f"{name}: attempt {i}: {n_valid[i]} increments against the reference's {want[i][0]}"
+    connected = int((n_valid == n_ext).sum())
+    print(f"{name}: {n} connect attempts, {connected} connect, {len(differ)} differ inside the band")
+    assert 0 < connected < n
