@@ -86,6 +86,9 @@ int vb_robot_limits(vb_robot, float *lo, float *range);
 int vb_random_config(vb_robot, uint64_t seed, uint64_t index, float *q);
 /* edge `index` of the synthetic edge stream: a = config(2*index), b = a + len * dir clipped to limits */
 int vb_random_edge(vb_robot, uint64_t seed, uint64_t index, float len_lo, float len_hi, float *a, float *b);
+/* the same streams in batches: rows first .. first+n-1 into host buffers, or generated on the device */
+int vb_random_configs(vb_robot, uint64_t seed, uint64_t first, size_t n, float *q /* [n][dim] */);
+int vb_random_edges(vb_robot, uint64_t seed, uint64_t first, size_t n, float len_lo, float len_hi, float *a, float *b);
 /* robots::sphere global radius (robots/sphere/fk.hh:16-18); default 0.2 */
 int vb_ctx_set_sphere_radius(vb_ctx *, float r);
 
@@ -193,6 +196,15 @@ int vb_validate_motion_noalloc_d(vb_ctx *, int slot, vb_robot, const float *base
 /* configurations first .. first+n-1 of the synthetic stream, generated in registers (0 input bytes) */
 int vb_fkcc_random_d(vb_ctx *, int slot, vb_robot, const float *base_xyz, const vb_env *, uint64_t seed,
                      uint64_t first, size_t n, uint32_t *valid_bits_d);
+int vb_random_configs_d(vb_ctx *, int slot, vb_robot, uint64_t seed, uint64_t first, size_t n, float *q_d);
+int vb_random_edges_d(vb_ctx *, int slot, vb_robot, uint64_t seed, uint64_t first, size_t n, float len_lo, float len_hi,
+                      float *a_d, float *b_d);
+/* page-locked host memory for the host-buffer queries (they run at PCIe speed only from pinned memory):
+ * allocate it here, or pin an existing buffer once instead of paying the staging copy on every call */
+int vb_host_alloc(size_t bytes, void **ptr);
+int vb_host_free(void *ptr);
+int vb_host_register(void *ptr, size_t bytes);
+int vb_host_unregister(void *ptr);
 /* CUDA-event timer on the slot's stream */
 int vb_timer_start(vb_ctx *, int slot);
 int vb_timer_stop(vb_ctx *, int slot, double *milliseconds);

@@ -39,6 +39,14 @@ _SIGNATURES = [
     ("vb_robot_limits", C.c_int, [C.c_int, _f32p, _f32p]),
     ("vb_random_config", C.c_int, [C.c_int, C.c_uint64, C.c_uint64, _f32p]),
     ("vb_random_edge", C.c_int, [C.c_int, C.c_uint64, C.c_uint64, C.c_float, C.c_float, _f32p, _f32p]),
+    ("vb_random_configs", C.c_int, [C.c_int, C.c_uint64, C.c_uint64, C.c_size_t, _f32p]),
+    ("vb_random_edges", C.c_int, [C.c_int, C.c_uint64, C.c_uint64, C.c_size_t, C.c_float, C.c_float, _f32p, _f32p]),
+    ("vb_random_configs_d", C.c_int, [_vp, C.c_int, C.c_int, C.c_uint64, C.c_uint64, C.c_size_t, _vp]),
+    ("vb_random_edges_d", C.c_int, [_vp, C.c_int, C.c_int, C.c_uint64, C.c_uint64, C.c_size_t, C.c_float, C.c_float, _vp, _vp]),
+    ("vb_host_alloc", C.c_int, [C.c_size_t, C.POINTER(_vp)]),
+    ("vb_host_free", C.c_int, [_vp]),
+    ("vb_host_register", C.c_int, [_vp, C.c_size_t]),
+    ("vb_host_unregister", C.c_int, [_vp]),
     ("vb_ctx_set_sphere_radius", C.c_int, [_vp, C.c_float]),
     ("vb_env_create", C.c_int, [_vp, C.POINTER(_vp)]),
     ("vb_env_destroy", None, [_vp]),
@@ -128,6 +136,33 @@ def _ptr(a: Optional[np.ndarray], typ=_f32p):
 def unpack_bits(words: np.ndarray, n: int) -> np.ndarray:
     """uint32 verdict words -> bool[n] (bit i%32 of word i//32)."""
     return np.unpackbits(words.view(np.uint8), bitorder="little")[:n].astype(bool)
+
+
+def pinned_empty(shape, dtype) -> np.ndarray:
+    """numpy array over page-locked host memory (vb_host_alloc): what the host-buffer queries want for PCIe-speed copies.
+    The memory is released when the array (and every view of it) is garbage collected."""
+    dtype = np.dtype(dtype)
+    n = int(np.prod(shape))
+    p = _vp()
+    _check(lib().vb_host_alloc(max(1, n * dtype.itemsize), C.byref(p)))
+    buf = (C.c_char * max(1, n * dtype.itemsize)).from_address(p.value)
+
+    class _Owner:
+        def __init__(self, ptr):
+            self.ptr = ptr
+
+        def __del__(self):
+            try:
+                lib().vb_host_free(self.ptr)
+            except Exception:
+                pass
+
+    arr = np.frombuffer(buf, dtype=dtype, count=n).reshape(shape)
+    _PINNED_OWNERS[id(buf)] = (buf, _Owner(p))
+    return arr
+
+
+_PINNED_OWNERS: dict = {}
 
 
 # ---- shapes (collision/factory.hh; arithmetic in float32 like the reference's Eigen::*f types) ----
@@ -512,15 +547,13 @@ class Robot:
     # -- synthetic streams shared with the device-side generators ---------------------------------
     def random_configs(self, seed: int, first: int, n: int) -> np.ndarray:
         out = np.zeros((n, self.dimension), dtype=np.float32)
-        for i in range(n):
-            _check(lib().vb_random_config(self.robot_id, seed, first + i, _ptr(out[i])))
+        _check(lib().vb_random_configs(self.robot_id, seed, first, n, _ptr(out)))
         return out
 
     def random_edges(self, seed: int, first: int, n: int, len_lo: float, len_hi: float):
         a = np.zeros((n, self.dimension), dtype=np.float32)
         b = np.zeros((n, self.dimension), dtype=np.float32)
-        for i in range(n):
-            _check(lib().vb_random_edge(self.robot_id, seed, first + i, len_lo, len_hi, _ptr(a[i]), _ptr(b[i])))
+        _check(lib().vb_random_edges(self.robot_id, seed, first, n, len_lo, len_hi, _ptr(a), _ptr(b)))
         return a, b
 
 

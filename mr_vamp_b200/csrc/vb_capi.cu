@@ -1097,6 +1097,72 @@ namespace
         }
     }
 
+    // synthetic streams on the device (same generator as vb_random_config / vb_random_edge)
+    struct StreamLimits
+    {
+        float lo[16], range[16];
+        int dim;
+    };
+
+    __global__ void random_configs_kernel(const StreamLimits lim, uint64_t seed, uint64_t first, size_t n, float *out)
+    {
+        const size_t total = n * lim.dim;
+        for (size_t t = static_cast<size_t>(blockIdx.x) * blockDim.x + threadIdx.x; t < total;
+             t += static_cast<size_t>(gridDim.x) * blockDim.x)
+        {
+            const size_t i = t / lim.dim;
+            const int j = static_cast<int>(t % lim.dim);
+            out[t] = VB_ADD(lim.lo[j], VB_MUL(vb::u01(seed, first + i, j), lim.range[j]));  // as random_config<Robot>
+        }
+    }
+
+    __host__ __device__ void random_edge_row(const StreamLimits &lim, uint64_t seed, uint64_t index, float len_lo, float len_hi,
+                                             float *a, float *b)
+    {
+        // a = config(2 index); direction ~ normalised uniform cube sample; length uniform in [len_lo, len_hi];
+        // b clipped to the joint ranges ("RRTC-shaped" edges)
+        // (every product and sum is rounded on its own -- VB_ADD / VB_MUL -- so that host and device agree bit for bit)
+        float dir[16], norm = 0.f;
+        for (int j = 0; j < lim.dim; ++j)
+        {
+            a[j] = VB_ADD(lim.lo[j], VB_MUL(vb::u01(seed, 2 * index, j), lim.range[j]));
+            dir[j] = VB_ADD(VB_MUL(2.f, vb::u01(seed ^ 0xED6Eull, index, j)), -1.f);
+            norm = VB_ADD(norm, VB_MUL(dir[j], dir[j]));
+        }
+        norm = sqrtf(fmaxf(norm, 1e-12f));
+        const float len = VB_ADD(len_lo, VB_MUL(vb::u01(seed ^ 0xED6Eull, index, 63), VB_ADD(len_hi, -len_lo)));
+        for (int j = 0; j < lim.dim; ++j)
+        {
+            const float v = VB_ADD(a[j], VB_MUL(len, dir[j]) / norm);
+            b[j] = fminf(fmaxf(v, lim.lo[j]), VB_ADD(lim.lo[j], lim.range[j]));
+        }
+    }
+
+    __global__ void random_edges_kernel(const StreamLimits lim, uint64_t seed, uint64_t first, size_t n, float len_lo,
+                                        float len_hi, float *a, float *b)
+    {
+        for (size_t i = static_cast<size_t>(blockIdx.x) * blockDim.x + threadIdx.x; i < n;
+             i += static_cast<size_t>(gridDim.x) * blockDim.x)
+        {
+            float qa[16], qb[16];
+            random_edge_row(lim, seed, first + i, len_lo, len_hi, qa, qb);
+            for (int j = 0; j < lim.dim; ++j)
+            {
+                a[i * lim.dim + j] = qa[j];
+                b[i * lim.dim + j] = qb[j];
+            }
+        }
+    }
+
+    StreamLimits limits_of(const vb::RobotOps *o)
+    {
+        StreamLimits l{};
+        l.dim = o->dim;
+        std::copy_n(o->lo, 16, l.lo);
+        std::copy_n(o->range, 16, l.range);
+        return l;
+    }
+
     struct Query
     {
         vb_ctx *ctx;
@@ -2085,27 +2151,107 @@ int vb_validate_pairs(vb_ctx *ctx, vb_robot robot_a, const float *base_a, vb_rob
 
 int vb_random_edge(vb_robot r, uint64_t seed, uint64_t index, float len_lo, float len_hi, float *a, float *b)
 {
+    return vb_random_edges(r, seed, index, 1, len_lo, len_hi, a, b);
+}
+
+int vb_random_configs(vb_robot r, uint64_t seed, uint64_t first, size_t n, float *q)
+{
     const vb::RobotOps *o = ops_of(r);
-    if (!o || !a || !b)
+    if (!o || (n && !q))
     {
-        return fail(VB_ERR_ARG, "vb_random_edge: bad arguments");
+        return fail(VB_ERR_ARG, "vb_random_configs: bad arguments");
     }
-    // a = config(2 index); direction ~ normalised uniform cube sample; length uniform in [len_lo, len_hi];
-    // b clipped to the joint ranges ("RRTC-shaped" edges)
-    o->random_config(seed, 2 * index, a);
-    float dir[16], norm = 0.f;
-    for (int j = 0; j < o->dim; ++j)
+    for (size_t i = 0; i < n; ++i)
     {
-        dir[j] = 2.f * vb::u01(seed ^ 0xED6Eull, index, j) - 1.f;
-        norm += dir[j] * dir[j];
+        o->random_config(seed, first + i, q + i * o->dim);
     }
-    norm = std::sqrt(std::max(norm, 1e-12f));
-    const float len = len_lo + vb::u01(seed ^ 0xED6Eull, index, 63) * (len_hi - len_lo);
-    for (int j = 0; j < o->dim; ++j)
+    return VB_OK;
+}
+
+int vb_random_edges(vb_robot r, uint64_t seed, uint64_t first, size_t n, float len_lo, float len_hi, float *a, float *b)
+{
+    const vb::RobotOps *o = ops_of(r);
+    if (!o || (n && (!a || !b)))
     {
-        const float v = a[j] + len * dir[j] / norm;
-        b[j] = std::min(std::max(v, o->lo[j]), o->lo[j] + o->range[j]);
+        return fail(VB_ERR_ARG, "vb_random_edges: bad arguments");
     }
+    const StreamLimits lim = limits_of(o);
+    for (size_t i = 0; i < n; ++i)
+    {
+        random_edge_row(lim, seed, first + i, len_lo, len_hi, a + i * o->dim, b + i * o->dim);
+    }
+    return VB_OK;
+}
+
+int vb_random_configs_d(vb_ctx *ctx, int slot, vb_robot r, uint64_t seed, uint64_t first, size_t n, float *q_d)
+{
+    VB_TRY(check_slot(ctx, slot));
+    const vb::RobotOps *o = ops_of(r);
+    if (!o || (n && !q_d))
+    {
+        return fail(VB_ERR_ARG, "vb_random_configs_d: bad arguments");
+    }
+    Slot &s = ctx->slots[slot];
+    VB_CUDA(cudaSetDevice(s.device));
+    if (n)
+    {
+        random_configs_kernel<<<s.sm_count * 8, 256, 0, s.stream>>>(limits_of(o), seed, first, n, q_d);
+        VB_CUDA(cudaGetLastError());
+        ctx->launches += 1;
+    }
+    return VB_OK;
+}
+
+int vb_random_edges_d(vb_ctx *ctx, int slot, vb_robot r, uint64_t seed, uint64_t first, size_t n, float len_lo, float len_hi,
+                      float *a_d, float *b_d)
+{
+    VB_TRY(check_slot(ctx, slot));
+    const vb::RobotOps *o = ops_of(r);
+    if (!o || (n && (!a_d || !b_d)))
+    {
+        return fail(VB_ERR_ARG, "vb_random_edges_d: bad arguments");
+    }
+    Slot &s = ctx->slots[slot];
+    VB_CUDA(cudaSetDevice(s.device));
+    if (n)
+    {
+        random_edges_kernel<<<s.sm_count * 8, 256, 0, s.stream>>>(limits_of(o), seed, first, n, len_lo, len_hi, a_d, b_d);
+        VB_CUDA(cudaGetLastError());
+        ctx->launches += 1;
+    }
+    return VB_OK;
+}
+
+/* ---- pinned host memory for the host-buffer entry points ------------------------------------- */
+int vb_host_alloc(size_t bytes, void **ptr)
+{
+    if (!ptr)
+    {
+        return fail(VB_ERR_ARG, "vb_host_alloc: null argument");
+    }
+    VB_CUDA(cudaHostAlloc(ptr, std::max<size_t>(bytes, 16), cudaHostAllocPortable));
+    return VB_OK;
+}
+
+int vb_host_free(void *ptr)
+{
+    VB_CUDA(cudaFreeHost(ptr));
+    return VB_OK;
+}
+
+int vb_host_register(void *ptr, size_t bytes)
+{
+    if (!ptr || !bytes)
+    {
+        return fail(VB_ERR_ARG, "vb_host_register: bad arguments");
+    }
+    VB_CUDA(cudaHostRegister(ptr, bytes, cudaHostRegisterPortable));
+    return VB_OK;
+}
+
+int vb_host_unregister(void *ptr)
+{
+    VB_CUDA(cudaHostUnregister(ptr));
     return VB_OK;
 }
 

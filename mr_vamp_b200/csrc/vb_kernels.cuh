@@ -529,7 +529,7 @@ namespace vb
 #pragma unroll
         for (int j = 0; j < Robot::kDim; ++j)
         {
-            q[j] = Robot::lo(j) + u01(seed, i, j) * Robot::range(j);
+            q[j] = VB_ADD(Robot::lo(j), VB_MUL(u01(seed, i, j), Robot::range(j)));  // no FMA: host and device agree bit for bit
         }
     }
 

@@ -168,6 +168,18 @@ namespace vb
     }
 #endif
 
+#ifdef VB_STATS
+    extern "C" int vb_debug_walk_stats(unsigned long long *out32, int reset)
+    {
+        if (reset)
+        {
+            unsigned long long z[32] = {};
+            return cudaMemcpyToSymbol(vb_stats, z, sizeof(z));
+        }
+        return cudaMemcpyFromSymbol(out32, vb_stats, 32 * sizeof(unsigned long long));
+    }
+#endif
+
     const RobotOps *VB_OPS()
     {
         static RobotOps ops = [] {

@@ -57,6 +57,41 @@ namespace vb
 #define VB_TICK(k)
 #endif
 
+    // development aid (-DVB_STATS): work counters of the walk (scripts/walk_stats.py); warp sums / maxima per stage pass
+#ifdef VB_STATS
+    __device__ unsigned long long vb_stats[32];
+#define VB_STAT_ADD(k, v)                                                                          \
+    do                                                                                             \
+    {                                                                                              \
+        const unsigned s_ = __reduce_add_sync(0xffffffffu, static_cast<unsigned>(v));              \
+        if ((threadIdx.x & 31) == 0)                                                               \
+        {                                                                                          \
+            atomicAdd(&vb_stats[k], static_cast<unsigned long long>(s_));                          \
+        }                                                                                          \
+    } while (0)
+#define VB_STAT_MAX(k, v)                                                                          \
+    do                                                                                             \
+    {                                                                                              \
+        const unsigned s_ = __reduce_max_sync(0xffffffffu, static_cast<unsigned>(v));              \
+        if ((threadIdx.x & 31) == 0)                                                               \
+        {                                                                                          \
+            atomicAdd(&vb_stats[k], static_cast<unsigned long long>(s_));                          \
+        }                                                                                          \
+    } while (0)
+#define VB_STAT_ONE(k, v)                                                                          \
+    do                                                                                             \
+    {                                                                                              \
+        if ((threadIdx.x & 31) == 0)                                                               \
+        {                                                                                          \
+            atomicAdd(&vb_stats[k], static_cast<unsigned long long>(v));                           \
+        }                                                                                          \
+    } while (0)
+#else
+#define VB_STAT_ADD(k, v)
+#define VB_STAT_MAX(k, v)
+#define VB_STAT_ONE(k, v)
+#endif
+
     // The walk addresses its shared memory as INDICES from the start of the dynamic shared-memory window
     // (not as pointers carried through structs): the compiler then knows the address space and emits
     // LDS/STS/ATOMS instead of generic loads that resolve the window at run time.
@@ -356,19 +391,26 @@ namespace vb
         {
             const WalkTables w = Robot::walk_tables();
             const int lane = threadIdx.x & 31;
+            VB_STAT_ONE(10, np);
             for (int base = 0; base < np; base += 32)
             {
                 const int i = base + lane;
+                int nb_ = 0;
                 if (i < np)
                 {
                     const unsigned code = pairq(c)[i];
                     const int L = code & 31;
                     const SelfUnit u = T::unit(code >> 5);
-                    if (!done(c, L) && pair_unit(c, w, L, u))
+                    const bool skip_ = done(c, L);
+                    nb_ = skip_ ? 0 : u.b_count();
+                    if (!skip_ && pair_unit(c, w, L, u))
                     {
                         atomicOr(cmask(c), 1u << L);
                     }
                 }
+                VB_STAT_ONE(11, 1);
+                VB_STAT_ADD(12, nb_);
+                VB_STAT_MAX(13, nb_);
             }
             __syncwarp();
         }
@@ -436,7 +478,7 @@ namespace vb
         }
 
         // one fine sphere refs[idx] of configuration L against the tight candidates of its group
-        VB_D static bool fine_unit(const WalkCtx &c, const WalkTables &w, const PrimIndex &ix, int L, int idx)
+        VB_D static bool fine_unit(const WalkCtx &c, const WalkTables &w, const PrimIndex &ix, int L, int idx, int *n_tested = nullptr)
         {
             const int g = T::ref_group(idx) & 0x7fff;
             uint32_t tight = gmask(c)[32 * g + L];
@@ -449,6 +491,12 @@ namespace vb
                  o = next_candidate(tight, thigh, ix.first[5], cur))
             {
                 hit = object_hit(object_dist(c.prims, ix, o, s.x, s.y, s.z), s.r);
+#ifdef VB_STATS
+                if (n_tested)
+                {
+                    ++*n_tested;
+                }
+#endif
             }
             return hit;
         }
@@ -461,18 +509,23 @@ namespace vb
             const PrimIndex ix = prim_index(env);
             __syncwarp();
             const int nu = min(static_cast<int>(vol(cmask(c) + 1)), Robot::kPairQ);
+            VB_STAT_ONE(6, nu);
             for (int base = 0; base < nu; base += 32)
             {
                 const int i = base + lane;
+                int nt_ = 0;
                 if (i < nu)
                 {
                     const unsigned code = pairq(c)[i];
                     const int L = code & 31;
-                    if (!done(c, L) && fine_unit(c, w, ix, L, code >> 5))
+                    if (!done(c, L) && fine_unit(c, w, ix, L, code >> 5, &nt_))
                     {
                         atomicOr(cmask(c), 1u << L);
                     }
                 }
+                VB_STAT_ONE(7, 1);
+                VB_STAT_ADD(8, nt_);
+                VB_STAT_MAX(9, nt_);
             }
             __syncwarp();
             if (lane == 0)
@@ -495,9 +548,11 @@ namespace vb
             const bool has_other = (env.n_heightfields | env.n_capts) != 0;
             const PrimIndex ix = prim_index(env);
             const int n_obj = ix.first[5];
+            VB_STAT_ONE(1, ne);
             for (int base = 0; base < ne; base += 32)
             {
                 const int i = base + lane;
+                int nc_ = 0, gh_ = 0;
                 if (i < ne)
                 {
                     const unsigned code = envq(c)[i];
@@ -525,6 +580,7 @@ namespace vb
                                  o = next_candidate(low, high, n_obj, cursor))
                             {
                                 const ObjDist d = object_dist(c.prims, ix, o, b.x, b.y, b.z);
+                                ++nc_;
                                 ghit = ghit || object_hit(d, b.r);
                                 if (slack < 0.f || object_hit(d, b.r + slack))
                                 {
@@ -537,6 +593,7 @@ namespace vb
                             }
                             else if (ghit)
                             {
+                                gh_ = 1;
                                 gmask(c)[32 * g + L] = tight;
                                 const unsigned at = atomicAdd(cmask(c) + 1, static_cast<unsigned>(uc));
                                 for (int k = 0; k < uc; ++k)
@@ -569,6 +626,10 @@ namespace vb
                     }
                 }
                 __syncwarp();
+                VB_STAT_ONE(2, 1);
+                VB_STAT_ADD(3, nc_);
+                VB_STAT_MAX(4, nc_);
+                VB_STAT_ADD(5, gh_);
                 if (vol(cmask(c) + 1) >= static_cast<unsigned>(Robot::kPairQ) / 2)
                 {
                     fine_stage(env, c);
@@ -593,6 +654,8 @@ namespace vb
             const int lane = threadIdx.x & 31;
             const unsigned lt = (1u << lane) - 1u;
             const float *col = shm_f32() + c.wcol + lane;
+            VB_STAT_ONE(0, 1);
+            VB_STAT_ADD(19, collided ? 0 : 1);
             if (lane < 2)
             {
                 cmask(c)[lane] = 0u;
@@ -669,6 +732,13 @@ namespace vb
                 {
                     fired[wi] &= live & ~pfree[wi];
                     collided = collided || (fired[wi] & Robot::self_leaf_mask(wi)) != 0u;
+                    VB_STAT_ADD(14, __popc(fired[wi]));
+#ifdef VB_STATS
+                    {
+                        const unsigned any_ = __reduce_or_sync(kFull, fired[wi]);  // (all lanes: not inside VB_STAT_ONE's lane-0 branch)
+                        VB_STAT_ONE(15, __popc(any_));
+                    }
+#endif
                 }
                 VB_TICK(4);
                 // a-side filters of the fired groups, lane-parallel and straight-line; the surviving (group, a_i)
@@ -689,6 +759,7 @@ namespace vb
             {
                 __syncthreads();
             }
+            VB_STAT_ADD(18, collided ? 1 : 0);
             if (__all_sync(kFull, collided))
             {
                 return false;
@@ -749,6 +820,7 @@ namespace vb
 #pragma unroll
             for (int wi = 0; wi < Robot::kEnvWords; ++wi)
             {
+                VB_STAT_ADD(16, collided ? 0 : __popc(cert[wi] & ~Robot::env_const_mask(wi)));
                 const uint32_t mine = collided ? 0u : (maybe[wi] & ~Robot::env_const_mask(wi));
                 uint32_t any = __reduce_or_sync(kFull, mine);
                 while (any)

@@ -24,6 +24,25 @@ def test_shard_ranges_cover_the_batch_on_word_boundaries():
             assert all(hi - lo <= 32 * sharding.words_per_rank(n, world) for lo, hi in spans)
 
 
+def test_unique_id_rendezvous_through_a_file(tmp_path):
+    import threading
+
+    path = str(tmp_path / "id")
+    uid = bytes(range(128))
+    got = {}
+
+    def other(r):
+        got[r] = sharding.exchange_unique_id(lambda: b"", r, 3, path, timeout_s=20)
+
+    ts = [threading.Thread(target=other, args=(r,)) for r in (1, 2)]
+    for t in ts:
+        t.start()
+    assert sharding.exchange_unique_id(lambda: uid, 0, 3, path) == uid
+    for t in ts:
+        t.join()
+    assert got == {1: uid, 2: uid}
+
+
 def test_bit_packing_round_trip():
     rng = np.random.default_rng(0)
     for n in [1, 31, 32, 33, 1000]:
@@ -51,10 +70,15 @@ def _worker(rank, world, port, n, out_path):
     a, b = sharding.shard_range(n, rank, world)
     env = oracle_port.Env(scenes.cage())
     local = oracle_port.fkcc("panda", env, q[a:b]) if b > a else np.zeros(0, bool)
-    words = torch.from_numpy(sharding.pack_bits(local).view(np.int32).copy())
-    full = sharding.gather_verdicts(words, n)
+
+    def allgather(send):  # gloo stands in for the library's ncclAllGather (sharding.NcclComm) on this GPU-less box
+        recv = torch.empty(send.size * world, dtype=torch.int32)
+        dist.all_gather_into_tensor(recv, torch.from_numpy(send.view(np.int32).copy()))
+        return recv.numpy().view(np.uint32)
+
+    full = sharding.gather_verdicts(sharding.pack_bits(local), n, world, allgather)
     if rank == 0:
-        np.save(out_path, sharding.unpack_bits(full.numpy().view(np.uint32), n))
+        np.save(out_path, sharding.unpack_bits(full, n))
     dist.barrier()
     dist.destroy_process_group()
 
