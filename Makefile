@@ -16,7 +16,14 @@ HDRS := $(wildcard $(CSRC)/*.cuh) $(wildcard $(CSRC)/*.h) include/vamp_b200.h
 
 cap = $(shell echo $(1) | sed 's/./\U&/')
 
-all: $(LIB)
+PYEXT := $(PKG)/_core_ext$(shell $(PYTHON) -c "import sysconfig; print(sysconfig.get_config_var('EXT_SUFFIX'))")
+PYINC := $(shell $(PYTHON) -c "import pybind11, sysconfig; print('-I' + pybind11.get_include(), '-I' + sysconfig.get_paths()['include'])")
+
+all: $(LIB) $(PYEXT)
+
+# compiled Python module on the surface of the reference's nanobind module (pybind11; host code only, links the C ABI)
+$(PYEXT): $(CSRC)/vb_pymodule.cc include/vamp_b200.h $(LIB)
+	g++ -std=c++17 -O2 -fPIC -shared -fvisibility=hidden $(PYINC) $< -L$(PKG)/lib -lvamp_b200 -Wl,-rpath,'$$ORIGIN/lib' -o $@
 
 # The traces are generated from the VAMP checkout the library is built against; without a checkout
 # (e.g. on a GPU box that received prebuilt files) existing generated headers are used as they are.

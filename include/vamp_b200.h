@@ -23,6 +23,8 @@
  *                           robots/<robot>/fk.hh interleaved_sphere_fk[_attachment]; one verdict per
  *                           configuration (= the reference called on a broadcast block,
  *                           bindings/common.hh:172-182)
+ *   vb_sphere_validity      Helper::sphere_validate, bindings/common.hh:155-170 -> sphere_environment_get_collisions,
+ *                           collision/validity.hh:152-249 (per robot sphere: the obstacles it overlaps)
  *   vb_validate             Helper::validate_configuration, bindings/common.hh:172-182 (joint limits + fkcc)
  *   vb_validate_motion      planning::validate_motion / validate_vector, planning/validate.hh:23-75,
  *                           and Path::validate, planning/plan.hh:155-168 (edges of a path in one call)
@@ -115,6 +117,11 @@ int vb_env_commit(vb_env *);
 /* introspection (sorted order): kind 0 spheres[5] 1 capsules[9] 2 z-capsules[9] 3 cuboids[16] 4 z-cuboids[16];
  * rows are the shape floats followed by min_distance.  Returns the count via *n; writes when out != NULL. */
 int vb_env_export(const vb_env *, int kind, float *out, size_t *n);
+/* insertion sequence number (0-based over all vb_env_add_sphere/cuboid/capsule/heightfield calls since the last
+ * vb_env_clear) of every obstacle, in the library's object order: sorted spheres, capsules, z-capsules, cuboids,
+ * z-cuboids, then height fields.  This is how a binding maps the object numbers of vb_sphere_validity back to the
+ * names it keeps (the reference's shapes carry a std::string name, collision/shapes.hh). */
+int vb_env_object_ids(const vb_env *, uint32_t *ids, size_t *n);
 
 /* ---- queries, host buffers (sharded over the context's devices) --------------------------- */
 /* configs: row-major [n][dimension] float32; base_xyz: robot base offset in metres (Panda grid
@@ -125,6 +132,11 @@ int vb_sphere_fk(vb_ctx *, vb_robot, const float *base_xyz, const float *configs
  * margin_or_null: [n] smallest |signed clearance| in metres over the tests that decided the verdict. */
 int vb_fkcc(vb_ctx *, vb_robot, const float *base_xyz, const vb_env *, const float *configs, size_t n,
             uint32_t *valid_bits, float *margin_or_null);
+/* Per robot sphere (Robot::sphere_fk order) the obstacles it overlaps: counts[i * n_spheres + k] = how many, and
+ * the first min(count, cap) object numbers (vb_env_object_ids order) in hits[(i * n_spheres + k) * cap ..].  Point
+ * clouds are not reported (neither does the reference: validity.hh:152-249 has no CAPT loop). */
+int vb_sphere_validity(vb_ctx *, vb_robot, const float *base_xyz, const vb_env *, const float *configs, size_t n,
+                       uint32_t cap, uint32_t *hits, uint32_t *counts);
 /* joint-limit test && fkcc (Helper::validate_configuration) */
 int vb_validate(vb_ctx *, vb_robot, const float *base_xyz, const vb_env *, const float *configs, size_t n,
                 uint32_t *valid_bits);

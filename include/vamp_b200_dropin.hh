@@ -86,23 +86,40 @@ namespace vamp::b200
         return id;
     }
 
-    // Device-resident copy of a collision::Environment<float>; rebuilt only when constructed.
+    // scalar of an environment field: the value itself (Environment<float>) or lane 0 of its broadcast
+    // (Environment<FloatVector<rake>>: every lane holds the same number, collision/environment.hh:26-38)
+    template <typename T>
+    inline float scalar_of(const T &v)
+    {
+        if constexpr (std::is_arithmetic_v<T>)
+        {
+            return static_cast<float>(v);
+        }
+        else
+        {
+            return v.to_array()[0];
+        }
+    }
+
+    // Device-resident copy of a collision::Environment<float> (or of its vector form); rebuilt only when constructed.
     class DeviceEnvironment
     {
     public:
-        explicit DeviceEnvironment(const collision::Environment<float> &e, Context &ctx = Context::instance()) : ctx_(&ctx)
+        template <typename DataT>
+        explicit DeviceEnvironment(const collision::Environment<DataT> &e, Context &ctx = Context::instance()) : ctx_(&ctx)
         {
             check(vb_env_create(ctx.get(), &env_));
             try
             {
+                auto f = [](const auto &v) { return scalar_of(v); };
                 for (const auto &s : e.spheres)
                 {
-                    check(vb_env_add_sphere(env_, s.x, s.y, s.z, s.r));
+                    check(vb_env_add_sphere(env_, f(s.x), f(s.y), f(s.z), f(s.r)));
                 }
                 auto capsules = [&](const auto &list) {
                     for (const auto &c : list)
                     {
-                        const float raw[8] = {c.x1, c.y1, c.z1, c.xv, c.yv, c.zv, c.r, c.rdv};
+                        const float raw[8] = {f(c.x1), f(c.y1), f(c.z1), f(c.xv), f(c.yv), f(c.zv), f(c.r), f(c.rdv)};
                         check(vb_env_add_capsule(env_, raw));
                     }
                 };
@@ -111,9 +128,9 @@ namespace vamp::b200
                 auto cuboids = [&](const auto &list) {
                     for (const auto &c : list)
                     {
-                        const float raw[15] = {c.x,        c.y,        c.z,        c.axis_1_x, c.axis_1_y,
-                                               c.axis_1_z, c.axis_2_x, c.axis_2_y, c.axis_2_z, c.axis_3_x,
-                                               c.axis_3_y, c.axis_3_z, c.axis_1_r, c.axis_2_r, c.axis_3_r};
+                        const float raw[15] = {f(c.x),        f(c.y),        f(c.z),        f(c.axis_1_x), f(c.axis_1_y),
+                                               f(c.axis_1_z), f(c.axis_2_x), f(c.axis_2_y), f(c.axis_2_z), f(c.axis_3_x),
+                                               f(c.axis_3_y), f(c.axis_3_z), f(c.axis_1_r), f(c.axis_2_r), f(c.axis_3_r)};
                         check(vb_env_add_cuboid(env_, raw));
                     }
                 };
@@ -121,7 +138,7 @@ namespace vamp::b200
                 cuboids(e.z_aligned_cuboids);
                 for (const auto &h : e.heightfields)
                 {
-                    const float os[6] = {h.x, h.y, h.z, h.xs, h.ys, h.zs};
+                    const float os[6] = {f(h.x), f(h.y), f(h.z), f(h.xs), f(h.ys), f(h.zs)};
                     check(vb_env_add_heightfield(env_, os, h.xd, h.yd, h.data.data()));
                 }
                 for (const auto &c : e.pointclouds)
@@ -138,11 +155,11 @@ namespace vamp::b200
                 if (e.attachments)
                 {
                     const auto &a = *e.attachments;
-                    const float tf[7] = {a.tf_tx, a.tf_ty, a.tf_tz, a.tf_rx, a.tf_ry, a.tf_rz, a.tf_rw};
+                    const float tf[7] = {f(a.tf_tx), f(a.tf_ty), f(a.tf_tz), f(a.tf_rx), f(a.tf_ry), f(a.tf_rz), f(a.tf_rw)};
                     std::vector<float> sph;
                     for (const auto &s : a.spheres)
                     {
-                        sph.insert(sph.end(), {s.x, s.y, s.z, s.r});
+                        sph.insert(sph.end(), {f(s.x), f(s.y), f(s.z), f(s.r)});
                     }
                     check(vb_env_set_attachment(env_, tf, sph.data(), a.spheres.size()));
                 }

@@ -61,6 +61,8 @@ _SIGNATURES = [
     ("vb_env_clear_attachment", C.c_int, [_vp]),
     ("vb_env_commit", C.c_int, [_vp]),
     ("vb_env_export", C.c_int, [_vp, C.c_int, _f32p, C.POINTER(C.c_size_t)]),
+    ("vb_env_object_ids", C.c_int, [_vp, _u32p, C.POINTER(C.c_size_t)]),
+    ("vb_sphere_validity", C.c_int, [_vp, C.c_int, _f32p, _vp, _f32p, C.c_size_t, C.c_uint32, _u32p, _u32p]),
     ("vb_sphere_fk", C.c_int, [_vp, C.c_int, _f32p, _f32p, C.c_size_t, _f32p]),
     ("vb_fkcc", C.c_int, [_vp, C.c_int, _f32p, _vp, _f32p, C.c_size_t, _u32p, _f32p]),
     ("vb_validate", C.c_int, [_vp, C.c_int, _f32p, _vp, _f32p, C.c_size_t, _u32p]),
@@ -342,6 +344,7 @@ class Environment:
         self._h = _vp()
         _check(lib().vb_env_create(self.ctx.handle if self.ctx else None, C.byref(self._h)))
         self._dirty = True
+        self._names: list[str] = []  # by insertion id (vb_env_object_ids)
 
     def __del__(self):
         try:
@@ -352,18 +355,22 @@ class Environment:
 
     def add_sphere(self, s: Sphere):
         _check(lib().vb_env_add_sphere(self._h, s.x, s.y, s.z, s.r))
+        self._names.append(getattr(s, "name", ""))
         self._dirty = True
 
     def add_cuboid(self, c: Cuboid):
         _check(lib().vb_env_add_cuboid(self._h, _ptr(c.raw())))
+        self._names.append(getattr(c, "name", ""))
         self._dirty = True
 
     def add_capsule(self, c: Cylinder):
         _check(lib().vb_env_add_capsule(self._h, _ptr(c.raw())))
+        self._names.append(getattr(c, "name", ""))
         self._dirty = True
 
     def add_heightfield(self, h: HeightField):
         _check(lib().vb_env_add_heightfield(self._h, _ptr(h.off_scale), h.xd, h.yd, _ptr(h.data)))
+        self._names.append(getattr(h, "name", ""))
         self._dirty = True
 
     def add_capt_buffers(self, tests, aff_starts, aff_x, aff_y, aff_z, aabbs, aabb_top, r_point: float, nlog2: int):
@@ -387,6 +394,15 @@ class Environment:
     def detach(self):
         _check(lib().vb_env_clear_attachment(self._h))
         self._dirty = True
+
+    def object_names(self) -> list[str]:
+        """Obstacle names in the library's object order (sorted lists, then height fields)."""
+        n = C.c_size_t()
+        _check(lib().vb_env_object_ids(self._h, None, C.byref(n)))
+        ids = np.zeros(n.value, dtype=np.uint32)
+        if n.value:
+            _check(lib().vb_env_object_ids(self._h, _ptr(ids, _u32p), C.byref(n)))
+        return [self._names[i] for i in ids]
 
     def export(self, kind: int) -> np.ndarray:
         width = {0: 5, 1: 9, 2: 9, 3: 16, 4: 16}[kind]
@@ -519,6 +535,19 @@ class Robot:
     def fk(self, configuration) -> list[Sphere]:
         """vamp.<robot>.fk(configuration) -> list[Sphere] (bindings/common.hh:706-710)."""
         return [Sphere(s[:3], s[3]) for s in self.fk_batch(configuration)[0]]
+
+    def sphere_validity(self, configuration, environment: Optional[Environment] = None) -> list[list[str]]:
+        """vamp.<robot>.sphere_validity(configuration, environment) (bindings/common.hh:155-170,699-704): for every
+        collision sphere of the robot, the names of the obstacles it overlaps."""
+        q = self._configs(configuration)[:1]
+        env = self._env(environment)
+        names = env.object_names()
+        cap = max(1, len(names))
+        counts = np.zeros(self.n_spheres, dtype=np.uint32)
+        hits = np.zeros((self.n_spheres, cap), dtype=np.uint32)
+        _check(lib().vb_sphere_validity(self.ctx.handle, self.robot_id, _ptr(self.base), env.handle, _ptr(q), 1, cap,
+                                        _ptr(hits, _u32p), _ptr(counts, _u32p)))
+        return [[names[o] for o in hits[k, : counts[k]]] for k in range(self.n_spheres)]
 
     def validate_path(self, waypoints, environment: Optional[Environment] = None) -> bool:
         """Path.validate(env) (planning/plan.hh:155-168): every consecutive edge in ONE batch call."""

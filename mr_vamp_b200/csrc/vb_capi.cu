@@ -390,25 +390,31 @@ int vb_random_config(vb_robot r, uint64_t seed, uint64_t index, float *q)
 /* ================================ environment ================================================= */
 namespace
 {
+    // `id`: insertion sequence number over all vb_env_add_* calls of the environment (the caller's handle on an
+    // obstacle -- e.g. its name -- once the lists are sorted by min_distance)
     struct HostSphere
     {
         float x, y, z, r, min_d;
+        uint32_t id;
     };
     struct HostCapsule
     {
         float c[8];  // x1 y1 z1 xv yv zv r rdv
         float min_d;
+        uint32_t id;
     };
     struct HostCuboid
     {
         float c[15];  // centre, axis1, axis2, axis3, half extents
         float min_d;
+        uint32_t id;
     };
     struct HostHeightField
     {
         float os[6];
         size_t xd, yd;
         std::vector<float> data;
+        uint32_t id;
     };
     struct HostCapt
     {
@@ -483,6 +489,7 @@ struct vb_env
     std::vector<Replica> replicas;
     bool committed = false;
     uint64_t version = 0;
+    uint32_t next_id = 0;
 };
 
 namespace
@@ -594,7 +601,7 @@ int vb_env_add_sphere(vb_env *env, float x, float y, float z, float r)
         return fail(VB_ERR_ARG, "null environment");
     }
     // shapes.hh:236-239
-    env->spheres.push_back({x, y, z, r, std::sqrt(x * x + y * y + z * z) - r});
+    env->spheres.push_back({x, y, z, r, std::sqrt(x * x + y * y + z * z) - r, env->next_id++});
     sort_by_min_distance(env->spheres);
     env->committed = false;
     return VB_OK;
@@ -609,6 +616,7 @@ int vb_env_add_cuboid(vb_env *env, const float *c)
     HostCuboid h;
     std::copy_n(c, 15, h.c);
     h.min_d = cuboid_min_distance(c);
+    h.id = env->next_id++;
     // bindings/environment.cc:120-127
     auto &list = (c[11] == 1.f) ? env->zcuboids : env->cuboids;
     list.push_back(h);
@@ -626,6 +634,7 @@ int vb_env_add_capsule(vb_env *env, const float *c)
     HostCapsule h;
     std::copy_n(c, 8, h.c);
     h.min_d = capsule_min_distance(c);
+    h.id = env->next_id++;
     // bindings/environment.cc:134-141
     auto &list = (c[3] == 0.f && c[4] == 0.f) ? env->zcapsules : env->capsules;
     list.push_back(h);
@@ -645,6 +654,7 @@ int vb_env_add_heightfield(vb_env *env, const float *off_scale, size_t xd, size_
     h.xd = xd;
     h.yd = yd;
     h.data.assign(data, data + xd * yd);
+    h.id = env->next_id++;
     env->heightfields.push_back(std::move(h));
     env->committed = false;
     return VB_OK;
@@ -753,6 +763,27 @@ int vb_env_export(const vb_env *env, int kind, float *out, size_t *n)
             std::copy_n(v[i].c, 15, out + 16 * i);
             out[16 * i + 15] = v[i].min_d;
         }
+    }
+    return VB_OK;
+}
+
+int vb_env_object_ids(const vb_env *env, uint32_t *ids, size_t *n)
+{
+    if (!env || !n)
+    {
+        return fail(VB_ERR_ARG, "vb_env_object_ids: bad arguments");
+    }
+    std::vector<uint32_t> all;
+    for (const auto &s : env->spheres) all.push_back(s.id);
+    for (const auto &s : env->capsules) all.push_back(s.id);
+    for (const auto &s : env->zcapsules) all.push_back(s.id);
+    for (const auto &s : env->cuboids) all.push_back(s.id);
+    for (const auto &s : env->zcuboids) all.push_back(s.id);
+    for (const auto &s : env->heightfields) all.push_back(s.id);
+    *n = all.size();
+    if (ids)
+    {
+        std::copy(all.begin(), all.end(), ids);
     }
     return VB_OK;
 }
@@ -2147,6 +2178,90 @@ int vb_validate_pairs(vb_ctx *ctx, vb_robot robot_a, const float *base_a, vb_rob
         }
     }
     return vb_sync(ctx);
+}
+
+}  // extern "C"
+
+namespace
+{
+    // Helper::sphere_validate (bindings/common.hh:155-170) -> sphere_environment_get_collisions
+    // (collision/validity.hh:152-249): for ONE robot sphere, every primitive obstacle and height field it overlaps.
+    // One thread per (configuration, sphere); object numbering = the library's sorted order (vb_env_object_ids).
+    // The reference's min_distance break only skips obstacles that cannot touch the sphere, so all are tested.
+    __global__ void sphere_objects_kernel(const vb::EnvView env, const float4 *__restrict__ spheres, size_t n_spheres, uint32_t cap,
+                                          uint32_t *__restrict__ hits, uint32_t *__restrict__ counts)
+    {
+        const size_t i = static_cast<size_t>(blockIdx.x) * blockDim.x + threadIdx.x;
+        if (i >= n_spheres)
+        {
+            return;
+        }
+        const float4 s = spheres[i];
+        const vb::PrimIndex ix = vb::prim_index(env);
+        uint32_t c = 0;
+        for (int o = 0; o < ix.first[5]; ++o)
+        {
+            if (vb::object_hit(vb::object_dist(env.prims, ix, o, s.x, s.y, s.z), s.w))
+            {
+                if (c < cap)
+                {
+                    hits[i * cap + c] = static_cast<uint32_t>(o);
+                }
+                ++c;
+            }
+        }
+        for (int k = 0; k < env.n_heightfields; ++k)
+        {
+            if (vb::heightfield_value(env.heightfields[k], s.x, s.y, s.z, s.w) < 0.f)
+            {
+                if (c < cap)
+                {
+                    hits[i * cap + c] = static_cast<uint32_t>(ix.first[5] + k);
+                }
+                ++c;
+            }
+        }
+        counts[i] = c;
+    }
+}  // namespace
+
+extern "C" {
+
+int vb_sphere_validity(vb_ctx *ctx, vb_robot robot, const float *base, const vb_env *env, const float *configs, size_t n,
+                       uint32_t cap, uint32_t *hits, uint32_t *counts)
+{
+    if (!ctx || !env || (n && (!configs || !counts || (cap && !hits))))
+    {
+        return fail(VB_ERR_ARG, "vb_sphere_validity: null argument");
+    }
+    if (n == 0)
+    {
+        return VB_OK;
+    }
+    Query q;
+    VB_TRY(begin_query(ctx, 0, robot, base, env, q));
+    Slot &s = *q.slot;
+    const size_t total = n * static_cast<size_t>(q.ops->n_spheres);
+    VB_CUDA(s.in_a.reserve(n * q.ops->dim * sizeof(float)));
+    VB_CUDA(s.out.reserve(total * sizeof(float4)));
+    VB_CUDA(s.margin.reserve(total * (static_cast<size_t>(cap) + 1) * sizeof(uint32_t)));
+    VB_CUDA(cudaMemcpyAsync(s.in_a.p, configs, n * q.ops->dim * sizeof(float), cudaMemcpyHostToDevice, s.stream));
+    q.args.cfg = s.in_a.as<float>();
+    q.args.n = n;
+    q.args.spheres = s.out.as<float>();
+    VB_CUDA(q.ops->sphere_fk(q.args));
+    uint32_t *counts_d = s.margin.as<uint32_t>(), *hits_d = counts_d + total;
+    sphere_objects_kernel<<<static_cast<unsigned>((total + 255) / 256), 256, 0, s.stream>>>(q.args.env, s.out.as<float4>(), total, cap,
+                                                                                          hits_d, counts_d);
+    VB_CUDA(cudaGetLastError());
+    ctx->launches += 2;
+    VB_CUDA(cudaMemcpyAsync(counts, counts_d, total * sizeof(uint32_t), cudaMemcpyDeviceToHost, s.stream));
+    if (cap)
+    {
+        VB_CUDA(cudaMemcpyAsync(hits, hits_d, total * cap * sizeof(uint32_t), cudaMemcpyDeviceToHost, s.stream));
+    }
+    VB_CUDA(cudaStreamSynchronize(s.stream));
+    return VB_OK;
 }
 
 int vb_random_edge(vb_robot r, uint64_t seed, uint64_t index, float len_lo, float len_hi, float *a, float *b)

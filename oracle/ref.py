@@ -86,6 +86,7 @@ def lib():
         for fn in (L.vref_fkcc, L.vref_fkcc_packed, L.vref_fkcc_attach):
             fn.argtypes = [C.c_char_p, C.c_void_p, _f32p, C.c_size_t, _u8p, C.c_int]
         L.vref_validate_motion.argtypes = [C.c_char_p, C.c_void_p, _f32p, _f32p, C.c_size_t, _u8p, C.c_int]
+        L.vref_sphere_validity.argtypes = [C.c_char_p, C.c_void_p, _f32p, C.c_uint32, C.POINTER(C.c_uint32), C.POINTER(C.c_uint32)]
         L.vref_validate_vector.argtypes = [C.c_char_p, C.c_void_p, _f32p, _f32p, _f32p, C.c_size_t, _u8p, C.c_int]
         L.vref_env_float_ptr.argtypes = [C.c_void_p]
         L.vref_env_float_ptr.restype = C.c_void_p
@@ -268,6 +269,19 @@ def validate_motion(robot, env, a, b, threads=1):
     if rc:
         raise RuntimeError(f"reference call failed ({rc})")
     return out.astype(bool)
+
+
+def sphere_validity(robot, env, cfg, cap=64):
+    """Helper::sphere_validate of one configuration -> per robot sphere the insertion indices of the obstacles it overlaps."""
+    a, p = _f(cfg)
+    _, ns, _ = robot_info(robot)
+    hits = np.zeros((ns, cap), dtype=np.uint32)
+    counts = np.zeros(ns, dtype=np.uint32)
+    rc = lib().vref_sphere_validity(robot.encode(), env.h, p, cap, hits.ctypes.data_as(C.POINTER(C.c_uint32)),
+                                    counts.ctypes.data_as(C.POINTER(C.c_uint32)))
+    if rc:
+        raise RuntimeError(f"reference call failed ({rc})")
+    return [sorted(int(o) for o in hits[k, : counts[k]]) for k in range(ns)]
 
 
 def validate_vector(robot, env, a, v, dist, threads=1):

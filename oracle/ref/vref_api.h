@@ -77,6 +77,10 @@ int vref_fkcc_attach(const char *robot, const vref_env *, const float *cfg, size
 /* planning::validate_motion<Robot, 8, Robot::resolution>(a, b, env) (planning/validate.hh:67-75) */
 int vref_validate_motion(const char *robot, const vref_env *, const float *a, const float *b, size_t n,
                          uint8_t *valid, int threads);
+/* Helper::sphere_validate (bindings/common.hh:155-170) of ONE configuration: per robot sphere the obstacles
+ * sphere_environment_get_collisions reports, as their insertion indices (the order of the vref_env_add_* calls) */
+int vref_sphere_validity(const char *robot, const vref_env *, const float *cfg, uint32_t cap, uint32_t *hits,
+                         uint32_t *counts);
 /* planning::validate_vector<Robot, 8, Robot::resolution>(start, vector, distance, env) (planning/validate.hh:23-65) */
 int vref_validate_vector(const char *robot, const vref_env *, const float *a, const float *v, const float *dist,
                          size_t n, uint8_t *valid, int threads);

@@ -10,6 +10,7 @@ using FV = vamp::FloatVector<vref::rake>;
 struct vref_env
 {
     vref::EnvF f;
+    unsigned next_name = 0;  // shapes are named by their insertion index ("0", "1", ...) for vref_sphere_validity
     mutable bool dirty = true;
     mutable std::vector<vref::EnvV> per_thread;  // private copies, one per worker thread
 
@@ -105,6 +106,7 @@ void vref_env_destroy(vref_env *e)
 void vref_env_add_sphere(vref_env *e, float x, float y, float z, float r)
 {
     e->f.spheres.emplace_back(vc::Sphere<float>(x, y, z, r));
+    e->f.spheres.back().name = std::to_string(e->next_name++);
     e->f.sort();
     e->dirty = true;
 }
@@ -113,6 +115,7 @@ void vref_env_add_cuboid(vref_env *e, const float *c)
 {
     vc::Cuboid<float> s(
         c[0], c[1], c[2], c[3], c[4], c[5], c[6], c[7], c[8], c[9], c[10], c[11], c[12], c[13], c[14]);
+    s.name = std::to_string(e->next_name++);
     // bindings/environment.cc:120-127
     if (s.axis_3_z == 1.)
     {
@@ -129,6 +132,7 @@ void vref_env_add_cuboid(vref_env *e, const float *c)
 void vref_env_add_capsule(vref_env *e, const float *c)
 {
     vc::Cylinder<float> s(c[0], c[1], c[2], c[3], c[4], c[5], c[6], c[7]);
+    s.name = std::to_string(e->next_name++);
     // bindings/environment.cc:134-141
     if (s.xv == 0. and s.yv == 0.)
     {
@@ -146,6 +150,7 @@ void vref_env_add_heightfield(vref_env *e, const float *o, size_t xd, size_t yd,
 {
     std::vector<float> d(data, data + xd * yd);
     e->f.heightfields.emplace_back(vc::HeightField<float>(o[0], o[1], o[2], o[3], o[4], o[5], xd, yd, d));
+    e->f.heightfields.back().name = std::to_string(e->next_name++);
     e->dirty = true;
 }
 
@@ -376,6 +381,31 @@ int vref_validate_motion(
     }
     vref::parallel(
         n, threads, env, [&](const vref::EnvV &ev, size_t lo, size_t hi) { vt->motion(ev, a, b, lo, hi, valid); });
+    return 0;
+}
+
+// Helper::sphere_validate (bindings/common.hh:155-170): fk, then sphere_environment_get_collisions per sphere
+int vref_sphere_validity(const char *robot, const vref_env *env, const float *cfg, uint32_t cap, uint32_t *hits,
+                         uint32_t *counts)
+{
+    const auto *vt = vref::find(robot);
+    if (not vt)
+    {
+        return -1;
+    }
+    std::vector<float> spheres(static_cast<size_t>(vt->n_spheres) * 4);
+    vt->sphere_fk(cfg, 1, spheres.data());
+    const auto &ev = env->vec();
+    for (int k = 0; k < vt->n_spheres; ++k)
+    {
+        const float *s = spheres.data() + 4 * k;
+        const auto names = vamp::sphere_environment_get_collisions<>(ev, s[0], s[1], s[2], s[3]);
+        counts[k] = static_cast<uint32_t>(names.size());
+        for (size_t i = 0; i < names.size() and i < cap; ++i)
+        {
+            hits[static_cast<size_t>(k) * cap + i] = static_cast<uint32_t>(std::stoul(names[i]));
+        }
+    }
     return 0;
 }
 

@@ -111,3 +111,27 @@ def test_queries_fail_loudly_without_a_device():
     env = api.Environment(host_only=True)
     with pytest.raises(api.VampB200Error):
         _ = env.handle  # commit needs a device context
+
+
+def test_compiled_python_module_loads_and_exposes_the_reference_surface():
+    """mr_vamp_b200._core_ext (pybind11): importable without a device, robot metadata from the library, shape math equal
+    to the ctypes layer's; the reference's names for this path are all there (bindings/common.hh:685-710)."""
+    import mr_vamp_b200._core_ext as m
+
+    for sub in ("sphere", "ur5", "panda", "fetch", "baxter", "panda_0_0", "panda_1_0", "panda_2_2"):
+        mod = getattr(m, sub)
+        for fn in ("validate", "fk", "sphere_validity", "validate_batch", "validate_motion_batch", "validate_vector_batch",
+                   "fk_batch", "fkcc_batch", "dimension", "resolution", "n_spheres"):
+            assert hasattr(mod, fn), (sub, fn)
+    for cls in ("Environment", "Sphere", "Cuboid", "Cylinder", "HeightField", "Attachment"):
+        assert hasattr(m, cls)
+    assert (m.baxter.dimension(), m.baxter.n_spheres(), m.fetch.dimension()) == (14, 75, 8)
+    rng = np.random.default_rng(0)
+    for _ in range(20):
+        c, e, h = rng.uniform(-1, 1, 3), rng.uniform(-3, 3, 3), rng.uniform(0.05, 0.4, 3)
+        # (three float32 matrix products: the last bit depends on the summation order)
+        assert np.allclose(np.asarray(m.Cuboid(c, e, h).raw(), np.float32), api.Cuboid(c, e, h).raw(), rtol=0, atol=1e-6)
+        yaw = [0.0, 0.0, e[2]]
+        assert np.array_equal(np.asarray(m.Cuboid(c, yaw, h).raw(), np.float32), api.Cuboid(c, yaw, h).raw())
+        assert np.allclose(np.asarray(m.Cylinder(c, e, 0.05, 0.3).raw(), np.float32), api.Cylinder(c, e, 0.05, 0.3).raw(), rtol=0, atol=1e-6)
+    assert np.asarray(m.Cuboid([0, 0, 0], [0, 0, 1.234], [1, 1, 1]).raw())[11] == 1.0  # yaw only: z-aligned

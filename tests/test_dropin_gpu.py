@@ -19,3 +19,16 @@ def test_reference_program_through_the_dropin_layer():
     print(out.stdout, out.stderr)
     assert out.returncode == 0, out.stdout + out.stderr
     assert "dropin_check: OK" in out.stdout
+
+
+def test_reference_planner_code_runs_on_the_device_unchanged():
+    """include/vamp_b200_planners.hh: the reference's Path::validate (planning/plan.hh:155-168) and shortcut_path
+    (planning/simplify.hh:115-140), compiled unchanged, call the device through redirected validate_motion /
+    validate_vector; verdicts and simplified paths equal the reference's CPU functions'."""
+    exe = os.path.join(ROOT, "build", "planners_check")
+    if not os.path.exists(exe):
+        pytest.skip("build/planners_check not built (needs the reference checkout at build time)")
+    out = subprocess.run([exe], capture_output=True, text=True, timeout=300)
+    print(out.stdout, out.stderr)
+    assert out.returncode == 0, out.stdout + out.stderr
+    assert "planners_check: OK" in out.stdout
