@@ -78,6 +78,9 @@ void vb_ctx_destroy(vb_ctx *);
 int vb_ctx_device_count(const vb_ctx *);
 int vb_ctx_sm_count(const vb_ctx *, int slot);
 int vb_sync(vb_ctx *);
+/* "domain:bus:device.function" of a CUDA device: lets a host place its threads and pinned staging memory on the
+ * GPU's NUMA node (/sys/bus/pci/devices/<id>/numa_node, local_cpulist) -- mr_vamp_b200/hostbind.py does */
+int vb_device_pci_bus_id(int device, char *out, int len);
 
 /* ---- robots ------------------------------------------------------------------------------- */
 int vb_robot_by_name(const char *name, vb_robot *out);

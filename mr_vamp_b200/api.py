@@ -34,6 +34,7 @@ _SIGNATURES = [
     ("vb_ctx_device_count", C.c_int, [_vp]),
     ("vb_ctx_sm_count", C.c_int, [_vp, C.c_int]),
     ("vb_sync", C.c_int, [_vp]),
+    ("vb_device_pci_bus_id", C.c_int, [C.c_int, C.c_char_p, C.c_int]),
     ("vb_robot_by_name", C.c_int, [C.c_char_p, C.POINTER(C.c_int)]),
     ("vb_robot_info", C.c_int, [C.c_int, C.POINTER(C.c_int), C.POINTER(C.c_int), C.POINTER(C.c_int)]),
     ("vb_robot_limits", C.c_int, [C.c_int, _f32p, _f32p]),

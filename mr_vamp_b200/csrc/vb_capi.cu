@@ -307,6 +307,16 @@ int vb_sync(vb_ctx *ctx)
     return VB_OK;
 }
 
+int vb_device_pci_bus_id(int device, char *out, int len)
+{
+    if (!out || len < 16)
+    {
+        return fail(VB_ERR_ARG, "vb_device_pci_bus_id: need a buffer of at least 16 bytes");
+    }
+    VB_CUDA(cudaDeviceGetPCIBusId(out, len, device));
+    return VB_OK;
+}
+
 int vb_ctx_set_sphere_radius(vb_ctx *ctx, float r)
 {
     if (!ctx || !(r > 0.f))
