@@ -172,7 +172,9 @@ int vb_validate_path(vb_ctx *, vb_robot, const float *base_xyz, const vb_env *, 
 int vb_shortcut_path(vb_ctx *, vb_robot, const float *base_xyz, const vb_env *, const float *waypoints, size_t n,
                      int resolution, uint8_t *keep, size_t *n_kept_or_null);
 /* composite validity of two robots sharing one environment: fkcc(a) && fkcc(b) && no sphere of a
- * overlaps a sphere of b (world frame). */
+ * overlaps a sphere of b (world frame).  Two robots of one kind (the Panda grid) run as ONE fused kernel per chunk
+ * (both chains into shared memory, both walks, then the robot-robot spheres where they lie); robots of different
+ * kinds take three launches per chunk (fkcc twice, sphere_fk twice, a pair kernel). */
 int vb_validate_pairs(vb_ctx *, vb_robot robot_a, const float *base_a, vb_robot robot_b, const float *base_b,
                       const vb_env *, const float *cfg_a, const float *cfg_b, size_t n, uint32_t *valid_bits);
 
@@ -208,6 +210,9 @@ size_t vb_noalloc_max_edges(void);
 int vb_validate_motion_noalloc_d(vb_ctx *, int slot, vb_robot, const float *base_xyz, const vb_env *,
                                  const float *starts_d, const float *goals_d, size_t n_edges, int resolution,
                                  uint32_t *valid_bits_d);
+/* composite configurations of two robots of ONE kind (different bases): one launch, verdict words on the device */
+int vb_validate_pairs_d(vb_ctx *, int slot, vb_robot, const float *base_a, const float *base_b, const vb_env *,
+                        const float *cfg_a_d, const float *cfg_b_d, size_t n, uint32_t *valid_bits_d);
 /* configurations first .. first+n-1 of the synthetic stream, generated in registers (0 input bytes) */
 int vb_fkcc_random_d(vb_ctx *, int slot, vb_robot, const float *base_xyz, const vb_env *, uint64_t seed,
                      uint64_t first, size_t n, uint32_t *valid_bits_d);

@@ -72,6 +72,7 @@ _SIGNATURES = [
     ("vb_connect_increments", C.c_int, [_vp, C.c_int, _f32p, _vp, _f32p, _f32p, _f32p, C.c_size_t, C.c_float, C.c_int,
                                         _u32p, _u32p]),
     ("vb_validate_pairs", C.c_int, [_vp, C.c_int, _f32p, C.c_int, _f32p, _vp, _f32p, _f32p, C.c_size_t, _u32p]),
+    ("vb_validate_pairs_d", C.c_int, [_vp, C.c_int, C.c_int, _f32p, _f32p, _vp, _vp, _vp, C.c_size_t, _vp]),
     ("vb_dev_alloc", C.c_int, [_vp, C.c_int, C.c_size_t, C.POINTER(_vp)]),
     ("vb_dev_free", C.c_int, [_vp, C.c_int, _vp]),
     ("vb_dev_upload", C.c_int, [_vp, C.c_int, _vp, _vp, C.c_size_t]),

@@ -2120,6 +2120,95 @@ namespace
 
 extern "C" {
 
+// composite configurations of two robots of the SAME kind (the Panda grid): one launch of the fused kernel
+static int run_pairs_fused_d(Query &q, const float *base_b, const float *cfg_a_d, const float *cfg_b_d, size_t n, uint32_t *bits_d)
+{
+    if (n == 0)
+    {
+        return VB_OK;
+    }
+    q.args.cfg = cfg_a_d;
+    q.args.cfg_b = cfg_b_d;
+    q.args.n = n;
+    q.args.bits = bits_d;
+    for (int k = 0; k < 3; ++k)
+    {
+        q.args.base_b[k] = base_b ? base_b[k] : 0.f;
+    }
+    int blocks = 0, threads = 0;
+    VB_CUDA(q.ops->pairs_occupancy(q.args, &blocks, &threads));
+    if (blocks < 1)
+    {
+        return fail(VB_ERR_CUDA, "%s: the composite kernel does not fit one CTA's shared memory", q.ops->name);
+    }
+    const size_t need = (n + threads - 1) / threads;
+    const int grid = static_cast<int>(std::max<size_t>(1, std::min<size_t>(need, static_cast<size_t>(blocks) * q.slot->sm_count)));
+    VB_CUDA(q.ops->pairs_fused(q.args, grid));
+    q.ctx->launches += 1;
+    return VB_OK;
+}
+
+int vb_validate_pairs_d(vb_ctx *ctx, int slot, vb_robot robot, const float *base_a, const float *base_b, const vb_env *env,
+                        const float *cfg_a_d, const float *cfg_b_d, size_t n, uint32_t *valid_bits_d)
+{
+    if (!env || (n && (!cfg_a_d || !cfg_b_d || !valid_bits_d)))
+    {
+        return fail(VB_ERR_ARG, "vb_validate_pairs_d: null argument");
+    }
+    Query q;
+    VB_TRY(begin_query(ctx, slot, robot, base_a, env, q));
+    if (q.args.attach)
+    {
+        return fail(VB_ERR_STATE, "vb_validate_pairs_d: environments with an attachment are not supported");
+    }
+    return run_pairs_fused_d(q, base_b, cfg_a_d, cfg_b_d, n, valid_bits_d);
+}
+
+static int pairs_host_fused(vb_ctx *ctx, vb_robot robot, const float *base_a, const float *base_b, const vb_env *env,
+                            const float *cfg_a, const float *cfg_b, size_t n, uint32_t *valid_bits)
+{
+    const vb::RobotOps *ops = ops_of(robot);
+    const auto shards = shards_of(n, ctx->slots.size());
+    for (size_t i = 0; i < shards.size(); ++i)
+    {
+        const size_t m = shards[i].hi - shards[i].lo;
+        if (m == 0)
+        {
+            continue;
+        }
+        Query q;
+        VB_TRY(begin_query(ctx, static_cast<int>(i), robot, base_a, env, q));
+        Slot &s = *q.slot;
+        const size_t chunk = std::min(m, kHostChunk / 2), row = ops->dim * sizeof(float);
+        const bool two = m > chunk;
+        VB_CUDA(s.in_a.reserve(chunk * row));
+        VB_CUDA(s.in_b.reserve(chunk * row));
+        if (two)
+        {
+            VB_CUDA(s.in_a2.reserve(chunk * row));
+            VB_CUDA(s.in_b2.reserve(chunk * row));
+        }
+        VB_CUDA(s.bits.reserve((m + 31) / 32 * sizeof(uint32_t)));
+        VB_CUDA(cudaEventRecord(s.evj, s.stream));
+        VB_CUDA(cudaStreamWaitEvent(s.stream2, s.evj, 0));
+        size_t k = 0;
+        for (size_t lo = 0; lo < m; lo += chunk, ++k)
+        {
+            const size_t c = std::min(chunk, m - lo), g0 = shards[i].lo + lo;
+            const bool alt = two && (k & 1);
+            cudaStream_t st = alt ? s.stream2 : s.stream;
+            float *a_d = (alt ? s.in_a2 : s.in_a).as<float>(), *b_d = (alt ? s.in_b2 : s.in_b).as<float>();
+            uint32_t *bits_d = s.bits.as<uint32_t>() + lo / 32;
+            q.args.stream = st;
+            VB_CUDA(cudaMemcpyAsync(a_d, cfg_a + g0 * ops->dim, c * row, cudaMemcpyHostToDevice, st));
+            VB_CUDA(cudaMemcpyAsync(b_d, cfg_b + g0 * ops->dim, c * row, cudaMemcpyHostToDevice, st));
+            VB_TRY(run_pairs_fused_d(q, base_b, a_d, b_d, c, bits_d));
+            VB_CUDA(cudaMemcpyAsync(valid_bits + g0 / 32, bits_d, (c + 31) / 32 * sizeof(uint32_t), cudaMemcpyDeviceToHost, st));
+        }
+    }
+    return vb_sync(ctx);
+}
+
 int vb_validate_pairs(vb_ctx *ctx, vb_robot robot_a, const float *base_a, vb_robot robot_b, const float *base_b,
                       const vb_env *env, const float *cfg_a, const float *cfg_b, size_t n, uint32_t *valid_bits)
 {
@@ -2132,11 +2221,17 @@ int vb_validate_pairs(vb_ctx *ctx, vb_robot robot_a, const float *base_a, vb_rob
     {
         return fail(VB_ERR_ARG, "vb_validate_pairs: unknown robot id");
     }
+    if (robot_a == robot_b && !(oa->has_attach && env->has_attachment) && !std::getenv("VB_PAIRS_UNFUSED"))
+    {
+        // two robots of one kind (mr-vamp's Panda grid): the fused kernel, one launch per chunk
+        return pairs_host_fused(ctx, robot_a, base_a, base_b, env, cfg_a, cfg_b, n, valid_bits);
+    }
     if (oa->n_spheres > kPairMaxSpheres)
     {
         return fail(VB_ERR_ARG, "vb_validate_pairs: robot A has more than %d spheres", kPairMaxSpheres);
     }
-    // each robot's own validity (environment + self collision), all devices
+    // robots of different kinds: each robot's own validity (environment + self collision) on all devices, then the
+    // robot-robot pairs from both sphere sets, chunked so that the two sphere buffers stay below ~1 GB per device
     std::vector<uint32_t> bits_b((n + 31) / 32);
     VB_TRY(vb_fkcc(ctx, robot_a, base_a, env, cfg_a, n, valid_bits, nullptr));
     VB_TRY(vb_fkcc(ctx, robot_b, base_b, env, cfg_b, n, bits_b.data(), nullptr));
@@ -2144,7 +2239,6 @@ int vb_validate_pairs(vb_ctx *ctx, vb_robot robot_a, const float *base_a, vb_rob
     {
         valid_bits[w] &= bits_b[w];
     }
-    // robot-robot pairs, chunked so that the two sphere buffers stay below ~1 GB per device
     const size_t per_cfg = static_cast<size_t>(oa->n_spheres + ob->n_spheres) * sizeof(float4);
     const size_t chunk = std::max<size_t>(32, (size_t(1) << 30) / per_cfg / 32 * 32);
     const auto shards = shards_of(n, ctx->slots.size());

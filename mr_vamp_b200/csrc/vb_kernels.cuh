@@ -42,6 +42,7 @@ namespace vb
     {
         EnvView env;
         float base[3];         // robot base offset in metres (Panda grid variants; 0 otherwise)
+        float base_b[3];       // composite configurations: base offset of the second robot (cfg_b holds its configurations)
         const float *cfg;      // [n][dim] row-major, device
         const float *cfg_b;    // edges: goals [n][dim]
         size_t n;              // configurations or edges
@@ -284,10 +285,12 @@ namespace vb
 
     // Verdicts of 32 configurations, one per lane (all lanes must call; `alive` = lane has a configuration).
     // Attachment traces keep the lane-serial walk (rare, first rake pass only).
+    // `base`: robot base offset (default: a.base; the second robot of a composite configuration passes a.base_b)
     template <class Robot, bool kSync = false>
     VB_D bool check_warp(const LaunchArgs &a, const Scratch &sc, const float *q, bool alive, bool attach, int &cstate,
-                         bool octet = false)
+                         bool octet = false, const float *base = nullptr)
     {
+        const float *bs = base ? base : a.base;
         // kSync (CTA-uniform callers, `attach` uniform): the attachment decision must not depend on the warp
         if (Robot::kHasAttach && (kSync ? attach : __any_sync(kFull, attach && alive)))
         {
@@ -332,9 +335,9 @@ namespace vb
         wc.wcol = sc.col - (threadIdx.x & 31);
         wc.queues = sc.queues;
         wc.prims = sc.prims;
-        wc.bx = a.base[0];
-        wc.by = a.base[1];
-        wc.bz = a.base[2];
+        wc.bx = bs[0];
+        wc.by = bs[1];
+        wc.bz = bs[2];
         wc.radius = a.sphere_radius;
         wc.octet = octet;
         const bool ok = Walk<Robot>::template run<kSync>(a.env, wc, !alive || phit, cstate, pfree);
@@ -933,6 +936,115 @@ namespace vb
                         x[j] = VB_ADD(x[j], -back[j]);
                     }
                 }
+            }
+        }
+    }
+    // ---- K4: composite configurations of two robots of the same kind (mr-vamp's Panda grid) ---------------
+    // The fork's planned MultiRobotEnvironment::check_inter_robot_collisions (MR_DEV_PLAN.md:176-198; no reference
+    // implementation exists: PARITY UNPINNED): a composite configuration (q_a, q_b) is valid iff robot A at base_a
+    // and robot B at base_b are each valid (Robot::fkcc: environment + self collision) and no world-frame sphere of
+    // A overlaps a sphere of B (collision/sphere_sphere.hh:9-23).  ONE launch: the CTA runs with half its usual
+    // threads, thread t owns slot column t for A's chain and column t + kBlock/2 for B's, both walks run as in the
+    // fkcc kernels, and the robot-robot test reads both sets of centres where they already are -- no sphere buffer
+    // in HBM, no host round trip.  Robot-robot test of one lane: B's axis-aligned box from its spheres, every sphere
+    // of A outside that box is done, the others meet every sphere of B.
+    template <class Robot>
+    VB_D bool robots_overlap(const WalkCtx &ca, const WalkCtx &cb, int lane)
+    {
+        using W = Walk<Robot>;
+        using T = WT<Robot>;
+        float lo[3] = {3.0e38f, 3.0e38f, 3.0e38f}, hi[3] = {-3.0e38f, -3.0e38f, -3.0e38f};
+        for (int g = 0; g < Robot::kEnvGroups; ++g)
+        {
+            const RefGroup G = T::env(g);
+            for (int k = 0; k < G.ucount; ++k)
+            {
+                const Center s = W::centre(cb, lane, T::ref(G.ubegin + k));
+                lo[0] = fminf(lo[0], s.x - s.r), hi[0] = fmaxf(hi[0], s.x + s.r);
+                lo[1] = fminf(lo[1], s.y - s.r), hi[1] = fmaxf(hi[1], s.y + s.r);
+                lo[2] = fminf(lo[2], s.z - s.r), hi[2] = fmaxf(hi[2], s.z + s.r);
+            }
+        }
+        bool hit = false;
+        for (int g = 0; g < Robot::kEnvGroups && !hit; ++g)
+        {
+            const RefGroup G = T::env(g);
+            for (int k = 0; k < G.ucount && !hit; ++k)
+            {
+                const Center a = W::centre(ca, lane, T::ref(G.ubegin + k));
+                if (a.x + a.r < lo[0] || a.x - a.r > hi[0] || a.y + a.r < lo[1] || a.y - a.r > hi[1] || a.z + a.r < lo[2] ||
+                    a.z - a.r > hi[2])
+                {
+                    continue;
+                }
+                for (int g2 = 0; g2 < Robot::kEnvGroups; ++g2)
+                {
+                    const RefGroup G2 = T::env(g2);
+                    for (int k2 = 0; k2 < G2.ucount; ++k2)
+                    {
+                        const Center b = W::centre(cb, lane, T::ref(G2.ubegin + k2));
+                        const float dx = a.x - b.x, dy = a.y - b.y, dz = a.z - b.z, rs = a.r + b.r;
+                        hit = hit || (dx * dx + dy * dy + dz * dz - rs * rs < 0.f);
+                    }
+                }
+            }
+        }
+        return hit;
+    }
+
+    // threads of a composite CTA: half the warps of the robot's fkcc CTA (rounded down)
+    template <class Robot>
+    __host__ __device__ constexpr int pair_threads()
+    {
+        return (Robot::kBlock / 64) * 32;
+    }
+
+    template <class Robot>
+    __global__ void __launch_bounds__(pair_threads<Robot>(), Robot::kCtasPerSm) pairs_fused_kernel(const __grid_constant__ LaunchArgs a)
+    {
+        constexpr unsigned kHalf = static_cast<unsigned>(pair_threads<Robot>());
+        const Scratch sa = stage_env<Robot>(a, true);
+        Scratch sb = sa;
+        sb.col = sa.col + kHalf;                                    // B's columns: the upper half of the window
+        sb.queues = sa.queues + (kHalf / 32u) * queue_bytes<Robot>();  // and the queue blocks of the warps that are not there
+        int cstate_a = -1, cstate_b = -1;
+        const int lane = threadIdx.x & 31;
+        const size_t stride = static_cast<size_t>(gridDim.x) * blockDim.x;
+        const size_t n_round = (a.n + 31) / 32 * 32;
+        for (size_t base = static_cast<size_t>(blockIdx.x) * blockDim.x; base < n_round; base += stride)
+        {
+            const size_t i = base + threadIdx.x;
+            const bool alive = i < a.n;
+            if (kLockstep)
+            {
+                __syncthreads();
+            }
+            float qa[Robot::kDim], qb[Robot::kDim];
+#pragma unroll
+            for (int j = 0; j < Robot::kDim; ++j)
+            {
+                qa[j] = alive ? __ldg(a.cfg + i * Robot::kDim + j) : 0.f;
+                qb[j] = alive ? __ldg(a.cfg_b + i * Robot::kDim + j) : 0.f;
+            }
+            bool ok = check_warp<Robot>(a, sa, qa, alive, false, cstate_a, false, a.base);
+            ok = check_warp<Robot>(a, sb, qb, alive && ok, false, cstate_b, false, a.base_b) && ok;
+            if (ok)
+            {
+                WalkCtx ca, cb;
+                ca.wcol = sa.col - lane, cb.wcol = sb.col - lane;
+                ca.queues = sa.queues, cb.queues = sb.queues;
+                ca.prims = cb.prims = sa.prims;
+                ca.bx = a.base[0], ca.by = a.base[1], ca.bz = a.base[2];
+                cb.bx = a.base_b[0], cb.by = a.base_b[1], cb.bz = a.base_b[2];
+                ca.radius = cb.radius = a.sphere_radius;
+                ca.octet = cb.octet = false;
+                ok = !robots_overlap<Robot>(ca, cb, lane);
+            }
+            __syncwarp();
+            const uint32_t word = __ballot_sync(0xffffffffu, ok && alive);
+            if (lane == 0 && i < n_round)
+            {
+                a.bits[i >> 5] = word;
             }
         }
     }

@@ -54,6 +54,7 @@ namespace vb
         if (e == cudaSuccess) e = allow_smem(motion_kernel<R, false>);
         if (e == cudaSuccess) e = allow_smem(motion_rake_kernel<R, false>);
         if (e == cudaSuccess) e = allow_smem(motion_rake_kernel<R, true>);
+        if (e == cudaSuccess) e = allow_smem(pairs_fused_kernel<R>);
         if (e == cudaSuccess && dev >= 0 && dev < kMaxDevices)
         {
             ready[dev].store(1, std::memory_order_release);
@@ -141,6 +142,26 @@ namespace vb
         return cudaGetLastError();
     }
 
+    static cudaError_t launch_pairs_fused(const LaunchArgs &a, int grid)
+    {
+        if (cudaError_t e = prepare(); e != cudaSuccess)
+        {
+            return e;
+        }
+        pairs_fused_kernel<R><<<grid, pair_threads<R>(), smem_bytes(a, true), a.stream>>>(a);
+        return cudaGetLastError();
+    }
+
+    static cudaError_t pairs_occupancy(const LaunchArgs &a, int *blocks, int *threads)
+    {
+        if (cudaError_t e = prepare(); e != cudaSuccess)
+        {
+            return e;
+        }
+        *threads = pair_threads<R>();
+        return cudaOccupancyMaxActiveBlocksPerMultiprocessor(blocks, pairs_fused_kernel<R>, pair_threads<R>(), smem_bytes(a, true));
+    }
+
     static cudaError_t occupancy(const LaunchArgs &a, int *blocks, int *threads)
     {
         if (cudaError_t e = prepare(); e != cudaSuccess)
@@ -207,6 +228,8 @@ namespace vb
             o.motion = &launch_motion;
             o.motion_rake = &launch_motion_rake;
             o.limits = &launch_limits;
+            o.pairs_fused = &launch_pairs_fused;
+            o.pairs_occupancy = &pairs_occupancy;
             o.occupancy = &occupancy;
             o.random_config = &host_random_config;
             return o;

@@ -18,6 +18,9 @@ namespace vb
         cudaError_t (*motion)(const LaunchArgs &, bool margin, int grid);
         cudaError_t (*motion_rake)(const LaunchArgs &, bool margin, int grid);  // one rake block per octet, no scratch
         cudaError_t (*limits)(const LaunchArgs &);
+        // composite configurations of two robots of this kind: CTAs of kBlock / 2 threads; *_blocks = resident CTAs per SM
+        cudaError_t (*pairs_fused)(const LaunchArgs &, int grid);
+        cudaError_t (*pairs_occupancy)(const LaunchArgs &, int *blocks_per_sm, int *threads);
         cudaError_t (*occupancy)(const LaunchArgs &, int *blocks_per_sm, int *threads);  // of the fkcc kernel
         void (*random_config)(uint64_t seed, uint64_t index, float *q);
     };

@@ -175,14 +175,56 @@ def test_m4_other_robots_sweep(vb, ref, name, problem):
             cpu_packed_configs_per_s=cpu, cpu_threads=threads)
 
 
-def test_m5_two_pandas(vb, ref):
-    """configs[4]: two Pandas 1 m apart, cage duplicated at both bases, composite validation."""
+def test_m5_two_pandas(vb, ref, gpu_ctx):
+    """configs[4]: two Pandas 1 m apart, cage duplicated at both bases, composite validation (N = 1e7).
+    One fused launch per call (pairs_fused_kernel); device-resident and host-buffer rates, and the algorithmic-flop
+    fraction with W(composite) = W(q_a) + W(q_b) measured by the work-count kernel + the exhaustive 59 x 59 x 11
+    robot-robot term the fork's plan describes (MR_DEV_PLAN.md:176-198) for composites whose robots are both valid."""
+    import ctypes as C
+
     ra, rb = vb.robot("panda_0_0"), vb.robot("panda_1_0")
     spec = scenes.cage(offset=ra.base) + scenes.cage(offset=rb.base)
     env = scenes.apply(spec, vb.Environment())
-    n = 1_000_000
-    qa, qb = _cfgs(ra, 61, n), _cfgs(rb, 62, n)
-    ok = vb.validate_pairs_batch(ra, qa, rb, qb, env)
+    L, h = vb.lib(), gpu_ctx.handle
+    n = 10_000_000
+    ptrs = [C.c_void_p() for _ in range(4)]
+    for p, nbytes in zip(ptrs, (28 * n, 28 * n, n // 8 + 64, 4 * (1 << 20))):
+        vb._check(L.vb_dev_alloc(h, 0, nbytes, C.byref(p)))
+    qa_d, qb_d, bits_d, work_d = ptrs
+    vb._check(L.vb_random_configs_d(h, 0, ra.robot_id, 61, 0, n, qa_d))
+    vb._check(L.vb_random_configs_d(h, 0, rb.robot_id, 62, 0, n, qb_d))
+    ms = C.c_double()
+    best = 1e30
+    for rep in range(4):
+        vb._check(L.vb_timer_start(h, 0))
+        vb._check(L.vb_validate_pairs_d(h, 0, ra.robot_id, vb._ptr(ra.base), vb._ptr(rb.base), env.handle, qa_d, qb_d, n, bits_d))
+        vb._check(L.vb_timer_stop(h, 0, C.byref(ms)))
+        best = min(best, ms.value) if rep else best
+    valid = C.c_uint64()
+    vb._check(L.vb_popcount_d(h, 0, bits_d, n, C.byref(valid)))
+    # algorithmic flops on the first 2^20 composites
+    m = 1 << 20
+    w = np.zeros(m, np.float32)
+    w_sum, both = 0.0, None
+    for robot, q_d in ((ra, qa_d), (rb, qb_d)):
+        vb._check(L.vb_fkcc_work_d(h, 0, robot.robot_id, vb._ptr(robot.base), env.handle, q_d, m, bits_d, work_d))
+        vb._check(L.vb_dev_download(h, 0, w.ctypes.data_as(C.c_void_p), work_d, w.nbytes))
+        words = np.zeros(m // 32, np.uint32)
+        vb._check(L.vb_dev_download(h, 0, words.ctypes.data_as(C.c_void_p), bits_d, words.nbytes))
+        ok = vb.unpack_bits(words, m)
+        both = ok if both is None else (both & ok)
+        w_sum += float(w.astype(np.float64).mean())
+    w_comp = w_sum + float(both.mean()) * 59 * 59 * 11
+    rate = n / (best * 1e-3)
+    # host buffers, and the same answer
+    k = 1_000_000
+    qa, qb = ra.random_configs(61, 0, k), rb.random_configs(62, 0, k)
+    ok_h = vb.validate_pairs_batch(ra, qa, rb, qb, env)
     t = _timed(lambda: vb.validate_pairs_batch(ra, qa, rb, qb, env), reps=2)
-    _record("m5_two_pandas", composites=n, valid_fraction=float(ok.mean()), composites_per_s_host_buffers=n / t,
+    for p in ptrs:
+        L.vb_dev_free(h, 0, p)
+    _record("m5_two_pandas", composites=n, valid_fraction=valid.value / n, composites_per_s_device=rate, launches_per_call=1,
+            flops_per_composite=w_comp, fp32_fraction=w_comp * rate / 74.45e12, composites_per_s_host_buffers=k / t,
+            host_valid_fraction=float(ok_h.mean()),
             parity="unpinned (no reference implementation); checked against a CPU restatement in tests/test_pairs_gpu.py")
+    assert abs(ok_h.mean() - valid.value / n) < 2e-3

@@ -46,6 +46,27 @@ def test_two_robot_composite_validity(vb, ref, names):
     assert hard.sum() == 0
 
 
+@pytest.mark.parametrize("names", [("panda_0_0", "panda_1_0"), ("panda_1_0", "panda_0_0")])
+def test_fused_kernel_equals_the_three_launch_path(vb, names, monkeypatch):
+    """Two robots of one kind run as one fused kernel (pairs_fused_kernel); the sphere-buffer path (fkcc twice, sphere_fk
+    twice, pair kernel) that robots of different kinds use must give the same words."""
+    ra, rb = vb.robot(names[0]), vb.robot(names[1])
+    spec = scenes.cage(radius=0.12, offset=ra.base)[::2]
+    env = scenes.apply(spec, vb.Environment())
+    n = 100_003
+    qa, qb = _cfgs(ra, 71, n), _cfgs(rb, 72, n)
+    fused = vb.validate_pairs_batch(ra, qa, rb, qb, env)
+    monkeypatch.setenv("VB_PAIRS_UNFUSED", "1")
+    unfused = vb.validate_pairs_batch(ra, qa, rb, qb, env)
+    monkeypatch.delenv("VB_PAIRS_UNFUSED")
+    each = ra.fkcc_batch(qa, env) & rb.fkcc_batch(qb, env)
+    differ = int((fused != unfused).sum())
+    print(f"{names}: valid {fused.mean():.4f} (each robot alone {each.mean():.4f}), fused vs unfused differ on {differ}")
+    assert (fused != each).any(), "the robot-robot term must matter"
+    # the two paths round the sphere centres the same way (same chain); a handful of contacts within 1e-6 m^2 may differ
+    assert differ <= 2
+
+
 def test_far_apart_robots_reduce_to_the_and_of_both(vb, ref):
     ra, rb = vb.robot("panda_0_0"), vb.robot("panda_2_2")
     env = scenes.apply(scenes.cage(), vb.Environment())
