@@ -32,6 +32,10 @@
  *                           the form the planners' inner loops call (rrtc.hh:139,180; prm.hh; fcit.hh)
  *   vb_connect_increments   RRTC's connect loop, planning/rrtc.hh:172-194 (all n_extensions increments of many
  *                           attempts in one batch, first failing increment per attempt)
+ *   vb_sample_valid         the sampling loops of planning/prm.hh:111-124 and planning/fcit.hh:316-343 (draw, Robot::fkcc,
+ *                           keep the valid ones in stream order) for a whole batch: the first k valid of a stream
+ *   vb_validate_motion_indexed  the neighbour edges of planning/prm.hh:139 / planning/fcit.hh:230-236 as index pairs
+ *                           into a device-resident vertex table
  *   vb_validate_path        Path::validate, planning/plan.hh:155-168 (first invalid edge)
  *   vb_shortcut_path        planning::shortcut_path, planning/simplify.hh:115-140 (all candidates in one batch)
  *   vb_validate_pairs       the fork's planned MultiRobotEnvironment::check_inter_robot_collisions
@@ -161,6 +165,18 @@ int vb_validate_vector(vb_ctx *, vb_robot, const float *base_xyz, const vb_env *
 int vb_connect_increments(vb_ctx *, vb_robot, const float *base_xyz, const vb_env *, const float *from, const float *to,
                           const float *distances, size_t n, float range, int resolution, uint32_t *n_valid,
                           uint32_t *n_ext_or_null);
+/* PRM / FCIT* batching.
+ * vb_sample_valid: walks a stream of candidate configurations -- `candidates` [m][dim] (host), or when NULL rows
+ *   first .. first+m-1 of the library stream (seed) -- and returns its first k valid ones (Robot::fkcc) in stream order:
+ *   out_cfgs [k][dim], out_index [k] = position in the stream, *n_found <= k, *n_consumed = candidates drawn up to and
+ *   including the k-th valid one (all m when fewer than k are valid), i.e. where the reference's loop would stand.
+ * vb_validate_motion_indexed: edge e runs from row pairs[2e] to row pairs[2e+1] of `table_d`, a DEVICE-resident
+ *   [n_rows][dim] table (vb_dev_alloc / vb_dev_upload); 8 bytes per edge cross PCIe.  Out-of-range rows: edge invalid. */
+int vb_sample_valid(vb_ctx *, vb_robot, const float *base_xyz, const vb_env *, const float *candidates, uint64_t seed,
+                    uint64_t first, size_t m, size_t k, float *out_cfgs, uint64_t *out_index, size_t *n_found,
+                    size_t *n_consumed);
+int vb_validate_motion_indexed(vb_ctx *, vb_robot, const float *base_xyz, const vb_env *, const float *table_d, size_t n_rows,
+                               const uint32_t *pairs, size_t n_edges, int resolution, uint32_t *valid_bits);
 /* Batch edge callers.
  * vb_validate_path: Path::validate, planning/plan.hh:155-168 -- all consecutive edges of `waypoints` [n][dim] in one
  *   batch; *first_invalid_edge = index of the first invalid edge, -1 if the path is valid.
@@ -195,6 +211,9 @@ int vb_validate_motion_d(vb_ctx *, int slot, vb_robot, const float *base_xyz, co
 int vb_validate_vector_d(vb_ctx *, int slot, vb_robot, const float *base_xyz, const vb_env *, const float *starts_d,
                          const float *vectors_d, const float *distances_d, size_t n_edges, int resolution,
                          uint32_t *valid_bits_d, float *margin_d_or_null);
+int vb_validate_motion_indexed_d(vb_ctx *, int slot, vb_robot, const float *base_xyz, const vb_env *, const float *table_d,
+                                 size_t n_rows, const uint32_t *pairs_d, size_t n_edges, int resolution,
+                                 uint32_t *valid_bits_d);
 /* vb_validate_motion_noalloc_d: vb_validate_motion_d (verdicts only) for callers that cannot call cudaMalloc --
  * code under CUDA graph capture, tight serving loops, harnesses that forbid allocation.  It has NO counterpart in
  * the reference.  It runs the prefix-array form of the motion

@@ -71,6 +71,9 @@ _SIGNATURES = [
     ("vb_validate_vector", C.c_int, [_vp, C.c_int, _f32p, _vp, _f32p, _f32p, _f32p, C.c_size_t, C.c_int, _u32p, _f32p]),
     ("vb_connect_increments", C.c_int, [_vp, C.c_int, _f32p, _vp, _f32p, _f32p, _f32p, C.c_size_t, C.c_float, C.c_int,
                                         _u32p, _u32p]),
+    ("vb_sample_valid", C.c_int, [_vp, C.c_int, _f32p, _vp, _f32p, C.c_uint64, C.c_uint64, C.c_size_t, C.c_size_t, _f32p,
+                                  C.POINTER(C.c_uint64), C.POINTER(C.c_size_t), C.POINTER(C.c_size_t)]),
+    ("vb_validate_motion_indexed", C.c_int, [_vp, C.c_int, _f32p, _vp, _vp, C.c_size_t, _u32p, C.c_size_t, C.c_int, _u32p]),
     ("vb_validate_pairs", C.c_int, [_vp, C.c_int, _f32p, C.c_int, _f32p, _vp, _f32p, _f32p, C.c_size_t, _u32p]),
     ("vb_validate_pairs_d", C.c_int, [_vp, C.c_int, C.c_int, _f32p, _f32p, _vp, _vp, _vp, C.c_size_t, _vp]),
     ("vb_dev_alloc", C.c_int, [_vp, C.c_int, C.c_size_t, C.POINTER(_vp)]),
@@ -81,6 +84,7 @@ _SIGNATURES = [
     ("vb_fkcc_work_d", C.c_int, [_vp, C.c_int, C.c_int, _f32p, _vp, _vp, C.c_size_t, _vp, _vp]),
     ("vb_validate_motion_d", C.c_int, [_vp, C.c_int, C.c_int, _f32p, _vp, _vp, _vp, C.c_size_t, C.c_int, _vp, _vp]),
     ("vb_validate_vector_d", C.c_int, [_vp, C.c_int, C.c_int, _f32p, _vp, _vp, _vp, _vp, C.c_size_t, C.c_int, _vp, _vp]),
+    ("vb_validate_motion_indexed_d", C.c_int, [_vp, C.c_int, C.c_int, _f32p, _vp, _vp, C.c_size_t, _vp, C.c_size_t, C.c_int, _vp]),
     ("vb_noalloc_max_edges", C.c_size_t, []),
     ("vb_validate_motion_noalloc_d", C.c_int, [_vp, C.c_int, C.c_int, _f32p, _vp, _vp, _vp, C.c_size_t, C.c_int, _vp]),
     ("vb_fkcc_random_d", C.c_int, [_vp, C.c_int, C.c_int, _f32p, _vp, C.c_uint64, C.c_uint64, C.c_size_t, _vp]),
@@ -522,6 +526,19 @@ class Robot:
                                            _ptr(b), _ptr(d), n, range_, resolution, _ptr(n_valid, _u32p), _ptr(n_ext, _u32p)))
         return n_valid, n_ext
 
+    def sample_valid(self, k: int, env: Optional[Environment] = None, candidates=None, seed: int = 0, first: int = 0,
+                     max_candidates: int = 0):
+        """The first k valid configurations of a stream, in stream order (the sampling loops of planning/prm.hh:111-124,
+        planning/fcit.hh:316-343 for a whole batch) -> (configs float32[found, dim], stream index uint64[found], consumed)."""
+        cand = None if candidates is None else self._configs(candidates)
+        m = cand.shape[0] if cand is not None else (max_candidates or 64 * k)
+        out = np.zeros((k, self.dimension), dtype=np.float32)
+        idx = np.zeros(k, dtype=np.uint64)
+        found, consumed = C.c_size_t(), C.c_size_t()
+        _check(lib().vb_sample_valid(self.ctx.handle, self.robot_id, _ptr(self.base), self._env(env).handle, _ptr(cand), seed, first,
+                                     m, k, _ptr(out), idx.ctypes.data_as(C.POINTER(C.c_uint64)), C.byref(found), C.byref(consumed)))
+        return out[: found.value], idx[: found.value], int(consumed.value)
+
     def fk_batch(self, configs) -> np.ndarray:
         """Robot::sphere_fk -> float32[n, n_spheres, 4] (x, y, z, r), world frame."""
         q = self._configs(configs)
@@ -586,6 +603,40 @@ class Robot:
         b = np.zeros((n, self.dimension), dtype=np.float32)
         _check(lib().vb_random_edges(self.robot_id, seed, first, n, len_lo, len_hi, _ptr(a), _ptr(b)))
         return a, b
+
+
+class DeviceTable:
+    """A device-resident [n][dim] configuration table (roadmap vertices) for index-pair edge validation."""
+
+    def __init__(self, robot: Robot, rows):
+        self.robot = robot
+        rows = robot._configs(rows)
+        self.n = rows.shape[0]
+        self._p = _vp()
+        _check(lib().vb_dev_alloc(robot.ctx.handle, 0, max(16, rows.nbytes), C.byref(self._p)))
+        _check(lib().vb_dev_upload(robot.ctx.handle, 0, self._p, rows.ctypes.data_as(_vp), rows.nbytes))
+        _check(lib().vb_sync(robot.ctx.handle))
+
+    def validate_edges(self, pairs, env: Optional[Environment] = None, resolution: int = 0) -> np.ndarray:
+        """pairs uint32[n_edges, 2] (row of the start, row of the goal) -> bool[n_edges]."""
+        pairs = np.ascontiguousarray(pairs, dtype=np.uint32).reshape(-1, 2)
+        n = pairs.shape[0]
+        bits = np.zeros((n + 31) // 32, dtype=np.uint32)
+        r = self.robot
+        _check(lib().vb_validate_motion_indexed(r.ctx.handle, r.robot_id, _ptr(r.base), r._env(env).handle, self._p, self.n,
+                                                _ptr(pairs, _u32p), n, resolution, _ptr(bits, _u32p)))
+        return unpack_bits(bits, n)
+
+    def close(self):
+        if self._p:
+            lib().vb_dev_free(self.robot.ctx.handle, 0, self._p)
+            self._p = _vp()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
 
 
 def validate_pairs_batch(robot_a: Robot, cfg_a, robot_b: Robot, cfg_b, env: Optional[Environment] = None) -> np.ndarray:

@@ -1195,6 +1195,54 @@ namespace
         }
     }
 
+    // ---- first-K-valid compaction (PRM / FCIT* sampling, planning/prm.hh:111-124, planning/fcit.hh:316-343) -------
+    __global__ void word_popcount_kernel(const uint32_t *bits, size_t n, uint32_t *counts)
+    {
+        const size_t w = static_cast<size_t>(blockIdx.x) * blockDim.x + threadIdx.x;
+        const size_t n_words = (n + 31) / 32;
+        if (w <= n_words)
+        {
+            uint32_t v = w < n_words ? bits[w] : 0u;
+            const size_t rem = w < n_words ? n - w * 32 : 0;
+            if (rem < 32)
+            {
+                v &= rem ? ((1u << rem) - 1u) : 0u;
+            }
+            counts[w] = __popc(v);  // counts[n_words] = 0: its exclusive prefix is the total
+        }
+    }
+
+    // candidate i (valid, with `have` + rank < k) -> out rows; the k-th valid overall records where the stream stops
+    __global__ void compact_valid_kernel(const uint32_t *bits, const uint32_t *prefix, const float *cfg, int dim, size_t n,
+                                         uint64_t stream_first, size_t have, size_t k, float *out_cfg, uint64_t *out_index,
+                                         unsigned long long *consumed)
+    {
+        const size_t i = static_cast<size_t>(blockIdx.x) * blockDim.x + threadIdx.x;
+        if (i >= n)
+        {
+            return;
+        }
+        const uint32_t word = bits[i >> 5];
+        if (!((word >> (i & 31)) & 1u))
+        {
+            return;
+        }
+        const size_t rank = have + prefix[i >> 5] + __popc(word & ((1u << (i & 31)) - 1u));
+        if (rank >= k)
+        {
+            return;
+        }
+        for (int j = 0; j < dim; ++j)
+        {
+            out_cfg[rank * dim + j] = cfg[i * dim + j];
+        }
+        out_index[rank] = stream_first + i;
+        if (rank + 1 == k)
+        {
+            *consumed = static_cast<unsigned long long>(i + 1);
+        }
+    }
+
     StreamLimits limits_of(const vb::RobotOps *o)
     {
         StreamLimits l{};
@@ -2364,6 +2412,133 @@ int vb_sphere_validity(vb_ctx *ctx, vb_robot robot, const float *base, const vb_
     {
         VB_CUDA(cudaMemcpyAsync(hits, hits_d, total * cap * sizeof(uint32_t), cudaMemcpyDeviceToHost, s.stream));
     }
+    VB_CUDA(cudaStreamSynchronize(s.stream));
+    return VB_OK;
+}
+
+/* ---- PRM / FCIT* batching ------------------------------------------------------ */
+// The first k valid configurations of a stream, in stream order -- what the sampling loops of planning/prm.hh:111-124
+// and planning/fcit.hh:316-343 keep (sample -> Robot::fkcc -> continue when invalid), for a whole batch at once.
+int vb_sample_valid(vb_ctx *ctx, vb_robot robot, const float *base, const vb_env *env, const float *candidates, uint64_t seed,
+                    uint64_t first, size_t m, size_t k, float *out_cfgs, uint64_t *out_index, size_t *n_found, size_t *n_consumed)
+{
+    if (!ctx || !env || !n_found || !n_consumed || (k && (!out_cfgs || !out_index)))
+    {
+        return fail(VB_ERR_ARG, "vb_sample_valid: null argument");
+    }
+    *n_found = 0;
+    *n_consumed = 0;
+    if (k == 0 || m == 0)
+    {
+        return VB_OK;
+    }
+    Query q;
+    VB_TRY(begin_query(ctx, 0, robot, base, env, q));
+    Slot &s = *q.slot;
+    const int dim = q.ops->dim;
+    const size_t chunk_max = std::min<size_t>(m, std::max<size_t>(4096, std::min<size_t>(size_t(1) << 22, 4 * k)));
+    const size_t words_max = (chunk_max + 31) / 32;
+    VB_CUDA(s.in_a.reserve(chunk_max * dim * sizeof(float)));
+    VB_CUDA(s.bits.reserve(words_max * sizeof(uint32_t)));
+    VB_CUDA(s.in_d.reserve((words_max + 1) * sizeof(uint32_t)));   // word popcounts
+    VB_CUDA(s.in_d2.reserve((words_max + 1) * sizeof(uint32_t)));  // their exclusive prefix
+    VB_CUDA(s.out.reserve(k * dim * sizeof(float)));
+    VB_CUDA(s.margin.reserve(k * sizeof(uint64_t) + 16));
+    uint64_t *index_d = s.margin.as<uint64_t>();
+    unsigned long long *consumed_d = reinterpret_cast<unsigned long long *>(index_d + k);
+    size_t tmp_bytes = 0;
+    VB_CUDA(cub::DeviceScan::ExclusiveSum(nullptr, tmp_bytes, s.in_d.as<uint32_t>(), s.in_d2.as<uint32_t>(),
+                                          static_cast<int>(words_max + 1), s.stream));
+    VB_CUDA(s.scan_tmp.reserve(tmp_bytes));
+    const StreamLimits lim = limits_of(q.ops);
+    size_t have = 0, done = 0;
+    while (have < k && done < m)
+    {
+        const size_t c = std::min(chunk_max, m - done), words = (c + 31) / 32;
+        if (candidates)
+        {
+            VB_CUDA(cudaMemcpyAsync(s.in_a.p, candidates + done * dim, c * dim * sizeof(float), cudaMemcpyHostToDevice, s.stream));
+        }
+        else
+        {
+            random_configs_kernel<<<s.sm_count * 8, 256, 0, s.stream>>>(lim, seed, first + done, c, s.in_a.as<float>());
+            VB_CUDA(cudaGetLastError());
+            ctx->launches += 1;
+        }
+        VB_TRY(run_fkcc_d(q, s.in_a.as<float>(), c, s.bits.as<uint32_t>(), nullptr));
+        word_popcount_kernel<<<static_cast<unsigned>((words + 1 + 255) / 256), 256, 0, s.stream>>>(s.bits.as<uint32_t>(), c,
+                                                                                                   s.in_d.as<uint32_t>());
+        VB_CUDA(cudaGetLastError());
+        VB_CUDA(cub::DeviceScan::ExclusiveSum(s.scan_tmp.p, tmp_bytes, s.in_d.as<uint32_t>(), s.in_d2.as<uint32_t>(),
+                                              static_cast<int>(words + 1), s.stream));
+        VB_CUDA(cudaMemsetAsync(consumed_d, 0, sizeof(unsigned long long), s.stream));
+        compact_valid_kernel<<<static_cast<unsigned>((c + 255) / 256), 256, 0, s.stream>>>(
+            s.bits.as<uint32_t>(), s.in_d2.as<uint32_t>(), s.in_a.as<float>(), dim, c, first + done, have, k, s.out.as<float>(), index_d,
+            consumed_d);
+        VB_CUDA(cudaGetLastError());
+        ctx->launches += 4;
+        uint32_t found = 0;
+        unsigned long long consumed = 0;
+        VB_CUDA(cudaMemcpyAsync(&found, s.in_d2.as<uint32_t>() + words, sizeof(found), cudaMemcpyDeviceToHost, s.stream));
+        VB_CUDA(cudaMemcpyAsync(&consumed, consumed_d, sizeof(consumed), cudaMemcpyDeviceToHost, s.stream));
+        VB_CUDA(cudaStreamSynchronize(s.stream));
+        if (have + found >= k)
+        {
+            *n_consumed = done + static_cast<size_t>(consumed);
+            have = k;
+            break;
+        }
+        have += found;
+        done += c;
+        *n_consumed = done;
+    }
+    *n_found = have;
+    if (have)
+    {
+        VB_CUDA(cudaMemcpyAsync(out_cfgs, s.out.p, have * dim * sizeof(float), cudaMemcpyDeviceToHost, s.stream));
+        VB_CUDA(cudaMemcpyAsync(out_index, index_d, have * sizeof(uint64_t), cudaMemcpyDeviceToHost, s.stream));
+        VB_CUDA(cudaStreamSynchronize(s.stream));
+    }
+    return VB_OK;
+}
+
+// Edges as index pairs into a device-resident configuration table (roadmap vertices): the neighbour edges of
+// planning/prm.hh:139 / planning/fcit.hh:230-236 upload 8 bytes each instead of two configurations.
+int vb_validate_motion_indexed_d(vb_ctx *ctx, int slot, vb_robot robot, const float *base, const vb_env *env, const float *table_d,
+                                 size_t n_rows, const uint32_t *pairs_d, size_t n_edges, int resolution, uint32_t *valid_bits_d)
+{
+    if (!env || (n_edges && (!table_d || !pairs_d || !valid_bits_d)))
+    {
+        return fail(VB_ERR_ARG, "vb_validate_motion_indexed_d: null argument");
+    }
+    Query q;
+    VB_TRY(begin_query(ctx, slot, robot, base, env, q));
+    q.args.edge_idx = pairs_d;
+    q.args.table_rows = n_rows;
+    return run_motion_d(q, table_d, table_d, nullptr, false, n_edges, resolution, valid_bits_d, nullptr);
+}
+
+int vb_validate_motion_indexed(vb_ctx *ctx, vb_robot robot, const float *base, const vb_env *env, const float *table_d, size_t n_rows,
+                               const uint32_t *pairs, size_t n_edges, int resolution, uint32_t *valid_bits)
+{
+    if (!ctx || !env || (n_edges && (!table_d || !pairs || !valid_bits)))
+    {
+        return fail(VB_ERR_ARG, "vb_validate_motion_indexed: null argument");
+    }
+    if (n_edges == 0)
+    {
+        return VB_OK;
+    }
+    VB_TRY(check_slot(ctx, 0));
+    Slot &s = ctx->slots[0];
+    VB_CUDA(cudaSetDevice(s.device));
+    const size_t words = (n_edges + 31) / 32;
+    VB_CUDA(s.in_d.reserve(n_edges * 2 * sizeof(uint32_t)));
+    VB_CUDA(s.bits.reserve(words * sizeof(uint32_t)));
+    VB_CUDA(cudaMemcpyAsync(s.in_d.p, pairs, n_edges * 2 * sizeof(uint32_t), cudaMemcpyHostToDevice, s.stream));
+    VB_TRY(vb_validate_motion_indexed_d(ctx, 0, robot, base, env, table_d, n_rows, s.in_d.as<uint32_t>(), n_edges, resolution,
+                                        s.bits.as<uint32_t>()));
+    VB_CUDA(cudaMemcpyAsync(valid_bits, s.bits.p, words * sizeof(uint32_t), cudaMemcpyDeviceToHost, s.stream));
     VB_CUDA(cudaStreamSynchronize(s.stream));
     return VB_OK;
 }

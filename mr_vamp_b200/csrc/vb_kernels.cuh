@@ -58,6 +58,8 @@ namespace vb
         int attach;            // use the attachment trace
         float sphere_radius;   // robots::sphere global radius (robots/sphere/fk.hh:16)
         float edge_len[2];     // synthetic edges: length range
+        const uint32_t *edge_idx;  // edges as index pairs into ONE configuration table: start = cfg[idx[2e]], goal = cfg[idx[2e+1]]
+        size_t table_rows;         // rows of that table (out-of-range indices make the edge invalid)
         const float *dist;     // edges in (start, vector, distance) form: distances [n] (validate_vector), else null
         int vector_form;       // cfg_b holds vectors (goal - start) instead of goals
         cudaStream_t stream;
@@ -857,17 +859,29 @@ namespace vb
                 if (e == kNone && mine < count)
                 {
                     const size_t g = e_lo + mine;
+                    // rows of the two endpoints: edge g of two arrays, or an index pair into one table (PRM / FCIT*
+                    // neighbour edges, planning/prm.hh:139: 8 bytes per edge instead of two configurations)
+                    size_t row_a = g, row_b = g;
+                    bool in_range = true;
+                    if (a.edge_idx)
+                    {
+                        row_a = __ldg(a.edge_idx + 2 * g);
+                        row_b = __ldg(a.edge_idx + 2 * g + 1);
+                        in_range = row_a < a.table_rows && row_b < a.table_rows;
+                        row_a = in_range ? row_a : 0;
+                        row_b = in_range ? row_b : 0;
+                    }
                     float qa[Robot::kDim], v[Robot::kDim];
 #pragma unroll
                     for (int j = 0; j < Robot::kDim; ++j)
                     {
-                        qa[j] = __ldg(a.cfg + g * Robot::kDim + j);
-                        const float second = __ldg(a.cfg_b + g * Robot::kDim + j);
+                        qa[j] = __ldg(a.cfg + row_a * Robot::kDim + j);
+                        const float second = __ldg(a.cfg_b + row_b * Robot::kDim + j);
                         v[j] = a.vector_form ? second : VB_ADD(second, -qa[j]);
                     }
                     const float dist = a.dist ? __ldg(a.dist + g) : edge_norm<Robot::kDim>(v);
                     const float nf = fmaxf(ceilf(dist / static_cast<float>(kRake) * static_cast<float>(a.resolution)), 1.f);
-                    if (!(nf < 2147483648.f))
+                    if (!(nf < 2147483648.f) || !in_range)
                     {
                         if ((lane & 7) == 0)
                         {
