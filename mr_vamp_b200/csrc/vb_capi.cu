@@ -839,6 +839,109 @@ namespace
         }
     }
 
+    // Occupancy bitmap of a point cloud (vb_env.cuh: CaptView::occ).  Every point of the cloud is the representative of
+    // exactly one leaf, stored first in that leaf's affordance list (collision/capt.hh:166-177): one thread per leaf
+    // marks the voxels whose centre lies within reach + half a voxel diagonal of its representative.
+    constexpr float kCaptOccVoxel = 0.04f;
+    constexpr float kCaptOccReach = 0.25f;  // covers every robot's largest bounding sphere + the point radius
+
+    __global__ void capt_occupancy_kernel(const vb::CaptView c, size_t n_leaves, uint32_t *occ)
+    {
+        const size_t z = static_cast<size_t>(blockIdx.x) * blockDim.x + threadIdx.x;
+        if (z >= n_leaves || c.aff_starts[z] == c.aff_starts[z + 1])
+        {
+            return;
+        }
+        const float4 *v = c.aff + 6ull * c.aff_starts[z];
+        const float p[3] = {v[0].x, v[2].x, v[4].x};
+        if (!isfinite(p[0]))
+        {
+            return;
+        }
+        const float h = 1.f / c.occ_inv_h, reach = c.occ_reach + 0.5f * 1.7320508f * h * 1.001f;
+        int lo[3], hi[3];
+        for (int k = 0; k < 3; ++k)
+        {
+            lo[k] = max(0, static_cast<int>(floorf((p[k] - reach - c.occ_o[k]) * c.occ_inv_h)));
+            hi[k] = min(c.occ_n[k] - 1, static_cast<int>(floorf((p[k] + reach - c.occ_o[k]) * c.occ_inv_h)));
+        }
+        for (int iz = lo[2]; iz <= hi[2]; ++iz)
+        {
+            for (int iy = lo[1]; iy <= hi[1]; ++iy)
+            {
+                for (int ix = lo[0]; ix <= hi[0]; ++ix)
+                {
+                    const float dx = c.occ_o[0] + (ix + 0.5f) * h - p[0], dy = c.occ_o[1] + (iy + 0.5f) * h - p[1],
+                                dz = c.occ_o[2] + (iz + 0.5f) * h - p[2];
+                    if (dx * dx + dy * dy + dz * dz <= reach * reach)
+                    {
+                        const unsigned bit = (static_cast<unsigned>(iz) * c.occ_n[1] + iy) * c.occ_n[0] + ix;
+                        if (!((occ[bit >> 5] >> (bit & 31u)) & 1u))
+                        {
+                            atomicOr(occ + (bit >> 5), 1u << (bit & 31u));
+                        }
+                    }
+                }
+            }
+        }
+    }
+
+    // Fine level (vb_env.cuh: CaptView::dist): distance from every voxel centre to the nearest point, capped.  One
+    // thread per leaf splats its representative point into the voxels within the cap (atomicMin on the bit pattern of
+    // a non-negative float).
+    constexpr float kCaptDistCap = 0.10f;
+    constexpr float kCaptDistVoxel = 0.0125f;
+
+    __global__ void fill_float_bits_kernel(uint32_t *p, size_t n, float v)
+    {
+        for (size_t i = static_cast<size_t>(blockIdx.x) * blockDim.x + threadIdx.x; i < n; i += static_cast<size_t>(gridDim.x) * blockDim.x)
+        {
+            p[i] = __float_as_uint(v);
+        }
+    }
+
+    __global__ void capt_distance_kernel(const vb::CaptView c, size_t n_leaves, uint32_t *dist_bits)
+    {
+        const size_t z = static_cast<size_t>(blockIdx.x) * blockDim.x + threadIdx.x;
+        if (z >= n_leaves || c.aff_starts[z] == c.aff_starts[z + 1])
+        {
+            return;
+        }
+        const float4 *v = c.aff + 6ull * c.aff_starts[z];
+        const float p[3] = {v[0].x, v[2].x, v[4].x};
+        if (!isfinite(p[0]))
+        {
+            return;
+        }
+        const float h = 1.f / c.dist_inv_h, cap = c.dist_cap;
+        int lo[3], hi[3];
+        for (int k = 0; k < 3; ++k)
+        {
+            lo[k] = max(0, static_cast<int>(floorf((p[k] - cap - c.dist_o[k]) * c.dist_inv_h)));
+            hi[k] = min(c.dist_n[k] - 1, static_cast<int>(floorf((p[k] + cap - c.dist_o[k]) * c.dist_inv_h)));
+        }
+        for (int iz = lo[2]; iz <= hi[2]; ++iz)
+        {
+            for (int iy = lo[1]; iy <= hi[1]; ++iy)
+            {
+                for (int ix = lo[0]; ix <= hi[0]; ++ix)
+                {
+                    const float dx = c.dist_o[0] + (ix + 0.5f) * h - p[0], dy = c.dist_o[1] + (iy + 0.5f) * h - p[1],
+                                dz = c.dist_o[2] + (iz + 0.5f) * h - p[2];
+                    const float d = sqrtf(dx * dx + dy * dy + dz * dz);
+                    if (d < cap)
+                    {
+                        const size_t cell = (static_cast<size_t>(iz) * c.dist_n[1] + iy) * c.dist_n[0] + ix;
+                        if (__float_as_uint(d) < dist_bits[cell])
+                        {
+                            atomicMin(dist_bits + cell, __float_as_uint(d));
+                        }
+                    }
+                }
+            }
+        }
+    }
+
     // Bounding box of the primitive obstacles -> grid geometry.  The box is inflated by kSdfCover so that
     // "outside the grid" means "at least kSdfCover away from every obstacle"; scenes larger than the
     // +-kSdfReach cube around the origin are clipped to it and lose that guarantee (cover = 0).
@@ -1004,6 +1107,70 @@ namespace
             cv.r_point = c.r_point;
             cv.n_tests = static_cast<uint32_t>(c.tests.size());
             cv.nlog2 = c.nlog2;
+            // occupancy bitmap over aabb_top grown by the reach + one voxel (skipped for degenerate / huge clouds)
+            cv.occ = nullptr;
+            if (!std::getenv("VB_CAPT_NO_OCC") && std::isfinite(c.top[0]) && c.top[0] <= c.top[3])
+            {
+                const float grow = kCaptOccReach + 2.f * kCaptOccVoxel;
+                size_t voxels = 1;
+                for (int k = 0; k < 3; ++k)
+                {
+                    cv.occ_o[k] = c.top[k] - grow;
+                    cv.occ_n[k] = static_cast<int>(std::ceil((c.top[3 + k] - c.top[k] + 2.f * grow) / kCaptOccVoxel));
+                    voxels *= static_cast<size_t>(std::max(cv.occ_n[k], 1));
+                }
+                if (voxels <= (size_t(1) << 28))
+                {
+                    cv.occ_inv_h = 1.f / kCaptOccVoxel;
+                    cv.occ_reach = kCaptOccReach;
+                    rep.blobs.emplace_back();
+                    const size_t words = (voxels + 31) / 32;
+                    VB_CUDA(rep.blobs.back().reserve(words * sizeof(uint32_t)));
+                    uint32_t *occ = rep.blobs.back().as<uint32_t>();
+                    VB_CUDA(cudaMemsetAsync(occ, 0, words * sizeof(uint32_t), slot.stream));
+                    const size_t leaves = size_t(1) << c.nlog2;
+                    capt_occupancy_kernel<<<static_cast<unsigned>((leaves + 127) / 128), 128, 0, slot.stream>>>(cv, leaves, occ);
+                    VB_CUDA(cudaGetLastError());
+                    cv.occ = occ;
+                }
+            }
+            cv.dist = nullptr;
+            if (!std::getenv("VB_CAPT_NO_DIST") && std::isfinite(c.top[0]) && c.top[0] <= c.top[3])
+            {
+                float h = kCaptDistVoxel;
+                size_t voxels = 0;
+                for (;;)
+                {
+                    const float grow = kCaptDistCap + 2.f * h;
+                    voxels = 1;
+                    for (int k = 0; k < 3; ++k)
+                    {
+                        cv.dist_o[k] = c.top[k] - grow;
+                        cv.dist_n[k] = std::max(1, static_cast<int>(std::ceil((c.top[3 + k] - c.top[k] + 2.f * grow) / h)));
+                        voxels *= static_cast<size_t>(cv.dist_n[k]);
+                    }
+                    if (voxels <= (size_t(1) << 25) || h > 0.05f)
+                    {
+                        break;
+                    }
+                    h *= 1.26f;
+                }
+                if (voxels <= (size_t(1) << 25))
+                {
+                    cv.dist_inv_h = 1.f / h;
+                    cv.dist_cap = kCaptDistCap;
+                    cv.dist_pad = 0.5f * std::sqrt(3.f) * h * 1.001f + 1e-4f;
+                    rep.blobs.emplace_back();
+                    VB_CUDA(rep.blobs.back().reserve(voxels * sizeof(float)));
+                    uint32_t *bits = rep.blobs.back().as<uint32_t>();
+                    fill_float_bits_kernel<<<slot.sm_count * 8, 256, 0, slot.stream>>>(bits, voxels, kCaptDistCap);
+                    VB_CUDA(cudaGetLastError());
+                    const size_t leaves = size_t(1) << c.nlog2;
+                    capt_distance_kernel<<<static_cast<unsigned>((leaves + 127) / 128), 128, 0, slot.stream>>>(cv, leaves, bits);
+                    VB_CUDA(cudaGetLastError());
+                    cv.dist = rep.blobs.back().as<float>();
+                }
+            }
             cvs.push_back(cv);
         }
         VB_TRY(upload(rep.capt_desc, cvs, slot.stream));

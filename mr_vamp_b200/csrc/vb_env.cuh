@@ -14,6 +14,8 @@
 #ifndef VB_ENVHIT_ATTR
 #define VB_ENVHIT_ATTR __noinline__
 #endif
+#include <type_traits>
+
 #include "vb_numerics.cuh"
 
 namespace vb
@@ -35,6 +37,22 @@ namespace vb
         float r_point;
         uint32_t n_tests;
         int nlog2;
+        // occupancy bitmap over the cloud (built at vb_env_commit, vb_capi.cu: capt_occupancy_kernel): bit of voxel v set
+        // iff some point of the cloud lies within occ_reach + half a voxel diagonal of v's centre.  A query sphere
+        // whose voxel is clear (or that lies outside the bitmap's box) with r + r_point <= occ_reach cannot reach any
+        // point, so collides_simd -- which answers true only for a point of the cloud in range -- is false without the
+        // descent.  nullptr: none.
+        const uint32_t *occ;
+        float occ_o[3], occ_inv_h, occ_reach;
+        int occ_n[3];
+        // fine level: per voxel the distance from its centre to the nearest point of the cloud, capped at dist_cap
+        // (capt_distance_kernel).  d - dist_pad > r + r_point proves that no point is in range (distance to a point set is
+        // 1-Lipschitz; dist_pad = half a voxel diagonal + margin), which spares the leaf scan of the many spheres that
+        // pass close to a surface without touching it.  Only ever used to answer "false"; a hit is always found by the
+        // reference's own scan.  nullptr: none.
+        const float *dist;
+        float dist_o[3], dist_inv_h, dist_cap, dist_pad;
+        int dist_n[3];
     };
 
     struct HeightFieldView
@@ -128,6 +146,40 @@ namespace vb
         if (!inb)
         {
             return false;
+        }
+        if constexpr (std::is_same<M, NoMargin>::value)
+        {
+            // (verdict walks only: the margin / work-count walks execute every test of the reference)
+            if (c.occ != nullptr && r + c.r_point <= c.occ_reach)
+            {
+                const float fx = (x - c.occ_o[0]) * c.occ_inv_h, fy = (y - c.occ_o[1]) * c.occ_inv_h, fz = (z - c.occ_o[2]) * c.occ_inv_h;
+                const bool inside = fx >= 0.f && fy >= 0.f && fz >= 0.f && fx < static_cast<float>(c.occ_n[0]) &&
+                                    fy < static_cast<float>(c.occ_n[1]) && fz < static_cast<float>(c.occ_n[2]);
+                if (!inside)
+                {
+                    return false;  // the box extends occ_reach + a voxel beyond the cloud
+                }
+                const unsigned v = (static_cast<unsigned>(fz) * c.occ_n[1] + static_cast<unsigned>(fy)) * c.occ_n[0] + static_cast<unsigned>(fx);
+                if (!((__ldg(c.occ + (v >> 5)) >> (v & 31u)) & 1u))
+                {
+                    return false;
+                }
+            }
+            if (c.dist != nullptr && r + c.r_point < c.dist_cap - c.dist_pad)
+            {
+                const float fx = (x - c.dist_o[0]) * c.dist_inv_h, fy = (y - c.dist_o[1]) * c.dist_inv_h, fz = (z - c.dist_o[2]) * c.dist_inv_h;
+                const bool inside = fx >= 0.f && fy >= 0.f && fz >= 0.f && fx < static_cast<float>(c.dist_n[0]) &&
+                                    fy < static_cast<float>(c.dist_n[1]) && fz < static_cast<float>(c.dist_n[2]);
+                if (!inside)
+                {
+                    return false;  // the box extends dist_cap + a voxel beyond the cloud
+                }
+                const size_t v = (static_cast<size_t>(fz) * c.dist_n[1] + static_cast<size_t>(fy)) * c.dist_n[0] + static_cast<size_t>(fx);
+                if (__ldg(c.dist + v) - c.dist_pad > r + c.r_point)
+                {
+                    return false;
+                }
+            }
         }
         uint32_t idx = 0;
         int k = 0;

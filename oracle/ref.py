@@ -86,6 +86,8 @@ def lib():
         for fn in (L.vref_fkcc, L.vref_fkcc_packed, L.vref_fkcc_attach):
             fn.argtypes = [C.c_char_p, C.c_void_p, _f32p, C.c_size_t, _u8p, C.c_int]
         L.vref_validate_motion.argtypes = [C.c_char_p, C.c_void_p, _f32p, _f32p, C.c_size_t, _u8p, C.c_int]
+        L.vref_filter_pointcloud.argtypes = [_f32p, C.c_size_t, C.c_float, C.c_float, _f32p, _f32p, _f32p, C.c_int, _f32p]
+        L.vref_filter_pointcloud.restype = C.c_size_t
         L.vref_sphere_validity.argtypes = [C.c_char_p, C.c_void_p, _f32p, C.c_uint32, C.POINTER(C.c_uint32), C.POINTER(C.c_uint32)]
         L.vref_validate_vector.argtypes = [C.c_char_p, C.c_void_p, _f32p, _f32p, _f32p, C.c_size_t, _u8p, C.c_int]
         L.vref_env_float_ptr.argtypes = [C.c_void_p]
@@ -269,6 +271,17 @@ def validate_motion(robot, env, a, b, threads=1):
     if rc:
         raise RuntimeError(f"reference call failed ({rc})")
     return out.astype(bool)
+
+
+def filter_pointcloud(xyz, min_dist, max_range, origin, ws_min, ws_max, cull=True) -> np.ndarray:
+    """collision::filter_pointcloud (collision/filter.hh:176-275), as src/vamp/pointcloud.py:150-160 calls it."""
+    a, p = _f(xyz)
+    o, po = _f(origin)
+    lo, plo = _f(ws_min)
+    hi, phi = _f(ws_max)
+    out = np.zeros_like(a)
+    n = lib().vref_filter_pointcloud(p, a.shape[0], min_dist, max_range, po, plo, phi, int(cull), out.ctypes.data_as(_f32p))
+    return out[:n].copy()
 
 
 def sphere_validity(robot, env, cfg, cap=64):

@@ -77,6 +77,9 @@ int vref_fkcc_attach(const char *robot, const vref_env *, const float *cfg, size
 /* planning::validate_motion<Robot, 8, Robot::resolution>(a, b, env) (planning/validate.hh:67-75) */
 int vref_validate_motion(const char *robot, const vref_env *, const float *a, const float *b, size_t n,
                          uint8_t *valid, int threads);
+/* collision::filter_pointcloud (collision/filter.hh:176-275) -> number of points kept (written to out when != NULL) */
+size_t vref_filter_pointcloud(const float *xyz, size_t n, float min_dist, float max_range, const float *origin,
+                              const float *ws_min, const float *ws_max, int cull, float *out);
 /* Helper::sphere_validate (bindings/common.hh:155-170) of ONE configuration: per robot sphere the obstacles
  * sphere_environment_get_collisions reports, as their insertion indices (the order of the vref_env_add_* calls) */
 int vref_sphere_validity(const char *robot, const vref_env *, const float *cfg, uint32_t cap, uint32_t *hits,

@@ -4,6 +4,8 @@
 
 #include "vref_impl.hh"
 
+#include <vamp/collision/filter.hh>
+
 namespace vc = vamp::collision;
 using FV = vamp::FloatVector<vref::rake>;
 
@@ -382,6 +384,38 @@ int vref_validate_motion(
     vref::parallel(
         n, threads, env, [&](const vref::EnvV &ev, size_t lo, size_t hi) { vt->motion(ev, a, b, lo, hi, valid); });
     return 0;
+}
+
+// collision/filter.hh:176-275 (filter_pointcloud): the reference's own point-cloud thinning, as src/vamp/pointcloud.py
+// calls it before building the CAPT.  Returns the number of points kept; writes them when out != NULL.
+namespace
+{
+    struct PointView
+    {
+        const float *p;
+        size_t n;
+        size_t shape(int) const { return n; }
+        float operator()(size_t i, size_t k) const { return p[3 * i + k]; }
+    };
+}  // namespace
+
+size_t vref_filter_pointcloud(const float *xyz, size_t n, float min_dist, float max_range, const float *origin,
+                              const float *ws_min, const float *ws_max, int cull, float *out)
+{
+    const PointView pv{xyz, n};
+    const auto kept = vc::filter_pointcloud(pv, min_dist, max_range, vc::Point{origin[0], origin[1], origin[2]},
+                                            vc::Point{ws_min[0], ws_min[1], ws_min[2]}, vc::Point{ws_max[0], ws_max[1], ws_max[2]},
+                                            cull != 0);
+    if (out)
+    {
+        for (size_t i = 0; i < kept.size(); ++i)
+        {
+            out[3 * i] = kept[i][0];
+            out[3 * i + 1] = kept[i][1];
+            out[3 * i + 2] = kept[i][2];
+        }
+    }
+    return kept.size();
 }
 
 // Helper::sphere_validate (bindings/common.hh:155-170): fk, then sphere_environment_get_collisions per sphere
