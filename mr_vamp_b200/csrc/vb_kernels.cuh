@@ -35,6 +35,22 @@ namespace vb
 #define VB_LOCKSTEP_EVERY 1
 #endif
     constexpr unsigned kLockstepEvery = VB_LOCKSTEP_EVERY;
+    // Phase-staggered warp groups (fkcc kernels): the CTA's warps form kGroups groups that take turns in the straight-line
+    // ("dense": chain, guards, filters -- issue bound, ~100 KB of SASS streamed through the instruction caches) part of a
+    // step; while one group is there the others are in their sparse, latency-bound unit stages.  A ring of named barriers
+    // passes the dense section from group to group: group g waits on barrier 1 + g (bar.sync) before its chain and arrives
+    // at barrier 1 + (g + 1) % kGroups (bar.arrive) after its filters.  One group at a time streams the big code, so the
+    // instruction caches still serve a single stream, and the schedulers always have an issue-bound group to run.
+#ifndef VB_GROUPS
+#define VB_GROUPS 1
+#endif
+    constexpr int kGroupsWanted = VB_GROUPS;
+    template <class Robot>
+    __host__ __device__ constexpr int walk_groups()
+    {
+        // groups of equal size, at least 2 warps each
+        return (kGroupsWanted > 1 && (Robot::kBlock / 32) % kGroupsWanted == 0 && (Robot::kBlock / 32) / kGroupsWanted >= 2) ? kGroupsWanted : 1;
+    }
     // Every fkcc / motion kernel states its resident CTAs per SM (Robot::kCtasPerSm, fixed by the shared-memory
     // columns) as the second __launch_bounds__ argument: without it ptxas plans for 4 CTAs of kBlock threads,
     // caps the kernels at 64 registers and spills the in-flight grid cells (i.e. waits for every L2 load).
@@ -290,7 +306,7 @@ namespace vb
     // `base`: robot base offset (default: a.base; the second robot of a composite configuration passes a.base_b)
     template <class Robot, bool kSync = false>
     VB_D bool check_warp(const LaunchArgs &a, const Scratch &sc, const float *q, bool alive, bool attach, int &cstate,
-                         bool octet = false, const float *base = nullptr)
+                         bool octet = false, const float *base = nullptr, int release_id = 0, int release_count = 0)
     {
         const float *bs = base ? base : a.base;
         // kSync (CTA-uniform callers, `attach` uniform): the attachment decision must not depend on the warp
@@ -307,6 +323,10 @@ namespace vb
                 ok = check_config<Robot>(a, sc, q, attach, mg);
             }
             __syncwarp();
+            if (release_id != 0)
+            {
+                asm volatile("bar.arrive %0, %1;" ::"r"(release_id), "r"(release_count) : "memory");
+            }
             return ok;
         }
         VB_TICK_BEGIN;
@@ -342,6 +362,8 @@ namespace vb
         wc.bz = bs[2];
         wc.radius = a.sphere_radius;
         wc.octet = octet;
+        wc.release_id = release_id;
+        wc.release_count = release_count;
         const bool ok = Walk<Robot>::template run<kSync>(a.env, wc, !alive || phit, cstate, pfree);
         __syncwarp();  // columns are rewritten by the next configuration
         return ok;
@@ -397,7 +419,10 @@ namespace vb
         // configuration staging (verdict mode): [slot columns][queues][kBlock x dim floats][mbarrier]
         constexpr unsigned kCfgBytes = static_cast<unsigned>(Robot::kBlock) * Robot::kDim * 4u;
         constexpr unsigned stage_off = cfg_stage_offset<Robot>();
-        const bool staged = kMode == 0 && kStageAllowed && Robot::kStageCfg && kCfgBytes % 16u == 0u && (reinterpret_cast<uintptr_t>(a.cfg) & 15u) == 0u;
+        constexpr int kG = kMode == 0 ? walk_groups<Robot>() : 1;
+        constexpr int kGroupThreads = Robot::kBlock / kG;
+        const int group = static_cast<int>(threadIdx.x) / kGroupThreads;
+        const bool staged = kG == 1 && kMode == 0 && kStageAllowed && Robot::kStageCfg && kCfgBytes % 16u == 0u && (reinterpret_cast<uintptr_t>(a.cfg) & 15u) == 0u;
         const uint32_t stage_buf = shm_addr(stage_off), stage_bar = stage_buf + kCfgBytes;
         uint32_t stage_parity = 0u;
         if (staged)
@@ -487,7 +512,16 @@ namespace vb
                 // step's configurations).  Every reader fences before the barrier, the issuing thread after it.
                 asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
             }
-            if (staged || (kLockstep && (iter++ % kLockstepEvery) == 0))
+            const bool first_step = base == static_cast<size_t>(blockIdx.x) * blockDim.x, last_step = base + stride >= n_round;
+            if (kG > 1)
+            {
+                // wait for the dense section (the first group starts the ring)
+                if (!(first_step && group == 0))
+                {
+                    asm volatile("bar.sync %0, %1;" ::"r"(1 + group), "r"(2 * kGroupThreads) : "memory");
+                }
+            }
+            else if (staged || (kLockstep && (iter++ % kLockstepEvery) == 0))
             {
                 __syncthreads();  // (staging: every thread has taken its configuration out of the buffer)
             }
@@ -517,7 +551,9 @@ namespace vb
             }
             else
             {
-                ok = check_warp<Robot, kMidBarrier>(a, prims, q, alive, a.attach != 0, cstate);
+                // (the last group's last release would find nobody waiting: skipped)
+                const int rel = (kG > 1 && !(last_step && group == kG - 1)) ? 1 + (group + 1) % kG : 0;
+                ok = check_warp<Robot, kMidBarrier>(a, prims, q, alive, a.attach != 0, cstate, false, nullptr, rel, 2 * kGroupThreads);
             }
             const uint32_t word = __ballot_sync(0xffffffffu, ok);
             if ((threadIdx.x & 31) == 0 && i < n_round)
@@ -553,7 +589,18 @@ namespace vb
         {
             const size_t i = base + threadIdx.x;
             VB_TICK_BEGIN;
-            if (kLockstep && (iter++ % kLockstepEvery) == 0)
+            constexpr int kG = walk_groups<Robot>();
+            constexpr int kGroupThreads = Robot::kBlock / kG;
+            const int group = static_cast<int>(threadIdx.x) / kGroupThreads;
+            const bool first_step = base == static_cast<size_t>(blockIdx.x) * blockDim.x, last_step = base + stride >= n_round;
+            if (kG > 1)
+            {
+                if (!(first_step && group == 0))
+                {
+                    asm volatile("bar.sync %0, %1;" ::"r"(1 + group), "r"(2 * kGroupThreads) : "memory");
+                }
+            }
+            else if (kLockstep && (iter++ % kLockstepEvery) == 0)
             {
                 __syncthreads();
             }
@@ -562,7 +609,8 @@ namespace vb
             float q[Robot::kDim];
             random_config<Robot>(a.seed, first + i, q);
             VB_TICK(11);
-            const bool ok = check_warp<Robot, kMidBarrier>(a, prims, q, alive, a.attach != 0, cstate);
+            const int rel = (kG > 1 && !(last_step && group == kG - 1)) ? 1 + (group + 1) % kG : 0;
+            const bool ok = check_warp<Robot, kMidBarrier>(a, prims, q, alive, a.attach != 0, cstate, false, nullptr, rel, 2 * kGroupThreads);
             VB_TICK(12);
             const uint32_t word = __ballot_sync(0xffffffffu, ok);
             if ((threadIdx.x & 31) == 0 && i < n_round)
@@ -1052,6 +1100,8 @@ namespace vb
                 cb.bx = a.base_b[0], cb.by = a.base_b[1], cb.bz = a.base_b[2];
                 ca.radius = cb.radius = a.sphere_radius;
                 ca.octet = cb.octet = false;
+                ca.release_id = cb.release_id = 0;
+                ca.release_count = cb.release_count = 0;
                 ok = !robots_overlap<Robot>(ca, cb, lane);
             }
             __syncwarp();

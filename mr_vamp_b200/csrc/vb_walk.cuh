@@ -123,7 +123,19 @@ namespace vb
         // tests of ALL lanes.  That coupling changes verdicts where a guard query is unreliable: CAPT point
         // clouds queried with a bounding-sphere radius beyond the tree's r_max.
         bool octet;
+        // Phase-staggered warp groups (vb_kernels.cuh: kGroups): named barrier this warp's group ARRIVES at when it leaves
+        // the straight-line ("dense") part of a step, handing the dense section to the next group; 0: none.
+        int release_id, release_count;
     };
+
+    VB_D void group_release(const WalkCtx &c)
+    {
+        if (c.release_id != 0)
+        {
+            __syncwarp();
+            asm volatile("bar.arrive %0, %1;" ::"r"(c.release_id), "r"(c.release_count) : "memory");
+        }
+    }
 
     // ---- layout of the dynamic shared-memory window (bytes) -------------------------------------------------
     //   [3 * kSlots rows of kStride floats: one column per thread][per-warp work queues][staged configurations +
@@ -696,6 +708,7 @@ namespace vb
                     {
                         __syncthreads();
                     }
+                    group_release(c);
                     return false;
                 }
             }
@@ -727,6 +740,21 @@ namespace vb
                 }
                 VB_TICK(7);
                 const uint32_t live = collided ? 0u : 0xffffffffu;
+                if (c.octet)
+                {
+                    // rake coupling (planning/validate.hh:36-60 + robots/<robot>/fk.hh): a guard that fires in ANY of the 8
+                    // lanes of a block opens the fine tests of ALL its lanes.  Fine spheres overhang their traced bounding
+                    // spheres by up to 0.6 mm, so a lane whose own guard misses can still collide in that sliver.
+#pragma unroll
+                    for (int wi = 0; wi < Robot::kSelfWords; ++wi)
+                    {
+                        uint32_t v = fired[wi] & ~Robot::self_leaf_mask(wi);  // (a leaf group's guard IS its test: no coupling)
+                        v |= __shfl_xor_sync(kFull, v, 1);
+                        v |= __shfl_xor_sync(kFull, v, 2);
+                        v |= __shfl_xor_sync(kFull, v, 4);
+                        fired[wi] |= v;
+                    }
+                }
 #pragma unroll
                 for (int wi = 0; wi < Robot::kSelfWords; ++wi)
                 {
@@ -751,9 +779,19 @@ namespace vb
                 }
                 Robot::self_filters(col, fired, ubits);
                 VB_TICK(5);
+                group_release(c);  // end of the straight-line part of the step
                 run_units(c, ubits);
                 VB_TICK(6);
                 collided = collided || done(c, lane);
+            }
+            else
+            {
+                if (grid)
+                {
+                    Robot::env_classify(cells, inside, c.radius, env.sdf, maybe, cert, gmask(c) + lane);
+                    classified = true;
+                }
+                group_release(c);
             }
             if (kSync)
             {
@@ -815,6 +853,88 @@ namespace vb
                         maybe[wi] = v;
                     }
                 }
+            }
+            if (c.octet && grid)
+            {
+                // Edges: the exact guard test runs lane-parallel per group, so that its outcome can be OR-ed over the 8
+                // lanes of a rake block before the fine tests are opened (rake coupling, as above).  Lanes the grid calls
+                // free cannot collide whatever their siblings do (the grid's margin exceeds the overhang).
+                const PrimIndex ix = prim_index(env);
+                const int n_obj = ix.first[5];
+#pragma unroll
+                for (int wi = 0; wi < Robot::kEnvWords; ++wi)
+                {
+                    const uint32_t mine = collided ? 0u : (maybe[wi] & ~Robot::env_const_mask(wi));
+                    uint32_t any = __reduce_or_sync(kFull, mine);
+                    while (any)
+                    {
+                        const int b = __ffs(any) - 1;
+                        any &= any - 1u;
+                        const int g = wi * 32 + b;
+                        const bool on = (mine >> b) & 1u;
+                        const RefGroup G = T::env(g);
+                        bool ghit = false;
+                        uint32_t tight = 0u;
+                        if (on)
+                        {
+                            const uint32_t mask = gmask(c)[32 * g + lane];
+                            const Center s = centre(c, lane, G.guard);
+                            uint32_t low = mask & 0x7fffffffu;
+                            if (n_obj < 31)
+                            {
+                                low &= (1u << n_obj) - 1u;
+                            }
+                            const bool high = (mask >> 31) != 0u;
+                            int cursor = 0;
+                            for (int o = next_candidate(low, high, n_obj, cursor); o >= 0; o = next_candidate(low, high, n_obj, cursor))
+                            {
+                                const ObjDist d = object_dist(c.prims, ix, o, s.x, s.y, s.z);
+                                ghit = ghit || object_hit(d, s.r);
+                                if (G.slack < 0.f || object_hit(d, s.r + G.slack))
+                                {
+                                    tight |= 1u << (o < 31 ? o : 31);
+                                }
+                            }
+                        }
+                        const unsigned fired_lanes = __ballot_sync(kFull, ghit);
+                        const bool open = ((fired_lanes >> (lane & ~7)) & 0xffu) != 0u;
+                        if (G.count == 0)
+                        {
+                            if (ghit)
+                            {
+                                atomicOr(cmask(c), 1u << lane);  // leaf group: the guard is the test
+                            }
+                        }
+                        else if (on && open && tight != 0u)
+                        {
+                            gmask(c)[32 * g + lane] = tight;
+                            const unsigned at = atomicAdd(cmask(c) + 1, static_cast<unsigned>(G.ucount));
+                            bool hit = false;
+                            for (int k = 0; k < G.ucount; ++k)
+                            {
+                                if (at + k < static_cast<unsigned>(Robot::kPairQ))
+                                {
+                                    pairq(c)[at + k] = static_cast<uint16_t>(lane | ((G.ubegin + k) << 5));
+                                }
+                                else
+                                {
+                                    hit = hit || fine_unit(c, Robot::walk_tables(), ix, lane, G.ubegin + k);
+                                }
+                            }
+                            if (hit)
+                            {
+                                atomicOr(cmask(c), 1u << lane);
+                            }
+                        }
+                        __syncwarp();
+                        if (vol(cmask(c) + 1) >= static_cast<unsigned>(Robot::kPairQ) / 2)
+                        {
+                            fine_stage(env, c);
+                        }
+                    }
+                }
+                fine_stage(env, c);
+                return !(collided || done(c, lane));
             }
             int ne = 0;
 #pragma unroll

@@ -138,3 +138,35 @@ def test_validate_joint_limits(vb, ref):
     got = robot.validate_batch(q, env)
     want = ref.validate("panda_0_0", ref.Env(), q)
     assert np.array_equal(got, want)
+
+
+@pytest.mark.parametrize("name", ["panda", "ur5", "fetch"])
+@pytest.mark.parametrize("scene", ["65 primitives", "clipped grid"])
+def test_large_scenes_exercise_the_grid_fallbacks(vb, ref, name, scene):
+    """Branches of the acceleration structure the small scenes never reach: more than 31 obstacles (bit 31 of a candidate
+    mask = 'some obstacle with index >= 31': vb_sdf.cuh next_candidate / sdf_build_kernel) and a scene that does not fit
+    the +-4 m grid box (clipped grid, cover = 0, spheres outside the grid: grid_class with in == false)."""
+    from mr_vamp_b200 import api as _api
+
+    robot = vb.Robot(name)
+    if scene == "65 primitives":
+        spec = scenes.random_scene(23, n_spheres=15, n_cuboids=15, n_zcuboids=15, n_capsules=10, n_zcapsules=10, reach=1.1)
+        # thin the clutter around the base so that a fair share of the configurations stays valid
+        spec = [it for it in spec if it[0] != "sphere" or np.hypot(it[1], it[2]) > 0.45 or it[3] > 0.9]
+    else:
+        floor = _api.Cuboid([0.0, 0.0, -0.3], [0.0, 0.0, 0.3], [6.0, 6.0, 0.05]).raw()  # half extent 6 m > the 4 m box
+        far = _api.Cuboid([5.0, 0.5, 0.5], [0.3, 0.2, 0.1], [0.4, 0.4, 0.4]).raw()
+        spec = [("cuboid", floor), ("cuboid", far), ("sphere", 0.5, 0.3, 0.6, 0.15), ("sphere", -0.4, 0.5, 0.9, 0.2),
+                ("capsule", _api.Cylinder([0.6, -0.4, 0.4], [0.0, 0.0, 0.0], 0.06, 0.5).raw())]
+    env = scenes.apply(spec, vb.Environment())
+    renv = apply_ref(spec, ref.Env())
+    rn = REF_NAME.get(name, name)
+    q = _cfgs(robot, 33, 30000)
+    want, clr = ref.fkcc_clearance(rn, renv, q, threads=8)
+    ok, mg = robot.fkcc_batch(q, env, margin=True)
+    judge(f"{name}/{scene} lane-serial", ok, want, clr)
+    judge(f"{name}/{scene} warp walk", robot.fkcc_batch(q, env), want, clr)
+    a, b = q[:3000], np.clip(q[:3000] + np.float32(0.2) * np.sign(q[3000:6000]), robot.lower_bounds, robot.lower_bounds + robot.ranges)
+    e_want, e_clr = ref.motion_clearance(rn, renv, a, b, threads=8)
+    judge(f"{name}/{scene} edges", robot.validate_motion_batch(a, b, env), e_want, e_clr)
+    assert name == "fetch" or 0.02 < want.mean() < 0.98
