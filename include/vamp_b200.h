@@ -194,6 +194,11 @@ int vb_shortcut_path(vb_ctx *, vb_robot, const float *base_xyz, const vb_env *, 
 int vb_validate_pairs(vb_ctx *, vb_robot robot_a, const float *base_a, vb_robot robot_b, const float *base_b,
                       const vb_env *, const float *cfg_a, const float *cfg_b, size_t n, uint32_t *valid_bits);
 
+/* the robot-robot term alone (the fork's planned check_inter_robot_collisions, MR_DEV_PLAN.md:176-198): bit = 1 iff no
+ * world-frame sphere of robot a overlaps a sphere of robot b; environment and self collision are not looked at */
+int vb_inter_robot(vb_ctx *, vb_robot robot_a, const float *base_a, vb_robot robot_b, const float *base_b,
+                   const float *cfg_a, const float *cfg_b, size_t n, uint32_t *clear_bits);
+
 /* ---- queries, device-resident (single device slot, asynchronous on that slot's stream) ---- */
 int vb_dev_alloc(vb_ctx *, int slot, size_t bytes, void **ptr_d);
 int vb_dev_free(vb_ctx *, int slot, void *ptr_d);

@@ -75,6 +75,7 @@ _SIGNATURES = [
                                   C.POINTER(C.c_uint64), C.POINTER(C.c_size_t), C.POINTER(C.c_size_t)]),
     ("vb_validate_motion_indexed", C.c_int, [_vp, C.c_int, _f32p, _vp, _vp, C.c_size_t, _u32p, C.c_size_t, C.c_int, _u32p]),
     ("vb_validate_pairs", C.c_int, [_vp, C.c_int, _f32p, C.c_int, _f32p, _vp, _f32p, _f32p, C.c_size_t, _u32p]),
+    ("vb_inter_robot", C.c_int, [_vp, C.c_int, _f32p, C.c_int, _f32p, _f32p, _f32p, C.c_size_t, _u32p]),
     ("vb_validate_pairs_d", C.c_int, [_vp, C.c_int, C.c_int, _f32p, _f32p, _vp, _vp, _vp, C.c_size_t, _vp]),
     ("vb_dev_alloc", C.c_int, [_vp, C.c_int, C.c_size_t, C.POINTER(_vp)]),
     ("vb_dev_free", C.c_int, [_vp, C.c_int, _vp]),

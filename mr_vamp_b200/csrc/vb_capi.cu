@@ -2424,6 +2424,9 @@ static int pairs_host_fused(vb_ctx *ctx, vb_robot robot, const float *base_a, co
     return vb_sync(ctx);
 }
 
+static int pairs_host_unfused(vb_ctx *ctx, vb_robot robot_a, const float *base_a, vb_robot robot_b, const float *base_b,
+                              const vb_env *env, const float *cfg_a, const float *cfg_b, size_t n, uint32_t *valid_bits);
+
 int vb_validate_pairs(vb_ctx *ctx, vb_robot robot_a, const float *base_a, vb_robot robot_b, const float *base_b,
                       const vb_env *env, const float *cfg_a, const float *cfg_b, size_t n, uint32_t *valid_bits)
 {
@@ -2441,18 +2444,53 @@ int vb_validate_pairs(vb_ctx *ctx, vb_robot robot_a, const float *base_a, vb_rob
         // two robots of one kind (mr-vamp's Panda grid): the fused kernel, one launch per chunk
         return pairs_host_fused(ctx, robot_a, base_a, base_b, env, cfg_a, cfg_b, n, valid_bits);
     }
+    return pairs_host_unfused(ctx, robot_a, base_a, robot_b, base_b, env, cfg_a, cfg_b, n, valid_bits);
+}
+
+// The robot-robot term alone (MR_DEV_PLAN.md:176-198 check_inter_robot_collisions): bit = 1 iff NO world-frame sphere
+// of robot A overlaps a sphere of robot B; environment and self collision are not looked at.
+int vb_inter_robot(vb_ctx *ctx, vb_robot robot_a, const float *base_a, vb_robot robot_b, const float *base_b, const float *cfg_a,
+                   const float *cfg_b, size_t n, uint32_t *clear_bits)
+{
+    if (!ctx || (n && (!cfg_a || !cfg_b || !clear_bits)))
+    {
+        return fail(VB_ERR_ARG, "vb_inter_robot: null argument");
+    }
+    return pairs_host_unfused(ctx, robot_a, base_a, robot_b, base_b, nullptr, cfg_a, cfg_b, n, clear_bits);
+}
+
+// env == nullptr: the robot-robot term only (verdict words start as all ones)
+static int pairs_host_unfused(vb_ctx *ctx, vb_robot robot_a, const float *base_a, vb_robot robot_b, const float *base_b,
+                              const vb_env *env, const float *cfg_a, const float *cfg_b, size_t n, uint32_t *valid_bits)
+{
+    const vb::RobotOps *oa = ops_of(robot_a), *ob = ops_of(robot_b);
+    if (!oa || !ob)
+    {
+        return fail(VB_ERR_ARG, "unknown robot id");
+    }
     if (oa->n_spheres > kPairMaxSpheres)
     {
         return fail(VB_ERR_ARG, "vb_validate_pairs: robot A has more than %d spheres", kPairMaxSpheres);
     }
     // robots of different kinds: each robot's own validity (environment + self collision) on all devices, then the
     // robot-robot pairs from both sphere sets, chunked so that the two sphere buffers stay below ~1 GB per device
-    std::vector<uint32_t> bits_b((n + 31) / 32);
-    VB_TRY(vb_fkcc(ctx, robot_a, base_a, env, cfg_a, n, valid_bits, nullptr));
-    VB_TRY(vb_fkcc(ctx, robot_b, base_b, env, cfg_b, n, bits_b.data(), nullptr));
-    for (size_t w = 0; w < bits_b.size(); ++w)
+    if (env)
     {
-        valid_bits[w] &= bits_b[w];
+        std::vector<uint32_t> bits_b((n + 31) / 32);
+        VB_TRY(vb_fkcc(ctx, robot_a, base_a, env, cfg_a, n, valid_bits, nullptr));
+        VB_TRY(vb_fkcc(ctx, robot_b, base_b, env, cfg_b, n, bits_b.data(), nullptr));
+        for (size_t w = 0; w < bits_b.size(); ++w)
+        {
+            valid_bits[w] &= bits_b[w];
+        }
+    }
+    else
+    {
+        for (size_t w = 0; w < (n + 31) / 32; ++w)
+        {
+            const size_t rem = n - w * 32;
+            valid_bits[w] = rem >= 32 ? 0xffffffffu : ((1u << rem) - 1u);
+        }
     }
     const size_t per_cfg = static_cast<size_t>(oa->n_spheres + ob->n_spheres) * sizeof(float4);
     const size_t chunk = std::max<size_t>(32, (size_t(1) << 30) / per_cfg / 32 * 32);

@@ -8,6 +8,11 @@
 //   <robot>.fk(configuration)                                  bindings/common.hh:132-152,706-710
 //   <robot>.sphere_validity(configuration, environment)        bindings/common.hh:155-170,699-704
 //   <robot>.dimension() / resolution() / n_spheres() / lower_bounds() / upper_bounds()
+//   problem_dict_to_vamp(problem, ignore_names)                src/vamp/__init__.py:135-181 (here in C++)
+//   RobotFactory / Robot / MultiRobotEnvironment               robots/robot_factory.hh:23-189, robots/robot_interface.hh and
+//                                                              the planned collision/multi_robot_environment.hh + bindings
+//                                                              (MR_DEV_PLAN.md:176-198,244-279) over vb_validate_pairs /
+//                                                              vb_inter_robot
 //   + the batch calls the reference lists as a TODO (README.md:308), zero-copy numpy in / out, GIL released:
 //   <robot>.validate_batch / fkcc_batch / validate_motion_batch / validate_vector_batch / fk_batch
 //
@@ -17,8 +22,10 @@
 #include <pybind11/pybind11.h>
 #include <pybind11/stl.h>
 
+#include <algorithm>
 #include <array>
 #include <cmath>
+#include <cstdio>
 #include <memory>
 #include <stdexcept>
 #include <string>
@@ -408,6 +415,204 @@ namespace
         }
     };
 
+    // ---- the fork's OO multi-robot layer (robots/robot_factory.hh, MR_DEV_PLAN.md) ---------------------------------------
+    // RobotInterface: one Panda of the 3 x 3 grid (robots/panda_grid.hh:10-41), identified by name and base position
+    struct GridRobot
+    {
+        std::string name;
+        std::shared_ptr<Robot> robot;
+        std::string get_name() const { return name; }
+        std::array<float, 3> get_base_position() const { return robot->base; }
+    };
+
+    struct RobotFactory
+    {
+        static std::vector<std::string> variants()
+        {
+            std::vector<std::string> out;
+            for (int x = 0; x < 3; ++x)
+            {
+                for (int y = 0; y < 3; ++y)
+                {
+                    out.push_back("panda_" + std::to_string(x) + "_" + std::to_string(y));
+                }
+            }
+            return out;
+        }
+        // robots/robot_factory.hh:66-85 (create_panda_grid): "panda_X_Y" -> base (X, Y, 0.05) metres.  The generated FK the
+        // kernels run is PandaBase<X*100, Y*100, 0> (robots/panda_grid.hh: z = 0; the factory's comment says 5 cm), so z = 0.
+        static GridRobot create_panda_grid(const std::string &variant)
+        {
+            int x = -1, y = -1;
+            if (std::sscanf(variant.c_str(), "panda_%d_%d", &x, &y) != 2 || x < 0 || x > 2 || y < 0 || y > 2)
+            {
+                throw std::runtime_error("Unknown Panda grid variant: " + variant);
+            }
+            return GridRobot{variant, std::make_shared<Robot>("panda", std::array<float, 3>{static_cast<float>(x), static_cast<float>(y), 0.f})};
+        }
+        // robots/robot_factory.hh:33-64 (create_panda): nearest grid position, error when it is not on the grid
+        static GridRobot create_panda(float x, float y, float z)
+        {
+            const int gx = static_cast<int>(std::lround(x * 100)), gy = static_cast<int>(std::lround(y * 100)),
+                      gz = static_cast<int>(std::lround(z * 100));
+            if (gx % 100 != 0 || gy % 100 != 0 || gx < 0 || gx > 200 || gy < 0 || gy > 200 || (gz != 0 && gz != 5))
+            {
+                throw std::runtime_error("Position (" + std::to_string(x) + ", " + std::to_string(y) + ", " + std::to_string(z) +
+                                         ") not supported in grid");
+            }
+            return create_panda_grid("panda_" + std::to_string(gx / 100) + "_" + std::to_string(gy / 100));
+        }
+    };
+
+    // MR_DEV_PLAN.md:176-198: robots + one base environment; inter-robot collision checks on composite configurations
+    class MultiRobotEnvironment
+    {
+    public:
+        MultiRobotEnvironment() : env_(std::make_shared<Environment>()) {}
+        void add_robot(const GridRobot &r) { robots_.push_back(r); }
+        void remove_robot(size_t i)
+        {
+            if (i >= robots_.size())
+            {
+                throw std::out_of_range("remove_robot: index out of range");
+            }
+            robots_.erase(robots_.begin() + static_cast<std::ptrdiff_t>(i));
+        }
+        size_t size() const { return robots_.size(); }
+        void add_obstacle(const Sphere &s) { env_->add_sphere(s); }
+        void add_cuboid(const Cuboid &c) { env_->add_cuboid(c); }
+        void add_capsule(const Cylinder &c) { env_->add_capsule(c); }
+        std::shared_ptr<Environment> environment() const { return env_; }
+
+        // configs float32[n][n_robots][7].  inter_only: true = no sphere of any robot overlaps a sphere of another
+        // (check_inter_robot_collisions negated); false = additionally every robot is valid on its own (environment + self
+        // collision): the composite validity a multi-robot planner needs.  One batch per robot pair.
+        py::array_t<bool> batch(const FArray &configs, bool inter_only)
+        {
+            const size_t nr = robots_.size();
+            if (configs.ndim() != 3 || static_cast<size_t>(configs.shape(1)) != nr || configs.shape(2) != 7)
+            {
+                throw std::invalid_argument("expected float32[n, " + std::to_string(nr) + ", 7]");
+            }
+            const size_t n = static_cast<size_t>(configs.shape(0));
+            std::vector<uint32_t> all((n + 31) / 32, 0xffffffffu), bits((n + 31) / 32);
+            std::vector<std::vector<float>> q(nr, std::vector<float>(n * 7));
+            for (size_t i = 0; i < n; ++i)
+            {
+                for (size_t r = 0; r < nr; ++r)
+                {
+                    std::copy_n(configs.data() + (i * nr + r) * 7, 7, q[r].data() + i * 7);
+                }
+            }
+            vb_env *eh = env_->handle();
+            {
+                py::gil_scoped_release nogil;
+                if (nr == 1 && !inter_only)
+                {
+                    check(vb_fkcc(env_->ctx(), robots_[0].robot->id, robots_[0].robot->base.data(), eh, q[0].data(), n, all.data(), nullptr));
+                }
+                for (size_t a = 0; a < nr; ++a)
+                {
+                    for (size_t b = a + 1; b < nr; ++b)
+                    {
+                        const Robot &ra = *robots_[a].robot, &rb = *robots_[b].robot;
+                        if (inter_only)
+                        {
+                            check(vb_inter_robot(env_->ctx(), ra.id, ra.base.data(), rb.id, rb.base.data(), q[a].data(), q[b].data(), n,
+                                                 bits.data()));
+                        }
+                        else
+                        {
+                            check(vb_validate_pairs(env_->ctx(), ra.id, ra.base.data(), rb.id, rb.base.data(), eh, q[a].data(),
+                                                    q[b].data(), n, bits.data()));
+                        }
+                        for (size_t w = 0; w < all.size(); ++w)
+                        {
+                            all[w] &= bits[w];
+                        }
+                    }
+                }
+            }
+            return Robot::unpack(all, n);
+        }
+
+        // MR_DEV_PLAN.md:190: true iff some pair of robots collides at this composite configuration
+        bool check_inter_robot_collisions(const std::vector<std::vector<float>> &configs)
+        {
+            if (configs.size() != robots_.size())
+            {
+                throw std::invalid_argument("one configuration per robot expected");
+            }
+            FArray flat({static_cast<py::ssize_t>(1), static_cast<py::ssize_t>(robots_.size()), static_cast<py::ssize_t>(7)});
+            for (size_t r = 0; r < configs.size(); ++r)
+            {
+                if (configs[r].size() != 7)
+                {
+                    throw std::invalid_argument("7 joint values per Panda expected");
+                }
+                std::copy_n(configs[r].data(), 7, flat.mutable_data() + r * 7);
+            }
+            return !batch(flat, true).at(0);
+        }
+
+    private:
+        std::vector<GridRobot> robots_;
+        std::shared_ptr<Environment> env_;
+    };
+
+    // src/vamp/__init__.py:135-181 (problem_dict_to_vamp): MotionBenchMaker problem dictionary -> Environment
+    std::shared_ptr<Environment> problem_dict_to_vamp(const py::dict &problem, const std::vector<std::string> &ignore)
+    {
+        auto env = std::make_shared<Environment>();
+        auto ignored = [&](const py::handle &obj) {
+            const std::string name = obj.contains("name") ? py::cast<std::string>(obj["name"]) : std::string();
+            return std::find(ignore.begin(), ignore.end(), name) != ignore.end();
+        };
+        auto name_of = [](const py::handle &obj) { return obj.contains("name") ? py::cast<std::string>(obj["name"]) : std::string(); };
+        auto vec3 = [](const py::handle &v) { return py::cast<std::array<float, 3>>(v); };
+        auto list_of = [&](const char *key) { return problem.contains(key) ? py::cast<py::list>(problem[key]) : py::list(); };
+        for (const auto &obj : list_of("sphere"))
+        {
+            if (!ignored(obj))
+            {
+                const auto p = vec3(obj["position"]);
+                env->add_sphere(Sphere{p[0], p[1], p[2], py::cast<float>(obj["radius"]), name_of(obj)});
+            }
+        }
+        // "box" problems approximate their cylinders by boxes (a top-down grasp of the cylinder, __init__.py:146-160)
+        const bool box_problem = problem.contains("problem") && py::cast<std::string>(problem["problem"]) == "box";
+        for (const auto &obj : list_of("cylinder"))
+        {
+            if (ignored(obj))
+            {
+                continue;
+            }
+            const float radius = py::cast<float>(obj["radius"]), length = py::cast<float>(obj["length"]);
+            if (box_problem)
+            {
+                Cuboid c = make_cuboid(vec3(obj["position"]), vec3(obj["orientation_euler_xyz"]), {radius, radius, length / 2.f});
+                c.name = name_of(obj);
+                env->add_cuboid(c);
+            }
+            else
+            {
+                Cylinder c = make_cylinder(vec3(obj["position"]), vec3(obj["orientation_euler_xyz"]), radius, length);
+                c.name = name_of(obj);
+                env->add_capsule(c);
+            }
+        }
+        for (const auto &obj : list_of("box"))
+        {
+            if (!ignored(obj))
+            {
+                Cuboid c = make_cuboid(vec3(obj["position"]), vec3(obj["orientation_euler_xyz"]), vec3(obj["half_extents"]));
+                c.name = name_of(obj);
+                env->add_cuboid(c);
+            }
+        }
+        return env;
+    }
+
     void bind_robot(py::module_ &m, const char *module_name, const char *robot_name, std::array<float, 3> base)
     {
         auto sub = m.def_submodule(module_name);
@@ -511,6 +716,42 @@ PYBIND11_MODULE(_core_ext, m)
         .def("add_heightfield", &Environment::add_heightfield)
         .def("attach", &Environment::attach)
         .def("detach", &Environment::detach);
+
+    m.def("problem_dict_to_vamp", &problem_dict_to_vamp, "problem"_a, "ignore_names"_a = std::vector<std::string>{},
+          "MotionBenchMaker problem dictionary -> Environment (src/vamp/__init__.py:135-181)");
+
+    py::class_<GridRobot>(m, "Robot")
+        .def("get_name", &GridRobot::get_name)
+        .def("get_base_position", &GridRobot::get_base_position)
+        .def("fk", [](GridRobot &r, const FArray &q) { return r.robot->fk(q); })
+        .def("fk_batch", [](GridRobot &r, const FArray &q) { return r.robot->fk_batch(q); })
+        .def(
+            "validate", [](GridRobot &r, const FArray &q, Environment *env) { return r.robot->validate(q, env); }, "configuration"_a,
+            "environment"_a = py::none())
+        .def(
+            "validate_batch", [](GridRobot &r, const FArray &q, Environment *env) { return r.robot->validate_batch(q, env); },
+            "configurations"_a, "environment"_a = py::none());
+    py::class_<RobotFactory>(m, "RobotFactory")
+        .def_static("create_panda", &RobotFactory::create_panda, "x"_a, "y"_a, "z"_a)
+        .def_static("create_panda_grid", &RobotFactory::create_panda_grid, "variant"_a)
+        .def_static("get_available_variants", &RobotFactory::variants);
+    py::class_<MultiRobotEnvironment>(m, "MultiRobotEnvironment")
+        .def(py::init<>())
+        .def("add_robot", &MultiRobotEnvironment::add_robot)
+        .def("remove_robot", &MultiRobotEnvironment::remove_robot)
+        .def("__len__", &MultiRobotEnvironment::size)
+        .def("add_obstacle", &MultiRobotEnvironment::add_obstacle)
+        .def("add_cuboid", &MultiRobotEnvironment::add_cuboid)
+        .def("add_capsule", &MultiRobotEnvironment::add_capsule)
+        .def_property_readonly("environment", &MultiRobotEnvironment::environment)
+        .def("check_inter_robot_collisions", &MultiRobotEnvironment::check_inter_robot_collisions, "configurations"_a,
+             "True iff some pair of robots collides at this composite configuration (MR_DEV_PLAN.md:190).")
+        .def(
+            "inter_robot_clear_batch", [](MultiRobotEnvironment &e, const FArray &q) { return e.batch(q, true); }, "configurations"_a,
+            "float32[n, n_robots, 7] -> bool[n]: no sphere of any robot overlaps a sphere of another.")
+        .def(
+            "validate_batch", [](MultiRobotEnvironment &e, const FArray &q) { return e.batch(q, false); }, "configurations"_a,
+            "float32[n, n_robots, 7] -> bool[n]: every robot valid (environment + self collision) and no robot-robot overlap.");
 
     bind_robot(m, "sphere", "sphere", {0.f, 0.f, 0.f});
     bind_robot(m, "ur5", "ur5", {0.f, 0.f, 0.f});
