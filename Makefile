@@ -41,7 +41,11 @@ $(OBJ)/vb_capi.o: $(CSRC)/vb_capi.cu $(HDRS)
 	@mkdir -p $(OBJ)
 	$(NVCC) $(NVFLAGS) -c $< -o $@ 2> $(OBJ)/vb_capi.ptxas.log || (cat $(OBJ)/vb_capi.ptxas.log; exit 1)
 
-$(LIB): $(OBJ)/vb_capi.o $(foreach r,$(ROBOTS),$(OBJ)/vb_robot_$(r).o)
+$(OBJ)/vb_capt_build.o: $(CSRC)/vb_capt_build.cu $(CSRC)/vb_capt_build.h
+	@mkdir -p $(OBJ)
+	$(NVCC) $(NVFLAGS) -c $< -o $@ 2> $(OBJ)/vb_capt_build.ptxas.log || (cat $(OBJ)/vb_capt_build.ptxas.log; exit 1)
+
+$(LIB): $(OBJ)/vb_capi.o $(OBJ)/vb_capt_build.o $(foreach r,$(ROBOTS),$(OBJ)/vb_robot_$(r).o)
 	@mkdir -p $(dir $@)
 	$(NVCC) $(ARCH) -shared -o $@ $^ -ldl
 

@@ -16,6 +16,8 @@
  *                           collision/environment.hh:26-66 (per-call float->vector conversion: gone,
  *                           the device copy is rebuilt only by vb_env_commit)
  *   vb_env_add_capt         collision::CAPT query buffers, collision/capt.hh:588-621
+ *   vb_env_add_pointcloud   Environment.add_pointcloud, bindings/environment.cc:148-158 -> collision::CAPT(points, r_min,
+ *                           r_max, r_point), collision/capt.hh:137-398: the tree is BUILT by the library, on the device
  *   vb_env_set_attachment   Environment::attachments, collision/attachments.hh:11-73
  *   vb_sphere_fk            Robot::sphere_fk, robots/panda_base.hh:67-71 (+ ur5/fetch/baxter/sphere .hh),
  *                           bindings/common.hh:132-152 (Helper::fk)
@@ -116,6 +118,13 @@ int vb_env_add_heightfield(vb_env *, const float *off_scale, size_t xd, size_t y
 int vb_env_add_capt(vb_env *, const float *tests, size_t n_tests, const uint32_t *aff_starts, const float *aff_x,
                     const float *aff_y, const float *aff_z, size_t n_aff_vec, const float *aabbs, size_t n_aabbs,
                     const float *aabb_top, float r_point, int nlog2);
+/* a point cloud as raw points [n][3]: the CAPT (split values, per-leaf affordance lists, leaf boxes) is built on the
+ * context's first device exactly as collision::CAPT's constructor defines it; *build_ms = device time of the build */
+int vb_env_add_pointcloud(vb_env *, const float *xyz, size_t n, float r_min, float r_max, float r_point, double *build_ms);
+/* the query buffers of point cloud `idx` as the library holds them (affordances interleaved per 8-point vector:
+ * x[8] y[8] z[8]); counts always, data where the pointer is non-null */
+int vb_env_capt_export(const vb_env *, size_t idx, size_t *n_tests, size_t *n_aff_vec, float *tests, uint32_t *aff_starts,
+                       float *aff, float *aabbs, float *aabb_top, int *nlog2);
 /* tf[7] = tx ty tz qx qy qz qw; spheres [n][4] = x y z r (end-effector frame); n <= 16 */
 int vb_env_set_attachment(vb_env *, const float *tf, const float *spheres, size_t n);
 int vb_env_clear_attachment(vb_env *);

@@ -58,6 +58,9 @@ _SIGNATURES = [
     ("vb_env_add_heightfield", C.c_int, [_vp, _f32p, C.c_size_t, C.c_size_t, _f32p]),
     ("vb_env_add_capt", C.c_int, [_vp, _f32p, C.c_size_t, _u32p, _f32p, _f32p, _f32p, C.c_size_t, _f32p,
                                   C.c_size_t, _f32p, C.c_float, C.c_int]),
+    ("vb_env_add_pointcloud", C.c_int, [_vp, _f32p, C.c_size_t, C.c_float, C.c_float, C.c_float, C.POINTER(C.c_double)]),
+    ("vb_env_capt_export", C.c_int, [_vp, C.c_size_t, C.POINTER(C.c_size_t), C.POINTER(C.c_size_t), _f32p, _u32p, _f32p, _f32p, _f32p,
+                                     C.POINTER(C.c_int)]),
     ("vb_env_set_attachment", C.c_int, [_vp, _f32p, _f32p, C.c_size_t]),
     ("vb_env_clear_attachment", C.c_int, [_vp]),
     ("vb_env_commit", C.c_int, [_vp]),
@@ -392,6 +395,30 @@ class Environment:
             )
         )
         self._dirty = True
+
+    def add_pointcloud(self, points, r_min: float, r_max: float, r_point: float) -> float:
+        """Environment.add_pointcloud (bindings/environment.cc:148-158): builds the CAPT from raw points ON THE DEVICE
+        (collision/capt.hh:137-398); returns the build time in nanoseconds like the reference's binding."""
+        pts = _f32(points).reshape(-1, 3)
+        ms = C.c_double()
+        _check(lib().vb_env_add_pointcloud(self._h, _ptr(pts), pts.shape[0], r_min, r_max, r_point, C.byref(ms)))
+        self._dirty = True
+        return ms.value * 1e6
+
+    def capt(self, idx: int = 0) -> dict:
+        """Query buffers of point cloud idx (as ref.Env.capt of the oracle returns them; affordances split per axis)."""
+        nt, nv, nl = C.c_size_t(), C.c_size_t(), C.c_int()
+        _check(lib().vb_env_capt_export(self._h, idx, C.byref(nt), C.byref(nv), None, None, None, None, None, C.byref(nl)))
+        leaves = 1 << nl.value
+        tests = np.zeros(nt.value, np.float32)
+        starts = np.zeros(leaves + 1, np.uint32)
+        aff = np.zeros((nv.value, 3, 8), np.float32)
+        aabbs = np.zeros((leaves, 6), np.float32)
+        top = np.zeros(6, np.float32)
+        _check(lib().vb_env_capt_export(self._h, idx, C.byref(nt), C.byref(nv), _ptr(tests), _ptr(starts, _u32p), _ptr(aff),
+                                        _ptr(aabbs), _ptr(top), C.byref(nl)))
+        return {"nlog2": nl.value, "tests": tests, "aff_starts": starts, "aff_x": aff[:, 0, :].reshape(-1).copy(),
+                "aff_y": aff[:, 1, :].reshape(-1).copy(), "aff_z": aff[:, 2, :].reshape(-1).copy(), "aabbs": aabbs, "aabb_top": top}
 
     def attach(self, a: Attachment):
         sph = _f32([[s.x, s.y, s.z, s.r] for s in a.spheres]).reshape(-1, 4)

@@ -21,6 +21,7 @@
 #include <dlfcn.h>
 #include <nccl.h>  // types only: the library is dlopen()ed by vb_comm_* so the core path does not need it
 
+#include "vb_capt_build.h"
 #include "vb_robot_ops.h"
 
 namespace
@@ -426,15 +427,7 @@ namespace
         std::vector<float> data;
         uint32_t id;
     };
-    struct HostCapt
-    {
-        std::vector<float> tests, aabbs;
-        std::vector<uint32_t> aff_starts;
-        std::vector<float> aff;  // interleaved per vector: x[8] y[8] z[8]
-        float top[6];
-        float r_point;
-        int nlog2;
-    };
+    using HostCapt = vb::CaptBuffers;
 
     float dot3(float ax, float ay, float az, float bx, float by, float bz)
     {
@@ -706,6 +699,64 @@ int vb_env_add_capt(vb_env *env, const float *tests, size_t n_tests, const uint3
     h.nlog2 = nlog2;
     env->capts.push_back(std::move(h));
     env->committed = false;
+    return VB_OK;
+}
+
+// collision::Environment::pointclouds.emplace_back(points, r_min, r_max, r_point) (bindings/environment.cc:148-158):
+// the CAPT is BUILT here, on the device (vb_capt_build.cu), from raw points.
+int vb_env_add_pointcloud(vb_env *env, const float *xyz, size_t n, float r_min, float r_max, float r_point, double *build_ms)
+{
+    if (!env || !xyz || n == 0 || !(r_max >= r_min) || !(r_min >= 0.f) || !(r_point >= 0.f))
+    {
+        return fail(VB_ERR_ARG, "vb_env_add_pointcloud: bad arguments");
+    }
+    if (!env->ctx || env->ctx->slots.empty())
+    {
+        return fail(VB_ERR_STATE, "vb_env_add_pointcloud: the tree is built on the device; the environment needs a context");
+    }
+    Slot &s = env->ctx->slots[0];
+    VB_CUDA(cudaSetDevice(s.device));
+    HostCapt h;
+    const char *what = "";
+    VB_CUDA(cudaEventRecord(s.ev0, s.stream));
+    const cudaError_t e = vb::build_capt(s.stream, xyz, n, r_min, r_max, r_point, h, &what);
+    if (e != cudaSuccess)
+    {
+        return fail(e == cudaErrorInvalidValue ? VB_ERR_ARG : VB_ERR_CUDA, "vb_env_add_pointcloud: %s%s%s", cudaGetErrorString(e),
+                    what[0] ? ": " : "", what);
+    }
+    VB_CUDA(cudaEventRecord(s.ev1, s.stream));
+    VB_CUDA(cudaEventSynchronize(s.ev1));
+    float ms = 0.f;
+    VB_CUDA(cudaEventElapsedTime(&ms, s.ev0, s.ev1));
+    if (build_ms)
+    {
+        *build_ms = ms;
+    }
+    env->ctx->launches += 2 * static_cast<uint64_t>(h.nlog2) + 8;
+    env->capts.push_back(std::move(h));
+    env->committed = false;
+    return VB_OK;
+}
+
+// the buffers of point cloud `idx` as the library holds them (layout of vb_env_add_capt; affordances interleaved per
+// 8-point vector: x[8] y[8] z[8]); sizes via the count arguments, data when the pointers are non-null
+int vb_env_capt_export(const vb_env *env, size_t idx, size_t *n_tests, size_t *n_aff_vec, float *tests, uint32_t *aff_starts,
+                       float *aff, float *aabbs, float *aabb_top, int *nlog2)
+{
+    if (!env || idx >= env->capts.size())
+    {
+        return fail(VB_ERR_ARG, "vb_env_capt_export: no such point cloud");
+    }
+    const HostCapt &c = env->capts[idx];
+    if (n_tests) *n_tests = c.tests.size();
+    if (n_aff_vec) *n_aff_vec = c.aff.size() / 24;
+    if (nlog2) *nlog2 = c.nlog2;
+    if (tests) std::copy(c.tests.begin(), c.tests.end(), tests);
+    if (aff_starts) std::copy(c.aff_starts.begin(), c.aff_starts.end(), aff_starts);
+    if (aff) std::copy(c.aff.begin(), c.aff.end(), aff);
+    if (aabbs) std::copy(c.aabbs.begin(), c.aabbs.end(), aabbs);
+    if (aabb_top) std::copy_n(c.top, 6, aabb_top);
     return VB_OK;
 }
 

@@ -2,7 +2,7 @@
 // reference's nanobind module `vamp._core_ext` for the fkcc path:
 //
 //   Sphere / Cuboid / Cylinder / HeightField / Attachment      bindings/environment.cc:18-105
-//   Environment.add_sphere / add_cuboid / add_capsule / add_heightfield / attach / detach
+//   Environment.add_sphere / add_cuboid / add_capsule / add_heightfield / add_pointcloud / attach / detach
 //                                                              bindings/environment.cc:107-163
 //   <robot>.validate(configuration, environment)               bindings/common.hh:172-189,685-697
 //   <robot>.fk(configuration)                                  bindings/common.hh:132-152,706-710
@@ -181,6 +181,18 @@ namespace
         {
             check(vb_env_add_heightfield(env_, h.off_scale.data(), h.xd, h.yd, h.data.data()));
             named(h.name);
+        }
+        // bindings/environment.cc:148-158: the CAPT is built by the library on the device; returns nanoseconds
+        double add_pointcloud(const FArray &points, float r_min, float r_max, float r_point)
+        {
+            if (points.ndim() != 2 || points.shape(1) != 3)
+            {
+                throw std::invalid_argument("add_pointcloud: float32[n, 3] expected");
+            }
+            double ms = 0.0;
+            check(vb_env_add_pointcloud(env_, points.data(), static_cast<size_t>(points.shape(0)), r_min, r_max, r_point, &ms));
+            dirty_ = true;
+            return ms * 1e6;
         }
         void attach(const Attachment &a)
         {
@@ -714,6 +726,8 @@ PYBIND11_MODULE(_core_ext, m)
         .def("add_cuboid", &Environment::add_cuboid)
         .def("add_capsule", &Environment::add_capsule)
         .def("add_heightfield", &Environment::add_heightfield)
+        .def("add_pointcloud", &Environment::add_pointcloud, "pointcloud"_a, "r_min"_a, "r_max"_a, "r_point"_a,
+             "Builds the CAPT of the cloud on the device; returns the build time in nanoseconds.")
         .def("attach", &Environment::attach)
         .def("detach", &Environment::detach);
 
