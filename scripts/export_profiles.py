@@ -29,7 +29,7 @@ for r in data:
     cnt[r[kn]] += 1
 T = sum(tot.values())
 out = ["ncu --metrics gpu__time_duration.sum --clock-control none -c 400: python bench.py --steps 2 --warmup 3 --configs 20000000",
-       "(cold-cache, serialised per-launch times; share of the whole process, torch input synthesis and the FP32-peak probe included)"]
+       "(cold-cache, serialised per-launch times; share of the whole process: side metrics, work-count pass and the FP32-peak probe included)"]
 for k, v in tot.most_common(12):
     out.append(f"{v:10.3f} ms  {100 * v / T:6.2f}%  x{cnt[k]:<3d} {k[:110]}")
 open(f"profiles/{rp}_bench_launches_summary.txt", "w").write("\n".join(out) + "\n")
@@ -44,9 +44,12 @@ def metric(k):
 
 
 rd, wr = metric("dram__bytes_read.sum"), metric("dram__bytes_write.sum")
+fma = metric("sm__inst_executed_pipe_fma.avg.pct_of_peak_sustained_active")
 n = 8_000_000
 json.dump({"kernel": "fkcc_kernel<PandaTrace,0>", "configs_in_capture": n, "dram_bytes_read": rd, "dram_bytes_write": wr,
-           "bytes_per_config": (rd + wr) / n, "algorithmic_bytes_per_config": 28.125,
+           "bytes_per_config": (rd + wr) / n, "algorithmic_bytes_per_config": 28.125, "fma_pipe_pct": fma,
+           "issue_slots_busy_pct": metric("smsp__issue_active.avg.pct_of_peak_sustained_active"),
+           "threads_per_instruction": metric("smsp__thread_inst_executed_per_inst_executed.ratio"),
            "source": "ncu --set full --clock-control none, one launch of bench.py --configs 8000000 "
                      f"(profiles/{rp}_panda_fkcc_mbm_ncu_details.txt)"},
           open(f"profiles/{rp}_panda_fkcc_mbm_traffic.json", "w"), indent=1)
