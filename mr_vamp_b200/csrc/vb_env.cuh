@@ -132,6 +132,114 @@ namespace vb
         VB_D void count(int) {}
     };
 
+    // First part of collides_simd (capt.hh:457-513): top box, [the library's "no point in range" grids], descent, leaf box.
+    // false: the query is answered "no collision"; true: the affordance vectors [v0, v1) of the leaf must be scanned
+    // (capt_scan_warp).  Verdict walks only.
+    VB_D bool capt_probe(const CaptView &c, float x, float y, float z, float r, uint32_t &v0, uint32_t &v1)
+    {
+        const float ctr[3] = {x, y, z};
+        bool inb = true;
+#pragma unroll
+        for (int k = 0; k < 3; ++k)
+        {
+            inb = inb && (ctr[k] + r >= c.top[k]) && (ctr[k] - r <= c.top[3 + k]);
+        }
+        if (!inb)
+        {
+            return false;
+        }
+        if (c.occ != nullptr && r + c.r_point <= c.occ_reach)
+        {
+            const float fx = (x - c.occ_o[0]) * c.occ_inv_h, fy = (y - c.occ_o[1]) * c.occ_inv_h, fz = (z - c.occ_o[2]) * c.occ_inv_h;
+            const bool inside = fx >= 0.f && fy >= 0.f && fz >= 0.f && fx < static_cast<float>(c.occ_n[0]) &&
+                                fy < static_cast<float>(c.occ_n[1]) && fz < static_cast<float>(c.occ_n[2]);
+            if (!inside)
+            {
+                return false;
+            }
+            const unsigned v = (static_cast<unsigned>(fz) * c.occ_n[1] + static_cast<unsigned>(fy)) * c.occ_n[0] + static_cast<unsigned>(fx);
+            if (!((__ldg(c.occ + (v >> 5)) >> (v & 31u)) & 1u))
+            {
+                return false;
+            }
+        }
+        if (c.dist != nullptr && r + c.r_point < c.dist_cap - c.dist_pad)
+        {
+            const float fx = (x - c.dist_o[0]) * c.dist_inv_h, fy = (y - c.dist_o[1]) * c.dist_inv_h, fz = (z - c.dist_o[2]) * c.dist_inv_h;
+            const bool inside = fx >= 0.f && fy >= 0.f && fz >= 0.f && fx < static_cast<float>(c.dist_n[0]) &&
+                                fy < static_cast<float>(c.dist_n[1]) && fz < static_cast<float>(c.dist_n[2]);
+            if (!inside)
+            {
+                return false;
+            }
+            const size_t v = (static_cast<size_t>(fz) * c.dist_n[1] + static_cast<size_t>(fy)) * c.dist_n[0] + static_cast<size_t>(fx);
+            if (__ldg(c.dist + v) - c.dist_pad > r + c.r_point)
+            {
+                return false;
+            }
+        }
+        uint32_t idx = 0;
+        int k = 0;
+        for (int i = 0; i < c.nlog2; ++i)
+        {
+            idx = 2u * idx + 1u + (ctr[k] >= __ldg(c.tests + idx) ? 1u : 0u);
+            k = (k == 2) ? 0 : k + 1;
+        }
+        const uint32_t leaf = idx - c.n_tests;
+        const float R = r + c.r_point;
+        const float rsq = R * R;
+        const float *bb = c.aabbs + 6ull * leaf;
+        float dsq = 0.f;
+#pragma unroll
+        for (int a = 0; a < 3; ++a)
+        {
+            const float lo = __ldg(bb + a), hi = __ldg(bb + 3 + a);
+            const float cl = fminf(fmaxf(ctr[a], lo), hi);
+            const float d = ctr[a] - cl;
+            dsq += d * d;
+        }
+        if (!(dsq <= rsq))
+        {
+            return false;
+        }
+        v0 = __ldg(c.aff_starts + leaf);
+        v1 = __ldg(c.aff_starts + leaf + 1);
+        return v1 > v0;
+    }
+
+    // Second part (capt.hh:516-538) for ONE query, by the whole warp: lane l tests the 8 points of vector v0 + l,
+    // v0 + l + 32, ... (one coalesced 96-byte read each); true iff some point of the leaf's list is in range -- the same
+    // predicate as the reference's serial scan, whose order does not matter.  All 32 lanes call with the same arguments.
+    VB_D bool capt_scan_warp(const CaptView &c, uint32_t v0, uint32_t v1, float x, float y, float z, float r)
+    {
+        const float R = r + c.r_point, rsq = R * R;
+        const uint32_t lane = threadIdx.x & 31u;
+        for (uint32_t base = v0; base < v1; base += 32u)
+        {
+            const uint32_t i = base + lane;
+            bool hit = false;
+            if (i < v1)
+            {
+                const float4 *v = c.aff + 6ull * i;
+                const float4 x0 = __ldg(v), x1 = __ldg(v + 1), y0 = __ldg(v + 2), y1 = __ldg(v + 3), z0 = __ldg(v + 4), z1 = __ldg(v + 5);
+                const float px[8] = {x0.x, x0.y, x0.z, x0.w, x1.x, x1.y, x1.z, x1.w};
+                const float py[8] = {y0.x, y0.y, y0.z, y0.w, y1.x, y1.y, y1.z, y1.w};
+                const float pz[8] = {z0.x, z0.y, z0.z, z0.w, z1.x, z1.y, z1.z, z1.w};
+#pragma unroll
+                for (int j = 0; j < 8; ++j)
+                {
+                    const float dx = px[j] - x, dy = py[j] - y, dz = pz[j] - z;
+                    hit = hit || (dx * dx + dy * dy + dz * dz <= rsq);
+                }
+            }
+            if (__any_sync(0xffffffffu, hit))
+            {
+                return true;
+            }
+        }
+        return false;
+    }
+
     // collision/capt.hh:457-541 (collides_simd with one query per lane)
     template <class M>
     VB_D bool capt_hit(const CaptView &c, float x, float y, float z, float r, M &mg)
@@ -244,7 +352,7 @@ namespace vb
 
     // the non-primitive obstacle kinds of sphere_environment_in_collision (validity.hh:132-147):
     // heightfields, then CAPT point clouds
-    template <class M>
+    template <class M, bool kCapts = true>
     VB_D bool other_hit(const EnvView &e, float sx, float sy, float sz, float sr, M &mg)
     {
         for (int i = 0; i < e.n_heightfields; ++i)
@@ -257,11 +365,14 @@ namespace vb
                 return true;
             }
         }
-        for (int i = 0; i < e.n_capts; ++i)
+        if constexpr (kCapts)
         {
-            if (capt_hit(e.capts[i], sx, sy, sz, sr, mg))
+            for (int i = 0; i < e.n_capts; ++i)
             {
-                return true;
+                if (capt_hit(e.capts[i], sx, sy, sz, sr, mg))
+                {
+                    return true;
+                }
             }
         }
         return false;
@@ -277,7 +388,8 @@ namespace vb
     // Each loop stops at the first record whose min_distance is >= the sphere's largest distance
     // from the origin, as the reference does; with an exact sqrt the cut is conservative, so the
     // verdict equals the unpruned OR over all obstacles.
-    template <class M>
+    // kCapts == false: primitives and height fields only (the warp walk queries point clouds cooperatively: env_hit_warp)
+    template <class M, bool kCapts = true>
     __device__ VB_ENVHIT_ATTR bool env_hit(const EnvView &e, const float4 *P, float sx, float sy, float sz, float sr, M &mg)
     {
         const float ext = sqrtf(sx * sx + sy * sy + sz * sz) + sr;
@@ -387,6 +499,36 @@ namespace vb
                 return true;
             }
         }
-        return other_hit(e, sx, sy, sz, sr, mg);
+        return other_hit<M, kCapts>(e, sx, sy, sz, sr, mg);
+    }
+    // sphere_environment_in_collision (collision/validity.hh:46-150) for one sphere per lane, decided by the warp together:
+    // every active lane runs the primitive / height-field part and the descent of each point cloud on its own; the leaf
+    // scans that remain are then done one query at a time by all 32 lanes (capt_scan_warp).  Same boolean per lane as
+    // env_hit.  All 32 lanes must call, converged; verdict walks only.
+    VB_D bool env_hit_warp(const EnvView &e, const float4 *P, bool active, float sx, float sy, float sz, float sr)
+    {
+        NoMargin mg;
+        bool hit = active && env_hit<NoMargin, false>(e, P, sx, sy, sz, sr, mg);
+        for (int i = 0; i < e.n_capts; ++i)
+        {
+            const CaptView c = e.capts[i];
+            uint32_t v0 = 0u, v1 = 0u;
+            const bool pending = active && !hit && capt_probe(c, sx, sy, sz, sr, v0, v1);
+            unsigned todo = __ballot_sync(0xffffffffu, pending);
+            while (todo)
+            {
+                const int src = __ffs(todo) - 1;
+                todo &= todo - 1u;
+                const float qx = __shfl_sync(0xffffffffu, sx, src), qy = __shfl_sync(0xffffffffu, sy, src),
+                            qz = __shfl_sync(0xffffffffu, sz, src), qr = __shfl_sync(0xffffffffu, sr, src);
+                const uint32_t b0 = __shfl_sync(0xffffffffu, v0, src), b1 = __shfl_sync(0xffffffffu, v1, src);
+                const bool any = capt_scan_warp(c, b0, b1, qx, qy, qz, qr);
+                if (static_cast<int>(threadIdx.x & 31u) == src)
+                {
+                    hit = any;
+                }
+            }
+        }
+        return hit;
     }
 }  // namespace vb

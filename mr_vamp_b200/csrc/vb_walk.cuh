@@ -553,11 +553,57 @@ namespace vb
         // that touch the guard sphere inflated by the group's static slack.  The fine spheres of a fired
         // guard become units of stage 2 (the pair queue is free at this point and is reused), where they
         // are tested, with the exact primitive arithmetic of the reference, against those few obstacles.
+        // ---- environment with height fields / point clouds: the fine spheres of the queued (configuration, group) items
+        // get the full query of the reference (their guards were tested exactly), one sphere per lane and step, decided by
+        // the warp together (vb_env.cuh: env_hit_warp -- leaf scans of point clouds are done by all 32 lanes)
+        VB_STAGE static void env_stage_other(const EnvView &env, const WalkCtx c, int ne)
+        {
+            const int lane = threadIdx.x & 31;
+            for (int base = 0; base < ne; base += 32)
+            {
+                const int i = base + lane;
+                int L = 0, u0 = 0, uc = 0;
+                if (i < ne)
+                {
+                    const unsigned code = envq(c)[i];
+                    L = code & 31;
+                    if (!done(c, L))
+                    {
+                        const RefGroup G = T::env(code >> 5);
+                        u0 = G.ubegin;
+                        uc = G.ucount;
+                    }
+                }
+                const int max_uc = __reduce_max_sync(kFull, uc);
+                bool hit = false;
+                for (int k = 0; k < max_uc; ++k)
+                {
+                    const bool active = k < uc && !hit;
+                    Center s{0.f, 0.f, 0.f, 0.f};
+                    if (active)
+                    {
+                        s = centre(c, L, T::ref(u0 + k));
+                    }
+                    hit = env_hit_warp(env, c.prims, active, s.x, s.y, s.z, s.r) || hit;
+                }
+                if (hit)
+                {
+                    atomicOr(cmask(c), 1u << L);
+                }
+                __syncwarp();
+            }
+        }
+
         VB_STAGE static void env_stage(const EnvView &env, const WalkCtx c, int ne)
         {
             const WalkTables w = Robot::walk_tables();
             const int lane = threadIdx.x & 31;
             const bool has_other = (env.n_heightfields | env.n_capts) != 0;
+            if (has_other)
+            {
+                env_stage_other(env, c, ne);
+                return;
+            }
             const PrimIndex ix = prim_index(env);
             const int n_obj = ix.first[5];
             VB_STAT_ONE(1, ne);
@@ -621,16 +667,7 @@ namespace vb
                                 }
                             }
                         }
-                        else
-                        {
-                            // height fields / point clouds: the full query of the reference (guards were tested exactly)
-                            NoMargin mg;
-                            for (int k = 0; k < uc && !hit; ++k)
-                            {
-                                const Center s = centre(c, L, T::ref(u0 + k));
-                                hit = env_hit(env, c.prims, s.x, s.y, s.z, s.r, mg);
-                            }
-                        }
+                        // (height fields / point clouds never get here: env_stage_other)
                         if (hit)
                         {
                             atomicOr(cmask(c), 1u << L);
@@ -827,8 +864,7 @@ namespace vb
                 {
                     const RefGroup grp = t.env[g];
                     const Center b = centre(c, lane, grp.guard);
-                    NoMargin mg;
-                    const bool hit = !collided && env_hit(env, c.prims, b.x, b.y, b.z, b.r, mg);
+                    const bool hit = env_hit_warp(env, c.prims, !collided, b.x, b.y, b.z, b.r);
                     gmask(c)[32 * g + lane] = 0xffffffffu;
 #pragma unroll
                     for (int wi = 0; wi < Robot::kEnvWords; ++wi)
