@@ -1226,6 +1226,12 @@ namespace
         }
         VB_TRY(upload(rep.capt_desc, cvs, slot.stream));
         v.n_capts = static_cast<int>(cvs.size());
+        v.capt_heavy = 0;
+        for (const auto &c : env->capts)
+        {
+            const size_t leaves = size_t(1) << c.nlog2;
+            v.capt_heavy |= (c.aff.size() / 24 > 16 * leaves) ? 1 : 0;
+        }
         v.capts = rep.capt_desc.as<vb::CaptView>();
 
         VB_TRY(upload(rep.att_local, env->att_spheres, slot.stream));

@@ -93,6 +93,7 @@ namespace vb
         int n_quads;          // total float4 count of `prims`
         int n_spheres, n_capsules, n_zcapsules, n_cuboids, n_zcuboids;
         int n_heightfields, n_capts;
+        int capt_heavy;  // some point cloud averages more than 16 affordance vectors per leaf (long leaf scans)
         const HeightFieldView *heightfields;
         const CaptView *capts;
         AttachmentView attach;

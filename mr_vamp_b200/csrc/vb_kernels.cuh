@@ -890,6 +890,7 @@ namespace vb
             x[j] = back[j] = 0.f;
         }
         bool more = count > 0u;  // warp-uniform: the range may still hold edges nobody has taken
+        const bool free_running = !kMargin && a.env.capt_heavy != 0 && !(Robot::kHasAttach && a.attach);
         const float pct = static_cast<float>((lane & 7) + 1) / static_cast<float>(kRake);
         for (;;)
         {
@@ -952,8 +953,20 @@ namespace vb
                 }
             }
             const bool alive = e != kNone;
-            // CTA-uniform exit, and the barrier that keeps the warps of the CTA on one instruction stream
-            if (!__syncthreads_or(alive || more))
+            // CTA-uniform exit, and the barrier that keeps the warps of the CTA on one instruction stream.  With a dense
+            // point cloud (long leaf scans: EnvView::capt_heavy) the step time of a warp is dominated by how many scans
+            // its lanes draw, not by instruction fetch: waiting for the slowest warp every step costs more than it saves
+            // (ncu: 15 warps stalled at the barrier per issue on the 100k-point cloud; 3.2e7 -> 3.8e7 edges/s without it,
+            // while the reference-filtered 2 220-point cloud loses 15 %), so the warps run free there -- they share nothing
+            // but the edge counter.
+            if (free_running)
+            {
+                if (!__any_sync(0xffffffffu, alive || more))
+                {
+                    break;
+                }
+            }
+            else if (!__syncthreads_or(alive || more))
             {
                 break;
             }

@@ -13,5 +13,5 @@ objs=""
 for r in sphere ur5 panda fetch baxter; do
   if [ "$r" = "$robot" ]; then objs="$objs build/var/vb_robot_${robot}_${tag}.o"; else objs="$objs build/obj/vb_robot_$r.o"; fi
 done
-nvcc -gencode arch=compute_100a,code=sm_100a -shared -o build/lib_${tag}.so build/obj/vb_capi.o $objs -ldl
+nvcc -gencode arch=compute_100a,code=sm_100a -shared -o build/lib_${tag}.so build/obj/vb_capi.o build/obj/vb_capt_build.o $objs -ldl
 grep -A2 "fkcc_random_kernel" build/var/${robot}_${tag}.ptxas.log | grep -E "registers|spill" | head -3

@@ -54,22 +54,26 @@ def test_mbm_validity_counts(ref, robot, expect):
     path = os.path.join(scenes.GOLDEN_DIR, f"mbm_{robot}.json.gz")
     mbm = scenes.load_mbm(path)
     name = REF_NAME.get(robot, robot)
-    valid = total = 0
+    valid = collision_free = total = 0
     for problems in mbm["problems"].values():
         for p in problems:
             renv = apply_ref(scenes.problem_to_spec(p), ref.Env())
             q = np.asarray([p["start"]] + p["goals"], dtype=np.float32)
             ok = ref.validate(name, renv, q)
             valid += bool(ok[0] and ok[1:].any())
+            okc = ref.fkcc(name, renv, q)
+            collision_free += bool(okc[0] and okc[1:].any())
             total += 1
     print(f"{robot}: {valid} of {total} MotionBenchMaker problems valid (reference README: {expect})")
     assert total == 700
     if expect is not None:
         assert abs(valid - expect) <= 2  # the README numbers come from upstream VAMP's Eigen-built shapes
     else:
-        # Fetch: the README's 679 is not reproduced by the fork's own fetch trace compiled here (539);
-        # recorded in DESIGN.md as an unexplained difference of the reference, not used as a pin
-        assert valid == 539
+        # Fetch: the README's 679 (resources/README.md:210) is the number of problems whose start and goal are COLLISION
+        # FREE (Robot::fkcc); the fork's validate() = joint limits && fkcc (bindings/common.hh:172-182) rejects another
+        # 140 whose continuous joints (upperarm_roll, forearm_roll, wrist_roll) lie outside the +-3.14159 limits of its
+        # Fetch trace (robots/fetch/fk.hh scale_configuration).  Both numbers are pinned.
+        assert collision_free == 679 and valid == 539
 
 
 @pytest.mark.parametrize("name", ROBOTS)
