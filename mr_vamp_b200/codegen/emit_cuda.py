@@ -67,6 +67,11 @@ LINK_REDUCTION_OFF = {"fetch"}
 # env_fetch below).  Measured on the MBM scenes: panda 3.29 -> 3.55, ur5 3.33 -> 3.39 Gcfg/s; fetch 0.75 -> 0.70 and
 # baxter 0.48 -> 0.46 (instruction-fetch bound: the second level's code costs them more than its loads save).
 TWO_LEVEL_GRID_OFF = {"fetch", "baxter"}
+# Self-collision a-side filters as QUEUED work (one (configuration, a_i) test per lane, table driven; vb_walk.cuh:
+# filter_units) instead of straight-line lane-parallel code per group.  The straight-line form runs a group's filters on
+# all 32 lanes whenever one lane's guard fired (Baxter: 174 fired (lane, group) pairs in 81 distinct groups per warp
+# step = 2 useful lanes of 32, and 718 units of generated code); the queued form does exactly the fired tests.
+QUEUED_FILTERS = set(os.environ.get("VB_QUEUED_FILTERS", "fetch,baxter").split(","))
 MIN_LINK_SPHERES = int(os.environ.get("VB_MIN_LINK_SPHERES", "2"))  # links with fewer fine spheres are left alone
 DERIVE_GUARDS = os.environ.get("VB_DERIVE_GUARDS", "1") != "0"  # bounding spheres rebuilt from the link basis too
 
@@ -397,7 +402,7 @@ def _slack(v: float) -> str:
     return "-1.0f" if v < 0 else _f32(v)
 
 
-def _tables(name: str, em: _Emitter, walk: bool = False, stride: int = 0, const_row: int = 0) -> list[str]:
+def _tables(name: str, em: _Emitter, walk: bool = False, stride: int = 0, const_row: int = 0, queued: bool = False) -> list[str]:
     """Constant-memory check tables; with `walk` also the global-memory mirrors and work-unit tables of
     the warp walk (vb_walk.cuh).  Returns (lines, table type, geometry dict)."""
     refs = list(em.refs)
@@ -442,12 +447,15 @@ def _tables(name: str, em: _Emitter, walk: bool = False, stride: int = 0, const_
                 blist.append((sl, r, wts, gram))
         return blist_at[key]
 
+    filts = []
     for gi, g in enumerate(em.selfg):
         g["unit0"] = len(units)
         for i in range(g["a"][1]):
             sa, _, ra = em.refs[g["a"][0] + i]
             sb, _, rb = g["gb"]
             filt = float(F(F(ra) + F(rb)) + F(g["slack"])) if g["slack"] >= 0 else -1.0
+            R_ = F(F(ra) + F(rb)) + F(g["slack"])
+            filts.append((sa, sb, float(F(R_ * R_)) if g["slack"] >= 0 else -1.0))  # the threshold self_filters compares with
             b_slots = [em.refs[g["b"][0] + j][0] for j in range(g["b"][1])]
             b_der = [sl & (DERIVED_SLOT - 1) for sl in b_slots if sl & DERIVED_SLOT]
             if b_der:
@@ -531,6 +539,17 @@ def _tables(name: str, em: _Emitter, walk: bool = False, stride: int = 0, const_
             out.append("    " + ", ".join(f"{{{a}, {g}, {_f32(ra)}, {_f32(fr) if fr >= 0 else '-1.0f'}, {bb}, {bc}}}"
                                           for a, g, ra, fr, bb, bc in uu[i : i + 4]) + ",")
         out.append("};")
+        # queued a-side filters (vb_walk.cuh: filter_units): slot codes + squared threshold per unit, units per group
+        ff = filts or [(0, 0, -1.0)]
+        out.append(f"__device__ const FilterRec {name}_filts[{len(ff)}] = {{")
+        for i in range(0, len(ff), 6):
+            out.append("    " + ", ".join(f"{{{a}, {g}, {_f32(t2) if t2 >= 0 else '-1.0f'}}}" for a, g, t2 in ff[i : i + 6]) + ",")
+        out.append("};")
+        gu = [g["unit0"] | (g["a"][1] << 16) for g in em.selfg] or [0]
+        out.append(f"__device__ const uint32_t {name}_gunits[{len(gu)}] = {{")
+        for i in range(0, len(gu), 12):
+            out.append("    " + ", ".join(f"{v}u" for v in gu[i : i + 12]) + ",")
+        out.append("};")
         bl = blist or [(0, 0.0, None, None)]
         out.append(f"__device__ const BRef {name}_brefs[{len(bl)}] = {{")
         for i in range(0, len(bl), 8):
@@ -554,11 +573,13 @@ def _tables(name: str, em: _Emitter, walk: bool = False, stride: int = 0, const_
         geom = {"env_q": 256, "self_q": 256, "pair_q": 256, "env_groups": max(ne, 1),
                 # records of the warp walk that may live in shared memory (vb_walk.cuh: WT): (name, count, bytes each)
                 "tab": [("Units", len(uu), 16), ("Brefs", len(bl), 8), ("Bws", len(bl), 24), ("Ders", len(dd), 24),
-                        ("Env", max(ne, 1), 24), ("Refs", len(rr), 8), ("RefGroup", len(rg), 2)]}
+                        ("Env", max(ne, 1), 24), ("Refs", len(rr), 8), ("RefGroup", len(rg), 2)]
+                       + ([("Filts", len(ff), 8), ("GUnits", len(gu), 4)] if queued else []),
+                "max_a": max([g["a"][1] for g in em.selfg] or [1])}
     return out, t, geom
 
 
-def _uniform(em: _Emitter) -> list[str]:
+def _uniform(em: _Emitter, queued: bool = False) -> list[str]:
     """Straight-line guard phase of the warp walk (vb_walk.cuh): every self-collision guard pair, the
     a-side filters of the dense self groups and every environment guard lookup, with immediate
     shared-memory offsets and radii.  No lane-dependent branch, all loads independent: this is the
@@ -673,14 +694,15 @@ def _uniform(em: _Emitter) -> list[str]:
                 R = F(F(ra) + F(rb)) + F(g["slack"])
                 blk.append(f"u{pos // 32} |= ({d2g(sa, sb)} < {_f32(float(F(R * R)))}) ? {1 << (pos % 32)}u : 0u;")
         bit = f"(fired[{gi // 32}] & {1 << (gi % 32)}u)"
-        w(f"        if (__any_sync(0xffffffffu, {bit} != 0u))  // {g['name']}")
-        w("        {")
-        w(f"            if ({bit} != 0u)")
-        w("            {")
-        for ln in blk:
-            w("                " + ln)
-        w("            }")
-        w("        }")
+        if not queued:  # (queued filters: the function is never called, keep it out of the compile)
+            w(f"        if (__any_sync(0xffffffffu, {bit} != 0u))  // {g['name']}")
+            w("        {")
+            w(f"            if ({bit} != 0u)")
+            w("            {")
+            for ln in blk:
+                w("                " + ln)
+            w("            }")
+            w("        }")
         unit += ac
     for wi in range(uw):
         w(f"        ubits[{wi}] = u{wi};")
@@ -767,8 +789,9 @@ def _uniform(em: _Emitter) -> list[str]:
 
 
 def _queue_bytes(geom: dict) -> int:
-    # item queue (self items, then environment items: never live together) + pair/fine-unit queue + candidate masks + state
-    return 2 * (max(geom["env_q"], geom["self_q"]) + geom["pair_q"]) + 128 * geom["env_groups"] + 16
+    # item queue (self items, then environment items: never live together) + pair/fine-unit queue + filter-test queue
+    # + candidate masks + state
+    return 2 * (max(geom["env_q"], geom["self_q"]) + geom["pair_q"] + geom.get("filt_q", 0)) + 128 * geom["env_groups"] + 16
 
 
 def _geometry(n_slots: int, geom: dict, dim: int = 0) -> tuple[int, int]:
@@ -821,7 +844,10 @@ def emit_robot(ir: dict[str, Any]) -> str:
     w('#include "../csrc/vb_sdf.cuh"')
     w("namespace vb")
     w("{")
-    geom = {"env_q": 256, "self_q": 256, "pair_q": 256, "env_groups": max(len(em.env), 1)}
+    queued = robot in QUEUED_FILTERS
+    max_a = max([g["a"][1] for g in em.selfg] or [1])
+    geom = {"env_q": 256, "self_q": 256, "pair_q": 256, "env_groups": max(len(em.env), 1),
+            "filt_q": (max(256, (max_a + 31) // 32 * 32) if queued else 0)}
     # shared-memory rows: one per configuration-dependent centre (a column per thread), then the constant rows
     # (one copy per warp, 32 constants per row)
     const_row = max(em.n_rows, em_att.n_rows if em_att else 0)
@@ -831,7 +857,7 @@ def emit_robot(ir: dict[str, Any]) -> str:
     # the columns.  Scored with the effects measured on B200 (Panda, MBM scene): throughput ~ warps^0.4 (8 -> 11
     # warps: +14 %), staged configurations +3 %, tables in shared memory +5 %.  Overflowing queue units run in
     # place (vb_walk.cuh): correct, but slow when it happens often, so the capacities stay >= 192.
-    _, _, tgeom0 = _tables(f"k_{robot}_tables", em, walk=True, stride=33, const_row=const_row)
+    _, _, tgeom0 = _tables(f"k_{robot}_tables", em, walk=True, stride=33, const_row=const_row, queued=queued)
     tab_bytes = 0
     for _, cnt, size in tgeom0["tab"]:
         tab_bytes = (tab_bytes + cnt * size + 15) & ~15
@@ -864,7 +890,7 @@ def emit_robot(ir: dict[str, Any]) -> str:
         e_, s_, p_ = (int(v) for v in os.environ["VB_FORCE_Q"].split(","))
         geom = dict(geom, env_q=e_, self_q=s_, pair_q=p_)
         tables_in_shared = False
-    tab, ttype, tgeom = _tables(f"k_{robot}_tables", em, walk=True, stride=32 * warps + 1, const_row=const_row)
+    tab, ttype, tgeom = _tables(f"k_{robot}_tables", em, walk=True, stride=32 * warps + 1, const_row=const_row, queued=queued)
     out.extend(tab)
     tab_off, tab_lines = 0, []
     for tname, cnt, size in tgeom["tab"]:
@@ -895,6 +921,8 @@ def emit_robot(ir: dict[str, Any]) -> str:
     w("    static constexpr int kStride = kBlock + 1;  // slot-column stride in floats (odd: conflict free)")
     w(f"    static constexpr bool kStageCfg = {'true' if stage_cfg else 'false'};  // configurations staged in shared memory by bulk copy")
     w(f"    static constexpr int kEnvQ = {geom['env_q']}, kSelfQ = {geom['self_q']}, kPairQ = {geom['pair_q']};  // work-queue capacities (units)")
+    w(f"    static constexpr bool kQueuedFilters = {'true' if queued else 'false'};  // a-side filters as queued work (vb_walk.cuh: filter_units)")
+    w(f"    static constexpr int kFiltQ = {geom['filt_q']};  // filter-test queue (>= the largest a-side of a self group: {max_a})")
     w(f"    static constexpr int kChainFlops = {st['chain_flops']};")
     w(f"    static constexpr int kEnvGroups = {st['env_groups']}, kEnvFine = {st['env_fine']};")
     w(f"    static constexpr int kSelfGroups = {st['self_groups']}, kSelfFine = {st['self_fine']};")
@@ -902,7 +930,7 @@ def emit_robot(ir: dict[str, Any]) -> str:
     w(f"    __device__ __forceinline__ static const TablesT &tables() {{ return k_{robot}_tables; }}")
     w("    __device__ __forceinline__ static WalkTables walk_tables()")
     w("    {")
-    w(f"        return WalkTables{{k_{robot}_tables_grefs, k_{robot}_tables_ref_group, k_{robot}_tables_genv, k_{robot}_tables_gself, k_{robot}_tables_units, k_{robot}_tables_brefs, k_{robot}_tables_ders, k_{robot}_tables_bws}};")
+    w(f"        return WalkTables{{k_{robot}_tables_grefs, k_{robot}_tables_ref_group, k_{robot}_tables_genv, k_{robot}_tables_gself, k_{robot}_tables_units, k_{robot}_tables_brefs, k_{robot}_tables_ders, k_{robot}_tables_bws, k_{robot}_tables_filts, k_{robot}_tables_gunits}};")
     w("    }")
     w(f"    __device__ __forceinline__ static const DerivedRec *ders() {{ return k_{robot}_tables_ders; }}")
     w(f"    __device__ __forceinline__ static const DerivedRec *ders_attach() {{ return k_{robot}_tables{'_attach' if em_att else ''}_ders; }}")
@@ -941,7 +969,7 @@ def emit_robot(ir: dict[str, Any]) -> str:
             w("        " + ln)
         w("    }")
 
-    out.extend(_uniform(em))
+    out.extend(_uniform(em, queued))
     out.extend(pt_body)
     fn("chain", em.lines)
     fn("chain_attach", em_att.lines if em_att else ["chain(p, q);"])
@@ -970,5 +998,5 @@ def generate(robots=None, out_dir: str = GEN_DIR) -> list[str]:
 
 
 if __name__ == "__main__":
-    for p in generate(sys.argv[1:] or None):
+    for p in generate(sys.argv[1:] or None, os.environ.get("VB_GEN_OUT", GEN_DIR)):
         print(p, os.path.getsize(p))

@@ -76,6 +76,14 @@ namespace vb
     };
     static_assert(sizeof(SelfUnit) == 16, "SelfUnit is read as one 16-byte load");
 
+    // Queued a-side filter of one (self group, a_i) work unit (vb_walk.cuh: filter_units; Robot::kQueuedFilters): slot
+    // codes as in SlotRef (kConstSlot / kDerivedSlot flags), thr2 = (a_r + r(gb) + slack_b)^2 or < 0: always passes.
+    struct alignas(8) FilterRec
+    {
+        uint16_t a_slot, gb_slot;
+        float thr2;
+    };
+
     // b-side sphere of a reduced link: w[0..2] = weights over the basis EDGES e_k = c_k - c_0 of the link, w[3] =
     // w^T G w with G the (rigid-motion invariant) Gram matrix of the edges, + radius.  With u = a - c_0:
     //   |a - b|^2 = |u|^2 - 2 sum_k w_k (u . e_k) + w^T G w        (3 FMAs per b sphere once u . e_k are known)
@@ -155,5 +163,7 @@ namespace vb
         const BRef *brefs;  // refs as (column offset, radius)
         const DerivedRec *ders;
         const BWeights *bws;  // refs of reduced links as (basis weights, radius)
+        const FilterRec *filts;   // per work unit (queued filters)
+        const uint32_t *gunits;   // per self group: first work unit | a_count << 16
     };
 }  // namespace vb

@@ -143,7 +143,7 @@ namespace vb
     template <class Robot>
     __host__ __device__ constexpr int queue_bytes()
     {
-        return 2 * ((Robot::kEnvQ > Robot::kSelfQ ? Robot::kEnvQ : Robot::kSelfQ) + Robot::kPairQ) +
+        return 2 * ((Robot::kEnvQ > Robot::kSelfQ ? Robot::kEnvQ : Robot::kSelfQ) + Robot::kPairQ + Robot::kFiltQ) +
                128 * (Robot::kEnvGroups > 0 ? Robot::kEnvGroups : 1) + 16;
     }
     template <class Robot>
@@ -235,6 +235,11 @@ namespace vb
                 copy(base + Robot::kTabEnv, w.env, Robot::kTabEnvBytes);
                 copy(base + Robot::kTabRefs, w.refs, Robot::kTabRefsBytes);
                 copy(base + Robot::kTabRefGroup, w.ref_group, Robot::kTabRefGroupBytes);
+                if constexpr (Robot::kQueuedFilters)
+                {
+                    copy(base + Robot::kTabFilts, w.filts, Robot::kTabFiltsBytes);
+                    copy(base + Robot::kTabGUnits, w.gunits, Robot::kTabGUnitsBytes);
+                }
             }
         }
         // tables are arrays of 2-byte-multiple records at 16-byte aligned window offsets
@@ -254,6 +259,28 @@ namespace vb
         VB_D static RefGroup env(unsigned g) { return get(Robot::walk_tables().env, Robot::kTabEnv, g); }
         VB_D static SlotRef ref(unsigned i) { return get(Robot::walk_tables().refs, Robot::kTabRefs, i); }
         VB_D static uint16_t ref_group(unsigned i) { return get(Robot::walk_tables().ref_group, Robot::kTabRefGroup, i); }
+        VB_D static FilterRec filt(unsigned i)
+        {
+            if constexpr (Robot::kQueuedFilters)
+            {
+                return get(Robot::walk_tables().filts, Robot::kTabFilts, i);
+            }
+            else
+            {
+                return FilterRec{};
+            }
+        }
+        VB_D static uint32_t gunit(unsigned g)
+        {
+            if constexpr (Robot::kQueuedFilters)
+            {
+                return get(Robot::walk_tables().gunits, Robot::kTabGUnits, g);
+            }
+            else
+            {
+                return 0u;
+            }
+        }
     };
 
     template <class Robot>
@@ -269,7 +296,8 @@ namespace vb
         // self items and environment items are never queued at the same time: one array serves both
         VB_D static uint16_t *envq(const WalkCtx &c) { return shm_u16() + c.queues / 2; }
         VB_D static uint16_t *pairq(const WalkCtx &c) { return envq(c) + kItemQ; }
-        VB_D static unsigned *gmask(const WalkCtx &c) { return shm_u32() + (c.queues + 2 * (kItemQ + Robot::kPairQ)) / 4; }
+        VB_D static uint16_t *testq(const WalkCtx &c) { return pairq(c) + Robot::kPairQ; }  // (Robot::kFiltQ entries)
+        VB_D static unsigned *gmask(const WalkCtx &c) { return shm_u32() + (c.queues + 2 * (kItemQ + Robot::kPairQ + Robot::kFiltQ)) / 4; }
         VB_D static unsigned *cmask(const WalkCtx &c) { return gmask(c) + 32 * kGroups; }
 
         VB_D static unsigned vol(const unsigned *p)
@@ -487,6 +515,145 @@ namespace vb
                 atomicOr(cmask(c), 1u << lane);
             }
             __syncwarp();
+        }
+
+        // centre of a slot code (SlotRef::slot: stored column, per-warp constant or rebuilt from the link basis), no base offset
+        VB_D static void centre_xyz(const WalkCtx &c, int L, unsigned slot, float &x, float &y, float &z)
+        {
+            if (Robot::kDerived > 0 && (slot & kDerivedSlot))
+            {
+                derived(c, L, T::der(slot & (kDerivedSlot - 1u)), x, y, z);
+            }
+            else
+            {
+                const float *col = shm_f32() + slot_index<S, Robot::kConstRow>(c.wcol, L, slot);
+                x = col[0];
+                y = col[S];
+                z = col[2 * S];
+            }
+        }
+
+        VB_D static int warp_scan(int v, int lane)
+        {
+#pragma unroll
+            for (int d = 1; d < 32; d <<= 1)
+            {
+                const int o = __shfl_up_sync(kFull, v, d);
+                v += lane >= d ? o : 0;
+            }
+            return v;
+        }
+
+        // ---- self collision, queued a-side filters (Robot::kQueuedFilters) ------------------------------------------
+        // fired[]: this lane's guard hits (leaf groups, collided lanes and tabulated-free groups already cleared).  The
+        // (lane, group) items of the warp are queued, expanded into one (configuration, a_i) filter test per lane --
+        // a_i against the other link's bounding sphere inflated by the group's static slack, the comparison of the
+        // straight-line form -- and the survivors are compacted into the pair queue.  All 32 lanes call.
+        VB_STAGE static void filter_units(const WalkCtx c, uint32_t *fired)
+        {
+            const int lane = threadIdx.x & 31;
+            const unsigned lt = (1u << lane) - 1u;
+            uint16_t *iq = envq(c), *tq = testq(c), *pq = pairq(c);
+            int np = 0;  // units waiting in the pair queue
+            for (;;)
+            {
+                int cnt = 0;
+#pragma unroll
+                for (int wi = 0; wi < Robot::kSelfWords; ++wi)
+                {
+                    cnt += __popc(fired[wi]);
+                }
+                const int total = __reduce_add_sync(kFull, cnt);
+                if (total == 0)
+                {
+                    break;
+                }
+                // more items than the queue holds (rare): every lane queues its first kSelfQ / 32 now, the rest next round
+                int take = total > Robot::kSelfQ ? min(cnt, Robot::kSelfQ / 32) : cnt;
+                const int incl = warp_scan(take, lane);
+                const int n_items = __shfl_sync(kFull, incl, 31);
+                int at_ = incl - take;
+#pragma unroll
+                for (int wi = 0; wi < Robot::kSelfWords; ++wi)
+                {
+                    uint32_t m = fired[wi];
+                    while (m != 0u && take > 0)
+                    {
+                        const int b = __ffs(m) - 1;
+                        m &= m - 1u;
+                        iq[at_++] = static_cast<uint16_t>(lane | ((wi * 32 + b) << 5));
+                        --take;
+                    }
+                    fired[wi] = m;
+                }
+                __syncwarp();
+                for (int ib = 0; ib < n_items;)
+                {
+                    // expand up to 32 items into filter tests (as many whole items as the test queue holds)
+                    const int i = ib + lane;
+                    int L = 0, u0 = 0, ac = 0;
+                    if (i < n_items)
+                    {
+                        const unsigned code = iq[i];
+                        L = code & 31;
+                        if (!done(c, L))
+                        {
+                            const uint32_t gu = T::gunit(code >> 5);
+                            u0 = gu & 0xffffu;
+                            ac = gu >> 16;
+                        }
+                    }
+                    const int tin = warp_scan(ac, lane);
+                    const int nfit = __popc(__ballot_sync(kFull, tin <= Robot::kFiltQ));  // (>= 1: kFiltQ >= every a_count)
+                    const int n_tests = __shfl_sync(kFull, tin, nfit - 1);
+                    if (lane < nfit)
+                    {
+                        uint16_t *dst = tq + (tin - ac);
+                        for (int k = 0; k < ac; ++k)
+                        {
+                            dst[k] = static_cast<uint16_t>(L | ((u0 + k) << 5));
+                        }
+                    }
+                    __syncwarp();
+                    ib += nfit;
+                    for (int tb = 0; tb < n_tests; tb += 32)
+                    {
+                        const int t = tb + lane;
+                        bool pass = false;
+                        unsigned code = 0u;
+                        if (t < n_tests)
+                        {
+                            code = tq[t];
+                            const int Lt = code & 31;
+                            const FilterRec f = T::filt(code >> 5);
+                            pass = f.thr2 < 0.f;
+                            if (!pass)
+                            {
+                                float ax, ay, az, gx, gy, gz;
+                                centre_xyz(c, Lt, f.a_slot, ax, ay, az);
+                                centre_xyz(c, Lt, f.gb_slot, gx, gy, gz);
+                                const float dx = ax - gx, dy = ay - gy, dz = az - gz;
+                                pass = dx * dx + dy * dy + dz * dz < f.thr2;
+                            }
+                        }
+                        const unsigned m = __ballot_sync(kFull, pass);
+                        if (np + 32 > Robot::kPairQ)
+                        {
+                            __syncwarp();
+                            pair_stage(c, np);
+                            np = 0;
+                        }
+                        if (pass)
+                        {
+                            pq[np + __popc(m & lt)] = static_cast<uint16_t>(code);
+                        }
+                        np += __popc(m);
+                    }
+                    __syncwarp();
+                }
+            }
+            __syncwarp();
+            pair_stage(c, np);
         }
 
         // one fine sphere refs[idx] of configuration L against the tight candidates of its group
@@ -814,10 +981,19 @@ namespace vb
                 {
                     fired[wi] = collided ? 0u : (fired[wi] & ~Robot::self_leaf_mask(wi));
                 }
-                Robot::self_filters(col, fired, ubits);
-                VB_TICK(5);
-                group_release(c);  // end of the straight-line part of the step
-                run_units(c, ubits);
+                if constexpr (Robot::kQueuedFilters)
+                {
+                    group_release(c);
+                    VB_TICK(5);
+                    filter_units(c, fired);
+                }
+                else
+                {
+                    Robot::self_filters(col, fired, ubits);
+                    VB_TICK(5);
+                    group_release(c);  // end of the straight-line part of the step
+                    run_units(c, ubits);
+                }
                 VB_TICK(6);
                 collided = collided || done(c, lane);
             }

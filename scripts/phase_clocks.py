@@ -1,5 +1,5 @@
 """Dev tool: per-phase cycle shares of the Panda warp walk (library built with -DVB_PHASE_CLOCKS, see vb_walk.cuh).
-usage: VAMP_B200_LIB=build/libvamp_clk.so python scripts/phase_clocks.py [mbm|empty|clutter]"""
+usage: VAMP_B200_LIB=build/lib_clk.so python scripts/phase_clocks.py [mbm|empty|clutter] [robot]"""
 import ctypes as C
 import os
 import sys
@@ -12,15 +12,17 @@ names = {0: "config + pair lookup", 1: "chain", 2: "const groups + env_fetch iss
          11: "config synthesis", 12: "check_warp total"}
 ctx = api.default_context()
 L = api.lib()
-robot = api.Robot("panda")
+rname = sys.argv[2] if len(sys.argv) > 2 else "panda"
+robot = api.Robot(rname)
 which = sys.argv[1] if len(sys.argv) > 1 else "mbm"
 if which == "mbm":
-    mbm = scenes.load_mbm(os.path.join(scenes.GOLDEN_DIR, "mbm_panda.json.gz"))
-    spec = scenes.problem_to_spec(mbm["problems"]["table_pick"][0])
+    mbm = scenes.load_mbm(os.path.join(scenes.GOLDEN_DIR, f"mbm_{rname}.json.gz"))
+    probs = mbm["problems"]
+    spec = scenes.problem_to_spec(probs["table_pick" if "table_pick" in probs else sorted(probs)[0]][0])
 else:
     spec = {"empty": [], "clutter": scenes.random_scene(7)}[which]
 env = scenes.apply(spec, api.Environment())
-n = 1 << 24
+n = 1 << 22
 bits = C.c_void_p()
 api._check(L.vb_dev_alloc(ctx.handle, 0, n // 8, C.byref(bits)))
 out = (C.c_ulonglong * 16)()

@@ -9,11 +9,13 @@ from mr_vamp_b200 import api, scenes
 
 ctx = api.default_context()
 L = api.lib()
-robot = api.Robot("panda")
+rname = os.environ.get("VB_ROBOT", "panda")
+robot = api.Robot(rname)
 for which in (sys.argv[1:] or ["mbm"]):
     if which == "mbm":
-        mbm = scenes.load_mbm(os.path.join(scenes.GOLDEN_DIR, "mbm_panda.json.gz"))
-        spec = scenes.problem_to_spec(mbm["problems"]["table_pick"][0])
+        mbm = scenes.load_mbm(os.path.join(scenes.GOLDEN_DIR, f"mbm_{rname}.json.gz"))
+        probs = mbm["problems"]
+        spec = scenes.problem_to_spec(probs["table_pick" if "table_pick" in probs else sorted(probs)[0]][0])
     else:
         spec = {"empty": [], "clutter": scenes.random_scene(7), "cage": scenes.cage()}[which]
     env = scenes.apply(spec, api.Environment())
