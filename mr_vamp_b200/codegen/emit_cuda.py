@@ -858,9 +858,18 @@ def emit_robot(ir: dict[str, Any]) -> str:
     # warps: +14 %), staged configurations +3 %, tables in shared memory +5 %.  Overflowing queue units run in
     # place (vb_walk.cuh): correct, but slow when it happens often, so the capacities stay >= 192.
     _, _, tgeom0 = _tables(f"k_{robot}_tables", em, walk=True, stride=33, const_row=const_row, queued=queued)
-    tab_bytes = 0
-    for _, cnt, size in tgeom0["tab"]:
-        tab_bytes = (tab_bytes + cnt * size + 15) & ~15
+    # tables in the order in which they earn their place in shared memory (the unit stages' dependent reads first)
+    TAB_PRIORITY = ["Units", "Filts", "GUnits", "Brefs", "Bws", "Ders", "Refs", "RefGroup", "Env"]
+    tab_sizes = {tname: (cnt * size + 15) & ~15 for tname, cnt, size in tgeom0["tab"]}
+    tab_bytes = sum(tab_sizes.values())
+
+    def tables_that_fit(spare: int) -> list[str]:
+        got = []
+        for tname in TAB_PRIORITY:
+            if tname in tab_sizes and tab_sizes[tname] <= spare:
+                got.append(tname)
+                spare -= tab_sizes[tname]
+        return got
 
     def window_bytes(g, w_, stage):
         st = 32 * w_ + 1
@@ -868,35 +877,42 @@ def emit_robot(ir: dict[str, Any]) -> str:
         return (b + 15) & ~15
 
     best = None
+    force_warps = int(os.environ.get("VB_FORCE_WARPS", "0"))  # development: A/B of warps against tables in shared memory
     for cap in (256, 192):  # (128 was measured on Fetch: queue overflow, 0.73 -> 0.46 Gcfg/s)
         g = dict(geom, pair_q=cap, env_q=cap, self_q=cap)
         for stage in (False, True):
             w_, c_ = _geometry(n_slots, g, dim if stage else 0)
-            for drop in (0, 1):  # one warp less can buy both extras
+            for drop in ((w_ - force_warps,) if force_warps else (0, 1)):  # one warp less can buy both extras
                 ww = w_ - drop
                 if ww < 1:
                     continue
                 avail = 228 * 1024 // c_ - 1024
                 if window_bytes(g, ww, stage) > avail:
                     continue
-                tabs = window_bytes(g, ww, stage) + tab_bytes <= avail
-                score = (ww * c_) ** 0.4 * (1.03 if stage else 1.0) * (1.05 if tabs else 1.0)
+                got = tables_that_fit(avail - window_bytes(g, ww, stage))
+                share = sum(tab_sizes[t_] for t_ in got) / max(tab_bytes, 1)
+                score = (ww * c_) ** 0.4 * (1.03 if stage else 1.0) * (1.0 + 0.05 * share)
                 if best is None or score > best[0] + 1e-9:
-                    best = (score, g, ww, c_, stage, tabs)
-    _, geom, warps, ctas, stage_cfg, tables_in_shared = best
+                    best = (score, g, ww, c_, stage, got)
+    _, geom, warps, ctas, stage_cfg, shared_tabs = best
     if os.environ.get("VB_FORCE_STAGE") == "1":  # development: staged configurations whatever the plan says
-        stage_cfg, tables_in_shared = True, False
+        stage_cfg, shared_tabs = True, []
     if os.environ.get("VB_FORCE_Q"):  # development: "env,self,pair" capacities, to exercise the overflow paths
         e_, s_, p_ = (int(v) for v in os.environ["VB_FORCE_Q"].split(","))
         geom = dict(geom, env_q=e_, self_q=s_, pair_q=p_)
-        tables_in_shared = False
+        shared_tabs = []
     tab, ttype, tgeom = _tables(f"k_{robot}_tables", em, walk=True, stride=32 * warps + 1, const_row=const_row, queued=queued)
     out.extend(tab)
     tab_off, tab_lines = 0, []
     for tname, cnt, size in tgeom["tab"]:
-        tab_lines.append(f"    static constexpr unsigned kTab{tname} = {tab_off}, kTab{tname}Bytes = {cnt * size};")
-        tab_off = (tab_off + cnt * size + 15) & ~15
-    assert tab_off == tab_bytes
+        if tname in shared_tabs:
+            tab_lines.append(f"    static constexpr unsigned kTab{tname} = {tab_off}, kTab{tname}Bytes = {cnt * size};")
+            tab_off = (tab_off + cnt * size + 15) & ~15
+        else:
+            tab_lines.append(f"    static constexpr unsigned kTab{tname} = 0xffffffffu, kTab{tname}Bytes = {cnt * size};  // read through L1")
+    if not queued:
+        tab_lines.append("    static constexpr unsigned kTabFilts = 0xffffffffu, kTabFiltsBytes = 0, kTabGUnits = 0xffffffffu, kTabGUnitsBytes = 0;")
+    tables_in_shared = tab_off > 0
     if em_att:
         tab2, ttype2, _ = _tables(f"k_{robot}_tables_attach", em_att, stride=32 * warps + 1, const_row=const_row)
         out.extend(tab2)
@@ -912,7 +928,7 @@ def emit_robot(ir: dict[str, Any]) -> str:
     w(f"    static constexpr int kSlots = {n_slots};  // shared-memory slot rows: {const_row} per-thread + {n_slots - const_row} of per-warp constants")
     w(f"    static constexpr int kConstRow = {const_row};  // first constant row ({n_const} configuration-independent centres)")
     w(f"    static constexpr int kBlock = {32 * warps};  // threads per CTA: {warps} warps x {ctas} CTA(s) per SM fill the shared memory")
-    w(f"    static constexpr bool kTablesInShared = {'true' if tables_in_shared else 'false'};  // check tables of the warp walk in shared memory ({tab_off} bytes)")
+    w(f"    static constexpr bool kTablesInShared = {'true' if tables_in_shared else 'false'};  // check tables of the warp walk in shared memory ({tab_off} of {tab_bytes} bytes: {', '.join(shared_tabs) or 'none'})")
     w(f"    static constexpr unsigned kTabBytes = {tab_off};")
     for ln in tab_lines:
         w(ln)

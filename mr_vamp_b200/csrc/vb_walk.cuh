@@ -171,16 +171,18 @@ namespace vb
     // the slot columns (Robot::stage_tables() copies them in at kernel start) and they are read with LDS at fixed
     // window offsets; otherwise through the non-coherent global path.  The unit stages are chains of dependent table
     // reads, and the L1 left beside ~220 KB of shared memory is small.
+    constexpr unsigned kNoTab = 0xffffffffu;  // Robot::kTab<Name> of a table that is not in shared memory
+
     template <class Robot>
     struct WT
     {
-        template <class T>
-        VB_D static T get(const T *global, unsigned window_bytes, unsigned i)
+        template <unsigned kOff, class T>
+        VB_D static T get(const T *global, unsigned i)
         {
-            if constexpr (Robot::kTablesInShared)
+            if constexpr (kOff != kNoTab)
             {
                 extern __shared__ float4 vb_shared_window[];
-                const T *base = reinterpret_cast<const T *>(reinterpret_cast<const unsigned char *>(vb_shared_window) + tab_base<Robot>() + window_bytes);
+                const T *base = reinterpret_cast<const T *>(reinterpret_cast<const unsigned char *>(vb_shared_window) + tab_base<Robot>() + kOff);
                 T out;
                 if constexpr (sizeof(T) % 16 == 0 && alignof(T) >= 16)
                 {
@@ -220,26 +222,31 @@ namespace vb
                 }
             }
         }
-        // all threads of the CTA: copy the tables behind the staged configurations (caller synchronises)
+        // all threads of the CTA: copy the tables the code generator placed behind the staged configurations (caller
+        // synchronises)
+        template <unsigned kOff>
+        VB_D static void stage_one(const void *src, unsigned bytes)
+        {
+            if constexpr (kOff != kNoTab)
+            {
+                extern __shared__ float4 vb_shared_window[];
+                copy(reinterpret_cast<unsigned char *>(vb_shared_window) + tab_base<Robot>() + kOff, src, bytes);
+            }
+        }
         VB_D static void stage()
         {
             if constexpr (Robot::kTablesInShared)
             {
-                extern __shared__ float4 vb_shared_window[];
-                unsigned char *base = reinterpret_cast<unsigned char *>(vb_shared_window) + tab_base<Robot>();
                 const WalkTables w = Robot::walk_tables();
-                copy(base + Robot::kTabUnits, w.units, Robot::kTabUnitsBytes);
-                copy(base + Robot::kTabBrefs, w.brefs, Robot::kTabBrefsBytes);
-                copy(base + Robot::kTabBws, w.bws, Robot::kTabBwsBytes);
-                copy(base + Robot::kTabDers, w.ders, Robot::kTabDersBytes);
-                copy(base + Robot::kTabEnv, w.env, Robot::kTabEnvBytes);
-                copy(base + Robot::kTabRefs, w.refs, Robot::kTabRefsBytes);
-                copy(base + Robot::kTabRefGroup, w.ref_group, Robot::kTabRefGroupBytes);
-                if constexpr (Robot::kQueuedFilters)
-                {
-                    copy(base + Robot::kTabFilts, w.filts, Robot::kTabFiltsBytes);
-                    copy(base + Robot::kTabGUnits, w.gunits, Robot::kTabGUnitsBytes);
-                }
+                stage_one<Robot::kTabUnits>(w.units, Robot::kTabUnitsBytes);
+                stage_one<Robot::kTabBrefs>(w.brefs, Robot::kTabBrefsBytes);
+                stage_one<Robot::kTabBws>(w.bws, Robot::kTabBwsBytes);
+                stage_one<Robot::kTabDers>(w.ders, Robot::kTabDersBytes);
+                stage_one<Robot::kTabEnv>(w.env, Robot::kTabEnvBytes);
+                stage_one<Robot::kTabRefs>(w.refs, Robot::kTabRefsBytes);
+                stage_one<Robot::kTabRefGroup>(w.ref_group, Robot::kTabRefGroupBytes);
+                stage_one<Robot::kTabFilts>(w.filts, Robot::kTabFiltsBytes);
+                stage_one<Robot::kTabGUnits>(w.gunits, Robot::kTabGUnitsBytes);
             }
         }
         // tables are arrays of 2-byte-multiple records at 16-byte aligned window offsets
@@ -252,35 +259,15 @@ namespace vb
                 d16[i] = __ldg(s16 + i);
             }
         }
-        VB_D static SelfUnit unit(unsigned i) { return get(Robot::walk_tables().units, Robot::kTabUnits, i); }
-        VB_D static BRef bref(unsigned i) { return get(Robot::walk_tables().brefs, Robot::kTabBrefs, i); }
-        VB_D static BWeights bw(unsigned i) { return get(Robot::walk_tables().bws, Robot::kTabBws, i); }
-        VB_D static DerivedRec der(unsigned i) { return get(Robot::walk_tables().ders, Robot::kTabDers, i); }
-        VB_D static RefGroup env(unsigned g) { return get(Robot::walk_tables().env, Robot::kTabEnv, g); }
-        VB_D static SlotRef ref(unsigned i) { return get(Robot::walk_tables().refs, Robot::kTabRefs, i); }
-        VB_D static uint16_t ref_group(unsigned i) { return get(Robot::walk_tables().ref_group, Robot::kTabRefGroup, i); }
-        VB_D static FilterRec filt(unsigned i)
-        {
-            if constexpr (Robot::kQueuedFilters)
-            {
-                return get(Robot::walk_tables().filts, Robot::kTabFilts, i);
-            }
-            else
-            {
-                return FilterRec{};
-            }
-        }
-        VB_D static uint32_t gunit(unsigned g)
-        {
-            if constexpr (Robot::kQueuedFilters)
-            {
-                return get(Robot::walk_tables().gunits, Robot::kTabGUnits, g);
-            }
-            else
-            {
-                return 0u;
-            }
-        }
+        VB_D static SelfUnit unit(unsigned i) { return get<Robot::kTabUnits>(Robot::walk_tables().units, i); }
+        VB_D static BRef bref(unsigned i) { return get<Robot::kTabBrefs>(Robot::walk_tables().brefs, i); }
+        VB_D static BWeights bw(unsigned i) { return get<Robot::kTabBws>(Robot::walk_tables().bws, i); }
+        VB_D static DerivedRec der(unsigned i) { return get<Robot::kTabDers>(Robot::walk_tables().ders, i); }
+        VB_D static RefGroup env(unsigned g) { return get<Robot::kTabEnv>(Robot::walk_tables().env, g); }
+        VB_D static SlotRef ref(unsigned i) { return get<Robot::kTabRefs>(Robot::walk_tables().refs, i); }
+        VB_D static uint16_t ref_group(unsigned i) { return get<Robot::kTabRefGroup>(Robot::walk_tables().ref_group, i); }
+        VB_D static FilterRec filt(unsigned i) { return get<Robot::kTabFilts>(Robot::walk_tables().filts, i); }
+        VB_D static uint32_t gunit(unsigned g) { return get<Robot::kTabGUnits>(Robot::walk_tables().gunits, g); }
     };
 
     template <class Robot>
@@ -386,16 +373,26 @@ namespace vb
                 {
                     q[k] = -2.f * (ux * (px[k + 1] - px[0]) + uy * (py[k + 1] - py[0]) + uz * (pz[k + 1] - pz[0]));
                 }
+                // (bitwise accumulation, four b spheres per trip with their loads issued together: `hit = hit || ...` compiles
+                // to one dependent branch per sphere, i.e. a full load-to-compare latency chain each)
                 bool near = false;
-#pragma unroll 4
-                for (int j = 0; j < bc; ++j)
+                for (int j = 0; j < bc; j += 4)
                 {
-                    const BWeights bw = T::bw(u.b_begin + j);
-                    const float d2 = s0 + bw.w[0] * q[0] + bw.w[1] * q[1] + bw.w[2] * q[2] + bw.w[3];
-                    const float rs = u.a_r + bw.r;
-                    const float v = d2 - rs * rs;
-                    near = near || fabsf(v) < kGramBand;
-                    hit = hit || v < -kGramBand;
+                    BWeights bw[4];
+#pragma unroll
+                    for (int k = 0; k < 4; ++k)
+                    {
+                        bw[k] = T::bw(u.b_begin + min(j + k, bc - 1));  // (past the end: the last sphere again)
+                    }
+#pragma unroll
+                    for (int k = 0; k < 4; ++k)
+                    {
+                        const float d2 = s0 + bw[k].w[0] * q[0] + bw[k].w[1] * q[1] + bw[k].w[2] * q[2] + bw[k].w[3];
+                        const float rs = u.a_r + bw[k].r;
+                        const float v = d2 - rs * rs;
+                        near |= fabsf(v) < kGramBand;
+                        hit |= v < -kGramBand;
+                    }
                 }
                 if (near && !hit)
                 {
@@ -414,14 +411,26 @@ namespace vb
                 }
                 return hit;
             }
-#pragma unroll 4
-            for (int j = 0; j < bc; ++j)
+            for (int j = 0; j < bc; j += 4)
             {
-                const BRef br = T::bref(u.b_begin + j);
-                float bx, by, bz;
-                at(c, L, br.off, bx, by, bz);
-                const float dx = ax - bx, dy = ay - by, dz = az - bz, rs = u.a_r + br.r;
-                hit = hit || (dx * dx + dy * dy + dz * dz - rs * rs < 0.f);
+                BRef br[4];
+#pragma unroll
+                for (int k = 0; k < 4; ++k)
+                {
+                    br[k] = T::bref(u.b_begin + min(j + k, bc - 1));  // (past the end: the last sphere again)
+                }
+                float bx[4], by[4], bz[4];
+#pragma unroll
+                for (int k = 0; k < 4; ++k)
+                {
+                    at(c, L, br[k].off, bx[k], by[k], bz[k]);
+                }
+#pragma unroll
+                for (int k = 0; k < 4; ++k)
+                {
+                    const float dx = ax - bx[k], dy = ay - by[k], dz = az - bz[k], rs = u.a_r + br[k].r;
+                    hit |= dx * dx + dy * dy + dz * dz - rs * rs < 0.f;
+                }
             }
             return hit;
         }
@@ -554,6 +563,13 @@ namespace vb
             const int lane = threadIdx.x & 31;
             const unsigned lt = (1u << lane) - 1u;
             uint16_t *iq = envq(c), *tq = testq(c), *pq = pairq(c);
+            // tests per lane and trip (measured, MBM scenes: Fetch 1 / 2 / 4 -> 1.00 / 1.12 / 1.14 Gcfg/s; Baxter, whose rebuilt
+            // centres make the body branchy and which is at the register ceiling, 0.92 / 0.90 / 0.87)
+#ifdef VB_FILT_ILP
+            constexpr int kIlp = VB_FILT_ILP;
+#else
+            constexpr int kIlp = Robot::kDerived > 0 ? 1 : 4;
+#endif
             int np = 0;  // units waiting in the pair queue
             for (;;)
             {
@@ -616,38 +632,49 @@ namespace vb
                     }
                     __syncwarp();
                     ib += nfit;
-                    for (int tb = 0; tb < n_tests; tb += 32)
+                    // kIlp tests per lane and trip, their loads issued together (few resident warps: the dependent chain
+                    // queue -> record -> centres -> compare is what a pass costs)
+                    for (int tb = 0; tb < n_tests; tb += 32 * kIlp)
                     {
-                        const int t = tb + lane;
-                        bool pass = false;
-                        unsigned code = 0u;
-                        if (t < n_tests)
+                        unsigned code[kIlp];
+                        FilterRec f[kIlp];
+                        bool pass[kIlp];
+#pragma unroll
+                        for (int k = 0; k < kIlp; ++k)
                         {
-                            code = tq[t];
-                            const int Lt = code & 31;
-                            const FilterRec f = T::filt(code >> 5);
-                            pass = f.thr2 < 0.f;
-                            if (!pass)
-                            {
-                                float ax, ay, az, gx, gy, gz;
-                                centre_xyz(c, Lt, f.a_slot, ax, ay, az);
-                                centre_xyz(c, Lt, f.gb_slot, gx, gy, gz);
-                                const float dx = ax - gx, dy = ay - gy, dz = az - gz;
-                                pass = dx * dx + dy * dy + dz * dz < f.thr2;
-                            }
+                            code[k] = tq[min(tb + 32 * k + lane, n_tests - 1)];
                         }
-                        const unsigned m = __ballot_sync(kFull, pass);
-                        if (np + 32 > Robot::kPairQ)
+#pragma unroll
+                        for (int k = 0; k < kIlp; ++k)
+                        {
+                            f[k] = T::filt(code[k] >> 5);
+                        }
+#pragma unroll
+                        for (int k = 0; k < kIlp; ++k)
+                        {
+                            const int Lt = code[k] & 31;
+                            float ax, ay, az, gx, gy, gz;
+                            centre_xyz(c, Lt, f[k].a_slot, ax, ay, az);
+                            centre_xyz(c, Lt, f[k].gb_slot, gx, gy, gz);
+                            const float dx = ax - gx, dy = ay - gy, dz = az - gz;
+                            pass[k] = (tb + 32 * k + lane < n_tests) & ((f[k].thr2 < 0.f) | (dx * dx + dy * dy + dz * dz < f[k].thr2));
+                        }
+                        if (np + 32 * kIlp > Robot::kPairQ)
                         {
                             __syncwarp();
                             pair_stage(c, np);
                             np = 0;
                         }
-                        if (pass)
+#pragma unroll
+                        for (int k = 0; k < kIlp; ++k)
                         {
-                            pq[np + __popc(m & lt)] = static_cast<uint16_t>(code);
+                            const unsigned m = __ballot_sync(kFull, pass[k]);
+                            if (pass[k])
+                            {
+                                pq[np + __popc(m & lt)] = static_cast<uint16_t>(code[k]);
+                            }
+                            np += __popc(m);
                         }
-                        np += __popc(m);
                     }
                     __syncwarp();
                 }
