@@ -751,7 +751,7 @@ def _uniform(em: _Emitter, queued: bool = False) -> list[str]:
         w("            }")
         w("            else")
         w("            {")
-        w(f"                cells[{gi}] = grid_fetch(grid, {xyz[0]}, {xyz[1]}, {xyz[2]}, in); i{gi // 32} |= in ? {bit} : 0u;")
+        w(f"                cells[{gi}] = grid_fetch_inside(grid, {xyz[0]}, {xyz[1]}, {xyz[2]}, (ci{gi // 32} & {bit}) != 0u); i{gi // 32} |= ci{gi // 32} & {bit};")
         w("            }")
     w("        }")
     w("        else")
@@ -878,7 +878,7 @@ def emit_robot(ir: dict[str, Any]) -> str:
 
     best = None
     force_warps = int(os.environ.get("VB_FORCE_WARPS", "0"))  # development: A/B of warps against tables in shared memory
-    for cap in (256, 192):  # (128 was measured on Fetch: queue overflow, 0.73 -> 0.46 Gcfg/s)
+    for cap in (256, 224, 192):  # (128 was measured on Fetch: queue overflow, 0.73 -> 0.46 Gcfg/s)
         g = dict(geom, pair_q=cap, env_q=cap, self_q=cap)
         for stage in (False, True):
             w_, c_ = _geometry(n_slots, g, dim if stage else 0)

@@ -1000,7 +1000,41 @@ namespace
     constexpr size_t kSdfMaxVoxels = size_t(4) << 20;
     constexpr float kSdfMinVoxel = 0.015f;
 
-    constexpr float kSdfCoarseVoxel = 0.15f;  // coarse level of the two-level guard lookup (vb_sdf.cuh); swept 0.05 .. 0.3 m on B200
+    // coarse level of the two-level guard lookup (vb_sdf.cuh): 2^kCoarseShift = 8 fine voxels (0.12 m at the finest
+    // pitch; voxel edges of 0.05 .. 0.3 m were swept on B200, flat optimum around 0.15), on the fine lattice
+    constexpr float kSdfCoarseMaxVoxel = 0.3f;
+    constexpr int kSdfDimMultiple = 2 << vb::kCoarseShift;  // fine dimensions: even coarse dimensions (centred lookup)
+
+    void sdf_finish(vb::SdfView &g, float h)
+    {
+        g.inv_h = 1.f / h;
+        g.fnx = std::nextafterf(static_cast<float>(g.nx), 0.f);
+        g.fny = std::nextafterf(static_cast<float>(g.ny), 0.f);
+        g.fnz = std::nextafterf(static_cast<float>(g.nz), 0.f);
+        g.pad = 0.5f * std::sqrt(3.f) * h * 1.001f + vb::kSdfMargin;
+        g.hx = 0.5f * static_cast<float>(g.nx);
+        g.hy = 0.5f * static_cast<float>(g.ny);
+        g.hz = 0.5f * static_cast<float>(g.nz);
+        g.cx = -g.ox * g.inv_h - g.hx;
+        g.cy = -g.oy * g.inv_h - g.hy;
+        g.cz = -g.oz * g.inv_h - g.hz;
+    }
+    void sdf_attach(vb::SdfView &g, const uint2 *cells)
+    {
+        g.cell = cells;
+        g.centre = cells + (static_cast<size_t>(g.nz / 2) * g.ny + g.ny / 2) * g.nx + g.nx / 2;
+    }
+    // the coarse level of `g`: same lower corner, voxels of 2^kCoarseShift fine voxels
+    vb::SdfView sdf_coarse_of(const vb::SdfView &g)
+    {
+        vb::SdfView c = g;
+        c.cell = c.centre = nullptr;
+        c.nx = g.nx >> vb::kCoarseShift;
+        c.ny = g.ny >> vb::kCoarseShift;
+        c.nz = g.nz >> vb::kCoarseShift;
+        sdf_finish(c, static_cast<float>(1 << vb::kCoarseShift) / g.inv_h);
+        return c;
+    }
 
     bool sdf_geometry(const vb_env *env, vb::SdfView &g, float min_voxel_arg = kSdfMinVoxel)
     {
@@ -1068,9 +1102,10 @@ namespace
         float h = std::max(min_voxel, std::cbrt(ext[0] * ext[1] * ext[2] / static_cast<float>(kSdfMaxVoxels)));
         for (;;)
         {
-            g.nx = static_cast<int>(std::ceil(ext[0] / h));
-            g.ny = static_cast<int>(std::ceil(ext[1] / h));
-            g.nz = static_cast<int>(std::ceil(ext[2] / h));
+            auto dim = [&](float e) { return (static_cast<int>(std::ceil(e / h)) + kSdfDimMultiple - 1) / kSdfDimMultiple * kSdfDimMultiple; };
+            g.nx = dim(ext[0]);
+            g.ny = dim(ext[1]);
+            g.nz = dim(ext[2]);
             if (static_cast<size_t>(g.nx) * g.ny * g.nz <= kSdfMaxVoxels)
             {
                 break;
@@ -1080,11 +1115,7 @@ namespace
         g.ox = lo[0];
         g.oy = lo[1];
         g.oz = lo[2];
-        g.inv_h = 1.f / h;
-        g.fnx = std::nextafterf(static_cast<float>(g.nx), 0.f);
-        g.fny = std::nextafterf(static_cast<float>(g.ny), 0.f);
-        g.fnz = std::nextafterf(static_cast<float>(g.nz), 0.f);
-        g.pad = 0.5f * std::sqrt(3.f) * h * 1.001f + vb::kSdfMargin;
+        sdf_finish(g, h);
         g.cover = clipped ? 0.f : vb::kSdfCover;
         g.mask_reach = vb::kMaskReach;
         if (const char *v = std::getenv("VB_SDF_REACH"))  // development: candidate-mask reach in metres
@@ -1243,22 +1274,19 @@ namespace
         {
             const size_t voxels = static_cast<size_t>(v.sdf.nx) * v.sdf.ny * v.sdf.nz;
             VB_CUDA(rep.sdf.reserve(voxels * sizeof(uint2)));
-            v.sdf.cell = rep.sdf.as<uint2>();
+            sdf_attach(v.sdf, rep.sdf.as<uint2>());
             sdf_build_kernel<<<slot.sm_count * 8, 256, 0, slot.stream>>>(v, v.sdf, rep.sdf.as<uint2>());
             VB_CUDA(cudaGetLastError());
-            // coarse level: the same box at 8 cm voxels, when the fine grid is much finer than that
+            // coarse level on the same lattice, unless the fine voxels are already coarse (very large scenes)
             v.sdf_c = vb::SdfView{};
-            float coarse_voxel = kSdfCoarseVoxel;
-            if (const char *cv = std::getenv("VB_SDF_COARSE"))  // development: voxel edge of the coarse level in metres
+            const bool want_coarse = !std::getenv("VB_SDF_NO_COARSE") &&
+                                     static_cast<float>(1 << vb::kCoarseShift) / v.sdf.inv_h <= kSdfCoarseMaxVoxel;
+            if (want_coarse)
             {
-                coarse_voxel = std::max(0.02f, static_cast<float>(std::atof(cv)));
-            }
-            const bool want_coarse = !std::getenv("VB_SDF_NO_COARSE") && 1.f / v.sdf.inv_h < 0.5f * coarse_voxel;
-            if (want_coarse && sdf_geometry(env, v.sdf_c, coarse_voxel))
-            {
+                v.sdf_c = sdf_coarse_of(v.sdf);
                 const size_t cv = static_cast<size_t>(v.sdf_c.nx) * v.sdf_c.ny * v.sdf_c.nz;
                 VB_CUDA(rep.sdf_c.reserve(cv * sizeof(uint2)));
-                v.sdf_c.cell = rep.sdf_c.as<uint2>();
+                sdf_attach(v.sdf_c, rep.sdf_c.as<uint2>());
                 sdf_build_kernel<<<slot.sm_count * 8, 256, 0, slot.stream>>>(v, v.sdf_c, rep.sdf_c.as<uint2>());
                 VB_CUDA(cudaGetLastError());
             }

@@ -84,7 +84,16 @@ namespace vb
         float pad;             // half voxel diagonal + safety margin
         float cover;           // outside the grid every obstacle is at least this far away (0: unknown)
         float mask_reach;      // candidate masks hold every obstacle within mask_reach + pad of the voxel centre
+        // Lookup in CENTRED voxel coordinates g = x * inv_h + c (one FMA; c = -o * inv_h - n / 2; n is even): inside the
+        // grid iff |g| < n / 2 on every axis (one compare with |.|; NaN is outside), voxel = floor(g) relative to the
+        // grid's centre voxel `centre` = cell + ((nz/2) * ny + ny/2) * nx + nx/2.
+        float cx, cy, cz;
+        float hx, hy, hz;
+        const uint2 *centre;
     };
+    // the coarse level of the two-level lookup has voxels of 2^kCoarseShift fine voxels on the same lattice (the fine
+    // dimensions are multiples of 2 << kCoarseShift): its voxel index is the fine one shifted
+    constexpr int kCoarseShift = 3;
 
     // Passed by value to every kernel (lives in the parameter constant bank).
     struct EnvView

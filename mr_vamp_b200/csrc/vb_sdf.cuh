@@ -24,16 +24,34 @@ namespace vb
     constexpr float kSdfMargin = 1e-4f;  // safety margin on both classification thresholds
     constexpr float kMaskReach = 0.2f;   // candidate masks cover spheres within this distance of the voxel
 
-    // Branch free (the load address is clamped into the grid), so that a straight-line sequence of
-    // fetches keeps all its loads in flight at once.  `in` = the point lies inside the grid.
+    // Voxel of (x, y, z) relative to the grid's centre voxel (vb_env.cuh: SdfView); `in` = the point lies inside the grid.
+    // 3 FMA + 3 compares + 3 conversions: the guard phase does one such lookup per link and configuration.
+    VB_D void grid_coords(const SdfView &g, float x, float y, float z, int &ix, int &iy, int &iz, bool &in)
+    {
+        const float gx = fmaf(x, g.inv_h, g.cx), gy = fmaf(y, g.inv_h, g.cy), gz = fmaf(z, g.inv_h, g.cz);
+        in = fabsf(gx) < g.hx && fabsf(gy) < g.hy && fabsf(gz) < g.hz;
+        ix = __float2int_rd(gx);
+        iy = __float2int_rd(gy);
+        iz = __float2int_rd(gz);
+    }
+    // One level: the cell of (x, y, z), loaded only when the point is inside (a straight-line sequence of fetches keeps
+    // all its loads in flight at once).
     VB_D uint2 grid_fetch(const SdfView &g, float x, float y, float z, bool &in)
     {
-        const float fx = (x - g.ox) * g.inv_h, fy = (y - g.oy) * g.inv_h, fz = (z - g.oz) * g.inv_h;
-        // clamped in the float domain (inside the grid the clamp is the identity; NaN clamps to 0 and is "outside")
-        const float cx = fminf(fmaxf(fx, 0.f), g.fnx), cy = fminf(fmaxf(fy, 0.f), g.fny), cz = fminf(fmaxf(fz, 0.f), g.fnz);
-        in = cx == fx && cy == fy && cz == fz;
-        const int ix = static_cast<int>(cx), iy = static_cast<int>(cy), iz = static_cast<int>(cz);
-        return __ldg(g.cell + (iz * g.ny + iy) * g.nx + ix);
+        int ix, iy, iz;
+        grid_coords(g, x, y, z, ix, iy, iz, in);
+        return in ? __ldg(g.centre + (iz * g.ny + iy) * g.nx + ix) : make_uint2(0u, 0u);
+    }
+    // Two levels over the same box: the coarse cell is fetched with grid_fetch(coarse, ...); a guard it cannot call free
+    // then fetches its fine cell.  `in` comes from the coarse lookup (same box; the voxel is clamped, because the two
+    // roundings may disagree on a point within an ulp of the box's faces).
+    VB_D uint2 grid_fetch_inside(const SdfView &g, float x, float y, float z, bool in)
+    {
+        const float gx = fmaf(x, g.inv_h, g.cx), gy = fmaf(y, g.inv_h, g.cy), gz = fmaf(z, g.inv_h, g.cz);
+        const int hx = g.nx >> 1, hy = g.ny >> 1, hz = g.nz >> 1;
+        const int ix = min(max(__float2int_rd(gx), -hx), hx - 1), iy = min(max(__float2int_rd(gy), -hy), hy - 1),
+                  iz = min(max(__float2int_rd(gz), -hz), hz - 1);
+        return in ? __ldg(g.centre + (iz * g.ny + iy) * g.nx + ix) : make_uint2(0u, 0u);
     }
 
     // coarse level of the two-level lookup: true iff the coarse cell alone proves that no primitive touches a sphere

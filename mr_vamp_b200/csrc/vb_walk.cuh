@@ -138,7 +138,8 @@ namespace vb
     }
 
     // ---- layout of the dynamic shared-memory window (bytes) -------------------------------------------------
-    //   [3 * kSlots rows of kStride floats: one column per thread][per-warp work queues][staged configurations +
+    //   [3 * kSlots rows of kStride floats: one column per thread][per-warp work queues: items u16, units u16, filter tests
+    //   u16, candidate masks u32 x 32 x groups, state u32 x 4][staged configurations +
     //   mbarrier][check tables]
     template <class Robot>
     __host__ __device__ constexpr int queue_bytes()
@@ -286,6 +287,10 @@ namespace vb
         VB_D static uint16_t *testq(const WalkCtx &c) { return pairq(c) + Robot::kPairQ; }  // (Robot::kFiltQ entries)
         VB_D static unsigned *gmask(const WalkCtx &c) { return shm_u32() + (c.queues + 2 * (kItemQ + Robot::kPairQ + Robot::kFiltQ)) / 4; }
         VB_D static unsigned *cmask(const WalkCtx &c) { return gmask(c) + 32 * kGroups; }
+        // rake blocks (WalkCtx::octet): bit L of gfire[g] = the exact guard test of group g fired for configuration L.  The
+        // words live in the last kFireQ entries of the item queue, which holds that many items less for rake blocks.
+        static constexpr int kFireQ = 2 * ((static_cast<int>(kGroups) + 1) & ~1);
+        VB_D static unsigned *gfire(const WalkCtx &c) { return shm_u32() + (c.queues + 2 * (kItemQ - kFireQ)) / 4; }
 
         VB_D static unsigned vol(const unsigned *p)
         {
@@ -801,6 +806,102 @@ namespace vb
             const PrimIndex ix = prim_index(env);
             const int n_obj = ix.first[5];
             VB_STAT_ONE(1, ne);
+            if (c.octet)
+            {
+                // Edges: the 8 lanes of an octet are one rake block of the reference, whose guard opens the fine tests of ALL
+                // its lanes when it fires in ANY of them (planning/validate.hh:36-60).  Two sweeps over the queued items: the
+                // exact guard tests (bit L of gfire[g], candidates narrowed into gmask), then the fine units of every item
+                // whose block fired.  The items of one group are queued together, so both sweeps see all of them.
+                if (lane < static_cast<int>(kGroups))
+                {
+                    gfire(c)[lane] = 0u;
+                }
+                __syncwarp();
+                for (int base = 0; base < ne; base += 32)
+                {
+                    const int i = base + lane;
+                    if (i < ne)
+                    {
+                        const unsigned code = envq(c)[i];
+                        const int L = code & 31, g = code >> 5;
+                        if (!done(c, L))
+                        {
+                            const RefGroup G = T::env(g);
+                            const uint32_t mask = gmask(c)[32 * g + L];
+                            const Center b = centre(c, L, G.guard);
+                            uint32_t low = mask & 0x7fffffffu, tight = 0u;
+                            if (n_obj < 31)
+                            {
+                                low &= (1u << n_obj) - 1u;
+                            }
+                            const bool high = (mask >> 31) != 0u;
+                            bool ghit = false;
+                            int cursor = 0;
+                            for (int o = next_candidate(low, high, n_obj, cursor); o >= 0; o = next_candidate(low, high, n_obj, cursor))
+                            {
+                                const ObjDist d = object_dist(c.prims, ix, o, b.x, b.y, b.z);
+                                ghit |= object_hit(d, b.r);
+                                if (G.slack < 0.f || object_hit(d, b.r + G.slack))
+                                {
+                                    tight |= 1u << (o < 31 ? o : 31);
+                                }
+                            }
+                            gmask(c)[32 * g + L] = tight;
+                            if (ghit)
+                            {
+                                atomicOr(gfire(c) + g, 1u << L);
+                            }
+                        }
+                    }
+                }
+                __syncwarp();
+                for (int base = 0; base < ne; base += 32)
+                {
+                    const int i = base + lane;
+                    if (i < ne)
+                    {
+                        const unsigned code = envq(c)[i];
+                        const int L = code & 31, g = code >> 5;
+                        const unsigned fired = vol(gfire(c) + g);
+                        if (!done(c, L) && ((fired >> (L & ~7)) & 0xffu) != 0u)
+                        {
+                            const RefGroup G = T::env(g);
+                            bool hit = false;
+                            if (G.count == 0)
+                            {
+                                hit = (fired >> L) & 1u;  // leaf group: the guard is the test
+                            }
+                            else if (gmask(c)[32 * g + L] != 0u)
+                            {
+                                const int u0 = G.ubegin, uc = G.ucount;
+                                const unsigned at = atomicAdd(cmask(c) + 1, static_cast<unsigned>(uc));
+                                for (int k = 0; k < uc; ++k)
+                                {
+                                    if (at + k < static_cast<unsigned>(Robot::kPairQ))
+                                    {
+                                        pairq(c)[at + k] = static_cast<uint16_t>(L | ((u0 + k) << 5));
+                                    }
+                                    else
+                                    {
+                                        hit = hit || fine_unit(c, w, ix, L, u0 + k);  // queue full: run the unit here
+                                    }
+                                }
+                            }
+                            if (hit)
+                            {
+                                atomicOr(cmask(c), 1u << L);
+                            }
+                        }
+                    }
+                    __syncwarp();
+                    if (vol(cmask(c) + 1) >= static_cast<unsigned>(Robot::kPairQ) / 2)
+                    {
+                        fine_stage(env, c);
+                    }
+                }
+                fine_stage(env, c);
+                return;
+            }
             for (int base = 0; base < ne; base += 32)
             {
                 const int i = base + lane;
@@ -1093,88 +1194,6 @@ namespace vb
                     }
                 }
             }
-            if (c.octet && grid)
-            {
-                // Edges: the exact guard test runs lane-parallel per group, so that its outcome can be OR-ed over the 8
-                // lanes of a rake block before the fine tests are opened (rake coupling, as above).  Lanes the grid calls
-                // free cannot collide whatever their siblings do (the grid's margin exceeds the overhang).
-                const PrimIndex ix = prim_index(env);
-                const int n_obj = ix.first[5];
-#pragma unroll
-                for (int wi = 0; wi < Robot::kEnvWords; ++wi)
-                {
-                    const uint32_t mine = collided ? 0u : (maybe[wi] & ~Robot::env_const_mask(wi));
-                    uint32_t any = __reduce_or_sync(kFull, mine);
-                    while (any)
-                    {
-                        const int b = __ffs(any) - 1;
-                        any &= any - 1u;
-                        const int g = wi * 32 + b;
-                        const bool on = (mine >> b) & 1u;
-                        const RefGroup G = T::env(g);
-                        bool ghit = false;
-                        uint32_t tight = 0u;
-                        if (on)
-                        {
-                            const uint32_t mask = gmask(c)[32 * g + lane];
-                            const Center s = centre(c, lane, G.guard);
-                            uint32_t low = mask & 0x7fffffffu;
-                            if (n_obj < 31)
-                            {
-                                low &= (1u << n_obj) - 1u;
-                            }
-                            const bool high = (mask >> 31) != 0u;
-                            int cursor = 0;
-                            for (int o = next_candidate(low, high, n_obj, cursor); o >= 0; o = next_candidate(low, high, n_obj, cursor))
-                            {
-                                const ObjDist d = object_dist(c.prims, ix, o, s.x, s.y, s.z);
-                                ghit = ghit || object_hit(d, s.r);
-                                if (G.slack < 0.f || object_hit(d, s.r + G.slack))
-                                {
-                                    tight |= 1u << (o < 31 ? o : 31);
-                                }
-                            }
-                        }
-                        const unsigned fired_lanes = __ballot_sync(kFull, ghit);
-                        const bool open = ((fired_lanes >> (lane & ~7)) & 0xffu) != 0u;
-                        if (G.count == 0)
-                        {
-                            if (ghit)
-                            {
-                                atomicOr(cmask(c), 1u << lane);  // leaf group: the guard is the test
-                            }
-                        }
-                        else if (on && open && tight != 0u)
-                        {
-                            gmask(c)[32 * g + lane] = tight;
-                            const unsigned at = atomicAdd(cmask(c) + 1, static_cast<unsigned>(G.ucount));
-                            bool hit = false;
-                            for (int k = 0; k < G.ucount; ++k)
-                            {
-                                if (at + k < static_cast<unsigned>(Robot::kPairQ))
-                                {
-                                    pairq(c)[at + k] = static_cast<uint16_t>(lane | ((G.ubegin + k) << 5));
-                                }
-                                else
-                                {
-                                    hit = hit || fine_unit(c, Robot::walk_tables(), ix, lane, G.ubegin + k);
-                                }
-                            }
-                            if (hit)
-                            {
-                                atomicOr(cmask(c), 1u << lane);
-                            }
-                        }
-                        __syncwarp();
-                        if (vol(cmask(c) + 1) >= static_cast<unsigned>(Robot::kPairQ) / 2)
-                        {
-                            fine_stage(env, c);
-                        }
-                    }
-                }
-                fine_stage(env, c);
-                return !(collided || done(c, lane));
-            }
             int ne = 0;
 #pragma unroll
             for (int wi = 0; wi < Robot::kEnvWords; ++wi)
@@ -1188,7 +1207,7 @@ namespace vb
                     any &= any - 1u;
                     const bool on = (mine >> b) & 1u;
                     const unsigned m = __ballot_sync(kFull, on);
-                    if (ne + 32 > Robot::kEnvQ)
+                    if (ne + 32 > Robot::kEnvQ - (c.octet ? kFireQ : 0))
                     {
                         __syncwarp();
                         env_stage(env, c, ne);
