@@ -58,6 +58,12 @@ CONST_SLOT = 0x4000  # slot code of a configuration-independent centre: CONST_SL
 
 
 DERIVED_SLOT = 0x2000  # slot code of a centre that is NOT stored: DERIVED_SLOT | index into the derived table
+# slot code of a "translated constant": a centre whose x and y are constants and whose z is a constant plus the z of ONE
+# stored centre (Fetch: the 38 spheres of the torso and the head ride on the prismatic torso_lift joint).  (x, y, dz) is
+# kept once per warp in the rows behind the constants; z = dz + z(reference slot) is added where the centre is read.
+# 37 fewer per-thread rows = 7 resident warps instead of 5.
+LIFT_SLOT = 0x1000
+LIFT_ON = os.environ.get("VB_LIFT_SLOTS", "1") != "0"
 # Rigid-link reduction (plan_links) is a per-robot build decision, taken from measurements on B200 (MotionBenchMaker
 # table_pick scene 1, 33.5 M uniform configurations, Gcfg/s without -> with): panda 2.44 -> 2.92, ur5 3.02 -> 3.32,
 # fetch 0.73 -> 0.46 (its reduced links are on both sides of most of its 465 pair units; rebuilding them costs more
@@ -76,9 +82,13 @@ MIN_LINK_SPHERES = int(os.environ.get("VB_MIN_LINK_SPHERES", "2"))  # links with
 DERIVE_GUARDS = os.environ.get("VB_DERIVE_GUARDS", "1") != "0"  # bounding spheres rebuilt from the link basis too
 
 
-def slot_offset(slot: int, stride: int, const_row: int) -> int:
+def slot_offset(slot: int, stride: int, const_row: int, lift_row: int = 0) -> int:
     """Float offset of a slot's x coordinate from the warp's first column (y, z follow at +stride each).
-    Regular slots add the lane; constant slots (offset >= 3 * const_row * stride) do not."""
+    Regular slots add the lane; constant slots (offset >= 3 * const_row * stride) do not; translated constants
+    (offset >= 3 * lift_row * stride) add the reference slot's z."""
+    if slot & LIFT_SLOT:
+        j = slot & (LIFT_SLOT - 1)
+        return 3 * (lift_row + j // 32) * stride + j % 32
     if slot & CONST_SLOT:
         j = slot & (CONST_SLOT - 1)
         return 3 * (const_row + j // 32) * stride + j % 32
@@ -88,8 +98,9 @@ def slot_offset(slot: int, stride: int, const_row: int) -> int:
 class _Emitter:
     """Lowers one traced function to (chain lines, check tables)."""
 
-    def __init__(self, fn: dict[str, Any], samples=None, reduce_links: bool = True):
+    def __init__(self, fn: dict[str, Any], samples=None, reduce_links: bool = True, use_lift: bool = False):
         self.reduce_links = reduce_links
+        self.use_lift = use_lift
         self.values = fn["values"]
         self.program = fn["program"]
         self.samples = samples  # (vals, n) from ir_eval, for the static containment slack
@@ -110,6 +121,9 @@ class _Emitter:
         self.link_weights: dict[tuple, tuple[list, list[float]]] = {}  # stored non-basis spheres of reduced links
         self.slot_weights: dict[int, list[float]] = {}  # their slot -> weights over the link's basis
         self.link_gram: dict[tuple, list[list[float]]] = {}  # basis keys -> Gram matrix of the basis edges
+        # translated constants (LIFT_SLOT): slot code -> (x, y, dz) literals; lift_ref = (stored slot, z value id)
+        self.lift_xyz: dict[int, list[str]] = {}
+        self.lift_ref: tuple[int, int] | None = None
 
     # -- operands -----------------------------------------------------------------------------
     def opnd(self, o) -> str:
@@ -138,6 +152,19 @@ class _Emitter:
             self.slots[key] = DERIVED_SLOT | len(self.derived)
             self.derived.append({"basis": [self.ref(b)[0] for b in basis], "w": list(wts),
                                  "gram": self.link_gram[tuple(self.key(b) for b in basis)]})
+        if key not in self.slots and self.lift_candidate(s):
+            zv = s[2]["v"]
+            if self.lift_ref is not None:
+                import numpy as np
+
+                vals, _ = self.samples
+                d = vals[zv].astype(np.float64) - vals[self.lift_ref[1]].astype(np.float64)
+                dz = float(d.mean())
+                if float(np.abs(d - dz).max()) < 5e-7:  # (float32 rounding of the two traced sums: ~1.2e-7 m on Fetch)
+                    j = len(self.lift_xyz)
+                    self.slots[key] = LIFT_SLOT | j
+                    self.lift_xyz[self.slots[key]] = [self.coord(s[0]), self.coord(s[1]), _f32(dz)]
+                    self.lines.append(f"p.put_c<kStride>(kLiftRow + {j // 32}, {j % 32}, {self.coord(s[0])}, {self.coord(s[1])}, {_f32(dz)});")
         if key not in self.slots:
             xyz = [self.coord(a) for a in s[:3]]
             if all(a["v"] is None for a in s[:3]):
@@ -150,6 +177,8 @@ class _Emitter:
             else:
                 self.slots[key] = self.n_rows
                 self.n_rows += 1
+                if self.lift_ref is None and self.lift_candidate(s):
+                    self.lift_ref = (self.slots[key], s[2]["v"])  # the stored centre the translated constants ride on
                 if key in self.link_weights:
                     self.slot_weights[self.slots[key]] = list(self.link_weights[key][1])
                 self.lines.append(f"p.put_s<kStride>({self.slots[key]}, {xyz[0]}, {xyz[1]}, {xyz[2]});")
@@ -160,6 +189,11 @@ class _Emitter:
         radius = -1.0 if r.get("sym") == "radius" else float(r["c"])
         assert r.get("sym") == "radius" or r["v"] is None
         return (self.slots[key], mask, radius)
+
+    def lift_candidate(self, s) -> bool:
+        """x and y literal, z traced, no base offset, not part of a reduced link: may become a translated constant"""
+        return (self.use_lift and self.samples is not None and s[0]["v"] is None and s[1]["v"] is None and s[2]["v"] is not None
+                and not any(a.get("base") for a in s[:3]) and self.key(s) not in self.plan and self.key(s) not in self.link_weights)
 
     @staticmethod
     def key(s) -> tuple:
@@ -402,7 +436,8 @@ def _slack(v: float) -> str:
     return "-1.0f" if v < 0 else _f32(v)
 
 
-def _tables(name: str, em: _Emitter, walk: bool = False, stride: int = 0, const_row: int = 0, queued: bool = False) -> list[str]:
+def _tables(name: str, em: _Emitter, walk: bool = False, stride: int = 0, const_row: int = 0, queued: bool = False,
+            lift_row: int = 0) -> list[str]:
     """Constant-memory check tables; with `walk` also the global-memory mirrors and work-unit tables of
     the warp walk (vb_walk.cuh).  Returns (lines, table type, geometry dict)."""
     refs = list(em.refs)
@@ -465,8 +500,8 @@ def _tables(name: str, em: _Emitter, walk: bool = False, stride: int = 0, const_
                 assert all((sl & DERIVED_SLOT) or sl in em.derived[b_der[0]]["basis"] or sl in em.slot_weights for sl in b_slots), g["name"]
             assert g["b"][1] < 64 and len(em.derived) < 511, g["name"]
             pack = g["b"][1] | (((b_der[0] + 1) if b_der else 0) << 6) | ((1 << 15) if sa & DERIVED_SLOT else 0)
-            units.append(((sa & (DERIVED_SLOT - 1)) if sa & DERIVED_SLOT else slot_offset(sa, stride, const_row),
-                          0 if sb & DERIVED_SLOT else slot_offset(sb, stride, const_row), ra, filt, b_list(g), pack))
+            units.append(((sa & (DERIVED_SLOT - 1)) if sa & DERIVED_SLOT else slot_offset(sa, stride, const_row, lift_row),
+                          0 if sb & DERIVED_SLOT else slot_offset(sb, stride, const_row, lift_row), ra, filt, b_list(g), pack))
     assert len(refs) < 2048 and len(units) < 2048, (name, len(refs), len(units))
     ne, ns, na, nr = len(em.env), len(em.selfg), len(em.att), len(refs)
     t = f"Tables<{max(ne, 1)}, {max(ns, 1)}, {max(na, 1)}, {max(nr, 1)}>"
@@ -493,14 +528,14 @@ def _tables(name: str, em: _Emitter, walk: bool = False, stride: int = 0, const_
     # centres the chain does not store (plan_links): pre-multiplied basis offsets + weights
     dd = em.derived or [{"basis": [0, 0, 0, 0], "w": [0.0, 0.0, 0.0, 0.0]}]
     assert all(not (b & DERIVED_SLOT) for d in dd for b in d["basis"])
-    assert all(slot_offset(b, stride or 1, const_row) < 65536 for d in dd for b in d["basis"]), name
+    assert all(slot_offset(b, stride or 1, const_row, lift_row) < 65536 for d in dd for b in d["basis"]), name
     out = [f"__device__ const DerivedRec {name}_ders[{len(dd)}] = {{"]
     for d in dd:
-        offs = ", ".join(str(slot_offset(b, stride, const_row)) for b in d["basis"])
+        offs = ", ".join(str(slot_offset(b, stride, const_row, lift_row)) for b in d["basis"])
         out.append(f"    {{{{{offs}}}, {{{', '.join(_f32(v) for v in d['w'])}}}}},")
     out.append("};")
     out.append(f"__constant__ {t} {name} = {{")
-    out.append(f"    {em.n_rows}, {ne}, {ns}, {na}, {em.att_env},")
+    out.append(f"    {em.n_rows}, {ne}, {ns}, {na}, {em.att_env}, {3 * em.lift_ref[0] + 2 if em.lift_xyz else -1},")
     out.append("    {")
     out.extend("    " + r for r in env_rows())
     out.append("    },")
@@ -553,7 +588,7 @@ def _tables(name: str, em: _Emitter, walk: bool = False, stride: int = 0, const_
         bl = blist or [(0, 0.0, None, None)]
         out.append(f"__device__ const BRef {name}_brefs[{len(bl)}] = {{")
         for i in range(0, len(bl), 8):
-            out.append("    " + ", ".join(f"{{{0 if sl & DERIVED_SLOT else slot_offset(sl, stride, const_row)}, {_f32(r) if r >= 0 else '-1.0f'}}}" for sl, r, _, _ in bl[i : i + 8]) + ",")
+            out.append("    " + ", ".join(f"{{{0 if sl & DERIVED_SLOT else slot_offset(sl, stride, const_row, lift_row)}, {_f32(r) if r >= 0 else '-1.0f'}}}" for sl, r, _, _ in bl[i : i + 8]) + ",")
         out.append("};")
         # b-side spheres of reduced links as weights over the link's basis (stored basis spheres: one-hot)
         def edge_form(wts, gram):
@@ -632,6 +667,10 @@ def _uniform(em: _Emitter, queued: bool = False) -> list[str]:
                 if slot & CONST_SLOT:
                     x, y, z = em.const_xyz[slot]
                     body.append(f"const float s{slot}x = {x}, s{slot}y = {y}, s{slot}z = {z};")
+                    return
+                if slot & LIFT_SLOT:
+                    x, y, dz = em.lift_xyz[slot]
+                    body.append(f"const float s{slot}x = {x}, s{slot}y = {y}, s{slot}z = {dz} + col[{3 * em.lift_ref[0] + 2} * kStride];")
                     return
                 body.append(
                     f"const float s{slot}x = col[{3 * slot} * kStride], s{slot}y = col[{3 * slot + 1} * kStride], s{slot}z = col[{3 * slot + 2} * kStride];"
@@ -724,14 +763,14 @@ def _uniform(em: _Emitter, queued: bool = False) -> list[str]:
     guards = []
     for gi, g in enumerate(em.env):
         slot, mask, r = g["guard"]
-        if slot & DERIVED_SLOT:
+        if slot & (DERIVED_SLOT | LIFT_SLOT):
             fetch_need(slot)
             for ln in fetch_body:
                 w("        " + ln)
             fetch_body.clear()
         xyz = []
         for c in range(3):
-            e = (f"s{slot}{'xyz'[c]}" if slot & DERIVED_SLOT else em.const_xyz[slot][c] if slot & CONST_SLOT
+            e = (f"s{slot}{'xyz'[c]}" if slot & (DERIVED_SLOT | LIFT_SLOT) else em.const_xyz[slot][c] if slot & CONST_SLOT
                  else f"col[{3 * slot + c} * kStride]")
             if mask & (1 << c):
                 e += f" + b{'xyz'[c]}"
@@ -826,8 +865,8 @@ def emit_robot(ir: dict[str, Any]) -> str:
         return ir_eval.evaluate(fn, q), n
 
     reduce_links = robot not in LINK_REDUCTION_OFF or os.environ.get("VB_REDUCE_ALL") == "1"
-    em = _Emitter(fns["interleaved_sphere_fk"], sampled(fns["interleaved_sphere_fk"]), reduce_links).run_checks()
-    em_att = (_Emitter(fns["interleaved_sphere_fk_attachment"], sampled(fns["interleaved_sphere_fk_attachment"]), reduce_links).run_checks()
+    em = _Emitter(fns["interleaved_sphere_fk"], sampled(fns["interleaved_sphere_fk"]), reduce_links, LIFT_ON).run_checks()
+    em_att = (_Emitter(fns["interleaved_sphere_fk_attachment"], sampled(fns["interleaved_sphere_fk_attachment"]), reduce_links, LIFT_ON).run_checks()
               if has_attach else None)
     # self groups decided by a two-joint table are rare work for the walk, whatever their guard's fire rate
     ptabs = pair_tables.build(ir, fns["interleaved_sphere_fk"])
@@ -852,12 +891,14 @@ def emit_robot(ir: dict[str, Any]) -> str:
     # (one copy per warp, 32 constants per row)
     const_row = max(em.n_rows, em_att.n_rows if em_att else 0)
     n_const = max(len(em.const_slots), len(em_att.const_slots) if em_att else 0)
-    n_slots = const_row + (n_const + 31) // 32
+    lift_row = const_row + (n_const + 31) // 32  # translated constants (LIFT_SLOT) behind the constants
+    n_lift = max(len(em.lift_xyz), len(em_att.lift_xyz) if em_att else 0)
+    n_slots = lift_row + (n_lift + 31) // 32
     # Window plan: resident warps, queue capacities, and which of {staged configurations, check tables} go behind
     # the columns.  Scored with the effects measured on B200 (Panda, MBM scene): throughput ~ warps^0.4 (8 -> 11
     # warps: +14 %), staged configurations +3 %, tables in shared memory +5 %.  Overflowing queue units run in
     # place (vb_walk.cuh): correct, but slow when it happens often, so the capacities stay >= 192.
-    _, _, tgeom0 = _tables(f"k_{robot}_tables", em, walk=True, stride=33, const_row=const_row, queued=queued)
+    _, _, tgeom0 = _tables(f"k_{robot}_tables", em, walk=True, stride=33, const_row=const_row, queued=queued, lift_row=lift_row)
     # tables in the order in which they earn their place in shared memory (the unit stages' dependent reads first)
     TAB_PRIORITY = ["Units", "Filts", "GUnits", "Brefs", "Bws", "Ders", "Refs", "RefGroup", "Env"]
     tab_sizes = {tname: (cnt * size + 15) & ~15 for tname, cnt, size in tgeom0["tab"]}
@@ -901,7 +942,7 @@ def emit_robot(ir: dict[str, Any]) -> str:
         e_, s_, p_ = (int(v) for v in os.environ["VB_FORCE_Q"].split(","))
         geom = dict(geom, env_q=e_, self_q=s_, pair_q=p_)
         shared_tabs = []
-    tab, ttype, tgeom = _tables(f"k_{robot}_tables", em, walk=True, stride=32 * warps + 1, const_row=const_row, queued=queued)
+    tab, ttype, tgeom = _tables(f"k_{robot}_tables", em, walk=True, stride=32 * warps + 1, const_row=const_row, queued=queued, lift_row=lift_row)
     out.extend(tab)
     tab_off, tab_lines = 0, []
     for tname, cnt, size in tgeom["tab"]:
@@ -914,7 +955,7 @@ def emit_robot(ir: dict[str, Any]) -> str:
         tab_lines.append("    static constexpr unsigned kTabFilts = 0xffffffffu, kTabFiltsBytes = 0, kTabGUnits = 0xffffffffu, kTabGUnitsBytes = 0;")
     tables_in_shared = tab_off > 0
     if em_att:
-        tab2, ttype2, _ = _tables(f"k_{robot}_tables_attach", em_att, stride=32 * warps + 1, const_row=const_row)
+        tab2, ttype2, _ = _tables(f"k_{robot}_tables_attach", em_att, stride=32 * warps + 1, const_row=const_row, lift_row=lift_row)
         out.extend(tab2)
     pt_head, pt_body = pair_tables.emit(robot, ir, ptabs, max((len(em.selfg) + 31) // 32, 1))
     out.extend(pt_head)
@@ -927,6 +968,9 @@ def emit_robot(ir: dict[str, Any]) -> str:
     w(f"    static constexpr bool kHasAttach = {'true' if has_attach else 'false'};")
     w(f"    static constexpr int kSlots = {n_slots};  // shared-memory slot rows: {const_row} per-thread + {n_slots - const_row} of per-warp constants")
     w(f"    static constexpr int kConstRow = {const_row};  // first constant row ({n_const} configuration-independent centres)")
+    w(f"    static constexpr int kLiftRow = {lift_row};  // first row of the translated constants ({n_lift} centres: x, y constant, z = dz + z of one stored centre)")
+    w(f"    static constexpr int kLiftCount = {n_lift};")
+    w(f"    static constexpr int kLiftZRow = {3 * em.lift_ref[0] + 2 if em.lift_xyz else 0};  // row of that centre's z (non-attachment trace)")
     w(f"    static constexpr int kBlock = {32 * warps};  // threads per CTA: {warps} warps x {ctas} CTA(s) per SM fill the shared memory")
     w(f"    static constexpr bool kTablesInShared = {'true' if tables_in_shared else 'false'};  // check tables of the warp walk in shared memory ({tab_off} of {tab_bytes} bytes: {', '.join(shared_tabs) or 'none'})")
     w(f"    static constexpr unsigned kTabBytes = {tab_off};")

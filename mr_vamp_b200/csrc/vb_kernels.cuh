@@ -122,13 +122,14 @@ namespace vb
     }
 
     // ---- the table walk: every collision test of one configuration -------------------------------
-    template <int kStride, int kConstRow>
+    template <int kStride, int kConstRow, int kLiftRow = 0>
     struct TableCtx
     {
         const EnvView &env;
         Scratch sc;
         float bx, by, bz, radius;
         const DerivedRec *ders;  // centres rebuilt from their link's basis (vb_tables.cuh)
+        int lift_z_row;          // Tables::lift_z_row of the trace being walked
         VB_D Center load(const SlotRef &ref) const
         {
             Center c;
@@ -149,10 +150,14 @@ namespace vb
             }
             else
             {
-                const float *col = shm_f32() + slot_index<kStride, kConstRow>(sc.col & ~31u, sc.col & 31u, ref.slot);
+                const float *col = shm_f32() + slot_index<kStride, kConstRow, kLiftRow>(sc.col & ~31u, sc.col & 31u, ref.slot);
                 c.x = col[0];
                 c.y = col[kStride];
                 c.z = col[2 * kStride];
+                if (kLiftRow > 0 && (ref.slot & kLiftSlot))
+                {
+                    c.z += shm_f32()[sc.col + static_cast<unsigned>(lift_z_row) * kStride];
+                }
             }
             if (ref.base & 1)
             {
@@ -192,8 +197,8 @@ namespace vb
         return v < 0.f;
     }
 
-    template <class T, class M, int kStride, int kConstRow>
-    VB_D bool walk_tables(const T &t, const TableCtx<kStride, kConstRow> &c, M &mg)
+    template <class T, class M, int kStride, int kConstRow, int kLiftRow>
+    VB_D bool walk_tables(const T &t, const TableCtx<kStride, kConstRow, kLiftRow> &c, M &mg)
     {
         // environment groups (robots/<robot>/fk.hh: `if (sphere_environment_in_collision(bounding)) {...}`)
         for (int g = 0; g < t.n_env; ++g)
@@ -291,12 +296,13 @@ namespace vb
         SlotSink sink{sc.col, sc.stride, &a.env.attach, sc.att_col, sc.att_stride};
         if (Robot::kHasAttach && attach)
         {
-            const TableCtx<Robot::kStride, Robot::kConstRow> ctx{a.env, sc, a.base[0], a.base[1], a.base[2], a.sphere_radius,
-                                                                 Robot::ders_attach()};
+            const TableCtx<Robot::kStride, Robot::kConstRow, Robot::kLiftRow> ctx{
+                a.env, sc, a.base[0], a.base[1], a.base[2], a.sphere_radius, Robot::ders_attach(), Robot::tables_attach().lift_z_row};
             Robot::chain_attach(sink, q);
             return walk_tables(Robot::tables_attach(), ctx, mg);
         }
-        const TableCtx<Robot::kStride, Robot::kConstRow> ctx{a.env, sc, a.base[0], a.base[1], a.base[2], a.sphere_radius, Robot::ders()};
+        const TableCtx<Robot::kStride, Robot::kConstRow, Robot::kLiftRow> ctx{
+            a.env, sc, a.base[0], a.base[1], a.base[2], a.sphere_radius, Robot::ders(), Robot::tables().lift_z_row};
         Robot::chain(sink, q);
         return walk_tables(Robot::tables(), ctx, mg);
     }

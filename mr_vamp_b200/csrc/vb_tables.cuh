@@ -15,6 +15,11 @@ namespace vb
     // plan_links); it is rebuilt where a fired group needs it.
     constexpr unsigned kDerivedSlot = 0x2000u;
 
+    // slot code of a translated constant: kLiftSlot | j.  (x, y, dz) lives once per warp in the rows from Robot::kLiftRow;
+    // the centre is (x, y, dz + z of the stored centre whose z row is Tables::lift_z_row) -- Fetch's torso and head
+    // spheres ride on the prismatic torso_lift joint (codegen/emit_cuda.py: LIFT_SLOT).
+    constexpr unsigned kLiftSlot = 0x1000u;
+
     struct alignas(8) DerivedRec
     {
         uint16_t off[4];  // pre-multiplied column offsets of the link's basis centres (as SelfUnit::a_off)
@@ -105,6 +110,7 @@ namespace vb
     struct Tables
     {
         int n_slots, n_env, n_self, n_att, att_env;
+        int lift_z_row;  // row of the z coordinate the translated constants (kLiftSlot) add; -1: none
         RefGroup env[NE];
         SelfGroup self[NS];
         RefGroup att[NA];  // attachment_sphere_collision groups (robot sphere vs every attachment sphere)
@@ -114,9 +120,14 @@ namespace vb
 #ifdef __CUDACC__
     // float index of a slot's x coordinate (y, z at +kStride each): `wcol` = first column of the warp, L = lane
     // whose configuration is addressed
-    template <int kStride, int kConstRow>
+    template <int kStride, int kConstRow, int kLiftRow = 0>
     __device__ __forceinline__ unsigned slot_index(unsigned wcol, int L, unsigned slot)
     {
+        if (kLiftRow > 0 && (slot & kLiftSlot))
+        {
+            const unsigned j = slot & (kLiftSlot - 1u);
+            return 3u * (kLiftRow + (j >> 5)) * kStride + wcol + (j & 31u);
+        }
         const unsigned j = slot & (kConstSlot - 1u);
         return (slot & kConstSlot) ? 3u * (kConstRow + (j >> 5)) * kStride + wcol + (j & 31u) : 3u * slot * kStride + wcol + L;
     }

@@ -279,6 +279,10 @@ namespace vb
         static constexpr unsigned kGroups = Robot::kEnvGroups > 0 ? Robot::kEnvGroups : 1;
 
         static constexpr unsigned kConstOff = 3u * Robot::kConstRow * S;
+        // translated constants (vb_tables.cuh: kLiftSlot): offsets from kLiftOff on add the z at kLiftZOff (+ lane)
+        static constexpr bool kHasLift = Robot::kLiftCount > 0;
+        static constexpr unsigned kLiftOff = 3u * Robot::kLiftRow * S;
+        static constexpr unsigned kLiftZOff = static_cast<unsigned>(Robot::kLiftZRow) * S;
         static constexpr int kItemQ = Robot::kEnvQ > Robot::kSelfQ ? Robot::kEnvQ : Robot::kSelfQ;
 
         // self items and environment items are never queued at the same time: one array serves both
@@ -311,10 +315,14 @@ namespace vb
             }
             else
             {
-                const float *col = shm_f32() + slot_index<S, Robot::kConstRow>(c.wcol, L, ref.slot);
+                const float *col = shm_f32() + slot_index<S, Robot::kConstRow, Robot::kLiftRow>(c.wcol, L, ref.slot);
                 s.x = col[0];
                 s.y = col[S];
                 s.z = col[2 * S];
+                if (kHasLift && (ref.slot & kLiftSlot))
+                {
+                    s.z += shm_f32()[c.wcol + kLiftZOff + L];
+                }
             }
             s.x += (ref.base & 1) ? c.bx : 0.f;
             s.y += (ref.base & 2) ? c.by : 0.f;
@@ -344,6 +352,10 @@ namespace vb
             x = col[0];
             y = col[S];
             z = col[2 * S];
+            if (kHasLift && off >= kLiftOff)
+            {
+                z += shm_f32()[c.wcol + kLiftZOff + L];
+            }
         }
 
         // a_i of configuration L against every b_j of its group
@@ -540,10 +552,14 @@ namespace vb
             }
             else
             {
-                const float *col = shm_f32() + slot_index<S, Robot::kConstRow>(c.wcol, L, slot);
+                const float *col = shm_f32() + slot_index<S, Robot::kConstRow, Robot::kLiftRow>(c.wcol, L, slot);
                 x = col[0];
                 y = col[S];
                 z = col[2 * S];
+                if (kHasLift && (slot & kLiftSlot))
+                {
+                    z += shm_f32()[c.wcol + kLiftZOff + L];
+                }
             }
         }
 
