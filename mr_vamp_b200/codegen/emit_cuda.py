@@ -78,8 +78,6 @@ TWO_LEVEL_GRID_OFF = {"fetch", "baxter"}
 # all 32 lanes whenever one lane's guard fired (Baxter: 174 fired (lane, group) pairs in 81 distinct groups per warp
 # step = 2 useful lanes of 32, and 718 units of generated code); the queued form does exactly the fired tests.
 QUEUED_FILTERS = set(os.environ.get("VB_QUEUED_FILTERS", "fetch,baxter").split(","))
-# Unit stages pooled over the CTA in the fkcc kernels (vb_walk.cuh: run_pooled)
-POOLED = set(os.environ.get("VB_POOLED", "").split(","))
 MIN_LINK_SPHERES = int(os.environ.get("VB_MIN_LINK_SPHERES", "2"))  # links with fewer fine spheres are left alone
 DERIVE_GUARDS = os.environ.get("VB_DERIVE_GUARDS", "1") != "0"  # bounding spheres rebuilt from the link basis too
 
@@ -984,7 +982,6 @@ def emit_robot(ir: dict[str, Any]) -> str:
     w(f"    static constexpr bool kStageCfg = {'true' if stage_cfg else 'false'};  // configurations staged in shared memory by bulk copy")
     w(f"    static constexpr int kEnvQ = {geom['env_q']}, kSelfQ = {geom['self_q']}, kPairQ = {geom['pair_q']};  // work-queue capacities (units)")
     w(f"    static constexpr bool kQueuedFilters = {'true' if queued else 'false'};  // a-side filters as queued work (vb_walk.cuh: filter_units)")
-    w(f"    static constexpr bool kPooled = {'true' if robot in POOLED else 'false'};  // unit stages pooled over the CTA (fkcc kernels)")
     w(f"    static constexpr int kFiltQ = {geom['filt_q']};  // filter-test queue (>= the largest a-side of a self group: {max_a})")
     w(f"    static constexpr int kChainFlops = {st['chain_flops']};")
     w(f"    static constexpr int kEnvGroups = {st['env_groups']}, kEnvFine = {st['env_fine']};")

@@ -312,8 +312,7 @@ namespace vb
     // `base`: robot base offset (default: a.base; the second robot of a composite configuration passes a.base_b)
     template <class Robot, bool kSync = false>
     VB_D bool check_warp(const LaunchArgs &a, const Scratch &sc, const float *q, bool alive, bool attach, int &cstate,
-                         bool octet = false, const float *base = nullptr, int release_id = 0, int release_count = 0,
-                         int pool_step = -1)
+                         bool octet = false, const float *base = nullptr, int release_id = 0, int release_count = 0)
     {
         const float *bs = base ? base : a.base;
         // kSync (CTA-uniform callers, `attach` uniform): the attachment decision must not depend on the warp
@@ -371,13 +370,6 @@ namespace vb
         wc.octet = octet;
         wc.release_id = release_id;
         wc.release_count = release_count;
-        // unit stages pooled over the CTA (fkcc kernels of Robot::kPooled robots; every condition is CTA-uniform)
-        if (Walk<Robot>::kPoolable && Robot::kPooled && pool_step >= 0 && !octet && !attach && a.attach == 0 && a.env.sdf.cell != nullptr &&
-            (a.env.n_heightfields | a.env.n_capts) == 0 && a.env.n_quads > 0 && Robot::tables().n_self > 0)
-        {
-            const bool ok = Walk<Robot>::run_pooled(a.env, wc, !alive || phit, cstate, pfree, static_cast<unsigned>(pool_step));
-            return ok;  // (run_pooled ends with a CTA barrier)
-        }
         const bool ok = Walk<Robot>::template run<kSync>(a.env, wc, !alive || phit, cstate, pfree);
         __syncwarp();  // columns are rewritten by the next configuration
         return ok;
@@ -470,7 +462,6 @@ namespace vb
         // CTA-uniform trip count with a barrier per iteration: the warps of a CTA walk the (large, mostly
         // straight-line) code together, so the instruction cache serves one stream instead of seven
         unsigned iter = 0;
-        int pool_step = 0;
         for (size_t base = static_cast<size_t>(blockIdx.x) * blockDim.x; base < n_round; base += stride)
         {
             const size_t i = base + threadIdx.x;
@@ -568,8 +559,7 @@ namespace vb
             {
                 // (the last group's last release would find nobody waiting: skipped)
                 const int rel = (kG > 1 && !(last_step && group == kG - 1)) ? 1 + (group + 1) % kG : 0;
-                ok = check_warp<Robot, kMidBarrier>(a, prims, q, alive, a.attach != 0, cstate, false, nullptr, rel, 2 * kGroupThreads,
-                                                    kG == 1 ? pool_step++ : -1);
+                ok = check_warp<Robot, kMidBarrier>(a, prims, q, alive, a.attach != 0, cstate, false, nullptr, rel, 2 * kGroupThreads);
             }
             const uint32_t word = __ballot_sync(0xffffffffu, ok);
             if ((threadIdx.x & 31) == 0 && i < n_round)
@@ -626,8 +616,7 @@ namespace vb
             random_config<Robot>(a.seed, first + i, q);
             VB_TICK(11);
             const int rel = (kG > 1 && !(last_step && group == kG - 1)) ? 1 + (group + 1) % kG : 0;
-            const bool ok = check_warp<Robot, kMidBarrier>(a, prims, q, alive, a.attach != 0, cstate, false, nullptr, rel, 2 * kGroupThreads,
-                                                           kG == 1 ? static_cast<int>(iter - 1u) : -1);
+            const bool ok = check_warp<Robot, kMidBarrier>(a, prims, q, alive, a.attach != 0, cstate, false, nullptr, rel, 2 * kGroupThreads);
             VB_TICK(12);
             const uint32_t word = __ballot_sync(0xffffffffu, ok);
             if ((threadIdx.x & 31) == 0 && i < n_round)

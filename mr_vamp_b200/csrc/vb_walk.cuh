@@ -998,327 +998,6 @@ namespace vb
             fine_stage(env, c);
         }
 
-        // ================= unit stages pooled over the CTA (fkcc kernels; Robot::kPooled) ===============================
-        // The per-warp queues above hold little work per step (Panda: 22 pair units, 7 environment items, 56 fine units
-        // per 32 configurations): passes run part-filled and the warp that drew the most work decides when the CTA's
-        // step barrier opens.  Here every warp PUBLISHES its work to three CTA-level queues in one dense phase, and all
-        // warps then drain each queue in full 32-lane passes, whatever warp the configuration belongs to.
-        //   step = dense phase (chain, guards, filters; pushes) | barrier | pair units + environment items (push fine
-        //   units) | barrier | fine units | barrier | verdict words
-        // The queue entries live in the memory of the per-warp item and unit queues, seen as one segmented array of u32
-        // codes (configuration's thread index | unit << 10); the tails alternate between two sets of counters (cmask
-        // words 2 of warps 0..5) so that a step can reset the other step's.
-        static constexpr int kWarps = Robot::kBlock / 32;
-        static constexpr unsigned kSeg = static_cast<unsigned>(kItemQ + Robot::kPairQ) / 2u;  // u32 entries per warp segment
-        static constexpr unsigned kPoolAll = kSeg * kWarps;
-        static constexpr unsigned kPoolE = kPoolAll / 8u, kPoolP = kPoolAll / 8u * 3u, kPoolF = kPoolAll - kPoolE - kPoolP;
-        static constexpr bool kPoolable = kWarps >= 6 && Robot::kBlock <= 1024 && !Robot::kQueuedFilters;
-
-        // warp-uniform view of the CTA: this warp's context moved to warp 0
-        struct PoolCtx
-        {
-            unsigned q0;  // byte offset of warp 0's queue block
-        };
-        VB_D static unsigned *pool_entry(unsigned q0, unsigned i)
-        {
-            return shm_u32() + (q0 + (i / kSeg) * queue_bytes<Robot>()) / 4u + (i % kSeg);
-        }
-        VB_D static unsigned *pool_tail(unsigned q0, unsigned parity, int which)
-        {
-            const unsigned w = 3u * parity + static_cast<unsigned>(which);
-            return shm_u32() + (q0 + w * queue_bytes<Robot>() + 2u * (kItemQ + Robot::kPairQ + Robot::kFiltQ)) / 4u + 32u * kGroups + 2u;
-        }
-        // the walk context of the configuration held by thread t of the CTA
-        VB_D static WalkCtx ctx_of(const WalkCtx &c, unsigned q0, unsigned t)
-        {
-            WalkCtx o = c;
-            o.wcol = t & ~31u;
-            o.queues = q0 + (t >> 5) * queue_bytes<Robot>();
-            return o;
-        }
-
-        // one environment item (configuration L of context x, group g): exact guard test, candidates narrowed, fine units
-        // pushed to the CTA queue (run in place when it is full).  Returns true when the item itself decides a collision.
-        VB_D static bool pooled_env_item(const WalkCtx &x, const PrimIndex &ix, int n_obj, unsigned t, int g, unsigned q0, unsigned *tail_f)
-        {
-            const int L = t & 31;
-            const RefGroup G = T::env(g);
-            const uint32_t mask = gmask(x)[32 * g + L];
-            const Center b = centre(x, L, G.guard);
-            uint32_t low = mask & 0x7fffffffu, tight = 0u;
-            if (n_obj < 31)
-            {
-                low &= (1u << n_obj) - 1u;
-            }
-            const bool high = (mask >> 31) != 0u;
-            bool ghit = false;
-            int cursor = 0;
-            for (int o = next_candidate(low, high, n_obj, cursor); o >= 0; o = next_candidate(low, high, n_obj, cursor))
-            {
-                const ObjDist d = object_dist(x.prims, ix, o, b.x, b.y, b.z);
-                ghit |= object_hit(d, b.r);
-                if (G.slack < 0.f || object_hit(d, b.r + G.slack))
-                {
-                    tight |= 1u << (o < 31 ? o : 31);
-                }
-            }
-            if (G.count == 0)
-            {
-                return ghit;  // leaf group: the guard is the test
-            }
-            bool hit = false;
-            if (ghit)
-            {
-                gmask(x)[32 * g + L] = tight;
-                const int u0 = G.ubegin, uc = G.ucount;
-                const unsigned at = atomicAdd(tail_f, static_cast<unsigned>(uc));
-                for (int k = 0; k < uc; ++k)
-                {
-                    if (at + k < kPoolF)
-                    {
-                        *pool_entry(q0, kPoolE + kPoolP + at + k) = t | (static_cast<unsigned>(u0 + k) << 10);
-                    }
-                    else
-                    {
-                        hit = hit || fine_unit(x, Robot::walk_tables(), ix, L, u0 + k);
-                    }
-                }
-            }
-            return hit;
-        }
-
-        VB_D static bool run_pooled(const EnvView &env, const WalkCtx &c, bool collided, int &cstate, const uint32_t *pfree, unsigned step)
-        {
-            const auto &t = Robot::tables();
-            const WalkTables w = Robot::walk_tables();
-            const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-            const unsigned me = threadIdx.x;
-            const float *col = shm_f32() + c.wcol + lane;
-            const unsigned q0 = c.queues - static_cast<unsigned>(warp) * queue_bytes<Robot>();
-            const unsigned par = step & 1u;
-            unsigned *tail_e = pool_tail(q0, par, 0), *tail_p = pool_tail(q0, par, 1), *tail_f = pool_tail(q0, par, 2);
-            if (step == 0u)
-            {
-                if (me < 6u)
-                {
-                    *pool_tail(q0, me / 3u, static_cast<int>(me % 3u)) = 0u;
-                }
-                __syncthreads();
-            }
-            else if (me < 3u)
-            {
-                *pool_tail(q0, par ^ 1u, static_cast<int>(me)) = 0u;  // the other step's counters (idle since its last barrier)
-            }
-            // configuration-independent environment groups: a property of (environment, base), once per warp
-            if (Robot::kEnvConstAny)
-            {
-                const unsigned alive = __ballot_sync(kFull, !collided);
-                if (cstate < 0 && alive != 0u)
-                {
-                    const int L0 = __ffs(alive) - 1;
-                    NoMargin mg;
-                    bool hit = false;
-                    for (int g = 0; g < t.n_env && !hit; ++g)
-                    {
-                        if (!((Robot::env_const_mask(g >> 5) >> (g & 31)) & 1u))
-                        {
-                            continue;
-                        }
-                        const RefGroup grp = t.env[g];
-                        const Center b = centre(c, L0, grp.guard);
-                        if (env_hit(env, c.prims, b.x, b.y, b.z, b.r, mg))
-                        {
-                            hit = grp.count == 0;
-                            for (int k = 0; k < grp.count && !hit; ++k)
-                            {
-                                const Center s = centre(c, L0, t.refs[grp.begin + k]);
-                                hit = env_hit(env, c.prims, s.x, s.y, s.z, s.r, mg);
-                            }
-                        }
-                    }
-                    cstate = hit ? 1 : 0;
-                }
-                collided = collided || cstate > 0;
-            }
-            // ---- dense phase ------------------------------------------------------------------------------------------
-            uint2 cells[kGroups];
-            uint32_t inside[Robot::kEnvWords], maybe[Robot::kEnvWords], cert[Robot::kEnvWords];
-            Robot::env_fetch(col, c.bx, c.by, c.bz, env.sdf, env.sdf_c, c.radius, cells, inside);
-            uint32_t fired[Robot::kSelfWords], ubits[Robot::kUnitWords];
-            Robot::self_guards(col, fired);
-            Robot::env_classify(cells, inside, c.radius, env.sdf, maybe, cert, gmask(c) + lane);
-#pragma unroll
-            for (int wi = 0; wi < Robot::kSelfWords; ++wi)
-            {
-                fired[wi] &= (collided ? 0u : 0xffffffffu) & ~pfree[wi];
-                collided = collided || (fired[wi] & Robot::self_leaf_mask(wi)) != 0u;
-            }
-#pragma unroll
-            for (int wi = 0; wi < Robot::kSelfWords; ++wi)
-            {
-                fired[wi] = collided ? 0u : (fired[wi] & ~Robot::self_leaf_mask(wi));
-            }
-            Robot::self_filters(col, fired, ubits);
-            {
-                const unsigned cm = __ballot_sync(kFull, collided);
-                if (lane == 0)
-                {
-                    cmask(c)[0] = cm;
-                }
-            }
-            __syncwarp();
-            // ---- publish: pair units, then environment items ------------------------------------------------------------
-            {
-                int cnt = 0;
-#pragma unroll
-                for (int wi = 0; wi < Robot::kUnitWords; ++wi)
-                {
-                    cnt += __popc(ubits[wi]);
-                }
-                const int incl = warp_scan(cnt, lane);
-                const int total = __shfl_sync(kFull, incl, 31);
-                if (total > 0)
-                {
-                    unsigned base = 0u;
-                    if (lane == 31)
-                    {
-                        base = atomicAdd(tail_p, static_cast<unsigned>(total));
-                    }
-                    base = __shfl_sync(kFull, base, 31);
-                    unsigned at_ = base + static_cast<unsigned>(incl - cnt);
-                    bool hit = false;
-#pragma unroll
-                    for (int wi = 0; wi < Robot::kUnitWords; ++wi)
-                    {
-                        uint32_t m = ubits[wi];
-                        while (m)
-                        {
-                            const int b = __ffs(m) - 1;
-                            m &= m - 1u;
-                            if (at_ < kPoolP)
-                            {
-                                *pool_entry(q0, kPoolE + at_) = me | (static_cast<unsigned>(wi * 32 + b) << 10);
-                            }
-                            else
-                            {
-                                hit = hit || pair_unit(c, w, lane, T::unit(wi * 32 + b));  // queue full: run the unit here
-                            }
-                            ++at_;
-                        }
-                    }
-                    if (hit)
-                    {
-                        atomicOr(cmask(c), 1u << lane);
-                    }
-                }
-            }
-            const PrimIndex ix = prim_index(env);
-            const int n_obj = ix.first[5];
-            {
-                int cnt = 0;
-                uint32_t mine[Robot::kEnvWords];
-#pragma unroll
-                for (int wi = 0; wi < Robot::kEnvWords; ++wi)
-                {
-                    mine[wi] = collided ? 0u : (maybe[wi] & ~Robot::env_const_mask(wi));
-                    cnt += __popc(mine[wi]);
-                }
-                const int incl = warp_scan(cnt, lane);
-                const int total = __shfl_sync(kFull, incl, 31);
-                if (total > 0)
-                {
-                    unsigned base = 0u;
-                    if (lane == 31)
-                    {
-                        base = atomicAdd(tail_e, static_cast<unsigned>(total));
-                    }
-                    base = __shfl_sync(kFull, base, 31);
-                    unsigned at_ = base + static_cast<unsigned>(incl - cnt);
-                    bool hit = false;
-#pragma unroll
-                    for (int wi = 0; wi < Robot::kEnvWords; ++wi)
-                    {
-                        uint32_t m = mine[wi];
-                        while (m)
-                        {
-                            const int b = __ffs(m) - 1;
-                            m &= m - 1u;
-                            if (at_ < kPoolE)
-                            {
-                                *pool_entry(q0, at_) = me | (static_cast<unsigned>(wi * 32 + b) << 10);
-                            }
-                            else
-                            {
-                                hit = hit || pooled_env_item(c, ix, n_obj, me, wi * 32 + b, q0, tail_f);
-                            }
-                            ++at_;
-                        }
-                    }
-                    if (hit)
-                    {
-                        atomicOr(cmask(c), 1u << lane);
-                    }
-                }
-            }
-            __syncthreads();  // ---- every warp's work is published ---------------------------------------------------------
-            {
-                const unsigned np = min(vol(tail_p), kPoolP);
-                for (unsigned base = 32u * warp; base < np; base += 32u * kWarps)
-                {
-                    const unsigned i = base + lane;
-                    if (i < np)
-                    {
-                        const unsigned code = *pool_entry(q0, kPoolE + i);
-                        const unsigned tt = code & 1023u;
-                        const WalkCtx x = ctx_of(c, q0, tt);
-                        const int L = tt & 31;
-                        if (!done(x, L) && pair_unit(x, w, L, T::unit(code >> 10)))
-                        {
-                            atomicOr(cmask(x), 1u << L);
-                        }
-                    }
-                }
-                const unsigned ne = min(vol(tail_e), kPoolE);
-                // (the warps that drew the fewest pair passes start on the environment items)
-                for (unsigned base = 32u * (kWarps - 1 - warp); base < ne; base += 32u * kWarps)
-                {
-                    const unsigned i = base + lane;
-                    if (i < ne)
-                    {
-                        const unsigned code = *pool_entry(q0, i);
-                        const unsigned tt = code & 1023u;
-                        const WalkCtx x = ctx_of(c, q0, tt);
-                        const int L = tt & 31;
-                        if (!done(x, L) && pooled_env_item(x, ix, n_obj, tt, static_cast<int>(code >> 10), q0, tail_f))
-                        {
-                            atomicOr(cmask(x), 1u << L);
-                        }
-                    }
-                }
-            }
-            __syncthreads();  // ---- fine units are published ------------------------------------------------------------------
-            {
-                const unsigned nf = min(vol(tail_f), kPoolF);
-                for (unsigned base = 32u * warp; base < nf; base += 32u * kWarps)
-                {
-                    const unsigned i = base + lane;
-                    if (i < nf)
-                    {
-                        const unsigned code = *pool_entry(q0, kPoolE + kPoolP + i);
-                        const unsigned tt = code & 1023u;
-                        const WalkCtx x = ctx_of(c, q0, tt);
-                        const int L = tt & 31;
-                        if (!done(x, L) && fine_unit(x, w, ix, L, static_cast<int>(code >> 10)))
-                        {
-                            atomicOr(cmask(x), 1u << L);
-                        }
-                    }
-                }
-            }
-            __syncthreads();  // ---- verdicts -----------------------------------------------------------------------------------
-            return !(collided || done(c, lane));
-        }
-
         // Must be called by all 32 lanes of a warp, converged, after the chain of every live lane has
         // written its slot column (and a __syncwarp).  `collided` enters true for lanes without a
         // configuration.  Returns this lane's verdict (true = collision free).
