@@ -886,7 +886,7 @@ def emit_robot(ir: dict[str, Any]) -> str:
     queued = robot in QUEUED_FILTERS
     max_a = max([g["a"][1] for g in em.selfg] or [1])
     geom = {"env_q": 256, "self_q": 256, "pair_q": 256, "env_groups": max(len(em.env), 1),
-            "filt_q": (max(256, (max_a + 31) // 32 * 32) if queued else 0)}
+            "filt_q": (max(int(os.environ.get("VB_FORCE_FILTQ", "256")), (max_a + 31) // 32 * 32) if queued else 0)}
     # shared-memory rows: one per configuration-dependent centre (a column per thread), then the constant rows
     # (one copy per warp, 32 constants per row)
     const_row = max(em.n_rows, em_att.n_rows if em_att else 0)

@@ -294,6 +294,7 @@ namespace vb
         // rake blocks (WalkCtx::octet): bit L of gfire[g] = the exact guard test of group g fired for configuration L.  The
         // words live in the last kFireQ entries of the item queue, which holds that many items less for rake blocks.
         static constexpr int kFireQ = 2 * ((static_cast<int>(kGroups) + 1) & ~1);
+        static_assert(Robot::kEnvQ >= kFireQ + 32, "the item queue holds the fired-guard words and at least one group's items");
         VB_D static unsigned *gfire(const WalkCtx &c) { return shm_u32() + (c.queues + 2 * (kItemQ - kFireQ)) / 4; }
 
         VB_D static unsigned vol(const unsigned *p)
@@ -591,6 +592,7 @@ namespace vb
 #else
             constexpr int kIlp = Robot::kDerived > 0 ? 1 : 4;
 #endif
+            static_assert(Robot::kPairQ >= 32 * kIlp && Robot::kFiltQ >= 32, "a trip's survivors must fit the pair queue");
             int np = 0;  // units waiting in the pair queue
             for (;;)
             {
