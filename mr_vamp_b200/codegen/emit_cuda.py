@@ -715,6 +715,10 @@ def _uniform(em: _Emitter, queued: bool = False) -> list[str]:
     w("        auto sqd = [](float dx, float dy, float dz) { return dx * dx + dy * dy + dz * dz; };")
     for wi in range(uw):
         w(f"        uint32_t u{wi} = 0u;")
+    if not queued:
+        # groups fired somewhere in the warp: one reduction per word, then warp-uniform branches (no vote per group)
+        for wi in range(sw):
+            w(f"        const uint32_t any{wi} = __reduce_or_sync(0xffffffffu, fired[{wi}]);")
     unit = 0
     for gi, g in enumerate(em.selfg):
         ac = g["a"][1]
@@ -734,7 +738,7 @@ def _uniform(em: _Emitter, queued: bool = False) -> list[str]:
                 blk.append(f"u{pos // 32} |= ({d2g(sa, sb)} < {_f32(float(F(R * R)))}) ? {1 << (pos % 32)}u : 0u;")
         bit = f"(fired[{gi // 32}] & {1 << (gi % 32)}u)"
         if not queued:  # (queued filters: the function is never called, keep it out of the compile)
-            w(f"        if (__any_sync(0xffffffffu, {bit} != 0u))  // {g['name']}")
+            w(f"        if ((any{gi // 32} & {1 << (gi % 32)}u) != 0u)  // {g['name']}")
             w("        {")
             w(f"            if ({bit} != 0u)")
             w("            {")
