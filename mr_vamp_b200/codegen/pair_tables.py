@@ -10,11 +10,28 @@ of the joint ranges is tabulated at code-generation time:
     hit     the guard pair and one fine pair overlap everywhere in the cell (the configuration collides),
     unsure  anything else: the kernel runs the group's tests exactly as the reference does.
 
-`free` and `hit` are decided from the clearances at the four cell corners with a margin that bounds the
-variation inside the cell (a quarter of the corner spread + MARGIN metres, which covers the bilinear
-interpolation error of these smooth functions at the grid pitch used and the float32 rounding differences
-between this interpreter and the kernels); cells the margin cannot decide stay `unsure`, so the table never
-changes a verdict, only who computes it.  tests/test_oracle_cpu.py re-checks random points against the cells.
+`free` and `hit` are decided from the clearances f = |p| - R (p = c_a - c_b, R = r_a + r_b) at the four cell
+corners with a margin; cells the margin cannot decide stay `unsure`, so the table never changes a verdict, only
+who computes it.
+
+The margin, derived (interpolation_bound below, asserted for every table at generation time).  Inside a cell the
+bilinear interpolant of the corner values lies between the smallest and the largest corner value, and f differs
+from it by at most
+
+    eps = (h_a^2 M_aa + h_b^2 M_bb) / 8 + h_a h_b M_ab / 4,     M_ij >= sup |d2 f / dq_i dq_j|
+
+(the standard error bound of bilinear interpolation on an h_a x h_b cell).  For f = |p| - R,
+d2f/dq_i dq_j = (p_i . p_j + p . p_ij) / |p| - (p . p_i)(p . p_j) / |p|^3, hence |d2f| <= |p_ij| + |p_i| |p_j| / |p|.
+The derivative maxima |p_i|, |p_ij| are taken by finite differences over the (N_CELLS + 1)^2 corner grid the table
+is built from anyway (smooth trigonometric polynomials sampled at the cell pitch; inflated by 10 %), and |p| is
+bounded below by R_eff = max(R - 1 cm, R / 2): the sign of f is only at stake where |p| is within the margin of R
+(where the corners have |p| < R_eff, |p| stays below R inside the cell by the Lipschitz bound |p_i| h_i << R / 2).
+Every pair is then classified with margin_g = max(MARGIN, 1.1 eps_g + RESIDUE) (+ a quarter of the corner spread,
+kept from the first version as slack), RESIDUE covering what the model leaves out: the traced link frames are not
+perfectly rigid (polynomial sin / cos: distances move by up to ~3e-5 m with joints that are not between the two
+links, see dependencies()) and this interpreter and the kernels round differently (~1e-6 m).  Bounds of the tables built today:
+Panda (5, 6) 2.1e-4 m, UR5 (1, 2) 1.2e-3 (margin 1.35e-3) / (2, 3) 2.1e-4, Fetch 4.2e-5 / 6.9e-5, Baxter 1.3e-4.
+tests/test_oracle_cpu.py re-checks random points against the cells.
 """
 from __future__ import annotations
 
@@ -25,7 +42,9 @@ import numpy as np
 from . import ir_eval
 
 N_CELLS = 256  # cells per joint
-MARGIN = 1.0e-3  # metres
+MARGIN = 1.0e-3  # metres (floor of the per-pair margin)
+RESIDUE = 5.0e-5  # metres: non-rigidity of the traced frames + rounding differences (see the module docstring)
+MAX_MARGIN = 5.0e-3  # a table whose derived margin exceeds this is not worth building: assert
 MAX_GROUPS = 16  # per table: cell = free bits [0, 16) | hit bits [16, 32)
 F = np.float32
 
@@ -83,6 +102,20 @@ def dependencies(ir: dict[str, Any], fn, bases: int = 32, variations: int = 8, t
     return out
 
 
+def interpolation_bound(vals, a, b, m: int, ha: float, hb: float) -> float:
+    """Upper bound (metres) of |f - bilinear interpolant of the corner values| inside any cell, for the pair (a, b);
+    `vals` = the trace evaluated on the m x m corner grid ([ib, ia] order).  See the module docstring."""
+    p = (ir_eval.centre(vals, a, m * m) - ir_eval.centre(vals, b, m * m)).reshape(m, m, 3)
+    R = float(F(a[3]["c"])) + float(F(b[3]["c"]))
+    r_eff = max(R - 1.0e-2, 0.5 * R)
+    nrm = lambda d: float(np.linalg.norm(d, axis=2).max())
+    da, db = 1.1 * nrm(np.diff(p, axis=1)) / ha, 1.1 * nrm(np.diff(p, axis=0)) / hb
+    daa, dbb = 1.1 * nrm(np.diff(p, 2, axis=1)) / ha**2, 1.1 * nrm(np.diff(p, 2, axis=0)) / hb**2
+    dab = 1.1 * nrm(np.diff(np.diff(p, axis=0), axis=1)) / (ha * hb)
+    maa, mbb, mab = daa + da * da / r_eff, dbb + db * db / r_eff, dab + da * db / r_eff
+    return (ha * ha * maa + hb * hb * mbb) / 8.0 + ha * hb * mab / 4.0
+
+
 def _cells(c: np.ndarray):
     """corner values [N+1, N+1] -> (min, max) over the four corners of every cell, [N, N] each."""
     c4 = np.stack([c[:-1, :-1], c[1:, :-1], c[:-1, 1:], c[1:, 1:]])
@@ -119,27 +152,40 @@ def build(ir: dict[str, Any], fn, n_cells: int = N_CELLS) -> list[dict[str, Any]
             q[:, jb] = (lo[jb] + ib.ravel().astype(F) * F(rg[jb] / F(n_cells))).astype(F)
             vals = ir_eval.evaluate(fn, q)
             cells = np.zeros((n_cells, n_cells), np.uint32)
+            ha, hb = float(rg[ja]) / n_cells, float(rg[jb]) / n_cells
+            worst = 0.0
             for k, gi in enumerate(part):
                 guard, fine = _pairs(items[gi])
+
+                def margin_of(a, b):
+                    nonlocal worst
+                    eps = interpolation_bound(vals, a, b, m, ha, hb)
+                    worst = max(worst, eps)
+                    mg = max(MARGIN, 1.1 * eps + RESIDUE)
+                    assert mg <= MAX_MARGIN, (ir["robot"], (ja, jb), gi, eps)
+                    return mg
+
+                g_mg = margin_of(guard[0], guard[1])
                 gmn, gmx = _cells(_clear(vals, guard[0], guard[1], m * m).reshape(m, m))
                 g_sp = gmx - gmn
-                guard_fires = gmx + 0.25 * g_sp + MARGIN < 0.0
-                guard_free = gmn - 0.25 * g_sp - MARGIN > 0.0
+                guard_fires = gmx + 0.25 * g_sp + g_mg < 0.0
+                guard_free = gmn - 0.25 * g_sp - g_mg > 0.0
                 if fine:
                     free_lb = np.full((n_cells, n_cells), np.inf)
                     hit_ub = np.full((n_cells, n_cells), np.inf)
                     for a, b in fine:
+                        mg = margin_of(a, b)
                         mn, mx = _cells(_clear(vals, a, b, m * m).reshape(m, m))
                         sp = mx - mn
-                        free_lb = np.minimum(free_lb, mn - 0.25 * sp - MARGIN)
-                        hit_ub = np.minimum(hit_ub, mx + 0.25 * sp + MARGIN)
+                        free_lb = np.minimum(free_lb, mn - 0.25 * sp - mg)
+                        hit_ub = np.minimum(hit_ub, mx + 0.25 * sp + mg)
                     free = guard_free | (free_lb > 0.0)
                     hit = guard_fires & (hit_ub < 0.0)
                 else:
                     free, hit = guard_free, guard_fires
                 assert not np.any(free & hit)
                 cells |= (free.astype(np.uint32) << np.uint32(k)) | (hit.astype(np.uint32) << np.uint32(16 + k))
-            tables.append({"joints": (ja, jb), "groups": part, "cells": cells.ravel(), "n": n_cells})
+            tables.append({"joints": (ja, jb), "groups": part, "cells": cells.ravel(), "n": n_cells, "eps": worst})
     # a table that decides nothing is not worth a load
     return [t for t in tables if np.any(t["cells"])]
 
@@ -151,7 +197,8 @@ def emit(robot: str, ir: dict[str, Any], tables: list[dict[str, Any]], self_word
     body: list[str] = []
     for ti, t in enumerate(tables):
         c = t["cells"]
-        head.append(f"// joint-pair table {ti}: joints {t['joints']}, self groups {t['groups']} (codegen/pair_tables.py)")
+        head.append(f"// joint-pair table {ti}: joints {t['joints']}, self groups {t['groups']} (codegen/pair_tables.py); derived "
+                    f"interpolation-error bound {t.get('eps', 0.0):.2e} m, margin max({MARGIN:g}, 1.1 eps + {RESIDUE:g}) m")
         head.append(f"__device__ const uint32_t k_{robot}_pair_cells{ti}[{c.size}] = {{")
         for i in range(0, c.size, 32):
             head.append("    " + ",".join(str(int(v)) for v in c[i : i + 32]) + ",")
