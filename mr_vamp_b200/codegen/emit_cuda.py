@@ -309,6 +309,12 @@ class _Emitter:
             if [a.get("base") for a in s[:3]] != [a.get("base") for a in guard[:3]]:
                 return -1.0
             d = ((ir_eval.centre(vals, s, n) - cg) ** 2).sum(axis=1) ** 0.5
+            # The bound holds beyond the samples because the two centres sit on ONE rigid link: their distance is a
+            # constant of the robot, which the samples show (spread below the ~3e-5 m non-rigidity of the polynomial
+            # sin / cos).  A sphere that moves relative to its guard gets no containment bound at all.
+            self.rigid_spread = max(getattr(self, "rigid_spread", 0.0), float(d.max() - d.min()))
+            if float(d.max() - d.min()) > 5e-5:
+                return -1.0
             worst = max(worst, float(d.max()) + s[3]["c"] - guard[3]["c"])
         return max(worst, 0.0) + 1e-4
 
