@@ -1073,61 +1073,72 @@ namespace vb
         return hit;
     }
 
-    // threads of a composite CTA: half the warps of the robot's fkcc CTA (rounded down)
+    // composites per step of a composite CTA: half the warps of the robot's fkcc CTA (rounded down) walk robot A, the
+    // other half robot B of the same composites
     template <class Robot>
     __host__ __device__ constexpr int pair_threads()
     {
         return (Robot::kBlock / 64) * 32;
     }
 
+    // Composite configurations (q_a, q_b) of two robots of one type at two bases.  Warps [0, W/2) walk robot A
+    // of 32 composites each, warp w + W/2 walks robot B of warp w's composites AT THE SAME TIME (all W warps resident, as
+    // in the fkcc kernels); after a CTA barrier the A warp combines the two verdicts and, for the composites whose robots
+    // are both valid on their own, tests A's spheres against B's (both columns are in shared memory).
     template <class Robot>
-    __global__ void __launch_bounds__(pair_threads<Robot>(), Robot::kCtasPerSm) pairs_fused_kernel(const __grid_constant__ LaunchArgs a)
+    __global__ void __launch_bounds__(2 * pair_threads<Robot>(), Robot::kCtasPerSm) pairs_fused_kernel(const __grid_constant__ LaunchArgs a)
     {
         constexpr unsigned kHalf = static_cast<unsigned>(pair_threads<Robot>());
-        const Scratch sa = stage_env<Robot>(a, true);
-        Scratch sb = sa;
-        sb.col = sa.col + kHalf;                                    // B's columns: the upper half of the window
-        sb.queues = sa.queues + (kHalf / 32u) * queue_bytes<Robot>();  // and the queue blocks of the warps that are not there
-        int cstate_a = -1, cstate_b = -1;
+        __shared__ uint32_t b_words[kHalf / 32u];
+        const Scratch sc = stage_env<Robot>(a, true);
+        const bool is_b = threadIdx.x >= kHalf;  // warp-uniform
+        const unsigned slot = threadIdx.x - (is_b ? kHalf : 0u);
+        int cstate = -1;
         const int lane = threadIdx.x & 31;
-        const size_t stride = static_cast<size_t>(gridDim.x) * blockDim.x;
+        const size_t stride = static_cast<size_t>(gridDim.x) * kHalf;
         const size_t n_round = (a.n + 31) / 32 * 32;
-        for (size_t base = static_cast<size_t>(blockIdx.x) * blockDim.x; base < n_round; base += stride)
+        for (size_t base = static_cast<size_t>(blockIdx.x) * kHalf; base < n_round; base += stride)
         {
-            const size_t i = base + threadIdx.x;
+            const size_t i = base + slot;
             const bool alive = i < a.n;
-            if (kLockstep)
-            {
-                __syncthreads();
-            }
-            float qa[Robot::kDim], qb[Robot::kDim];
+            __syncthreads();  // lockstep; and the previous step's b_words and columns have been consumed
+            float q[Robot::kDim];
+            const float *src = is_b ? a.cfg_b : a.cfg;
 #pragma unroll
             for (int j = 0; j < Robot::kDim; ++j)
             {
-                qa[j] = alive ? __ldg(a.cfg + i * Robot::kDim + j) : 0.f;
-                qb[j] = alive ? __ldg(a.cfg_b + i * Robot::kDim + j) : 0.f;
+                q[j] = alive ? __ldg(src + i * Robot::kDim + j) : 0.f;
             }
-            bool ok = check_warp<Robot>(a, sa, qa, alive, false, cstate_a, false, a.base);
-            ok = check_warp<Robot>(a, sb, qb, alive && ok, false, cstate_b, false, a.base_b) && ok;
-            if (ok)
+            bool ok = check_warp<Robot>(a, sc, q, alive, false, cstate, false, is_b ? a.base_b : a.base);
+            const uint32_t mine = __ballot_sync(0xffffffffu, ok && alive);
+            if (is_b && lane == 0)
             {
-                WalkCtx ca, cb;
-                ca.wcol = sa.col - lane, cb.wcol = sb.col - lane;
-                ca.queues = sa.queues, cb.queues = sb.queues;
-                ca.prims = cb.prims = sa.prims;
-                ca.bx = a.base[0], ca.by = a.base[1], ca.bz = a.base[2];
-                cb.bx = a.base_b[0], cb.by = a.base_b[1], cb.bz = a.base_b[2];
-                ca.radius = cb.radius = a.sphere_radius;
-                ca.octet = cb.octet = false;
-                ca.release_id = cb.release_id = 0;
-                ca.release_count = cb.release_count = 0;
-                ok = !robots_overlap<Robot>(ca, cb, lane);
+                b_words[slot >> 5] = mine;
             }
-            __syncwarp();
-            const uint32_t word = __ballot_sync(0xffffffffu, ok && alive);
-            if (lane == 0 && i < n_round)
+            __syncthreads();
+            if (!is_b)
             {
-                a.bits[i >> 5] = word;
+                ok = ok && alive && ((b_words[slot >> 5] >> lane) & 1u);
+                if (ok)
+                {
+                    WalkCtx ca, cb;
+                    ca.wcol = sc.col - lane, cb.wcol = sc.col - lane + kHalf;
+                    ca.queues = sc.queues, cb.queues = sc.queues + (kHalf / 32u) * queue_bytes<Robot>();
+                    ca.prims = cb.prims = sc.prims;
+                    ca.bx = a.base[0], ca.by = a.base[1], ca.bz = a.base[2];
+                    cb.bx = a.base_b[0], cb.by = a.base_b[1], cb.bz = a.base_b[2];
+                    ca.radius = cb.radius = a.sphere_radius;
+                    ca.octet = cb.octet = false;
+                    ca.release_id = cb.release_id = 0;
+                    ca.release_count = cb.release_count = 0;
+                    ok = !robots_overlap<Robot>(ca, cb, lane);
+                }
+                __syncwarp();
+                const uint32_t word = __ballot_sync(0xffffffffu, ok);
+                if (lane == 0 && i < n_round)
+                {
+                    a.bits[i >> 5] = word;
+                }
             }
         }
     }

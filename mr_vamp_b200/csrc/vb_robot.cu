@@ -148,7 +148,7 @@ namespace vb
         {
             return e;
         }
-        pairs_fused_kernel<R><<<grid, pair_threads<R>(), smem_bytes(a, true), a.stream>>>(a);
+        pairs_fused_kernel<R><<<grid, 2 * pair_threads<R>(), smem_bytes(a, true), a.stream>>>(a);
         return cudaGetLastError();
     }
 
@@ -158,8 +158,8 @@ namespace vb
         {
             return e;
         }
-        *threads = pair_threads<R>();
-        return cudaOccupancyMaxActiveBlocksPerMultiprocessor(blocks, pairs_fused_kernel<R>, pair_threads<R>(), smem_bytes(a, true));
+        *threads = pair_threads<R>();  // composites per CTA step (the CTA has twice as many threads)
+        return cudaOccupancyMaxActiveBlocksPerMultiprocessor(blocks, pairs_fused_kernel<R>, 2 * pair_threads<R>(), smem_bytes(a, true));
     }
 
     static cudaError_t occupancy(const LaunchArgs &a, int *blocks, int *threads)
