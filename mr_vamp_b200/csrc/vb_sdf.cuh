@@ -40,7 +40,8 @@ namespace vb
     {
         int ix, iy, iz;
         grid_coords(g, x, y, z, ix, iy, iz, in);
-        return in ? __ldg(g.centre + (iz * g.ny + iy) * g.nx + ix) : make_uint2(0u, 0u);
+        // (outside: the centre voxel is loaded and ignored -- a select instead of a branch around the load)
+        return __ldg(g.centre + (in ? (iz * g.ny + iy) * g.nx + ix : 0));
     }
     // Two levels over the same box: the coarse cell is fetched with grid_fetch(coarse, ...); a guard it cannot call free
     // then fetches its fine cell.  `in` comes from the coarse lookup (same box; the voxel is clamped, because the two
@@ -51,7 +52,7 @@ namespace vb
         const int hx = g.nx >> 1, hy = g.ny >> 1, hz = g.nz >> 1;
         const int ix = min(max(__float2int_rd(gx), -hx), hx - 1), iy = min(max(__float2int_rd(gy), -hy), hy - 1),
                   iz = min(max(__float2int_rd(gz), -hz), hz - 1);
-        return in ? __ldg(g.centre + (iz * g.ny + iy) * g.nx + ix) : make_uint2(0u, 0u);
+        return __ldg(g.centre + (in ? (iz * g.ny + iy) * g.nx + ix : 0));
     }
 
     // coarse level of the two-level lookup: true iff the coarse cell alone proves that no primitive touches a sphere
