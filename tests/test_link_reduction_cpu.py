@@ -98,3 +98,50 @@ def test_gram_form_of_the_pair_distance(robot):
     assert checked > 0
     # the kernels decide by the direct formula whenever the Gram form lands within GRAM_BAND of contact
     assert worst < GRAM_BAND / 4
+
+
+def test_translated_constants_match_the_trace():
+    """codegen/emit_cuda.py: LIFT_SLOT -- Fetch's torso / head centres ride on the prismatic torso_lift joint: x and y
+    are literals and z is a constant offset from ONE stored centre's z.  Checked on fresh configurations against the
+    trace: the rebuilt z within 5e-7 m (float32 rounding of the two traced sums), and the rows really are saved."""
+    ir = trace_parser.parse_robot("fetch")
+    fn = ir["functions"]["interleaved_sphere_fk"]
+    lo, rg = np.array(ir["scale"]["lo"]), np.array(ir["scale"]["range"])
+    rng = np.random.default_rng(0)
+    q = (lo + rng.random((1024, ir["dimension"])) * rg).astype(F)
+    em = emit_cuda._Emitter(fn, (ir_eval.evaluate(fn, q), 1024), False, True).run_checks()
+    plain = emit_cuda._Emitter(fn, (ir_eval.evaluate(fn, q), 1024), False, False).run_checks()
+    assert len(em.lift_xyz) >= 30 and em.lift_ref is not None
+    assert em.n_rows == plain.n_rows - len(em.lift_xyz)
+    n = 4000
+    vals = _fresh(ir, fn, n, 321)
+    by_key = {}
+    for it in fn["program"]:
+        if it.get("k") == "env":
+            for s in it["fine"] + [it["guard"]]:
+                by_key[em.key(s)] = s
+        elif it.get("k") == "self":
+            for s in it["guard"]:
+                by_key[em.key(s)] = s
+            for a, b in it.get("fine", []):
+                by_key[em.key(a)] = a
+                by_key[em.key(b)] = b
+    slot_key = {slot: key for key, slot in em.slots.items()}
+    zref = vals[em.lift_ref[1]].astype(F)
+    worst = 0.0
+    for slot, (x, y, dz) in em.lift_xyz.items():
+        s = by_key[slot_key[slot]]
+        want = ir_eval.centre(vals, s, n)
+        assert s[0]["v"] is None and s[1]["v"] is None and s[2]["v"] is not None
+        got_z = (F(float(dz.rstrip("f"))) + zref).astype(F)
+        worst = max(worst, float(np.abs(got_z.astype(np.float64) - want[:, 2]).max()))
+        assert abs(float(x.rstrip("f")) - s[0]["c"]) < 1e-7 and abs(float(y.rstrip("f")) - s[1]["c"]) < 1e-7
+    print(f"fetch: {len(em.lift_xyz)} translated constants, rows {plain.n_rows} -> {em.n_rows}, worst z error {worst:.2e} m")
+    assert worst < 5e-7
+    # robots without a prismatic joint have none
+    for robot in ("panda", "ur5"):
+        ir2 = trace_parser.parse_robot(robot)
+        fn2 = ir2["functions"]["interleaved_sphere_fk"]
+        lo2, rg2 = np.array(ir2["scale"]["lo"]), np.array(ir2["scale"]["range"])
+        q2 = (lo2 + rng.random((256, ir2["dimension"])) * rg2).astype(F)
+        assert not emit_cuda._Emitter(fn2, (ir_eval.evaluate(fn2, q2), 256), True, True).run_checks().lift_xyz

@@ -58,3 +58,46 @@ def test_lookup_outside_the_joint_ranges_is_undecided():
     q[2, ja] = np.nan
     cell = pair_tables.classify(t, ir, q)
     assert cell[0] == 0 and cell[1] == 0 and cell[2] == 0 and cell[3] != 0
+
+
+@pytest.mark.parametrize("robot", ["panda", "ur5", "fetch", "baxter"])
+def test_derived_interpolation_bound_holds(robot):
+    """codegen/pair_tables.py: interpolation_bound -- the margin of a table is derived from the error bound of bilinear
+    interpolation with second-derivative maxima taken over the table's corner grid.  Checked here the other way round:
+    at random points INSIDE the cells the pair clearance never leaves [min corner - eps, max corner + eps]."""
+    ir = trace_parser.parse_robot(robot)
+    fn = ir["functions"]["interleaved_sphere_fk"]
+    tables = pair_tables.build(ir, fn)
+    items = [it for it in fn["program"] if it["k"] == "self"]
+    lo, rg = np.array(ir["scale"]["lo"], F), np.array(ir["scale"]["range"], F)
+    rng = np.random.default_rng(11)
+    n_cells = pair_tables.N_CELLS
+    for t in tables:
+        assert 0.0 < t["eps"] and max(pair_tables.MARGIN, 1.1 * t["eps"] + pair_tables.RESIDUE) <= pair_tables.MAX_MARGIN
+        ja, jb = t["joints"]
+        m = 20_000
+        ca, cb = rng.integers(0, n_cells, m), rng.integers(0, n_cells, m)
+        ua, ub = rng.random(m), rng.random(m)
+
+        def configs(fa, fb):
+            q = np.tile((lo + F(0.5) * rg)[None, :], (m, 1)).astype(F)
+            q[:, ja] = (lo[ja] + (ca + fa).astype(F) * F(rg[ja] / F(n_cells))).astype(F)
+            q[:, jb] = (lo[jb] + (cb + fb).astype(F) * F(rg[jb] / F(n_cells))).astype(F)
+            return q
+
+        inner = ir_eval.evaluate(fn, configs(ua, ub))
+        corners = [ir_eval.evaluate(fn, configs(np.full(m, fa), np.full(m, fb))) for fa in (0.0, 1.0) for fb in (0.0, 1.0)]
+        for gi in t["groups"]:
+            guard, fine = pair_tables._pairs(items[gi])
+            for a, b in [guard] + fine:
+                f = pair_tables._clear(inner, a, b, m)
+                c = np.stack([pair_tables._clear(v, a, b, m) for v in corners])
+                over = np.maximum(f - c.max(axis=0), c.min(axis=0) - f)
+                # the bound is derived for |p| >= R_eff = max(R - 1 cm, R / 2), i.e. f >= -min(1 cm, R / 2): where the sign
+                # of f is at stake.  Deeper inside (both spheres far into each other) only the sign is asserted.
+                R = float(F(a[3]["c"])) + float(F(b[3]["c"]))
+                near = c.min(axis=0) >= -min(1.0e-2, 0.5 * R)
+                if near.any():
+                    assert over[near].max() <= t["eps"] + 1e-6, (robot, t["joints"], gi, over[near].max(), t["eps"])
+                deep = c.max(axis=0) < -min(1.0e-2, 0.5 * R)
+                assert np.all(f[deep] < 0.0)
