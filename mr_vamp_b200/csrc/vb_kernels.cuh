@@ -699,7 +699,8 @@ namespace vb
         }
         const float ss = VB_ADD(VB_ADD(VB_ADD(s[0], s[4]), VB_ADD(s[2], s[6])), VB_ADD(VB_ADD(s[1], s[5]), VB_ADD(s[3], s[7])));
         const float dist = sqrtf(ss);
-        return fmaxf(ceilf(dist / static_cast<float>(kRake) * static_cast<float>(resolution)), 1.f);
+        // (a NaN length stays NaN: fmaxf alone would turn it into one pass of NaN interpolants, which compare "free")
+        return dist <= 3.0e38f ? fmaxf(ceilf(dist / static_cast<float>(kRake) * static_cast<float>(resolution)), 1.f) : dist;
     }
 
     // Prefix-array form of the motion kernels (only the allocation-free entry point still uses it: at most 2^18 edges
@@ -936,7 +937,8 @@ namespace vb
                     }
                     const float dist = a.dist ? __ldg(a.dist + g) : edge_norm<Robot::kDim>(v);
                     const float nf = fmaxf(ceilf(dist / static_cast<float>(kRake) * static_cast<float>(a.resolution)), 1.f);
-                    if (!(nf < 2147483648.f) || !in_range)
+                    // (NaN / Inf lengths: the reference's pass count is undefined for them; the edge is invalid)
+                    if (!(dist <= 3.0e38f) || !(nf < 2147483648.f) || !in_range)
                     {
                         if ((lane & 7) == 0)
                         {

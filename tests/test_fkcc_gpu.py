@@ -140,6 +140,41 @@ def test_validate_joint_limits(vb, ref):
     assert np.array_equal(got, want)
 
 
+@pytest.mark.parametrize("name", ["panda", "ur5", "fetch", "baxter"])
+def test_non_finite_and_far_out_of_range_inputs(vb, ref, name):
+    """NaN / Inf / 1e30 joint values.  `validate` (joint limits && fkcc, bindings/common.hh:172-182) rejects all of them
+    in the reference and here.  `fkcc` alone: a NaN INPUT makes every clearance NaN and the configuration "free" in
+    both (the reference reads sign bits -- FloatVector::test_zero, vector/avx.hh:386-389 -- and the input NaN is
+    positive; the kernels compare, and a NaN compares false).  An Inf input is where the two may part: x86 turns
+    inf - inf into its NEGATIVE default NaN, whose sign bit the reference reads as a collision, while the GPU's
+    canonical NaN is positive; such configurations are outside every joint range, `validate` never lets them reach
+    fkcc, and DESIGN.md section 5 records the difference instead of emulating x86 NaN signs.  Edges with a non-finite
+    endpoint are reported invalid (the reference's pass count is undefined for them and its loop does not end)."""
+    robot = vb.Robot(name)
+    rn = REF_NAME.get(name, name)
+    env, renv = vb.Environment(), ref.Env()
+    mid = (robot.lower_bounds + np.float32(0.5) * robot.ranges).astype(np.float32)
+    q = np.tile(mid, (6, 1)).astype(np.float32)
+    q[1, 0] = np.nan
+    q[2, min(3, robot.dimension - 1)] = np.inf
+    q[3, robot.dimension - 1] = -np.inf
+    q[4, :] = np.nan
+    q[5, 1] = np.float32(1e30)
+    assert np.array_equal(robot.validate_batch(q, env), ref.validate(rn, renv, q))
+    assert not robot.validate_batch(q, env)[1:].any()
+    got, want = robot.fkcc_batch(q, env), ref.fkcc(rn, renv, q)
+    assert got[0] == want[0]
+    assert got[1] and want[1] and got[4] and want[4]  # NaN inputs: free in both
+    a = np.tile(mid, (4, 1)).astype(np.float32)
+    b = a.copy()
+    b[1, 0] = np.nan
+    b[2, 1] = np.inf
+    a[3, 0] = -np.inf
+    ok = robot.validate_motion_batch(a, b, env)
+    assert ok[0] == ref.validate_motion(rn, renv, a[:1], b[:1])[0]
+    assert not ok[1:].any()
+
+
 @pytest.mark.parametrize("name", ["panda", "ur5", "fetch"])
 @pytest.mark.parametrize("scene", ["65 primitives", "clipped grid"])
 def test_large_scenes_exercise_the_grid_fallbacks(vb, ref, name, scene):
