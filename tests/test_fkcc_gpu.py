@@ -140,6 +140,42 @@ def test_validate_joint_limits(vb, ref):
     assert np.array_equal(got, want)
 
 
+@pytest.mark.parametrize("name", ["panda", "ur5", "fetch"])
+def test_empty_and_ragged_batches(vb, ref, name):
+    """Batch sizes around the 32-configuration verdict words (0, 1, 31, 32, 33, 95 ...), zero-length and very long
+    edges: same verdicts as the reference, and an empty batch is not an error."""
+    robot = vb.Robot(name)
+    rn = REF_NAME.get(name, name)
+    spec = scenes.cage() if name == "panda" else scenes.random_scene(5)
+    env, renv = scenes.apply(spec, vb.Environment()), apply_ref(spec, ref.Env())
+    q_all = _cfgs(robot, 77, 200)
+    want_all, clr_all = ref.fkcc_clearance(rn, renv, q_all)
+    for n in (0, 1, 31, 32, 33, 95, 200):
+        q = q_all[:n]
+        got = robot.fkcc_batch(q, env)
+        assert got.shape == (n,)
+        if n:
+            judge(f"{name} fkcc n={n}", got, want_all[:n], clr_all[:n])
+            assert robot.fk_batch(q).shape == (n, robot.n_spheres, 4)
+            assert np.array_equal(robot.validate_batch(q, env), ref.validate(rn, renv, q))
+        else:
+            assert robot.validate_batch(q, env).shape == (0,)
+            assert robot.validate_motion_batch(q, q, env).shape == (0,)
+            assert robot.fk_batch(q).shape[0] == 0
+    # edges: zero length (one pass of 8 copies of the start), short, and long enough for hundreds of rake passes
+    a = q_all[:66].copy()
+    b = q_all[66:132].copy()
+    b[:8] = a[:8]  # zero-length edges
+    b[8:16] = (a[8:16] + np.float32(1e-4)).astype(np.float32)
+    lo, hi = robot.lower_bounds, robot.lower_bounds + robot.ranges
+    a[16:20], b[16:20] = lo, hi  # across the whole joint box: the longest edges inside the limits
+    b[20:24] = (a[20:24] + np.float32(40.0)).astype(np.float32)  # far beyond the limits: > 400 passes
+    for n in (1, 7, 33, 66):
+        got = robot.validate_motion_batch(a[:n], b[:n], env)
+        want, clr = ref.motion_clearance(rn, renv, a[:n], b[:n])
+        judge(f"{name} edges n={n}", got, want, clr)
+
+
 @pytest.mark.parametrize("name", ["panda", "ur5", "fetch", "baxter"])
 def test_non_finite_and_far_out_of_range_inputs(vb, ref, name):
     """NaN / Inf / 1e30 joint values.  `validate` (joint limits && fkcc, bindings/common.hh:172-182) rejects all of them
