@@ -80,6 +80,13 @@ TWO_LEVEL_GRID_OFF = {"fetch", "baxter"}
 QUEUED_FILTERS = set(os.environ.get("VB_QUEUED_FILTERS", "fetch,baxter").split(","))
 MIN_LINK_SPHERES = int(os.environ.get("VB_MIN_LINK_SPHERES", "2"))  # links with fewer fine spheres are left alone
 DERIVE_GUARDS = os.environ.get("VB_DERIVE_GUARDS", "1") != "0"  # bounding spheres rebuilt from the link basis too
+MERGE_BODIES = os.environ.get("VB_MERGE_BODIES", "1") != "0"  # links joined by fixed joints share one basis
+# Largest accepted difference between a rebuilt centre and the traced one (float32, over the sampled configurations).
+# One link: 1e-6 m.  A body of several links: the traced centres of its links come out of different chains of float32
+# operations and are themselves ~1e-6 m off a common affine image (Panda link7 / hand / fingers: 1.9e-6 m); 2.5e-6 m is
+# a quarter of the 1e-5 m the centres (and the verdict band) are allowed.
+REBUILD_TOL = float(os.environ.get("VB_REBUILD_TOL", "1e-6"))
+BODY_REBUILD_TOL = float(os.environ.get("VB_BODY_REBUILD_TOL", "2.5e-6"))
 
 
 def slot_offset(slot: int, stride: int, const_row: int, lift_row: int = 0) -> int:
@@ -124,6 +131,8 @@ class _Emitter:
         # translated constants (LIFT_SLOT): slot code -> (x, y, dz) literals; lift_ref = (stored slot, z value id)
         self.lift_xyz: dict[int, list[str]] = {}
         self.lift_ref: tuple[int, int] | None = None
+        self.last_vid = -1  # last value the chain has emitted
+        self.pending_puts: dict[int, list[str]] = {}  # value id -> stores waiting for it
 
     # -- operands -----------------------------------------------------------------------------
     def opnd(self, o) -> str:
@@ -181,7 +190,14 @@ class _Emitter:
                     self.lift_ref = (self.slots[key], s[2]["v"])  # the stored centre the translated constants ride on
                 if key in self.link_weights:
                     self.slot_weights[self.slots[key]] = list(self.link_weights[key][1])
-                self.lines.append(f"p.put_s<kStride>({self.slots[key]}, {xyz[0]}, {xyz[1]}, {xyz[2]});")
+                put = f"p.put_s<kStride>({self.slots[key]}, {xyz[0]}, {xyz[1]}, {xyz[2]});"
+                # a basis centre of a body of several links may be referenced (by a rebuilt centre of an earlier link)
+                # before the chain has computed it: its store waits for the last of its values
+                need = max(a["v"] for a in s[:3] if a["v"] is not None)
+                if need <= self.last_vid:
+                    self.lines.append(put)
+                else:
+                    self.pending_puts.setdefault(need, []).append(put)
         mask = sum((1 << i) for i, a in enumerate(s[:3]) if a.get("base"))
         for i, a in enumerate(s[:3]):
             assert a.get("base") in (None, "xyz"[i]), s
@@ -201,7 +217,9 @@ class _Emitter:
 
     def plan_links(self):
         """Rigid-link reduction of the shared-memory columns.  The fine spheres of one environment group sit on
-        one rigid link, so each centre is a constant affine combination of (at most) four of them.  For links
+        one rigid link -- and links joined by fixed joints form one rigid BODY (Panda: link7, the hand and both fingers;
+        found from the samples, MERGE_BODIES) -- so each centre is a constant affine combination of (at most) four of
+        the body's centres.  For links
         with >= MIN_LINK_SPHERES fine spheres only that basis is stored by the chain; the others are rebuilt
         where a fired group needs them (<= 1e-6 m from the traced value, checked here over the sampled
         configurations in float32), and their chain arithmetic becomes dead code.  Fewer slot rows = more
@@ -219,16 +237,18 @@ class _Emitter:
             elif it.get("k") == "self":
                 guards.add(self.key(it["guard"][0]))
                 guards.add(self.key(it["guard"][1]))
-        for it in self.program:
-            if it.get("k") != "env":
-                continue
+        def eligible(it) -> bool:
             fine = it["fine"]
             if len(fine) < MIN_LINK_SPHERES or fine == [it["guard"]]:
-                continue
+                return False
             if any(all(a["v"] is None for a in s[:3]) for s in fine):
-                continue  # configuration-independent centres live in the constant rows
-            if len({tuple(a.get("base") for a in s[:3]) for s in fine}) != 1:
-                continue
+                return False  # configuration-independent centres live in the constant rows
+            return len({tuple(a.get("base") for a in s[:3]) for s in fine}) == 1
+
+        def plan_set(fine, guard_list, tol=REBUILD_TOL):
+            """One rigid body: `fine` = its fine spheres (of one or several environment groups), `guard_list` = the
+            bounding spheres of those groups.  Returns (plan, link weights, (basis keys, Gram matrix)) or None when
+            some centre cannot be rebuilt to 1e-6 m."""
             C = [ir_eval.centre(vals, s, n) for s in fine]  # float64 copies of the float32 samples
             # greedy basis on the first sample: farthest pair, then farthest from the line, then from the plane
             # (many links carry collinear or coplanar sphere sets: 2 or 3 basis centres then suffice)
@@ -248,52 +268,119 @@ class _Emitter:
                     break
                 basis.append(k)
             m = min(n, 128)
-            A = np.concatenate([np.stack([C[b][t] - C[basis[0]][t] for b in basis[1:]], axis=1) for t in range(m)])
+            fine_keys = {self.key(sj) for sj in fine}
 
-            def weights(Cj):
-                """Affine weights of a centre over the basis and the float32 reconstruction error over all samples."""
-                y = np.concatenate([Cj[t] - C[basis[0]][t] for t in range(m)])
-                wk, *_ = np.linalg.lstsq(A, y, rcond=None)
-                wts = [1.0 - float(wk.sum())] + [float(v) for v in wk]
-                rec = np.zeros((n, 3), np.float32)
-                for wv, b in zip(wts, basis):
-                    rec = (rec + np.float32(wv) * C[b].astype(np.float32)).astype(np.float32)
-                err = float(np.abs(rec.astype(np.float64) - Cj).max())
-                return wts + [0.0] * (4 - len(wts)), err
+            def with_basis(basis):
+                A = np.concatenate([np.stack([C[b][t] - C[basis[0]][t] for b in basis[1:]], axis=1) for t in range(m)])
 
-            basis_args = [fine[b] for b in basis] + [fine[basis[0]]] * (4 - len(basis))
-            # Gram matrix of the basis edges e_k = c_bk - c_b0 (a rigid-motion invariant): lets the pair stage
-            # evaluate |a - b_j|^2 = |a - c_b0|^2 - 2 sum_k w_k (a - c_b0).e_k + w^T G w with w^T G w a constant
-            E = [C[b] - C[basis[0]] for b in basis[1:]] + [np.zeros_like(C[0])] * (4 - len(basis))
-            gram = [[float((E[k] * E[l]).sum(axis=1).mean()) for l in range(3)] for k in range(3)]
-            self.link_gram[tuple(self.key(b) for b in basis_args)] = gram
-            ok = True
-            plan = {}
-            lw = {}
-            for j, sj in enumerate(fine):
-                if j in basis:
-                    continue
-                wts, err = weights(C[j])
-                if err > 1e-6:
-                    ok = False
-                    break
-                if self.key(sj) in guards:
-                    lw[self.key(sj)] = (basis_args, wts)  # stays stored; the weights serve the b-side loop of the pair stage
-                else:
-                    plan[self.key(sj)] = (basis_args, wts)
-            if not ok:
+                def weights(Cj):
+                    """Affine weights of a centre over the basis and the float32 reconstruction error over all samples."""
+                    y = np.concatenate([Cj[t] - C[basis[0]][t] for t in range(m)])
+                    wk, *_ = np.linalg.lstsq(A, y, rcond=None)
+                    wts = [1.0 - float(wk.sum())] + [float(v) for v in wk]
+                    rec = np.zeros((n, 3), np.float32)
+                    for wv, b in zip(wts, basis):
+                        rec = (rec + np.float32(wv) * C[b].astype(np.float32)).astype(np.float32)
+                    err = float(np.abs(rec.astype(np.float64) - Cj).max())
+                    return wts + [0.0] * (4 - len(wts)), err
+
+                basis_args = [fine[b] for b in basis] + [fine[basis[0]]] * (4 - len(basis))
+                # Gram matrix of the basis edges e_k = c_bk - c_b0 (a rigid-motion invariant): lets the pair stage
+                # evaluate |a - b_j|^2 = |a - c_b0|^2 - 2 sum_k w_k (a - c_b0).e_k + w^T G w with w^T G w a constant
+                E = [C[b] - C[basis[0]] for b in basis[1:]] + [np.zeros_like(C[0])] * (4 - len(basis))
+                gram = [[float((E[k] * E[l]).sum(axis=1).mean()) for l in range(3)] for k in range(3)]
+                plan, lw = {}, {}
+                for j, sj in enumerate(fine):
+                    if j in basis:
+                        continue
+                    wts, err = weights(C[j])
+                    if err > tol:
+                        return None
+                    if self.key(sj) in guards:
+                        lw[self.key(sj)] = (basis_args, wts)  # stays stored; the weights serve the b-side loop of the pair stage
+                    else:
+                        plan[self.key(sj)] = (basis_args, wts)
+                # the links' bounding spheres (guards of these groups and of their self-collision groups) are rigid with
+                # the body too: rebuilt from the basis where they lie in its affine span
+                for g in guard_list:
+                    gkey = self.key(g)
+                    if (DERIVE_GUARDS and gkey not in fine_keys and not all(a["v"] is None for a in g[:3])
+                            and gkey not in self.plan and gkey not in plan):
+                        wts, err = weights(ir_eval.centre(vals, g, n))
+                        if err <= tol:
+                            plan[gkey] = (basis_args, wts)
+                return plan, lw, (tuple(self.key(b) for b in basis_args), gram)
+
+            res = with_basis(basis)
+            if res is None and len(fine) > len(basis):
+                # the farthest-point basis is not always the best conditioned one for float32: try others of the same size
+                pick = np.random.default_rng(len(fine))
+                for _ in range(48):
+                    cand = [int(v) for v in pick.choice(len(fine), size=len(basis), replace=False)]
+                    B = P[cand[1:]] - P[cand[0]]
+                    if np.linalg.svd(B, compute_uv=False)[-1] < 2e-2:
+                        continue  # (nearly) degenerate simplex
+                    res = with_basis(cand)
+                    if res is not None:
+                        break
+            return res
+
+        def commit(res) -> bool:
+            if res is None or not res[0]:
+                return False
+            plan, lw, (bkeys, gram) = res
+            self.link_gram[bkeys] = gram
+            self.plan.update(plan)
+            self.link_weights.update(lw)
+            return True
+
+        # Rigid BODIES first: environment groups whose spheres keep their mutual distances over the samples sit on one
+        # rigid body (Panda: link7, the hand and the two fingers -- fixed joints between them), and one basis of four
+        # centres serves all of them: 15 stored rows become 4.
+        groups = [it for it in self.program if it.get("k") == "env" and eligible(it)]
+
+        def union(members):
+            fine, seen = [], set()
+            for i in members:
+                for sj in groups[i]["fine"]:
+                    if self.key(sj) not in seen:
+                        seen.add(self.key(sj))
+                        fine.append(sj)
+            return fine
+
+        def rigid(ga, gb) -> bool:
+            """candidate test only (plan_set decides): a few centre pairs keep their distance over the samples"""
+            pa = [ga["fine"][0], ga["fine"][-1]]
+            pb = [gb["fine"][0], gb["fine"][-1]]
+            if any(tuple(a.get("base") for a in x[:3]) != tuple(a.get("base") for a in pa[0][:3]) for x in pb):
+                return False
+            pb.append(gb["guard"])  # (local-frame values: the base offset is a property of the reference to a centre)
+            for x in pa:
+                cx = ir_eval.centre(vals, x, n)
+                for y in pb:
+                    dd = np.linalg.norm(cx - ir_eval.centre(vals, y, n), axis=1)
+                    if float(dd.max() - dd.min()) > 2e-4:
+                        return False
+            return True
+
+        bodies: list[list[int]] = []
+        for i in range(len(groups)):
+            home = None
+            if MERGE_BODIES:
+                for body in bodies:
+                    if rigid(groups[body[0]], groups[i]) and \
+                            plan_set(union(body + [i]), [groups[k]["guard"] for k in body + [i]], BODY_REBUILD_TOL) is not None:
+                        home = body
+                        break
+            if home is None:
+                bodies.append([i])
+            else:
+                home.append(i)
+        for body in bodies:
+            if len(body) > 1 and commit(plan_set(union(body), [groups[k]["guard"] for k in body], BODY_REBUILD_TOL)):
                 continue
-            # the link's bounding sphere (guard of this group and of its self-collision groups) is rigid with the
-            # link too: rebuilt from the basis where it lies in its affine span
-            gkey = self.key(it["guard"])
-            if (DERIVE_GUARDS and gkey not in {self.key(sj) for sj in fine} and not all(a["v"] is None for a in it["guard"][:3])
-                    and gkey not in self.plan):
-                wts, err = weights(ir_eval.centre(vals, it["guard"], n))
-                if err <= 1e-6:
-                    plan[gkey] = (basis_args, wts)
-            if plan:
-                self.plan.update(plan)
-                self.link_weights.update(lw)
+            for i in body:
+                commit(plan_set(groups[i]["fine"], [groups[i]["guard"]]))
         return self
 
     def slack(self, fine_spheres, guard) -> float:
@@ -345,6 +432,9 @@ class _Emitter:
         else:
             raise ValueError(op)
         self.lines.append(f"const float v{vid} = {rhs};")
+        self.last_vid = max(self.last_vid, vid)
+        for put in self.pending_puts.pop(vid, []):
+            self.lines.append(put)
 
     def group(self, it: dict[str, Any]):
         k = it["k"]
@@ -402,6 +492,7 @@ class _Emitter:
                 raise ValueError("out in check trace")
             else:
                 self.group(it)
+        assert not self.pending_puts, "a stored centre was never computed"
         return self
 
     def run_spheres(self) -> list[str]:
@@ -850,9 +941,13 @@ def _geometry(n_slots: int, geom: dict, dim: int = 0) -> tuple[int, int]:
     fixed = 3 * n_slots * 4 + 16 + 16  # stride padding, staging mbarrier
     best = (1, 1)
     forced = int(os.environ.get("VB_FORCE_CTAS", "0"))  # development: A/B of the CTA geometry
+    # The register file bounds the resident warps as well: the walk of an articulated robot takes ~125 registers per
+    # thread, i.e. 65536 / (32 x 125) = 16 warps per SM, and more CTAs than one per SM do not add warps then (they only
+    # add instruction streams).  The one-sphere robot (a handful of rows, ~40 registers) may fill all 32 warp slots.
+    max_warps = 16 if n_slots > 8 else 32
     for ctas in ((forced,) if forced else (1, 2, 3, 4, 6, 8)):
         # 228 KB per SM, 1 KB of it reserved per resident CTA
-        w = min((228 * 1024 // ctas - 1024 - fixed) // per_warp, 16, 32 // ctas)
+        w = min((228 * 1024 // ctas - 1024 - fixed) // per_warp, 16, max_warps // ctas)
         if w >= 1 and w * ctas > best[0] * best[1]:
             best = (int(w), ctas)
     return best
