@@ -143,9 +143,14 @@ namespace vb
                 {
                     const unsigned off = d.off[k];
                     const float *col = shm_f32() + (sc.col & ~31u) + off + (off >= kConstOff ? 0u : (sc.col & 31u));
+                    float z = col[2 * kStride];
+                    if (kLiftRow > 0 && off >= 3u * kLiftRow * kStride)
+                    {
+                        z += shm_f32()[sc.col + static_cast<unsigned>(lift_z_row) * kStride];  // a translated constant as basis centre
+                    }
                     c.x += d.w[k] * col[0];
                     c.y += d.w[k] * col[kStride];
-                    c.z += d.w[k] * col[2 * kStride];
+                    c.z += d.w[k] * z;
                 }
             }
             else
