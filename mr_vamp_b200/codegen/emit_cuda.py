@@ -243,6 +243,8 @@ class _Emitter:
                 return False
             if any(all(a["v"] is None for a in s[:3]) for s in fine):
                 return False  # configuration-independent centres live in the constant rows
+            if self.use_lift and all(s[0]["v"] is None and s[1]["v"] is None for s in fine):
+                return False  # translated constants (LIFT_SLOT) are cheaper than rebuilt centres
             return len({tuple(a.get("base") for a in s[:3]) for s in fine}) == 1
 
         def plan_set(fine, guard_list, tol=REBUILD_TOL):
@@ -379,6 +381,8 @@ class _Emitter:
         for body in bodies:
             if len(body) > 1 and commit(plan_set(union(body), [groups[k]["guard"] for k in body], BODY_REBUILD_TOL)):
                 continue
+            if self.reduce_links == "bodies":
+                continue  # (development: only bodies of several links are reduced)
             for i in body:
                 commit(plan_set(groups[i]["fine"], [groups[i]["guard"]]))
         return self
@@ -970,6 +974,8 @@ def emit_robot(ir: dict[str, Any]) -> str:
         return ir_eval.evaluate(fn, q), n
 
     reduce_links = robot not in LINK_REDUCTION_OFF or os.environ.get("VB_REDUCE_ALL") == "1"
+    if not reduce_links and os.environ.get("VB_REDUCE_BODIES") == "1":
+        reduce_links = "bodies"
     em = _Emitter(fns["interleaved_sphere_fk"], sampled(fns["interleaved_sphere_fk"]), reduce_links, LIFT_ON).run_checks()
     em_att = (_Emitter(fns["interleaved_sphere_fk_attachment"], sampled(fns["interleaved_sphere_fk_attachment"]), reduce_links, LIFT_ON).run_checks()
               if has_attach else None)
