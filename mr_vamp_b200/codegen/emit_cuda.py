@@ -80,6 +80,7 @@ TWO_LEVEL_GRID_OFF = {"fetch", "baxter"}
 QUEUED_FILTERS = set(os.environ.get("VB_QUEUED_FILTERS", "fetch,baxter").split(","))
 MIN_LINK_SPHERES = int(os.environ.get("VB_MIN_LINK_SPHERES", "2"))  # links with fewer fine spheres are left alone
 DERIVE_GUARDS = os.environ.get("VB_DERIVE_GUARDS", "1") != "0"  # bounding spheres rebuilt from the link basis too
+GUARD_BLOCK = int(os.environ.get("VB_GUARD_BLOCK", "0"))  # self-collision guard pairs per scoped block of self_guards (0: one block)
 MERGE_BODIES = os.environ.get("VB_MERGE_BODIES", "1") != "0"  # links joined by fixed joints share one basis
 # Largest accepted difference between a rebuilt centre and the traced one (float32, over the sampled configurations).
 # One link: 1e-6 m.  A body of several links: the traced centres of its links come out of different chains of float32
@@ -786,14 +787,24 @@ def _uniform(em: _Emitter, queued: bool = False) -> list[str]:
         return d2
 
     body: list[str] = []
-    d2 = sphere_loads(set(), body)
     for wi in range(sw):
         body.append(f"uint32_t f{wi} = 0u;")
-    for gi, g in enumerate(em.selfg):
-        (sa, _, ra), (sb, _, rb) = g["ga"], g["gb"]
-        rs = F(ra) + F(rb)
-        rs2 = F(rs * rs)
-        body.append(f"f{gi // 32} |= ({d2(sa, sb)} < {_f32(float(rs2))}) ? {1 << (gi % 32)}u : 0u;  // {g['name']}")
+    # Robots with hundreds of guard pairs (Baxter: 355 pairs over 82 centres) would keep every centre they ever loaded
+    # in registers to the end of the function: the pairs are emitted in scoped blocks, each loading what it needs.
+    blk_pairs = GUARD_BLOCK if len(em.selfg) > 2 * GUARD_BLOCK > 0 else max(len(em.selfg), 1)
+    for first in range(0, len(em.selfg), blk_pairs):
+        scoped = blk_pairs < len(em.selfg)
+        d2 = sphere_loads(set(), body)
+        if scoped:
+            body.append("{")
+        for gi in range(first, min(first + blk_pairs, len(em.selfg))):
+            g = em.selfg[gi]
+            (sa, _, ra), (sb, _, rb) = g["ga"], g["gb"]
+            rs = F(ra) + F(rb)
+            rs2 = F(rs * rs)
+            body.append(f"f{gi // 32} |= ({d2(sa, sb)} < {_f32(float(rs2))}) ? {1 << (gi % 32)}u : 0u;  // {g['name']}")
+        if scoped:
+            body.append("}")
     for wi in range(sw):
         body.append(f"fired[{wi}] = f{wi};")
     w("    // self-collision guard pairs (bit g of fired[])")

@@ -1072,6 +1072,13 @@ namespace vb
             if (grid)
             {
                 Robot::env_fetch(col, c.bx, c.by, c.bz, env.sdf, env.sdf_c, c.radius, cells, inside);
+                if constexpr (Robot::kEnvGroups > 16)
+                {
+                    // many guards (Baxter: 33): 2 registers of in-flight cell per guard held across the self-collision
+                    // guards cost more in spills than the hidden latency earns (1.57 -> 1.61 Gcfg/s)
+                    Robot::env_classify(cells, inside, c.radius, env.sdf, maybe, cert, gmask(c) + lane);
+                    classified = true;
+                }
             }
 
             // ---------------- self collision ----------------
@@ -1081,7 +1088,7 @@ namespace vb
                 VB_TICK(2);
                 Robot::self_guards(col, fired);
                 VB_TICK(3);
-                if (grid)
+                if (grid && !classified)
                 {
                     // consumed here, not after the stages below: 22 registers of in-flight loads held across
                     // their calls would be spilled, i.e. waited for, at the first call
